@@ -1,0 +1,166 @@
+/*
+ * srt_render.h -- C ABI of the B200-native render loop (BUILD-DEFINED).
+ *
+ * The reference tree (achernigin1987/SimpleRayTracer) ships no renderer: its
+ * only code is model_runner/ (SURVEY.md section 0).  BASELINE.json still puts the
+ * per-pixel render loop on the hot path, so this header defines the boundary a
+ * host application would bind for it: plain pointers and sizes, no C++ or
+ * torch types.  The frame is written into the same dense HWC fp32 layout the
+ * reference uses for images (model_runner.h:139, image.cpp:43), so a rendered
+ * frame can be consumed by mlInfer() without a host copy (srtRenderToImage).
+ *
+ * The arithmetic every function below performs is fixed by docs/RENDER_SPEC.md;
+ * oracle/ holds the independent CPU restatement used by the tests.
+ */
+#ifndef SRT_RENDER_H_B200
+#define SRT_RENDER_H_B200
+
+#include <stddef.h>
+#include <stdint.h>
+#include "model_runner.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct srt_scene_t* srt_scene;
+
+/* Pinhole camera.  forward/right/up are unit vectors; half_w = tan(fov_x/2),
+ * half_h = tan(fov_y/2), evaluated once on the host (never on the device). */
+struct srt_camera
+{
+    float origin[3];
+    float forward[3];
+    float right[3];
+    float up[3];
+    float half_w;
+    float half_h;
+};
+
+/* One point light; radiant intensity per channel. */
+struct srt_light
+{
+    float position[3];
+    float intensity[3];
+};
+
+enum srt_shade_mode
+{
+    SRT_SHADE_ALBEDO = 0,  /* closest hit only: rgb = albedo of the hit triangle    */
+    SRT_SHADE_LAMBERT = 1, /* Lambert + point light, no visibility test             */
+    SRT_SHADE_SHADOW = 2   /* Lambert + point light + one any-hit shadow ray        */
+};
+
+enum srt_accel_mode
+{
+    SRT_ACCEL_BRUTE = 0, /* every ray tests every triangle (FP32-pipe roofline)   */
+    SRT_ACCEL_BVH = 1    /* stack traversal of the scene BVH                      */
+};
+
+struct srt_render_params
+{
+    uint32_t width;      /* full frame size, pixels                               */
+    uint32_t height;
+    uint32_t y0;         /* rows [y0,y1) are rendered (row-band sharding)         */
+    uint32_t y1;
+    uint32_t buf_y0;     /* frame row that the output pointers' first row holds   */
+    uint32_t spp;        /* samples per pixel, accumulated in index order         */
+    uint32_t jitter;     /* 0: pixel centre; 1: hashed sub-pixel jitter           */
+    uint32_t seed;
+    uint32_t shade;      /* srt_shade_mode                                        */
+    uint32_t accel;      /* srt_accel_mode                                        */
+    uint32_t collect_stats; /* 1: also count box/triangle tests (slower variant)  */
+    float t_min;         /* primary rays accept t > t_min                         */
+    float shadow_eps;    /* shadow-ray origin offset along the facing normal      */
+    float background[3];
+};
+
+struct srt_render_stats
+{
+    uint64_t primary_rays;
+    uint64_t shadow_rays;
+    uint64_t box_tests;   /* only with collect_stats                             */
+    uint64_t tri_tests;   /* only with collect_stats                             */
+    float kernel_ms;      /* CUDA-event time of the render kernel(s)             */
+};
+
+struct srt_scene_info
+{
+    uint64_t n_triangles;
+    uint64_t n_bvh_nodes;
+    uint64_t device_bytes;
+    float bvh_build_ms;   /* host wall time                                      */
+    float upload_ms;      /* host->device copy, CUDA events                      */
+    float bounds_min[3];
+    float bounds_max[3];
+};
+
+/* ---- scene ------------------------------------------------------------ */
+
+/* vertices: 9 floats per triangle (v0,v1,v2); albedo: 3 floats per triangle
+ * (NULL: 0.8 grey).  build_bvh = 0 skips the BVH (brute force only).
+ * Failure: returns NULL and leaves a message on the context
+ * (same convention as mlCreateImage/mlCreateModel). */
+ML_API_ENTRY srt_scene srtCreateScene(ml_context context, size_t n_triangles,
+                                      float const* vertices, float const* albedo,
+                                      int build_bvh);
+ML_API_ENTRY ml_status srtGetSceneInfo(srt_scene scene, srt_scene_info* info);
+ML_API_ENTRY char* srtGetSceneError(srt_scene scene, char* buffer, size_t buffer_size);
+ML_API_ENTRY void srtReleaseScene(srt_scene scene);
+
+/* Copies the flattened BVH to the caller for inspection/tests.  nodes: 16
+ * floats per node (see docs/RENDER_SPEC.md), order: n_triangles original ids
+ * in leaf order.  Either pointer may be NULL.  Returns the node count. */
+ML_API_ENTRY size_t srtGetSceneBvh(srt_scene scene, float* nodes, size_t max_nodes,
+                                   int32_t* order, size_t max_order);
+
+/* ---- synthetic scenes (host-side generators, seeded, deterministic) ---- */
+
+/* Cornell box: 5 walls + 2 inner blocks... returns the triangle count; call
+ * with NULL arrays to query it.  Fills a matching camera and light. */
+ML_API_ENTRY size_t srtGenCornellBox(float* vertices, float* albedo,
+                                     srt_camera* camera, srt_light* light,
+                                     uint32_t width, uint32_t height);
+/* Displaced-grid terrain plus a sphere soup, exactly n_triangles triangles. */
+ML_API_ENTRY ml_status srtGenMesh(uint32_t seed, size_t n_triangles,
+                                  float* vertices, float* albedo,
+                                  srt_camera* camera, srt_light* light,
+                                  uint32_t width, uint32_t height);
+
+/* ---- render ----------------------------------------------------------- */
+
+/* Host-buffer entry point: renders rows [y0,y1) and copies them into the
+ * caller's buffers (any of rgb/hit_id/hit_t may be NULL).  Synchronous.
+ * rgb: H*W*3 floats (HWC); hit_id: H*W int32 (-1 = miss); hit_t: H*W floats
+ * (+inf = miss).  With spp > 1, hit_id/hit_t are those of sample 0. */
+ML_API_ENTRY ml_status srtRender(srt_scene scene, srt_camera const* camera,
+                                 srt_light const* light, srt_render_params const* params,
+                                 float* rgb, int32_t* hit_id, float* hit_t,
+                                 srt_render_stats* stats);
+
+/* Device-buffer entry point: pointers are device addresses on the scene's
+ * GPU (they may be peer-mapped memory of another GPU), stream is a
+ * cudaStream_t (NULL: the context's stream).  Asynchronous; ray counters are
+ * fetched with srtGetRenderStats(), which synchronises. */
+ML_API_ENTRY ml_status srtRenderDevice(srt_scene scene, srt_camera const* camera,
+                                       srt_light const* light, srt_render_params const* params,
+                                       void* d_rgb, void* d_hit_id, void* d_hit_t,
+                                       void* stream);
+ML_API_ENTRY ml_status srtGetRenderStats(srt_scene scene, srt_render_stats* stats);
+
+/* Renders straight into an ml_image (FLOAT32, 3 channels, width x height):
+ * the frame stays in HBM and becomes the image's authoritative copy, so a
+ * following mlInfer(model, image, out) reads it without a host round trip. */
+ML_API_ENTRY ml_status srtRenderToImage(srt_scene scene, srt_camera const* camera,
+                                        srt_light const* light, srt_render_params const* params,
+                                        ml_image image, srt_render_stats* stats);
+
+/* Independent-FFMA microbenchmark over all SMs: the FP32 roofline denominator
+ * (MEASURED_PEAKS.json carries no FP32 figure).  Returns TFLOP/s (FMA = 2). */
+ML_API_ENTRY double srtMeasureFp32Peak(ml_context context, int repeats);
+
+#ifdef __cplusplus
+} /* extern "C" */
+#endif
+
+#endif /* SRT_RENDER_H_B200 */

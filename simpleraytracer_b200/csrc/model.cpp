@@ -1,0 +1,864 @@
+// model.cpp -- model object and its six C entry points.
+//
+// Contract (what callers can observe) follows the reference:
+//   constructor       model.cpp:73-139   path checks, node auto-detection (first /
+//                                        last node), dtype + last-3-dims discovery
+//   GetInfo           model.cpp:141-159
+//   SetInputInfo      model.cpp:161-235  dtype / known-dimension checks, no-op when
+//                                        unchanged, output shape known afterwards
+//   Infer             model.cpp:237-294  handle + output-dimension checks
+//   InferToCache      model.cpp:301-347  unspecified-dimension + byte-size checks
+//   C wrappers        model.cpp:352-395
+// The arithmetic (reference: one tensorflow::Session::Run, model.cpp:339) is an
+// execution plan of hand-written CUDA kernels over device-resident NHWC tensors;
+// the input is read from and the result written to the images' device buffers.
+#include "model.h"
+
+#include "dtype.h"
+#include "image.h"
+
+#include <algorithm>
+#include <map>
+
+namespace ML {
+namespace {
+
+// dtype from attr "dtype" or "T"; H,W,C = last three dims of _output_shapes[0]
+// with -1 -> 0 (reference model.cpp:23-48).  Divergence: a node without
+// _output_shapes falls back to a Placeholder's "shape" attr, else all-unknown,
+// instead of aborting inside protobuf's Map::at.
+void FillImageInfo(pb::Node const& node, ml_image_info& info)
+{
+    pb::Attr const* dtype = node.Find("dtype");
+    if (dtype == nullptr || !dtype->has_type) dtype = node.Find("T");
+    if (dtype == nullptr || !dtype->has_type)
+        throw std::runtime_error("Unable to detect node dtype: " + node.name);
+    info.dtype = DataTypeFromTF(dtype->type);
+
+    pb::Shape const* shape = nullptr;
+    if (pb::Attr const* os = node.Find("_output_shapes"))
+        if (!os->list_shape.empty()) shape = &os->list_shape.front();
+    if (shape == nullptr)
+        if (pb::Attr const* sh = node.Find("shape"))
+            if (sh->has_shape) shape = &sh->shape;
+
+    auto dim = [shape](int from_end) -> size_t {
+        if (shape == nullptr) return 0;
+        int n = static_cast<int>(shape->dims.size());
+        int i = n - from_end;
+        if (i < 0) return 0;
+        int64_t v = shape->dims[static_cast<size_t>(i)];
+        return v > 0 ? static_cast<size_t>(v) : 0;
+    };
+    info.height = dim(3);
+    info.width = dim(2);
+    info.channels = dim(1);
+}
+
+std::string CleanInputName(std::string const& raw)
+{
+    std::string name = raw;
+    size_t colon = name.rfind(':');
+    if (colon != std::string::npos)
+    {
+        if (name.substr(colon + 1) != "0")
+            throw std::runtime_error("Unimplemented: output " + raw + " (only output :0 is supported)");
+        name.erase(colon);
+    }
+    return name;
+}
+
+[[noreturn]] void Unimplemented(pb::Node const& node, std::string const& why)
+{
+    throw std::runtime_error("Error creating graph: Unimplemented: " + why + " (node '" + node.name
+                             + "', op '" + node.op + "')");
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------
+// construction
+// ---------------------------------------------------------------------------
+Model::Model(DeviceStatePtr device, ml_model_params const* params) : m_device(std::move(device))
+{
+    if (params == nullptr) throw std::runtime_error("Bad parameters argument");
+    if (params->model_path == nullptr) throw std::runtime_error("Bad model_path model parameter value");
+
+    pb::Graph graph = pb::ReadGraphDefFile(params->model_path);
+
+    int input_idx = 0;
+    int output_idx = static_cast<int>(graph.nodes.size()) - 1;
+    for (int i = 0; i < static_cast<int>(graph.nodes.size()); i++)
+    {
+        if (params->input_node != nullptr && graph.nodes[i].name == params->input_node) input_idx = i;
+        if (params->output_node != nullptr && graph.nodes[i].name == params->output_node) output_idx = i;
+    }
+    FillImageInfo(graph.nodes[input_idx], m_input_info);
+    FillImageInfo(graph.nodes[output_idx], m_output_info);
+    m_input_node = graph.nodes[input_idx].name;
+    m_output_node = graph.nodes[output_idx].name;
+
+    BuildPlan(graph, input_idx, output_idx);
+    FusePlan();
+
+    // Upload constants once; they stay resident in HBM for the model's life.
+    m_device->MakeCurrent();
+    try
+    {
+        for (auto& c : m_consts)
+        {
+            ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&c.dev), std::max<size_t>(c.host.size(), 1) * sizeof(float)));
+            ML_CUDA_CHECK(cudaMemcpyAsync(c.dev, c.host.data(), c.host.size() * sizeof(float),
+                                          cudaMemcpyHostToDevice, m_device->stream));
+        }
+        ML_CUDA_CHECK(cudaStreamSynchronize(m_device->stream));
+    }
+    catch (...)
+    {
+        for (auto& c : m_consts) cudaFree(c.dev);
+        throw;
+    }
+    m_loaded = true;
+
+    // Static channel propagation gives the output channel count even when the
+    // output node carries no _output_shapes.
+    try
+    {
+        InferShapes(m_input_info.height, m_input_info.width, m_input_info.channels);
+        TensorInfo const& out = m_tensors[m_output_tensor];
+        if (m_output_info.channels == 0) m_output_info.channels = static_cast<size_t>(out.C);
+        if (m_input_info.height && m_input_info.width && m_input_info.channels)
+        {
+            // Fully specified graph: ready to run without mlSetModelInputInfo
+            // (the reference would dereference an empty input map here).
+            m_output_info.height = static_cast<size_t>(out.H);
+            m_output_info.width = static_cast<size_t>(out.W);
+            m_output_info.channels = static_cast<size_t>(out.C);
+            AllocateBuffers();
+            m_ready = true;
+        }
+    }
+    catch (std::exception const& e)
+    {
+        for (auto& c : m_consts) cudaFree(c.dev);
+        throw std::runtime_error(std::string("Error creating graph: Invalid argument: ") + e.what());
+    }
+}
+
+Model::~Model()
+{
+    cudaSetDevice(m_device->device);
+    cudaStreamSynchronize(m_device->stream);
+    ReleaseBuffers();
+    for (auto& c : m_consts) cudaFree(c.dev);
+}
+
+int Model::AddConst(std::vector<float> values)
+{
+    m_consts.push_back(DeviceConst{std::move(values), nullptr});
+    return static_cast<int>(m_consts.size()) - 1;
+}
+
+int Model::NewTensor(int channels)
+{
+    TensorInfo t;
+    t.C = channels;
+    m_tensors.push_back(t);
+    return static_cast<int>(m_tensors.size()) - 1;
+}
+
+void Model::BuildPlan(pb::Graph const& graph, int input_idx, int output_idx)
+{
+    std::vector<Value> memo(graph.nodes.size());
+    std::vector<char> state(graph.nodes.size(), 0);
+    m_name_index.clear();
+    for (int i = 0; i < static_cast<int>(graph.nodes.size()); i++) m_name_index[graph.nodes[i].name] = i;
+    Value out = Evaluate(graph, output_idx, memo, state, input_idx);
+    if (out.is_const) Unimplemented(graph.nodes[output_idx], "output node is a constant");
+    if (m_input_tensor < 0)
+        throw std::runtime_error("Error creating graph: Invalid argument: output node '"
+                                 + graph.nodes[output_idx].name + "' does not depend on input node '"
+                                 + graph.nodes[input_idx].name + "'");
+    m_output_tensor = out.tensor;
+    if (m_output_tensor == m_input_tensor)
+    {
+        Op op;
+        op.kind = OpKind::Copy;
+        op.in = {m_input_tensor};
+        op.out = NewTensor(m_tensors[m_input_tensor].C);
+        op.name = graph.nodes[output_idx].name;
+        m_ops.push_back(op);
+        m_output_tensor = op.out;
+    }
+}
+
+Model::Value Model::Evaluate(pb::Graph const& graph, int idx, std::vector<Value>& memo,
+                             std::vector<char>& state, int input_idx)
+{
+    if (state[idx] == 2) return memo[idx];
+    pb::Node const& node = graph.nodes[idx];
+    if (state[idx] == 1) Unimplemented(node, "graph cycle");
+    state[idx] = 1;
+
+    auto input_value = [&](size_t k) -> Value {
+        size_t seen = 0;
+        for (auto const& raw : node.inputs)
+        {
+            if (!raw.empty() && raw[0] == '^') continue; // control dependency
+            if (seen++ == k)
+            {
+                std::string name = CleanInputName(raw);
+                auto it = m_name_index.find(name);
+                if (it == m_name_index.end()) Unimplemented(node, "unknown input '" + raw + "'");
+                return Evaluate(graph, it->second, memo, state, input_idx);
+            }
+        }
+        Unimplemented(node, "missing input #" + std::to_string(k));
+    };
+    auto data_input_count = [&]() {
+        size_t n = 0;
+        for (auto const& raw : node.inputs)
+            if (raw.empty() || raw[0] != '^') n++;
+        return n;
+    };
+    auto activation = [&](size_t k) -> int {
+        Value v = input_value(k);
+        if (v.is_const) Unimplemented(node, "constant activation input #" + std::to_string(k));
+        return v.tensor;
+    };
+    auto parse_act = [&](std::string const& op, nn::Act& act, float& alpha) -> bool {
+        alpha = 0.2f;
+        if (op == "Relu") act = nn::Act::Relu;
+        else if (op == "Relu6") act = nn::Act::Relu6;
+        else if (op == "Sigmoid") act = nn::Act::Sigmoid;
+        else if (op == "Tanh") act = nn::Act::Tanh;
+        else if (op == "LeakyRelu")
+        {
+            act = nn::Act::LeakyRelu;
+            if (pb::Attr const* a = node.Find("alpha"))
+                if (a->has_f) alpha = a->f;
+        }
+        else return false;
+        return true;
+    };
+
+    Value result;
+    nn::Act act;
+    float alpha;
+    if (idx == input_idx)
+    {
+        if (m_input_tensor < 0) m_input_tensor = NewTensor(static_cast<int>(m_input_info.channels));
+        result.tensor = m_input_tensor;
+    }
+    else if (node.op == "Placeholder")
+    {
+        Unimplemented(node, "more than one graph input");
+    }
+    else if (node.op == "Const")
+    {
+        pb::Attr const* v = node.Find("value");
+        if (v == nullptr || !v->tensor) Unimplemented(node, "Const without value");
+        result.is_const = true;
+        result.constant = v->tensor;
+    }
+    else if (node.op == "Identity" || node.op == "StopGradient" || node.op == "PlaceholderWithDefault")
+    {
+        result = input_value(0);
+    }
+    else if (node.op == "Conv2D")
+    {
+        int in = activation(0);
+        Value f = input_value(1);
+        if (!f.is_const || f.constant->shape.dims.size() != 4 || f.constant->values.empty())
+            Unimplemented(node, "Conv2D filter must be a 4-D float constant");
+        if (pb::Attr const* df = node.Find("data_format"))
+            if (df->has_s && df->s != "NHWC") Unimplemented(node, "data_format " + df->s);
+        Op op;
+        op.kind = OpKind::Conv;
+        op.name = node.name;
+        op.in = {in};
+        op.KH = static_cast<int>(f.constant->shape.dims[0]);
+        op.KW = static_cast<int>(f.constant->shape.dims[1]);
+        int cin = static_cast<int>(f.constant->shape.dims[2]);
+        int cout = static_cast<int>(f.constant->shape.dims[3]);
+        if (pb::Attr const* s = node.Find("strides"))
+            if (s->list_i.size() == 4)
+            {
+                if (s->list_i[0] != 1 || s->list_i[3] != 1 || s->list_i[1] != s->list_i[2] || s->list_i[1] < 1)
+                    Unimplemented(node, "strides");
+                op.stride = static_cast<int>(s->list_i[1]);
+            }
+        if (pb::Attr const* dl = node.Find("dilations"))
+            if (dl->list_i.size() == 4)
+            {
+                if (dl->list_i[0] != 1 || dl->list_i[3] != 1 || dl->list_i[1] != dl->list_i[2] || dl->list_i[1] < 1)
+                    Unimplemented(node, "dilations");
+                op.dilation = static_cast<int>(dl->list_i[1]);
+            }
+        pb::Attr const* pad = node.Find("padding");
+        if (pad == nullptr || !pad->has_s || (pad->s != "SAME" && pad->s != "VALID"))
+            Unimplemented(node, "padding");
+        op.same_padding = pad->s == "SAME";
+        int known = m_tensors[in].C;
+        if (known != 0 && known != cin)
+            throw std::runtime_error("Error creating graph: Invalid argument: Conv2D '" + node.name
+                                     + "' expects " + std::to_string(cin) + " input channels, got "
+                                     + std::to_string(known));
+        op.weights = AddConst(f.constant->values);
+        op.out = NewTensor(cout);
+        m_ops.push_back(op);
+        result.tensor = op.out;
+    }
+    else if (node.op == "BiasAdd" || node.op == "Add" || node.op == "AddV2")
+    {
+        if (data_input_count() != 2) Unimplemented(node, "expected two inputs");
+        Value a = input_value(0), b = input_value(1);
+        if (a.is_const && b.is_const) Unimplemented(node, "constant folding");
+        if (a.is_const) std::swap(a, b);
+        if (b.is_const)
+        {
+            size_t n = b.constant->values.size();
+            int C = m_tensors[a.tensor].C;
+            if (n == 0 || (n != 1 && C != 0 && static_cast<int>(n) != C))
+                Unimplemented(node, "bias of " + std::to_string(n) + " values on " + std::to_string(C) + " channels");
+            Op op;
+            op.kind = OpKind::BiasAct;
+            op.name = node.name;
+            op.in = {a.tensor};
+            std::vector<float> bias = b.constant->values;
+            if (n == 1 && C > 1) bias.assign(static_cast<size_t>(C), bias[0]);
+            op.bias = AddConst(std::move(bias));
+            op.out = NewTensor(C != 0 ? C : static_cast<int>(n));
+            m_ops.push_back(op);
+            result.tensor = op.out;
+        }
+        else
+        {
+            if (node.op == "BiasAdd") Unimplemented(node, "BiasAdd with a non-constant bias");
+            Op op;
+            op.kind = OpKind::Add;
+            op.name = node.name;
+            op.in = {a.tensor, b.tensor};
+            op.out = NewTensor(m_tensors[a.tensor].C);
+            m_ops.push_back(op);
+            result.tensor = op.out;
+        }
+    }
+    else if (parse_act(node.op, act, alpha))
+    {
+        Op op;
+        op.kind = OpKind::BiasAct;
+        op.name = node.name;
+        op.in = {activation(0)};
+        op.act = act;
+        op.alpha = alpha;
+        op.out = NewTensor(m_tensors[op.in[0]].C);
+        m_ops.push_back(op);
+        result.tensor = op.out;
+    }
+    else if (node.op == "ConcatV2")
+    {
+        size_t n = data_input_count();
+        if (n < 2) Unimplemented(node, "ConcatV2 without inputs");
+        Value axis = input_value(n - 1);
+        if (!axis.is_const || axis.constant->ints.size() != 1) Unimplemented(node, "ConcatV2 axis");
+        int64_t ax = axis.constant->ints[0];
+        if (ax != 3 && ax != -1) Unimplemented(node, "ConcatV2 on axis " + std::to_string(ax));
+        Op op;
+        op.kind = OpKind::Concat;
+        op.name = node.name;
+        int total = 0;
+        for (size_t k = 0; k + 1 < n; k++)
+        {
+            int t = activation(k);
+            if (m_tensors[t].C == 0) Unimplemented(node, "ConcatV2 of tensors with unknown channel count");
+            op.in.push_back(t);
+            total += m_tensors[t].C;
+        }
+        op.out = NewTensor(total);
+        m_ops.push_back(op);
+        result.tensor = op.out;
+    }
+    else
+    {
+        Unimplemented(node, "unsupported op");
+    }
+
+    state[idx] = 2;
+    memo[idx] = result;
+    return result;
+}
+
+// Folds BiasAdd and activations into the producing op when nothing else reads
+// the intermediate tensor: Conv2D+BiasAdd+Relu becomes one kernel launch.
+void Model::FusePlan()
+{
+    bool changed = true;
+    while (changed)
+    {
+        changed = false;
+        std::vector<int> uses(m_tensors.size(), 0);
+        std::vector<int> producer(m_tensors.size(), -1);
+        for (size_t i = 0; i < m_ops.size(); i++)
+        {
+            for (int t : m_ops[i].in) uses[t]++;
+            producer[m_ops[i].out] = static_cast<int>(i);
+        }
+        uses[m_output_tensor]++;
+        for (size_t i = 0; i < m_ops.size() && !changed; i++)
+        {
+            Op& op = m_ops[i];
+            if (op.kind != OpKind::BiasAct) continue;
+            int src = op.in[0];
+            int p = producer[src];
+            if (p < 0 || uses[src] != 1) continue;
+            Op& prod = m_ops[p];
+            if (prod.act != nn::Act::None) continue; // activation already applied: order matters
+            bool const has_bias = op.bias >= 0;
+            if (prod.kind == OpKind::Conv || prod.kind == OpKind::BiasAct)
+            {
+                if (has_bias && prod.bias >= 0)
+                {
+                    // bias + bias: add the vectors
+                    auto& a = m_consts[prod.bias].host;
+                    auto const& b = m_consts[op.bias].host;
+                    if (a.size() != b.size()) continue;
+                    for (size_t k = 0; k < a.size(); k++) a[k] += b[k];
+                }
+                else if (has_bias) prod.bias = op.bias;
+            }
+            else if (prod.kind == OpKind::Add)
+            {
+                if (has_bias) continue;
+            }
+            else continue;
+            prod.act = op.act;
+            prod.alpha = op.alpha;
+            prod.out = op.out;
+            m_ops.erase(m_ops.begin() + static_cast<long>(i));
+            changed = true;
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------
+// shapes and memory
+// ---------------------------------------------------------------------------
+void Model::InferShapes(size_t H, size_t W, size_t C)
+{
+    for (auto& t : m_tensors) { t.H = 0; t.W = 0; t.last_use = -1; }
+    TensorInfo& in = m_tensors[m_input_tensor];
+    if (C != 0)
+    {
+        if (in.C != 0 && in.C != static_cast<int>(C))
+            throw std::runtime_error("input has " + std::to_string(C) + " channels, the graph expects "
+                                     + std::to_string(in.C));
+        in.C = static_cast<int>(C);
+    }
+    in.H = static_cast<int>(H);
+    in.W = static_cast<int>(W);
+
+    for (size_t i = 0; i < m_ops.size(); i++)
+    {
+        Op& op = m_ops[i];
+        for (int t : op.in) m_tensors[t].last_use = static_cast<int>(i);
+        TensorInfo const& a = m_tensors[op.in[0]];
+        TensorInfo& o = m_tensors[op.out];
+        switch (op.kind)
+        {
+            case OpKind::Conv:
+            {
+                size_t wsize = m_consts[op.weights].host.size();
+                int cin = static_cast<int>(wsize / (static_cast<size_t>(op.KH) * op.KW * o.C));
+                if (a.C != 0 && a.C != cin)
+                    throw std::runtime_error("Conv2D '" + op.name + "' expects " + std::to_string(cin)
+                                             + " input channels, got " + std::to_string(a.C));
+                auto out_dim = [&](int n, int k) {
+                    if (n == 0) return 0;
+                    int eff = (k - 1) * op.dilation + 1;
+                    if (op.same_padding) return (n + op.stride - 1) / op.stride;
+                    return n >= eff ? (n - eff) / op.stride + 1 : 0;
+                };
+                o.H = out_dim(a.H, op.KH);
+                o.W = out_dim(a.W, op.KW);
+                if ((a.H && !o.H) || (a.W && !o.W))
+                    throw std::runtime_error("Conv2D '" + op.name + "' output is empty for a "
+                                             + std::to_string(a.W) + " x " + std::to_string(a.H) + " input");
+                break;
+            }
+            case OpKind::BiasAct:
+            case OpKind::Copy:
+                if (o.C == 0) o.C = a.C;
+                if (op.bias >= 0 && a.C != 0 && static_cast<int>(m_consts[op.bias].host.size()) != a.C)
+                    throw std::runtime_error("'" + op.name + "' bias size does not match "
+                                             + std::to_string(a.C) + " channels");
+                o.H = a.H; o.W = a.W;
+                break;
+            case OpKind::Add:
+            {
+                TensorInfo const& b = m_tensors[op.in[1]];
+                if (a.C != b.C || a.H != b.H || a.W != b.W)
+                    throw std::runtime_error("'" + op.name + "' operands differ in shape");
+                if (o.C == 0) o.C = a.C;
+                o.H = a.H; o.W = a.W;
+                break;
+            }
+            case OpKind::Concat:
+                for (int t : op.in)
+                    if (m_tensors[t].H != a.H || m_tensors[t].W != a.W)
+                        throw std::runtime_error("'" + op.name + "' operands differ in spatial size");
+                o.H = a.H; o.W = a.W;
+                break;
+        }
+    }
+}
+
+void Model::ReleaseBuffers()
+{
+    for (void* p : m_buffers) cudaFree(p);
+    m_buffers.clear();
+    m_buffer_bytes.clear();
+    cudaFree(m_in_f32);
+    cudaFree(m_out_f32);
+    m_in_f32 = m_out_f32 = nullptr;
+}
+
+// Liveness-based buffer reuse: an intermediate's buffer returns to the free
+// list right after the last op that reads it.
+void Model::AllocateBuffers()
+{
+    m_device->MakeCurrent();
+    ReleaseBuffers();
+    std::vector<int> free_list;
+    for (auto& t : m_tensors) t.buffer = -1;
+    for (size_t i = 0; i < m_ops.size(); i++)
+    {
+        Op const& op = m_ops[i];
+        if (op.out != m_output_tensor)
+        {
+            TensorInfo& o = m_tensors[op.out];
+            size_t need = static_cast<size_t>(o.H) * o.W * o.C * sizeof(float);
+            int best = -1;
+            for (size_t k = 0; k < free_list.size(); k++)
+            {
+                int b = free_list[k];
+                if (m_buffer_bytes[b] >= need && (best < 0 || m_buffer_bytes[b] < m_buffer_bytes[free_list[best]]))
+                    best = static_cast<int>(k);
+            }
+            if (best >= 0)
+            {
+                o.buffer = free_list[best];
+                free_list.erase(free_list.begin() + best);
+            }
+            else
+            {
+                void* p = nullptr;
+                ML_CUDA_CHECK(cudaMalloc(&p, std::max<size_t>(need, 16)));
+                m_buffers.push_back(p);
+                m_buffer_bytes.push_back(need);
+                o.buffer = static_cast<int>(m_buffers.size()) - 1;
+            }
+        }
+        for (int t : op.in)
+            if (m_tensors[t].last_use == static_cast<int>(i) && m_tensors[t].buffer >= 0)
+            {
+                bool dup = std::find(free_list.begin(), free_list.end(), m_tensors[t].buffer) != free_list.end();
+                if (!dup) free_list.push_back(m_tensors[t].buffer);
+            }
+    }
+    if (m_input_info.dtype == ML_FLOAT16)
+    {
+        TensorInfo const& in = m_tensors[m_input_tensor];
+        TensorInfo const& out = m_tensors[m_output_tensor];
+        ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&m_in_f32), static_cast<size_t>(in.H) * in.W * in.C * 4));
+        ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&m_out_f32), static_cast<size_t>(out.H) * out.W * out.C * 4));
+    }
+}
+
+size_t Model::LaunchesPerInfer() const
+{
+    size_t n = 0;
+    for (auto const& op : m_ops) n += op.kind == OpKind::Concat ? op.in.size() : 1;
+    if (m_input_info.dtype == ML_FLOAT16) n += 2;
+    return n;
+}
+
+// ---------------------------------------------------------------------------
+// API methods
+// ---------------------------------------------------------------------------
+ml_status Model::GetInfo(ml_image_info* input_info, ml_image_info* output_info)
+{
+    if (!m_loaded) return ML_FAIL;
+    if (input_info != nullptr) *input_info = m_input_info;
+    if (output_info != nullptr) *output_info = m_output_info;
+    return ML_OK;
+}
+
+ml_status Model::SetInputInfo(ml_image_info const* info)
+{
+    m_error.clear();
+    if (info == nullptr)
+    {
+        m_error = "Bad info parameter";
+        return ML_FAIL;
+    }
+    if (m_input_info.dtype != info->dtype)
+    {
+        std::ostringstream os;
+        os << "Overriding data type " << m_input_info.dtype << " with " << info->dtype;
+        m_error = os.str();
+        return ML_FAIL;
+    }
+    bool ok = ForEachDim([&](auto dim, char const* name) {
+        if (m_input_info.*dim != 0 && info->*dim != m_input_info.*dim)
+        {
+            std::ostringstream os;
+            os << "Overriding " << name << " dimension " << m_input_info.*dim << " with " << info->*dim;
+            m_error = os.str();
+            return false;
+        }
+        return true;
+    });
+    if (!ok) return ML_FAIL;
+
+    bool same = ForEachDim([&](auto dim, char const*) { return m_input_info.*dim == info->*dim; });
+    if (same) return ML_OK; // nothing changed
+
+    // The reference allocates the input tensor and runs a dummy inference on
+    // zeros to learn the output shape (model.cpp:204-229); here the shape is
+    // computed analytically and the device arena is (re)allocated.
+    ml_image_info const previous = m_input_info;
+    try
+    {
+        ok = ForEachDim([&](auto dim, char const* name) {
+            if (info->*dim == 0)
+            {
+                m_error = std::string("Input image ") + name + " dimension is not specified";
+                return false;
+            }
+            return true;
+        });
+        if (!ok) return ML_FAIL;
+        m_input_info = *info;
+        m_ready = false;
+        InferShapes(info->height, info->width, info->channels);
+        AllocateBuffers();
+        TensorInfo const& out = m_tensors[m_output_tensor];
+        m_output_info.height = static_cast<size_t>(out.H);
+        m_output_info.width = static_cast<size_t>(out.W);
+        m_output_info.channels = static_cast<size_t>(out.C);
+        m_ready = true;
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        m_input_info = previous;
+        m_error = std::string("Inference error: Invalid argument: ") + e.what();
+        return ML_FAIL;
+    }
+}
+
+void Model::Run(float const* d_in, float* d_out, cudaStream_t stream)
+{
+    auto ptr = [&](int t) -> float* {
+        if (t == m_input_tensor) return const_cast<float*>(d_in);
+        if (t == m_output_tensor) return d_out;
+        return static_cast<float*>(m_buffers[m_tensors[t].buffer]);
+    };
+    for (Op const& op : m_ops)
+    {
+        TensorInfo const& a = m_tensors[op.in[0]];
+        TensorInfo const& o = m_tensors[op.out];
+        size_t const n_out = static_cast<size_t>(o.H) * o.W * o.C;
+        switch (op.kind)
+        {
+            case OpKind::Conv:
+            {
+                nn::ConvDesc d{};
+                d.H = a.H; d.W = a.W; d.Cin = a.C;
+                d.OH = o.H; d.OW = o.W; d.Cout = o.C;
+                d.KH = op.KH; d.KW = op.KW;
+                d.stride = op.stride; d.dilation = op.dilation;
+                if (op.same_padding)
+                {
+                    // TensorFlow SAME: total = max((out-1)*stride + eff_k - in, 0), low half first
+                    int effh = (op.KH - 1) * op.dilation + 1, effw = (op.KW - 1) * op.dilation + 1;
+                    int ph = std::max((o.H - 1) * op.stride + effh - a.H, 0);
+                    int pw = std::max((o.W - 1) * op.stride + effw - a.W, 0);
+                    d.pad_top = ph / 2;
+                    d.pad_left = pw / 2;
+                }
+                d.act = op.act;
+                d.alpha = op.alpha;
+                nn::Conv2dFp32(ptr(op.in[0]), m_consts[op.weights].dev,
+                               op.bias >= 0 ? m_consts[op.bias].dev : nullptr, ptr(op.out), d, stream);
+                break;
+            }
+            case OpKind::BiasAct:
+                nn::BiasAct(ptr(op.in[0]), op.bias >= 0 ? m_consts[op.bias].dev : nullptr, ptr(op.out),
+                            n_out, o.C, op.act, op.alpha, stream);
+                break;
+            case OpKind::Add:
+                nn::AddAct(ptr(op.in[0]), ptr(op.in[1]), ptr(op.out), n_out, op.act, op.alpha, stream);
+                break;
+            case OpKind::Concat:
+            {
+                int c0 = 0;
+                for (int t : op.in)
+                {
+                    nn::ConcatChannels(ptr(t), ptr(op.out), static_cast<size_t>(o.H) * o.W,
+                                       m_tensors[t].C, o.C, c0, stream);
+                    c0 += m_tensors[t].C;
+                }
+                break;
+            }
+            case OpKind::Copy:
+                ML_CUDA_CHECK(cudaMemcpyAsync(ptr(op.out), ptr(op.in[0]), n_out * sizeof(float),
+                                              cudaMemcpyDeviceToDevice, stream));
+                break;
+        }
+    }
+}
+
+ml_status Model::Infer(ml_image input, ml_image output)
+{
+    m_error.clear();
+    Image* in = Image::FromHandle(input);
+    Image* out = Image::FromHandle(output);
+    if (in == nullptr)
+    {
+        m_error = "Bad input image handle";
+        return ML_FAIL;
+    }
+    if (out == nullptr)
+    {
+        m_error = "Bad output image handle";
+        return ML_FAIL;
+    }
+
+    ml_image_info const& oi = out->Info();
+    bool ok = ForEachDim([&](auto dim, char const* name) {
+        if (oi.*dim != m_output_info.*dim)
+        {
+            std::ostringstream os;
+            os << "Output image " << name << " dimension " << oi.*dim << " does not match "
+               << m_output_info.*dim;
+            m_error = os.str();
+            return false;
+        }
+        return true;
+    });
+    if (!ok) return ML_FAIL;
+
+    ok = ForEachDim([&](auto dim, char const* name) {
+        if (m_input_info.*dim == 0)
+        {
+            m_error = std::string("Input image ") + name + " dimension is not specified";
+            return false;
+        }
+        return true;
+    });
+    if (!ok) return ML_FAIL;
+
+    size_t const item = DataTypeSize(m_input_info.dtype);
+    size_t const in_bytes = m_input_info.width * m_input_info.height * m_input_info.channels * item;
+    size_t const out_bytes = m_output_info.width * m_output_info.height * m_output_info.channels * item;
+    if (in->Bytes() != in_bytes)
+    {
+        std::ostringstream os;
+        os << "Internal error: input size does not match: " << in->Bytes() << " vs " << in_bytes;
+        m_error = os.str();
+        return ML_FAIL;
+    }
+    if (out->Bytes() != out_bytes)
+    {
+        std::ostringstream os;
+        os << "Internal error: output size does not match: " << out->Bytes() << " vs " << out_bytes;
+        m_error = os.str();
+        return ML_FAIL;
+    }
+
+    try
+    {
+        if (!m_ready) throw std::runtime_error("model input shape has not been set");
+        if (in->Device()->device != m_device->device || out->Device()->device != m_device->device)
+            throw std::runtime_error("images and model live on different devices");
+        m_device->MakeCurrent();
+        cudaStream_t s = m_device->stream;
+        void* d_in = in->DeviceRead(s);
+        void* d_out = out->DeviceWrite();
+        if (m_input_info.dtype == ML_FLOAT16)
+        {
+            nn::HalfToFloat(d_in, m_in_f32, in_bytes / item, s);
+            Run(m_in_f32, m_out_f32, s);
+            nn::FloatToHalf(m_out_f32, d_out, out_bytes / item, s);
+        }
+        else
+        {
+            Run(static_cast<float const*>(d_in), static_cast<float*>(d_out), s);
+        }
+        out->CommitDeviceWrite(s);
+        ML_CUDA_CHECK(cudaStreamSynchronize(s));
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        m_error = std::string("Inference error: ") + e.what();
+        return ML_FAIL;
+    }
+}
+
+char* Model::GetError(char* buffer, size_t buffer_size) const
+{
+    return FillBuffer(buffer, buffer_size, m_error);
+}
+
+} // namespace ML
+
+extern "C" {
+
+ML_API_ENTRY char* mlGetModelError(ml_model model, char* buffer, size_t buffer_size)
+{
+    if (ML::Model::FromHandle(model) == nullptr)
+        return ML::FillBuffer(buffer, buffer_size, "Bad model handle");
+    return ML::Model::FromHandle(model)->GetError(buffer, buffer_size);
+}
+
+ML_API_ENTRY ml_status mlGetModelInfo(ml_model model, ml_image_info* input_info, ml_image_info* output_info)
+{
+    if (ML::Model::FromHandle(model) == nullptr) return ML_FAIL;
+    return ML::Model::FromHandle(model)->GetInfo(input_info, output_info);
+}
+
+ML_API_ENTRY ml_status mlSetModelInputInfo(ml_model model, ml_image_info const* info)
+{
+    if (ML::Model::FromHandle(model) == nullptr) return ML_FAIL;
+    try
+    {
+        return ML::Model::FromHandle(model)->SetInputInfo(info);
+    }
+    catch (...)
+    {
+        return ML_FAIL;
+    }
+}
+
+ML_API_ENTRY ml_status mlInfer(ml_model model, ml_image input, ml_image output)
+{
+    if (ML::Model::FromHandle(model) == nullptr) return ML_FAIL;
+    try
+    {
+        return ML::Model::FromHandle(model)->Infer(input, output);
+    }
+    catch (...)
+    {
+        return ML_FAIL;
+    }
+}
+
+ML_API_ENTRY void mlReleaseModel(ml_model model)
+{
+    delete ML::Model::FromHandle(model);
+}
+
+} // extern "C"

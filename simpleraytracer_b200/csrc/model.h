@@ -1,0 +1,108 @@
+// model.h -- ML::Model: frozen-graph model (reference model.h:18-42) executed
+// by hand-written CUDA kernels instead of a TensorFlow session.
+#pragma once
+
+#include "common.h"
+#include "graphdef.h"
+#include "nn_kernels.h"
+
+#include <map>
+#include <vector>
+
+namespace ML {
+
+class Image;
+
+class Model
+{
+public:
+    static ml_model MakeHandle(Model* m) { return reinterpret_cast<ml_model>(m); }
+    static Model* FromHandle(ml_model m) { return reinterpret_cast<Model*>(m); }
+
+    Model(DeviceStatePtr device, ml_model_params const* params);
+    ~Model();
+    Model(Model const&) = delete;
+    Model& operator=(Model const&) = delete;
+
+    ml_status GetInfo(ml_image_info* input_info, ml_image_info* output_info);
+    ml_status SetInputInfo(ml_image_info const* info);
+    ml_status Infer(ml_image input, ml_image output);
+    char* GetError(char* buffer, size_t buffer_size) const;
+
+    // Number of kernel launches one Infer() enqueues (bench bookkeeping).
+    size_t LaunchesPerInfer() const;
+
+private:
+    // ---- execution plan ---------------------------------------------------
+    enum class OpKind { Conv, BiasAct, Add, Concat, Copy };
+
+    struct TensorInfo
+    {
+        int C = 0;             // channels (static)
+        int H = 0, W = 0;      // set by shape inference
+        int buffer = -1;       // index into m_buffers; -1 = external (input / output image)
+        int last_use = -1;     // index of the last op reading it
+    };
+
+    struct Op
+    {
+        OpKind kind;
+        std::vector<int> in;   // tensor ids
+        int out = -1;          // tensor id
+        // Conv
+        int KH = 0, KW = 0, stride = 1, dilation = 1;
+        bool same_padding = true;
+        int weights = -1;      // index into m_consts (HWIO filter)
+        int bias = -1;         // index into m_consts or -1
+        nn::Act act = nn::Act::None;
+        float alpha = 0.2f;
+        std::string name;      // for error messages
+    };
+
+    struct DeviceConst
+    {
+        std::vector<float> host;
+        float* dev = nullptr;
+    };
+
+    struct Value // what a graph node evaluates to while the plan is built
+    {
+        bool is_const = false;
+        int tensor = -1;                     // activation tensor id
+        std::shared_ptr<pb::Tensor> constant;
+    };
+
+    void BuildPlan(pb::Graph const& graph, int input_idx, int output_idx);
+    Value Evaluate(pb::Graph const& graph, int node_idx, std::vector<Value>& memo,
+                   std::vector<char>& state, int input_idx);
+    void FusePlan();
+    void InferShapes(size_t H, size_t W, size_t C); // throws on mismatch
+    void AllocateBuffers();
+    void ReleaseBuffers();
+    int AddConst(std::vector<float> values);
+    int NewTensor(int channels);
+    void Run(float const* d_in, float* d_out, cudaStream_t stream);
+
+    DeviceStatePtr m_device;
+    std::string m_input_node;
+    std::string m_output_node;
+    ml_image_info m_input_info{};
+    ml_image_info m_output_info{};
+    bool m_ready = false;        // shapes inferred and buffers allocated
+    bool m_loaded = false;       // plan built (the reference's "session != nullptr")
+
+    std::vector<TensorInfo> m_tensors;
+    std::vector<Op> m_ops;
+    std::vector<DeviceConst> m_consts;
+    std::map<std::string, int> m_name_index;
+    int m_input_tensor = -1;
+    int m_output_tensor = -1;
+
+    std::vector<void*> m_buffers;
+    std::vector<size_t> m_buffer_bytes;
+    float* m_in_f32 = nullptr;   // staging when images are FLOAT16
+    float* m_out_f32 = nullptr;
+    std::string m_error;
+};
+
+} // namespace ML

@@ -1,0 +1,304 @@
+// nn_kernels.cu -- fp32 inference kernels (CUDA cores) for sm_100a.
+//
+// conv2d_tile_kernel: stride-1 direct convolution.  A block owns a TH x TW
+// output tile and up to 4*CG output channels; the input tile (with halo) and
+// the filter slice for CI_T input channels are staged in shared memory, every
+// thread keeps PXT pixels x 4 channels of accumulators in registers, reads the
+// filter as one LDS.128 per (kh,kw,ci) and slides a register window along the
+// row so each input value is loaded once per kh.  Bias and activation are
+// fused into the store.  Bound: FP32 FMA pipe (2*KH*KW*Cin*Cout FLOP/pixel).
+//
+// conv2d_naive_kernel: any stride/dilation, one thread per output value.
+#include "nn_kernels.h"
+
+#include "common.h"
+
+#include <cuda_fp16.h>
+
+namespace ML {
+namespace nn {
+namespace {
+
+__device__ __forceinline__ float apply_act(float v, Act act, float alpha)
+{
+    switch (act)
+    {
+        case Act::Relu: return v > 0.f ? v : 0.f;
+        case Act::LeakyRelu: return v > 0.f ? v : v * alpha;
+        case Act::Relu6: return v < 0.f ? 0.f : (v > 6.f ? 6.f : v);
+        case Act::Sigmoid: return 1.0f / (1.0f + expf(-v));
+        case Act::Tanh: return tanhf(v);
+        default: return v;
+    }
+}
+
+template <int KS, int TH, int TW, int PXT, int CG, int CI_T>
+__global__ void __launch_bounds__(256)
+conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
+                   float const* __restrict__ bias, float* __restrict__ out, ConvDesc d)
+{
+    constexpr int IH = TH + KS - 1, IW = TW + KS - 1;
+    constexpr int CO_T = 4 * CG;
+    constexpr int GROUPS_PER_ROW = TW / PXT;
+    static_assert((TH * TW / PXT) * CG == 256, "thread mapping must cover 256 threads");
+
+    __shared__ float s_in[IH][IW][CI_T];
+    __shared__ __align__(16) float s_w[KS * KS][CI_T][CO_T];
+
+    int const tid = threadIdx.x;
+    int const cg = tid % CG;
+    int const pg = tid / CG;
+    int const row = pg / GROUPS_PER_ROW;
+    int const col0 = (pg % GROUPS_PER_ROW) * PXT;
+    int const ty0 = blockIdx.y * TH, tx0 = blockIdx.x * TW;
+    int const cot0 = blockIdx.z * CO_T;
+
+    float acc[PXT][4];
+#pragma unroll
+    for (int i = 0; i < PXT; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+
+    for (int c0 = 0; c0 < d.Cin; c0 += CI_T)
+    {
+        for (int idx = tid; idx < IH * IW * CI_T; idx += 256)
+        {
+            int ci = idx % CI_T, px = idx / CI_T;
+            int r = px / IW, c = px % IW;
+            int y = ty0 + r - d.pad_top, x = tx0 + c - d.pad_left;
+            float v = 0.f;
+            if (y >= 0 && y < d.H && x >= 0 && x < d.W && c0 + ci < d.Cin)
+                v = in[(static_cast<size_t>(y) * d.W + x) * d.Cin + c0 + ci];
+            s_in[r][c][ci] = v;
+        }
+        for (int idx = tid; idx < KS * KS * CI_T * CO_T; idx += 256)
+        {
+            int co = idx % CO_T, ci = (idx / CO_T) % CI_T, k = idx / (CO_T * CI_T);
+            float v = 0.f;
+            if (c0 + ci < d.Cin && cot0 + co < d.Cout)
+                v = w[(static_cast<size_t>(k) * d.Cin + c0 + ci) * d.Cout + cot0 + co];
+            s_w[k][ci][co] = v;
+        }
+        __syncthreads();
+
+#pragma unroll
+        for (int kh = 0; kh < KS; kh++)
+        {
+#pragma unroll 2
+            for (int ci = 0; ci < CI_T; ci++)
+            {
+                float xin[PXT + KS - 1];
+#pragma unroll
+                for (int j = 0; j < PXT + KS - 1; j++) xin[j] = s_in[row + kh][col0 + j][ci];
+#pragma unroll
+                for (int kw = 0; kw < KS; kw++)
+                {
+                    float4 wv = *reinterpret_cast<float4 const*>(&s_w[kh * KS + kw][ci][cg * 4]);
+#pragma unroll
+                    for (int i = 0; i < PXT; i++)
+                    {
+                        acc[i][0] = fmaf(xin[i + kw], wv.x, acc[i][0]);
+                        acc[i][1] = fmaf(xin[i + kw], wv.y, acc[i][1]);
+                        acc[i][2] = fmaf(xin[i + kw], wv.z, acc[i][2]);
+                        acc[i][3] = fmaf(xin[i + kw], wv.w, acc[i][3]);
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+
+    int const oy = ty0 + row;
+    if (oy >= d.OH) return;
+    int const co = cot0 + cg * 4;
+    float b[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) b[j] = (bias != nullptr && co + j < d.Cout) ? bias[co + j] : 0.f;
+    bool const vec = (d.Cout % 4 == 0) && (co + 3 < d.Cout);
+#pragma unroll
+    for (int i = 0; i < PXT; i++)
+    {
+        int ox = tx0 + col0 + i;
+        if (ox >= d.OW) continue;
+        float* o = out + (static_cast<size_t>(oy) * d.OW + ox) * d.Cout + co;
+        float r0 = apply_act(acc[i][0] + b[0], d.act, d.alpha);
+        float r1 = apply_act(acc[i][1] + b[1], d.act, d.alpha);
+        float r2 = apply_act(acc[i][2] + b[2], d.act, d.alpha);
+        float r3 = apply_act(acc[i][3] + b[3], d.act, d.alpha);
+        if (vec)
+        {
+            *reinterpret_cast<float4*>(o) = make_float4(r0, r1, r2, r3);
+        }
+        else
+        {
+            if (co + 0 < d.Cout) o[0] = r0;
+            if (co + 1 < d.Cout) o[1] = r1;
+            if (co + 2 < d.Cout) o[2] = r2;
+            if (co + 3 < d.Cout) o[3] = r3;
+        }
+    }
+}
+
+__global__ void conv2d_naive_kernel(float const* __restrict__ in, float const* __restrict__ w,
+                                    float const* __restrict__ bias, float* __restrict__ out, ConvDesc d)
+{
+    size_t const total = static_cast<size_t>(d.OH) * d.OW * d.Cout;
+    size_t idx = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= total) return;
+    int co = static_cast<int>(idx % d.Cout);
+    size_t px = idx / d.Cout;
+    int ox = static_cast<int>(px % d.OW), oy = static_cast<int>(px / d.OW);
+    float acc = 0.f;
+    for (int kh = 0; kh < d.KH; kh++)
+    {
+        int y = oy * d.stride + kh * d.dilation - d.pad_top;
+        if (y < 0 || y >= d.H) continue;
+        for (int kw = 0; kw < d.KW; kw++)
+        {
+            int x = ox * d.stride + kw * d.dilation - d.pad_left;
+            if (x < 0 || x >= d.W) continue;
+            float const* ip = in + (static_cast<size_t>(y) * d.W + x) * d.Cin;
+            float const* wp = w + (static_cast<size_t>(kh) * d.KW + kw) * d.Cin * d.Cout + co;
+            for (int ci = 0; ci < d.Cin; ci++) acc = fmaf(ip[ci], wp[static_cast<size_t>(ci) * d.Cout], acc);
+        }
+    }
+    if (bias) acc += bias[co];
+    out[idx] = apply_act(acc, d.act, d.alpha);
+}
+
+template <int KS, int TH, int TW, int PXT, int CG, int CI_T>
+void LaunchTile(float const* in, float const* w, float const* bias, float* out, ConvDesc const& d,
+                cudaStream_t stream)
+{
+    dim3 grid((d.OW + TW - 1) / TW, (d.OH + TH - 1) / TH, (d.Cout + 4 * CG - 1) / (4 * CG));
+    conv2d_tile_kernel<KS, TH, TW, PXT, CG, CI_T><<<grid, 256, 0, stream>>>(in, w, bias, out, d);
+}
+
+template <int KS, int CI_T>
+void LaunchTileForCout(float const* in, float const* w, float const* bias, float* out,
+                       ConvDesc const& d, cudaStream_t stream)
+{
+    if (d.Cout <= 4) LaunchTile<KS, 16, 16, 1, 1, CI_T>(in, w, bias, out, d, stream);
+    else if (d.Cout <= 16) LaunchTile<KS, 16, 32, 8, 4, CI_T>(in, w, bias, out, d, stream);
+    else if (d.Cout <= 32) LaunchTile<KS, 16, 16, 8, 8, CI_T>(in, w, bias, out, d, stream);
+    else LaunchTile<KS, 8, 16, 8, 16, CI_T>(in, w, bias, out, d, stream);
+}
+
+__global__ void bias_act_kernel(float const* __restrict__ in, float const* __restrict__ bias,
+                                float* __restrict__ out, size_t n, int C, Act act, float alpha)
+{
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride)
+    {
+        float v = in[i];
+        if (bias) v += bias[i % C];
+        out[i] = apply_act(v, act, alpha);
+    }
+}
+
+__global__ void add_act_kernel(float const* __restrict__ a, float const* __restrict__ b,
+                               float* __restrict__ out, size_t n, Act act, float alpha)
+{
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride) out[i] = apply_act(a[i] + b[i], act, alpha);
+}
+
+__global__ void concat_kernel(float const* __restrict__ in, float* __restrict__ out, size_t pixels,
+                              int C, int Ctotal, int c0)
+{
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    size_t const n = pixels * C;
+    for (; i < n; i += stride)
+    {
+        size_t p = i / C;
+        int c = static_cast<int>(i % C);
+        out[p * Ctotal + c0 + c] = in[i];
+    }
+}
+
+__global__ void half_to_float_kernel(__half const* __restrict__ in, float* __restrict__ out, size_t n)
+{
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride) out[i] = __half2float(in[i]);
+}
+
+__global__ void float_to_half_kernel(float const* __restrict__ in, __half* __restrict__ out, size_t n)
+{
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride) out[i] = __float2half_rn(in[i]);
+}
+
+inline unsigned EltGrid(size_t n)
+{
+    size_t blocks = (n + 255) / 256;
+    size_t const cap = 148u * 16u;
+    return static_cast<unsigned>(blocks < 1 ? 1 : (blocks > cap ? cap : blocks));
+}
+
+} // namespace
+
+void Conv2dFp32(float const* in, float const* w, float const* bias, float* out, ConvDesc const& d,
+                cudaStream_t stream)
+{
+    bool const tiled = d.stride == 1 && d.dilation == 1 && d.KH == d.KW
+                    && (d.KH == 1 || d.KH == 3 || d.KH == 5);
+    if (tiled)
+    {
+        if (d.KH == 1) LaunchTileForCout<1, 8>(in, w, bias, out, d, stream);
+        else if (d.KH == 3) LaunchTileForCout<3, 8>(in, w, bias, out, d, stream);
+        else LaunchTileForCout<5, 4>(in, w, bias, out, d, stream);
+    }
+    else
+    {
+        size_t const total = static_cast<size_t>(d.OH) * d.OW * d.Cout;
+        unsigned const blocks = static_cast<unsigned>((total + 255) / 256);
+        conv2d_naive_kernel<<<blocks, 256, 0, stream>>>(in, w, bias, out, d);
+    }
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void BiasAct(float const* in, float const* bias, float* out, size_t n, int C, Act act, float alpha,
+             cudaStream_t stream)
+{
+    if (n == 0) return;
+    bias_act_kernel<<<EltGrid(n), 256, 0, stream>>>(in, bias, out, n, C, act, alpha);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void AddAct(float const* a, float const* b, float* out, size_t n, Act act, float alpha,
+            cudaStream_t stream)
+{
+    if (n == 0) return;
+    add_act_kernel<<<EltGrid(n), 256, 0, stream>>>(a, b, out, n, act, alpha);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void ConcatChannels(float const* in, float* out, size_t pixels, int C, int Ctotal, int c0,
+                    cudaStream_t stream)
+{
+    if (pixels == 0) return;
+    concat_kernel<<<EltGrid(pixels * C), 256, 0, stream>>>(in, out, pixels, C, Ctotal, c0);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void HalfToFloat(void const* in, float* out, size_t n, cudaStream_t stream)
+{
+    if (n == 0) return;
+    half_to_float_kernel<<<EltGrid(n), 256, 0, stream>>>(static_cast<__half const*>(in), out, n);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void FloatToHalf(float const* in, void* out, size_t n, cudaStream_t stream)
+{
+    if (n == 0) return;
+    float_to_half_kernel<<<EltGrid(n), 256, 0, stream>>>(in, static_cast<__half*>(out), n);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+} // namespace nn
+} // namespace ML

@@ -1,0 +1,682 @@
+// render_kernels.cu -- the render loop as sm_100a CUDA kernels (SURVEY.md rows
+// R1-R5; BUILD-DEFINED arithmetic, fixed by docs/RENDER_SPEC.md).
+//
+//  * render_brute_kernel<R>: every ray tests every triangle.  Triangles are
+//    staged HBM -> shared memory as SoA float4 tiles with 1-D bulk async copies
+//    (cp.async.bulk + mbarrier, double buffered); every thread keeps R rays in
+//    registers and reads each triangle once per R tests as three broadcast
+//    LDS.128.  This is the FP32-FMA-pipe roofline kernel (45 FLOP per test).
+//  * render_bvh_kernel: one thread per pixel, stack traversal of the 64-byte
+//    two-child-box nodes through the read-only path, near child first.
+//
+// Both produce identical results: the winner of a closest-hit query is the
+// lexicographic minimum of (t, id) and the barycentric decision is a pure
+// function of (ray, triangle), so traversal order never shows in the output.
+//
+// Compiled with -fmad=false; every fused operation is an explicit __fmaf_rn.
+#include "scene.h"
+
+#include <cuda_runtime.h>
+
+namespace ML {
+namespace {
+
+// ---------------------------------------------------------------------------
+// spec arithmetic (docs/RENDER_SPEC.md section 0)
+// ---------------------------------------------------------------------------
+struct V3 { float x, y, z; };
+
+__device__ __forceinline__ float mul(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float sub(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fma_(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+
+__device__ __forceinline__ float dot3(V3 a, V3 b)
+{
+    return fma_(a.z, b.z, fma_(a.y, b.y, mul(a.x, b.x)));
+}
+__device__ __forceinline__ V3 cross3(V3 a, V3 b)
+{
+    V3 r;
+    r.x = fma_(a.y, b.z, -mul(a.z, b.y));
+    r.y = fma_(a.z, b.x, -mul(a.x, b.z));
+    r.z = fma_(a.x, b.y, -mul(a.y, b.x));
+    return r;
+}
+__device__ __forceinline__ V3 v3(float const* p) { return V3{p[0], p[1], p[2]}; }
+__device__ __forceinline__ V3 v3(float4 p) { return V3{p.x, p.y, p.z}; }
+__device__ __forceinline__ float pos_inf() { return __int_as_float(0x7f800000); }
+
+__device__ __forceinline__ uint32_t hash_sample(uint32_t pix, uint32_t s, uint32_t dim, uint32_t seed)
+{
+    uint32_t h = (pix * 0x9E3779B1u) ^ (s * 0x85EBCA77u + dim * 0xC2B2AE3Du + seed * 0x27D4EB2Fu + 0x165667B1u);
+    h ^= h >> 16; h *= 0x7FEB352Du; h ^= h >> 15; h *= 0x846CA68Bu; h ^= h >> 16;
+    return h;
+}
+__device__ __forceinline__ float u01(uint32_t h) { return static_cast<float>(h >> 8) * (1.0f / 16777216.0f); }
+
+// section 2: primary ray direction through pixel (x,y), sample s.
+__device__ __forceinline__ V3 primary_dir(RenderLaunch const& L, uint32_t x, uint32_t y, uint32_t s)
+{
+    float jx = 0.5f, jy = 0.5f;
+    if (L.params.jitter)
+    {
+        uint32_t pix = y * L.params.width + x;
+        jx = u01(hash_sample(pix, s, 0u, L.params.seed));
+        jy = u01(hash_sample(pix, s, 1u, L.params.seed));
+    }
+    float fx = add(static_cast<float>(x), jx);
+    float fy = add(static_cast<float>(y), jy);
+    float sx = mul(fma_(fx, L.inv2w, -1.0f), L.camera.half_w);
+    float sy = mul(-fma_(fy, L.inv2h, -1.0f), L.camera.half_h);
+    V3 r;
+    r.x = fma_(sy, L.camera.up[0], fma_(sx, L.camera.right[0], L.camera.forward[0]));
+    r.y = fma_(sy, L.camera.up[1], fma_(sx, L.camera.right[1], L.camera.forward[1]));
+    r.z = fma_(sy, L.camera.up[2], fma_(sx, L.camera.right[2], L.camera.forward[2]));
+    float len = __fsqrt_rn(dot3(r, r));
+    float inv = __fdiv_rn(1.0f, len);
+    return V3{mul(r.x, inv), mul(r.y, inv), mul(r.z, inv)};
+}
+
+// section 3: sign-normalised Moller-Trumbore.  Returns the `inside` decision;
+// ts/adet are the normalised numerator and |det| (t = ts/adet).
+__device__ __forceinline__ bool mt_inside(V3 o, V3 d, float4 v0, float4 e1, float4 e2,
+                                          float& ts, float& adet)
+{
+    V3 E1 = v3(e1), E2 = v3(e2);
+    V3 p = cross3(d, E2);
+    float det = dot3(E1, p);
+    V3 tv = V3{sub(o.x, v0.x), sub(o.y, v0.y), sub(o.z, v0.z)};
+    float us = dot3(tv, p);
+    V3 q = cross3(tv, E1);
+    float vs = dot3(d, q);
+    float tsr = dot3(E2, q);
+    uint32_t sgn = __float_as_uint(det) & 0x80000000u;
+    us = __uint_as_float(__float_as_uint(us) ^ sgn);
+    vs = __uint_as_float(__float_as_uint(vs) ^ sgn);
+    ts = __uint_as_float(__float_as_uint(tsr) ^ sgn);
+    adet = fabsf(det);
+    return (adet != 0.0f) & (us >= 0.0f) & (vs >= 0.0f) & (add(us, vs) <= adet);
+}
+
+// Closest-hit record: t, original triangle id (tie-break + output) and the
+// slot of the triangle in the leaf-ordered arrays (to fetch its edges later).
+struct Hit { float t; int id; uint32_t slot; };
+
+__device__ __forceinline__ Hit no_hit() { return Hit{pos_inf(), -1, 0u}; }
+
+__device__ __forceinline__ void closest_update(Hit& best, float ts, float adet, int id, uint32_t slot,
+                                               float t_min)
+{
+    float t = __fdiv_rn(ts, adet);
+    if (t > t_min && (t < best.t || (t == best.t && id < best.id)))
+    {
+        best.t = t;
+        best.id = id;
+        best.slot = slot;
+    }
+}
+
+// section 4 up to the shadow ray: the unshadowed radiance and, when a shadow
+// ray is needed, its origin/direction.
+struct ShadeOut { V3 rgb; V3 so, sd; bool need_shadow; };
+
+__device__ __forceinline__ ShadeOut shade_hit(RenderLaunch const& L, V3 o, V3 d, Hit h)
+{
+    ShadeOut out;
+    out.need_shadow = false;
+    out.so = V3{0.f, 0.f, 0.f};
+    out.sd = V3{0.f, 0.f, 0.f};
+    V3 alb = v3(__ldg(reinterpret_cast<float4 const*>(L.scene.albedo) + h.id));
+    if (L.params.shade == SRT_SHADE_ALBEDO) { out.rgb = alb; return out; }
+
+    float4 e1 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e1) + h.slot);
+    float4 e2 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e2) + h.slot);
+    V3 P = V3{fma_(h.t, d.x, o.x), fma_(h.t, d.y, o.y), fma_(h.t, d.z, o.z)};
+    V3 nr = cross3(v3(e1), v3(e2));
+    float nl = __fsqrt_rn(dot3(nr, nr));
+    float inl = __fdiv_rn(1.0f, nl);
+    V3 n = V3{mul(nr.x, inl), mul(nr.y, inl), mul(nr.z, inl)};
+    if (dot3(n, d) > 0.0f) n = V3{-n.x, -n.y, -n.z};
+    V3 Lv = V3{sub(L.light.position[0], P.x), sub(L.light.position[1], P.y), sub(L.light.position[2], P.z)};
+    float dist2 = dot3(Lv, Lv);
+    float dist = __fsqrt_rn(dist2);
+    float idist = __fdiv_rn(1.0f, dist);
+    V3 l = V3{mul(Lv.x, idist), mul(Lv.y, idist), mul(Lv.z, idist)};
+    float c = dot3(n, l);
+    if (!(c > 0.0f)) { out.rgb = V3{0.f, 0.f, 0.f}; return out; }
+    float k = __fdiv_rn(c, dist2);
+    out.rgb = V3{mul(mul(alb.x, L.light.intensity[0]), k),
+                 mul(mul(alb.y, L.light.intensity[1]), k),
+                 mul(mul(alb.z, L.light.intensity[2]), k)};
+    if (L.params.shade == SRT_SHADE_SHADOW)
+    {
+        out.need_shadow = true;
+        float eps = L.params.shadow_eps;
+        out.so = V3{fma_(eps, n.x, P.x), fma_(eps, n.y, P.y), fma_(eps, n.z, P.z)};
+        out.sd = V3{sub(L.light.position[0], out.so.x), sub(L.light.position[1], out.so.y),
+                    sub(L.light.position[2], out.so.z)};
+    }
+    return out;
+}
+
+__device__ __forceinline__ unsigned long long warp_sum(unsigned long long v)
+{
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    return v;
+}
+
+__device__ __forceinline__ void flush_counters(RenderLaunch const& L, unsigned long long primary,
+                                               unsigned long long shadow, unsigned long long boxes,
+                                               unsigned long long tris)
+{
+    primary = warp_sum(primary);
+    shadow = warp_sum(shadow);
+    boxes = warp_sum(boxes);
+    tris = warp_sum(tris);
+    if ((threadIdx.x & 31) == 0)
+    {
+        atomicAdd(L.d_counters + 0, primary);
+        atomicAdd(L.d_counters + 1, shadow);
+        if (L.params.collect_stats)
+        {
+            atomicAdd(L.d_counters + 2, boxes);
+            atomicAdd(L.d_counters + 3, tris);
+        }
+    }
+}
+
+// Writes one finished pixel (section 5).  `pix` is the full-frame pixel index.
+__device__ __forceinline__ void store_pixel(RenderLaunch const& L, uint32_t pix, V3 acc, Hit first)
+{
+    size_t const out = static_cast<size_t>(pix) - static_cast<size_t>(L.params.buf_y0) * L.params.width;
+    if (L.d_rgb)
+    {
+        float* p = L.d_rgb + out * 3;
+        p[0] = mul(acc.x, L.inv_spp);
+        p[1] = mul(acc.y, L.inv_spp);
+        p[2] = mul(acc.z, L.inv_spp);
+    }
+    if (L.d_hit_id) L.d_hit_id[out] = first.id;
+    if (L.d_hit_t) L.d_hit_t[out] = first.t;
+}
+
+// ---------------------------------------------------------------------------
+// mbarrier / bulk-copy helpers (PTX)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(void const* p)
+{
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    uint32_t done;
+    do
+    {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, void const* src_gmem, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+        ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// ---------------------------------------------------------------------------
+// brute force
+// ---------------------------------------------------------------------------
+constexpr int kBruteThreads = 256;
+constexpr uint32_t kTileBytes = kTriTile * sizeof(float4);
+
+struct BruteSmem
+{
+    float4 v0[2][kTriTile];
+    float4 e1[2][kTriTile];
+    float4 e2[2][kTriTile];
+    uint64_t bar[2];
+};
+
+__device__ __forceinline__ void brute_issue_tile(BruteSmem& sm, DeviceSceneView const& sc,
+                                                 uint32_t tile, uint32_t buf)
+{
+    mbar_expect_tx(&sm.bar[buf], 3u * kTileBytes);
+    size_t off = static_cast<size_t>(tile) * kTriTile;
+    bulk_g2s(sm.v0[buf], sc.tri_v0 + off, kTileBytes, &sm.bar[buf]);
+    bulk_g2s(sm.e1[buf], sc.tri_e1 + off, kTileBytes, &sm.bar[buf]);
+    bulk_g2s(sm.e2[buf], sc.tri_e2 + off, kTileBytes, &sm.bar[buf]);
+}
+
+// One block-collective sweep over all triangle tiles.  ANY = false: closest
+// hit for R rays; ANY = true: occlusion flags.  `seq` counts tiles consumed by
+// this block so far (buffer = seq & 1, mbarrier parity = (seq >> 1) & 1).
+template <int R, bool ANY>
+__device__ __forceinline__ void brute_sweep(BruteSmem& sm, DeviceSceneView const& sc, uint32_t& seq,
+                                            V3 const (&o)[R], V3 const (&d)[R], float t_min,
+                                            Hit (&best)[R], bool (&occluded)[R])
+{
+    uint32_t const n_tiles = sc.n_tris_padded / kTriTile;
+    if (threadIdx.x == 0)
+    {
+        brute_issue_tile(sm, sc, 0, seq & 1u);
+        if (n_tiles > 1) brute_issue_tile(sm, sc, 1, (seq + 1u) & 1u);
+    }
+    for (uint32_t tile = 0; tile < n_tiles; tile++, seq++)
+    {
+        uint32_t const buf = seq & 1u;
+        mbar_wait(&sm.bar[buf], (seq >> 1) & 1u);
+        float4 const* tv0 = sm.v0[buf];
+        float4 const* te1 = sm.e1[buf];
+        float4 const* te2 = sm.e2[buf];
+#pragma unroll 2
+        for (int j = 0; j < kTriTile; j++)
+        {
+            float4 v0 = tv0[j], e1 = te1[j], e2 = te2[j];
+#pragma unroll
+            for (int r = 0; r < R; r++)
+            {
+                float ts, adet;
+                if (mt_inside(o[r], d[r], v0, e1, e2, ts, adet))
+                {
+                    if (ANY)
+                    {
+                        float t = __fdiv_rn(ts, adet);
+                        if (t > 0.0f && t < 1.0f) occluded[r] = true;
+                    }
+                    else
+                    {
+                        closest_update(best[r], ts, adet, __float_as_int(v0.w),
+                                       tile * kTriTile + static_cast<uint32_t>(j), t_min);
+                    }
+                }
+            }
+        }
+        __syncthreads(); // everyone is done with `buf` before it is refilled
+        if (threadIdx.x == 0 && tile + 2 < n_tiles) brute_issue_tile(sm, sc, tile + 2, buf);
+    }
+}
+
+template <int R>
+__global__ void __launch_bounds__(kBruteThreads) render_brute_kernel(const __grid_constant__ RenderLaunch L)
+{
+    __shared__ __align__(128) BruteSmem sm;
+    if (threadIdx.x == 0)
+    {
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    uint32_t const W = L.params.width;
+    uint32_t const band_pixels = (L.params.y1 - L.params.y0) * W;
+    uint32_t const first_pixel = L.params.y0 * W;
+    uint32_t const chunk = blockIdx.x * (kBruteThreads * R);
+    V3 const cam_o = v3(L.camera.origin);
+    DeviceSceneView const& sc = L.scene;
+    bool const shadows = L.params.shade == SRT_SHADE_SHADOW;
+
+    uint32_t pix[R];
+    bool valid[R];
+    V3 acc[R];
+    Hit first_hit[R];
+#pragma unroll
+    for (int r = 0; r < R; r++)
+    {
+        uint32_t local = chunk + r * kBruteThreads + threadIdx.x;
+        valid[r] = local < band_pixels;
+        pix[r] = first_pixel + (valid[r] ? local : 0u);
+        acc[r] = V3{0.f, 0.f, 0.f};
+        first_hit[r] = no_hit();
+    }
+
+    uint32_t seq = 0;
+    unsigned long long n_primary = 0, n_shadow = 0;
+
+    for (uint32_t s = 0; s < L.params.spp; s++)
+    {
+        V3 o[R], d[R];
+        Hit best[R];
+        bool occ[R];
+#pragma unroll
+        for (int r = 0; r < R; r++)
+        {
+            uint32_t y = pix[r] / W, x = pix[r] - y * W;
+            o[r] = cam_o;
+            // Lanes past the end of the band trace a null ray (d = 0 => det = 0
+            // => never inside) so the block-collective sweep stays uniform.
+            d[r] = valid[r] ? primary_dir(L, x, y, s) : V3{0.f, 0.f, 0.f};
+            best[r] = no_hit();
+            occ[r] = false;
+            n_primary += valid[r] ? 1u : 0u;
+        }
+        brute_sweep<R, false>(sm, sc, seq, o, d, L.params.t_min, best, occ);
+
+        V3 rgb[R];
+#pragma unroll
+        for (int r = 0; r < R; r++)
+        {
+            if (s == 0) first_hit[r] = best[r];
+            V3 so = V3{0.f, 0.f, 0.f}, sd = V3{0.f, 0.f, 0.f};
+            if (best[r].id < 0 || !valid[r])
+            {
+                rgb[r] = v3(L.params.background);
+            }
+            else
+            {
+                ShadeOut sh = shade_hit(L, o[r], d[r], best[r]);
+                rgb[r] = sh.rgb;
+                if (sh.need_shadow)
+                {
+                    so = sh.so;
+                    sd = sh.sd;
+                    n_shadow += 1u;
+                }
+            }
+            o[r] = so;
+            d[r] = sd; // null ray when no shadow query is needed
+        }
+        if (shadows) // block-uniform
+        {
+            brute_sweep<R, true>(sm, sc, seq, o, d, 0.0f, best, occ);
+#pragma unroll
+            for (int r = 0; r < R; r++)
+                if (occ[r]) rgb[r] = V3{0.f, 0.f, 0.f};
+        }
+#pragma unroll
+        for (int r = 0; r < R; r++)
+        {
+            acc[r].x = add(acc[r].x, rgb[r].x);
+            acc[r].y = add(acc[r].y, rgb[r].y);
+            acc[r].z = add(acc[r].z, rgb[r].z);
+        }
+    }
+
+#pragma unroll
+    for (int r = 0; r < R; r++)
+        if (valid[r]) store_pixel(L, pix[r], acc[r], first_hit[r]);
+
+    unsigned long long tri_tests = (n_primary + n_shadow) * sc.n_tris;
+    flush_counters(L, n_primary, n_shadow, 0ull, tri_tests);
+}
+
+// ---------------------------------------------------------------------------
+// BVH traversal
+// ---------------------------------------------------------------------------
+constexpr int kBvhThreads = 256;  // 8 warps; each warp owns an 8x4 pixel tile
+constexpr int kBvhBlockW = 32;
+constexpr int kBvhBlockH = 8;
+
+struct RayBox
+{
+    V3 idir; // 1/d with |d| clamped away from 0
+    V3 ood;  // o * idir
+};
+
+__device__ __forceinline__ float safe_inv(float d)
+{
+    float const eps = 1e-30f;
+    float a = fabsf(d) > eps ? d : copysignf(eps, d);
+    return 1.0f / a;
+}
+
+// Culling only (docs/RENDER_SPEC.md section 6): boxes are padded at build time and
+// `t_far` carries a relative slack, so rounding here can only visit too much.
+template <bool ANY, bool STATS>
+__device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d, float t_min,
+                                          Hit& best, bool& occluded,
+                                          unsigned long long& n_box, unsigned long long& n_tri)
+{
+    float4 const* __restrict__ nodes = reinterpret_cast<float4 const*>(sc.nodes);
+    float4 const* __restrict__ tv0 = reinterpret_cast<float4 const*>(sc.tri_v0);
+    float4 const* __restrict__ te1 = reinterpret_cast<float4 const*>(sc.tri_e1);
+    float4 const* __restrict__ te2 = reinterpret_cast<float4 const*>(sc.tri_e2);
+
+    float const idx = safe_inv(d.x), idy = safe_inv(d.y), idz = safe_inv(d.z);
+    float const oodx = o.x * idx, oody = o.y * idy, oodz = o.z * idz;
+    float const slack = 1.000244140625f; // 1 + 2^-12
+    float t_far = ANY ? slack : pos_inf();
+    float const t_near = fmaxf(t_min, 0.0f);
+
+    int stack[kBvhStackDepth];
+    int sp = 0;
+    int node = 0; // root is always an inner node
+
+    while (true)
+    {
+        while (node >= 0)
+        {
+            float4 n0 = __ldg(nodes + 4 * node + 0);
+            float4 n1 = __ldg(nodes + 4 * node + 1);
+            float4 n2 = __ldg(nodes + 4 * node + 2);
+            float4 n3 = __ldg(nodes + 4 * node + 3);
+            if (STATS) n_box += 2;
+
+            float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
+            float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
+            float c0loz = fmaf(n2.x, idz, -oodz), c0hiz = fmaf(n2.y, idz, -oodz);
+            float c1lox = fmaf(n1.x, idx, -oodx), c1hix = fmaf(n1.y, idx, -oodx);
+            float c1loy = fmaf(n1.z, idy, -oody), c1hiy = fmaf(n1.w, idy, -oody);
+            float c1loz = fmaf(n2.z, idz, -oodz), c1hiz = fmaf(n2.w, idz, -oodz);
+
+            float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)),
+                                fmaxf(fminf(c0loz, c0hiz), t_near));
+            float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)),
+                                fminf(fmaxf(c0loz, c0hiz), t_far));
+            float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)),
+                                fmaxf(fminf(c1loz, c1hiz), t_near));
+            float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)),
+                                fminf(fmaxf(c1loz, c1hiz), t_far));
+
+            // Slack on the entry distance as well (relative + box-scale absolute
+            // error is already covered by the build-time padding).
+            bool hit0 = c0max * slack >= c0min;
+            bool hit1 = c1max * slack >= c1min;
+            int ref0 = __float_as_int(n3.x), ref1 = __float_as_int(n3.y);
+
+            if (!hit0 && !hit1)
+            {
+                if (sp == 0) return;
+                node = stack[--sp];
+            }
+            else if (hit0 && hit1)
+            {
+                bool swap = c1min < c0min;
+                node = swap ? ref1 : ref0;
+                stack[sp++] = swap ? ref0 : ref1;
+            }
+            else
+            {
+                node = hit0 ? ref0 : ref1;
+            }
+        }
+
+        // leaf
+        {
+            uint32_t enc = static_cast<uint32_t>(~node);
+            uint32_t first = enc >> kLeafCountBits;
+            uint32_t count = (enc & ((1u << kLeafCountBits) - 1u)) + 1u;
+            if (STATS) n_tri += count;
+            for (uint32_t i = first; i < first + count; i++)
+            {
+                float4 v0 = __ldg(tv0 + i), e1 = __ldg(te1 + i), e2 = __ldg(te2 + i);
+                float ts, adet;
+                if (mt_inside(o, d, v0, e1, e2, ts, adet))
+                {
+                    if (ANY)
+                    {
+                        float t = __fdiv_rn(ts, adet);
+                        if (t > 0.0f && t < 1.0f) { occluded = true; return; }
+                    }
+                    else
+                    {
+                        closest_update(best, ts, adet, __float_as_int(v0.w), i, t_min);
+                        t_far = best.t * slack;
+                    }
+                }
+            }
+        }
+        if (sp == 0) return;
+        node = stack[--sp];
+    }
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(kBvhThreads) render_bvh_kernel(const __grid_constant__ RenderLaunch L)
+{
+    uint32_t const W = L.params.width;
+    uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t const x = blockIdx.x * kBvhBlockW + (warp & 3u) * 8u + (lane & 7u);
+    uint32_t const y = L.params.y0 + blockIdx.y * kBvhBlockH + (warp >> 2) * 4u + (lane >> 3);
+    bool const valid = x < W && y < L.params.y1;
+
+    unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
+    if (valid)
+    {
+        V3 const o = v3(L.camera.origin);
+        V3 acc = V3{0.f, 0.f, 0.f};
+        Hit first_hit = no_hit();
+        for (uint32_t s = 0; s < L.params.spp; s++)
+        {
+            V3 d = primary_dir(L, x, y, s);
+            Hit best = no_hit();
+            bool occ = false;
+            n_primary++;
+            bvh_trace<false, STATS>(L.scene, o, d, L.params.t_min, best, occ, n_box, n_tri);
+            if (s == 0) first_hit = best;
+            V3 rgb;
+            if (best.id < 0)
+            {
+                rgb = v3(L.params.background);
+            }
+            else
+            {
+                ShadeOut sh = shade_hit(L, o, d, best);
+                rgb = sh.rgb;
+                if (sh.need_shadow)
+                {
+                    n_shadow++;
+                    Hit dummy = no_hit();
+                    bvh_trace<true, STATS>(L.scene, sh.so, sh.sd, 0.0f, dummy, occ, n_box, n_tri);
+                    if (occ) rgb = V3{0.f, 0.f, 0.f};
+                }
+            }
+            acc.x = add(acc.x, rgb.x);
+            acc.y = add(acc.y, rgb.y);
+            acc.z = add(acc.z, rgb.z);
+        }
+        store_pixel(L, y * W + x, acc, first_hit);
+    }
+    flush_counters(L, n_primary, n_shadow, n_box, n_tri);
+}
+
+// ---------------------------------------------------------------------------
+// FP32 peak microbenchmark: 8 independent FFMA chains per thread.
+// ---------------------------------------------------------------------------
+constexpr int kPeakIters = 4096;
+constexpr int kPeakChains = 8;
+
+__global__ void __launch_bounds__(256) fp32_peak_kernel(float* out, float a, float b)
+{
+    float x[kPeakChains];
+#pragma unroll
+    for (int i = 0; i < kPeakChains; i++) x[i] = static_cast<float>(threadIdx.x + i) * 1e-3f;
+#pragma unroll 1
+    for (int it = 0; it < kPeakIters; it++)
+    {
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+#pragma unroll
+            for (int i = 0; i < kPeakChains; i++) x[i] = __fmaf_rn(x[i], a, b);
+    }
+    float sum = 0.f;
+#pragma unroll
+    for (int i = 0; i < kPeakChains; i++) sum += x[i];
+    if (sum == 12345.678f) out[0] = sum; // never true; keeps the chains alive
+}
+
+} // namespace
+
+// ---------------------------------------------------------------------------
+// host launchers
+// ---------------------------------------------------------------------------
+void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
+{
+    srt_render_params const& p = launch.params;
+    uint32_t const rows = p.y1 - p.y0;
+    if (p.accel == SRT_ACCEL_BVH)
+    {
+        dim3 grid((p.width + kBvhBlockW - 1) / kBvhBlockW, (rows + kBvhBlockH - 1) / kBvhBlockH);
+        if (p.collect_stats)
+            render_bvh_kernel<true><<<grid, kBvhThreads, 0, stream>>>(launch);
+        else
+            render_bvh_kernel<false><<<grid, kBvhThreads, 0, stream>>>(launch);
+    }
+    else
+    {
+        // R rays per thread: 4 amortises the triangle LDS best; fall back to
+        // fewer when the band is too small to fill the SMs twice over.
+        uint64_t const pixels = static_cast<uint64_t>(rows) * p.width;
+        uint64_t const fill = static_cast<uint64_t>(sm_count) * 2u * kBruteThreads;
+        if (pixels >= 4 * fill)
+        {
+            uint32_t blocks = static_cast<uint32_t>((pixels + kBruteThreads * 4 - 1) / (kBruteThreads * 4));
+            render_brute_kernel<4><<<blocks, kBruteThreads, 0, stream>>>(launch);
+        }
+        else if (pixels >= 2 * fill)
+        {
+            uint32_t blocks = static_cast<uint32_t>((pixels + kBruteThreads * 2 - 1) / (kBruteThreads * 2));
+            render_brute_kernel<2><<<blocks, kBruteThreads, 0, stream>>>(launch);
+        }
+        else
+        {
+            uint32_t blocks = static_cast<uint32_t>((pixels + kBruteThreads - 1) / kBruteThreads);
+            render_brute_kernel<1><<<blocks, kBruteThreads, 0, stream>>>(launch);
+        }
+    }
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+double MeasureFp32Peak(DeviceState const& device, int repeats)
+{
+    device.MakeCurrent();
+    float* d_out = nullptr;
+    ML_CUDA_CHECK(cudaMalloc(&d_out, sizeof(float)));
+    int const blocks = device.prop.multiProcessorCount * 16;
+    cudaStream_t s = device.stream;
+    fp32_peak_kernel<<<blocks, 256, 0, s>>>(d_out, 0.999f, 1e-3f); // warm-up
+    double best_ms = 1e30;
+    for (int r = 0; r < (repeats > 0 ? repeats : 5); r++)
+    {
+        ML_CUDA_CHECK(cudaEventRecord(device.ev_start, s));
+        fp32_peak_kernel<<<blocks, 256, 0, s>>>(d_out, 0.999f, 1e-3f);
+        ML_CUDA_CHECK(cudaEventRecord(device.ev_stop, s));
+        ML_CUDA_CHECK(cudaStreamSynchronize(s));
+        float ms = 0.f;
+        ML_CUDA_CHECK(cudaEventElapsedTime(&ms, device.ev_start, device.ev_stop));
+        if (ms < best_ms) best_ms = ms;
+    }
+    cudaFree(d_out);
+    double flops = 2.0 * kPeakIters * 4.0 * kPeakChains * 256.0 * blocks;
+    return flops / (best_ms * 1e-3) / 1e12;
+}
+
+} // namespace ML

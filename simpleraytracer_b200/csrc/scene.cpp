@@ -1,0 +1,445 @@
+// scene.cpp -- scene object: SoA upload, BVH, render dispatch and the srt* C
+// entry points (include/srt_render.h).  BUILD-DEFINED (no reference code);
+// error conventions follow the reference's: factories report on the context
+// (context.cpp:20-49), operations return ML_FAIL and leave a message on the
+// object (model.cpp:161-176).
+#include "scene.h"
+
+#include "context.h"
+#include "image.h"
+
+#include <chrono>
+#include <cfloat>
+#include <cmath>
+
+namespace ML {
+
+namespace {
+inline float IntBitsToFloat(int32_t v)
+{
+    float f;
+    std::memcpy(&f, &v, 4);
+    return f;
+}
+} // namespace
+
+Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const* albedo,
+             bool build_bvh)
+    : m_device(std::move(device))
+{
+    if (n > 0 && vertices == nullptr) throw std::runtime_error("Bad vertices argument");
+    if (n >= (size_t(1) << 27)) throw std::runtime_error("Too many triangles");
+    for (size_t i = 0; i < 9 * n; i++)
+        if (!std::isfinite(vertices[i])) throw std::runtime_error("Non-finite vertex coordinate");
+
+    m_device->MakeCurrent();
+
+    // ---- BVH (host) ---------------------------------------------------------
+    std::vector<int32_t> order(n);
+    for (size_t i = 0; i < n; i++) order[i] = static_cast<int32_t>(i);
+    auto t0 = std::chrono::steady_clock::now();
+    if (build_bvh)
+    {
+        BvhBuildResult bvh = BuildBvh(n, vertices);
+        m_nodes_host = std::move(bvh.nodes);
+        order = bvh.order;
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    m_order_host = order;
+    m_info.bvh_build_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+
+    // ---- SoA in leaf order, padded to the tile size ---------------------------
+    size_t const padded = ((n + kTriTile - 1) / kTriTile) * kTriTile + (n == 0 ? kTriTile : 0);
+    std::vector<F4> soa(3 * padded, F4{0.f, 0.f, 0.f, 0.f});
+    F4* v0 = soa.data();
+    F4* e1 = v0 + padded;
+    F4* e2 = e1 + padded;
+    for (size_t i = 0; i < padded; i++) v0[i].w = IntBitsToFloat(-1);
+    float bmin[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, bmax[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (size_t i = 0; i < n; i++)
+    {
+        int32_t id = order[i];
+        float const* v = vertices + 9 * static_cast<size_t>(id);
+        v0[i] = {v[0], v[1], v[2], IntBitsToFloat(id)};
+        e1[i] = {v[3] - v[0], v[4] - v[1], v[5] - v[2], 0.f};
+        e2[i] = {v[6] - v[0], v[7] - v[1], v[8] - v[2], 0.f};
+        for (int k = 0; k < 3; k++)
+        {
+            bmin[k] = std::min(bmin[k], std::min(v[k], std::min(v[3 + k], v[6 + k])));
+            bmax[k] = std::max(bmax[k], std::max(v[k], std::max(v[3 + k], v[6 + k])));
+        }
+    }
+    std::vector<F4> alb(std::max<size_t>(n, 1), F4{0.8f, 0.8f, 0.8f, 0.f});
+    if (albedo)
+        for (size_t i = 0; i < n; i++) alb[i] = {albedo[3 * i], albedo[3 * i + 1], albedo[3 * i + 2], 0.f};
+
+    // ---- upload ----------------------------------------------------------------
+    size_t const tri_bytes = soa.size() * sizeof(F4);
+    size_t const alb_bytes = alb.size() * sizeof(F4);
+    size_t const node_bytes = m_nodes_host.size() * sizeof(BvhNode);
+    try
+    {
+        ML_CUDA_CHECK(cudaMalloc(&m_d_tris, tri_bytes));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_albedo, alb_bytes));
+        if (node_bytes) ML_CUDA_CHECK(cudaMalloc(&m_d_nodes, node_bytes));
+        ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&m_d_counters), 4 * sizeof(unsigned long long)));
+        cudaStream_t s = m_device->stream;
+        ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s));
+        ML_CUDA_CHECK(cudaMemcpyAsync(m_d_tris, soa.data(), tri_bytes, cudaMemcpyHostToDevice, s));
+        ML_CUDA_CHECK(cudaMemcpyAsync(m_d_albedo, alb.data(), alb_bytes, cudaMemcpyHostToDevice, s));
+        if (node_bytes)
+            ML_CUDA_CHECK(cudaMemcpyAsync(m_d_nodes, m_nodes_host.data(), node_bytes, cudaMemcpyHostToDevice, s));
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), s));
+        ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, s));
+        ML_CUDA_CHECK(cudaStreamSynchronize(s));
+        ML_CUDA_CHECK(cudaEventElapsedTime(&m_info.upload_ms, m_device->ev_start, m_device->ev_stop));
+    }
+    catch (...)
+    {
+        cudaFree(m_d_tris); cudaFree(m_d_albedo); cudaFree(m_d_nodes); cudaFree(m_d_counters);
+        throw;
+    }
+
+    m_view.tri_v0 = static_cast<F4 const*>(m_d_tris);
+    m_view.tri_e1 = m_view.tri_v0 + padded;
+    m_view.tri_e2 = m_view.tri_e1 + padded;
+    m_view.albedo = static_cast<F4 const*>(m_d_albedo);
+    m_view.nodes = static_cast<F4 const*>(m_d_nodes);
+    m_view.n_tris = static_cast<uint32_t>(n);
+    m_view.n_tris_padded = static_cast<uint32_t>(padded);
+
+    m_info.n_triangles = n;
+    m_info.n_bvh_nodes = m_nodes_host.size();
+    m_info.device_bytes = tri_bytes + alb_bytes + node_bytes;
+    for (int k = 0; k < 3; k++)
+    {
+        m_info.bounds_min[k] = n ? bmin[k] : 0.f;
+        m_info.bounds_max[k] = n ? bmax[k] : 0.f;
+    }
+}
+
+void Scene::FreeStaging()
+{
+    cudaFree(m_d_rgb); cudaFree(m_d_id); cudaFree(m_d_t);
+    cudaFreeHost(m_h_rgb); cudaFreeHost(m_h_id); cudaFreeHost(m_h_t);
+    m_d_rgb = m_d_id = m_d_t = m_h_rgb = m_h_id = m_h_t = nullptr;
+    m_stage_pixels = 0;
+}
+
+Scene::~Scene()
+{
+    cudaSetDevice(m_device->device);
+    cudaStreamSynchronize(m_device->stream);
+    FreeStaging();
+    cudaFree(m_d_tris); cudaFree(m_d_albedo); cudaFree(m_d_nodes); cudaFree(m_d_counters);
+}
+
+ml_status Scene::GetInfo(srt_scene_info* info) const
+{
+    if (info == nullptr) return ML_FAIL;
+    *info = m_info;
+    return ML_OK;
+}
+
+size_t Scene::GetBvh(float* nodes, size_t max_nodes, int32_t* order, size_t max_order) const
+{
+    if (nodes)
+        std::memcpy(nodes, m_nodes_host.data(), std::min(max_nodes, m_nodes_host.size()) * sizeof(BvhNode));
+    if (order)
+        std::memcpy(order, m_order_host.data(), std::min(max_order, m_order_host.size()) * sizeof(int32_t));
+    return m_nodes_host.size();
+}
+
+bool Scene::Validate(srt_camera const* camera, srt_light const* light, srt_render_params const* p)
+{
+    m_error.clear();
+    std::ostringstream os;
+    if (camera == nullptr) os << "Bad camera argument";
+    else if (light == nullptr) os << "Bad light argument";
+    else if (p == nullptr) os << "Bad render parameters argument";
+    else if (p->width == 0 || p->height == 0) os << "Unspecified frame dimension";
+    else if (static_cast<uint64_t>(p->width) * p->height >= (uint64_t(1) << 31)) os << "Frame too large";
+    else if (p->y0 > p->y1 || p->y1 > p->height)
+        os << "Bad row band [" << p->y0 << ", " << p->y1 << ") for height " << p->height;
+    else if (p->buf_y0 > p->y0) os << "Bad buffer row origin " << p->buf_y0 << " for band start " << p->y0;
+    else if (p->spp == 0) os << "Unspecified sample count";
+    else if (p->shade > SRT_SHADE_SHADOW) os << "Unsupported shade mode: " << p->shade;
+    else if (p->accel > SRT_ACCEL_BVH) os << "Unsupported acceleration mode: " << p->accel;
+    else if (p->accel == SRT_ACCEL_BVH && !HasBvh()) os << "Scene was created without a BVH";
+    m_error = os.str();
+    return m_error.empty();
+}
+
+ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
+                              srt_render_params const* params, void* d_rgb, void* d_hit_id,
+                              void* d_hit_t, cudaStream_t stream, bool timed)
+{
+    if (!Validate(camera, light, params)) return ML_FAIL;
+    try
+    {
+        m_device->MakeCurrent();
+        if (stream == nullptr) stream = m_device->stream;
+        RenderLaunch launch{};
+        launch.scene = m_view;
+        launch.camera = *camera;
+        launch.light = *light;
+        launch.params = *params;
+        launch.inv2w = 2.0f / static_cast<float>(params->width);
+        launch.inv2h = 2.0f / static_cast<float>(params->height);
+        launch.inv_spp = 1.0f / static_cast<float>(params->spp);
+        launch.d_rgb = static_cast<float*>(d_rgb);
+        launch.d_hit_id = static_cast<int32_t*>(d_hit_id);
+        launch.d_hit_t = static_cast<float*>(d_hit_t);
+        launch.d_counters = m_d_counters;
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), stream));
+        if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, stream));
+        if (params->y1 > params->y0)
+            LaunchRender(launch, m_device->prop.multiProcessorCount, stream);
+        if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, stream));
+        ML_CUDA_CHECK(cudaGetLastError());
+        m_timed_pending = timed;
+        m_timed_stream = stream;
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        m_error = e.what();
+        return ML_FAIL;
+    }
+}
+
+ml_status Scene::GetStats(srt_render_stats* stats)
+{
+    if (stats == nullptr) return ML_FAIL;
+    try
+    {
+        m_device->MakeCurrent();
+        cudaStream_t s = m_timed_stream ? m_timed_stream : m_device->stream;
+        unsigned long long c[4] = {};
+        ML_CUDA_CHECK(cudaMemcpyAsync(c, m_d_counters, sizeof(c), cudaMemcpyDeviceToHost, s));
+        ML_CUDA_CHECK(cudaStreamSynchronize(s));
+        stats->primary_rays = c[0];
+        stats->shadow_rays = c[1];
+        stats->box_tests = c[2];
+        stats->tri_tests = c[3];
+        stats->kernel_ms = 0.f;
+        if (m_timed_pending)
+            ML_CUDA_CHECK(cudaEventElapsedTime(&stats->kernel_ms, m_device->ev_start, m_device->ev_stop));
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        m_error = e.what();
+        return ML_FAIL;
+    }
+}
+
+void Scene::EnsureStaging(size_t pixels)
+{
+    if (pixels <= m_stage_pixels) return;
+    FreeStaging();
+    ML_CUDA_CHECK(cudaMalloc(&m_d_rgb, pixels * 12));
+    ML_CUDA_CHECK(cudaMalloc(&m_d_id, pixels * 4));
+    ML_CUDA_CHECK(cudaMalloc(&m_d_t, pixels * 4));
+    ML_CUDA_CHECK(cudaMallocHost(&m_h_rgb, pixels * 12));
+    ML_CUDA_CHECK(cudaMallocHost(&m_h_id, pixels * 4));
+    ML_CUDA_CHECK(cudaMallocHost(&m_h_t, pixels * 4));
+    m_stage_pixels = pixels;
+}
+
+ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
+                            srt_render_params const* params, float* rgb, int32_t* hit_id,
+                            float* hit_t, srt_render_stats* stats)
+{
+    if (!Validate(camera, light, params)) return ML_FAIL;
+    try
+    {
+        m_device->MakeCurrent();
+        cudaStream_t s = m_device->stream;
+        size_t const rows = params->y1 - params->y0;
+        size_t const pixels = rows * params->width;
+        EnsureStaging(std::max<size_t>(pixels, 1));
+
+        // Render the band into band-local device buffers (buf_y0 = y0) ...
+        srt_render_params band = *params;
+        band.buf_y0 = params->y0;
+        ml_status st = RenderDevice(camera, light, &band, m_d_rgb, m_d_id, m_d_t, s, true);
+        if (st != ML_OK) return st;
+
+        // ... then D2H through pinned staging and into the caller's frame at
+        // the rows' full-frame offsets (relative to the caller's buf_y0).
+        size_t const row_off = static_cast<size_t>(params->y0 - params->buf_y0) * params->width;
+        if (rgb) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_rgb, m_d_rgb, pixels * 12, cudaMemcpyDeviceToHost, s));
+        if (hit_id) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_id, m_d_id, pixels * 4, cudaMemcpyDeviceToHost, s));
+        if (hit_t) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_t, m_d_t, pixels * 4, cudaMemcpyDeviceToHost, s));
+        ML_CUDA_CHECK(cudaStreamSynchronize(s));
+        if (rgb) std::memcpy(rgb + row_off * 3, m_h_rgb, pixels * 12);
+        if (hit_id) std::memcpy(hit_id + row_off, m_h_id, pixels * 4);
+        if (hit_t) std::memcpy(hit_t + row_off, m_h_t, pixels * 4);
+        if (stats) return GetStats(stats);
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        m_error = e.what();
+        return ML_FAIL;
+    }
+}
+
+} // namespace ML
+
+// ---------------------------------------------------------------------------
+// C entry points
+// ---------------------------------------------------------------------------
+extern "C" {
+
+ML_API_ENTRY srt_scene srtCreateScene(ml_context context, size_t n_triangles,
+                                      float const* vertices, float const* albedo, int build_bvh)
+{
+    ML::Context* ctx = ML::Context::FromHandle(context);
+    if (ctx == nullptr) return nullptr;
+    ctx->ClearError();
+    try
+    {
+        return ML::Scene::MakeHandle(
+            new ML::Scene(ctx->Device(), n_triangles, vertices, albedo, build_bvh != 0));
+    }
+    catch (std::exception const& e)
+    {
+        ctx->SetError(e.what());
+        return nullptr;
+    }
+}
+
+ML_API_ENTRY ml_status srtGetSceneInfo(srt_scene scene, srt_scene_info* info)
+{
+    if (ML::Scene::FromHandle(scene) == nullptr) return ML_FAIL;
+    return ML::Scene::FromHandle(scene)->GetInfo(info);
+}
+
+ML_API_ENTRY char* srtGetSceneError(srt_scene scene, char* buffer, size_t buffer_size)
+{
+    if (ML::Scene::FromHandle(scene) == nullptr)
+        return ML::FillBuffer(buffer, buffer_size, "Bad scene handle");
+    return ML::Scene::FromHandle(scene)->GetError(buffer, buffer_size);
+}
+
+ML_API_ENTRY void srtReleaseScene(srt_scene scene)
+{
+    delete ML::Scene::FromHandle(scene);
+}
+
+ML_API_ENTRY size_t srtGetSceneBvh(srt_scene scene, float* nodes, size_t max_nodes,
+                                   int32_t* order, size_t max_order)
+{
+    if (ML::Scene::FromHandle(scene) == nullptr) return 0;
+    return ML::Scene::FromHandle(scene)->GetBvh(nodes, max_nodes, order, max_order);
+}
+
+ML_API_ENTRY size_t srtGenCornellBox(float* vertices, float* albedo, srt_camera* camera,
+                                     srt_light* light, uint32_t width, uint32_t height)
+{
+    return ML::GenCornellBox(vertices, albedo, camera, light, width, height);
+}
+
+ML_API_ENTRY ml_status srtGenMesh(uint32_t seed, size_t n_triangles, float* vertices,
+                                  float* albedo, srt_camera* camera, srt_light* light,
+                                  uint32_t width, uint32_t height)
+{
+    try
+    {
+        ML::GenMesh(seed, n_triangles, vertices, albedo, camera, light, width, height);
+        return ML_OK;
+    }
+    catch (...)
+    {
+        return ML_FAIL;
+    }
+}
+
+ML_API_ENTRY ml_status srtRender(srt_scene scene, srt_camera const* camera,
+                                 srt_light const* light, srt_render_params const* params,
+                                 float* rgb, int32_t* hit_id, float* hit_t,
+                                 srt_render_stats* stats)
+{
+    if (ML::Scene::FromHandle(scene) == nullptr) return ML_FAIL;
+    return ML::Scene::FromHandle(scene)->RenderHost(camera, light, params, rgb, hit_id, hit_t, stats);
+}
+
+ML_API_ENTRY ml_status srtRenderDevice(srt_scene scene, srt_camera const* camera,
+                                       srt_light const* light, srt_render_params const* params,
+                                       void* d_rgb, void* d_hit_id, void* d_hit_t, void* stream)
+{
+    if (ML::Scene::FromHandle(scene) == nullptr) return ML_FAIL;
+    return ML::Scene::FromHandle(scene)->RenderDevice(camera, light, params, d_rgb, d_hit_id, d_hit_t,
+                                                      static_cast<cudaStream_t>(stream), true);
+}
+
+ML_API_ENTRY ml_status srtGetRenderStats(srt_scene scene, srt_render_stats* stats)
+{
+    if (ML::Scene::FromHandle(scene) == nullptr) return ML_FAIL;
+    return ML::Scene::FromHandle(scene)->GetStats(stats);
+}
+
+ML_API_ENTRY ml_status srtRenderToImage(srt_scene scene, srt_camera const* camera,
+                                        srt_light const* light, srt_render_params const* params,
+                                        ml_image image, srt_render_stats* stats)
+{
+    ML::Scene* sc = ML::Scene::FromHandle(scene);
+    if (sc == nullptr) return ML_FAIL;
+    ML::Image* img = ML::Image::FromHandle(image);
+    if (img == nullptr) { sc->SetError("Bad image handle"); return ML_FAIL; }
+    if (params == nullptr) { sc->SetError("Bad render parameters argument"); return ML_FAIL; }
+    ml_image_info const& info = img->Info();
+    if (info.dtype != ML_FLOAT32 || info.channels != 3 || info.width != params->width
+        || info.height != params->height)
+    {
+        std::ostringstream os;
+        os << "Image " << info.width << " x " << info.height << " x " << info.channels
+           << " does not match a FLOAT32 frame " << params->width << " x " << params->height << " x 3";
+        sc->SetError(os.str());
+        return ML_FAIL;
+    }
+    if (img->Device()->device != sc->Device()->device)
+    {
+        sc->SetError("Image and scene live on different devices");
+        return ML_FAIL;
+    }
+    try
+    {
+        cudaStream_t s = sc->Device()->stream;
+        srt_render_params p = *params;
+        p.buf_y0 = 0;
+        // A partial band must keep the other rows: make the device copy current first.
+        bool const full = (p.y0 == 0 && p.y1 == p.height);
+        void* d = full ? img->DeviceWrite() : img->DeviceRead(s);
+        ml_status st = sc->RenderDevice(camera, light, &p, d, nullptr, nullptr, s, true);
+        if (st != ML_OK) return st;
+        img->CommitDeviceWrite(s);
+        ML_CUDA_CHECK(cudaStreamSynchronize(s));
+        if (stats) return sc->GetStats(stats);
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        sc->SetError(e.what());
+        return ML_FAIL;
+    }
+}
+
+ML_API_ENTRY double srtMeasureFp32Peak(ml_context context, int repeats)
+{
+    ML::Context* ctx = ML::Context::FromHandle(context);
+    if (ctx == nullptr) return 0.0;
+    try
+    {
+        return ML::MeasureFp32Peak(*ctx->Device(), repeats);
+    }
+    catch (std::exception const& e)
+    {
+        ctx->SetError(e.what());
+        return 0.0;
+    }
+}
+
+} // extern "C"

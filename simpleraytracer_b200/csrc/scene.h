@@ -1,0 +1,135 @@
+// scene.h -- ML::Scene: triangle set + BVH resident in HBM (BUILD-DEFINED; the
+// reference has no scene code).
+//
+// HBM layout (all float4 = 16 B, 16-byte aligned, SoA so that a tile of
+// triangles is three contiguous byte ranges a bulk copy can stage into shared
+// memory):
+//   tri_v0[i] = (v0.x, v0.y, v0.z, bits(original triangle id))
+//   tri_e1[i] = (v1 - v0, 0)        tri_e2[i] = (v2 - v0, 0)
+//   albedo[id] = (r, g, b, 0)                       indexed by ORIGINAL id
+//   nodes[4*k .. 4*k+3]: one 64-byte inner BVH node (two child boxes + refs)
+// Triangles are stored in BVH leaf order (identity when no BVH is built) and
+// padded with never-hit zero triangles (id -1) to a multiple of kTriTile so the
+// brute-force sweep needs no bounds checks.
+#pragma once
+
+#include "common.h"
+#include "srt_render.h"
+
+#include <cstdint>
+#include <vector>
+
+namespace ML {
+
+struct F4 { float x, y, z, w; };
+
+constexpr int kTriTile = 256;      // triangles per shared-memory tile (12 KB)
+constexpr int kMaxLeafTris = 4;    // BVH leaf size
+constexpr int kLeafCountBits = 4;  // child ref: ~ref = (first << 4) | (count-1)
+constexpr int kBvhStackDepth = 64;
+
+// 64-byte inner node as stored in HBM:
+//   n0 = (c0.min.x, c0.max.x, c0.min.y, c0.max.y)
+//   n1 = (c1.min.x, c1.max.x, c1.min.y, c1.max.y)
+//   n2 = (c0.min.z, c0.max.z, c1.min.z, c1.max.z)
+//   n3 = (bits(ref0), bits(ref1), 0, 0)
+struct BvhNode { F4 n0, n1, n2, n3; };
+
+struct BvhBuildResult
+{
+    std::vector<BvhNode> nodes;     // node 0 is the root (always an inner node)
+    std::vector<int32_t> order;     // leaf order -> original triangle id
+    int max_depth = 0;
+};
+
+// Deterministic binned-SAH top-down build over triangle bounds (host).
+BvhBuildResult BuildBvh(size_t n, float const* vertices /*9 per tri*/);
+
+struct DeviceSceneView
+{
+    F4 const* tri_v0;
+    F4 const* tri_e1;
+    F4 const* tri_e2;
+    F4 const* albedo;
+    F4 const* nodes;
+    uint32_t n_tris;        // real triangles
+    uint32_t n_tris_padded; // multiple of kTriTile
+};
+
+class Scene
+{
+public:
+    static srt_scene MakeHandle(Scene* s) { return reinterpret_cast<srt_scene>(s); }
+    static Scene* FromHandle(srt_scene s) { return reinterpret_cast<Scene*>(s); }
+
+    Scene(DeviceStatePtr device, size_t n_triangles, float const* vertices,
+          float const* albedo, bool build_bvh);
+    ~Scene();
+    Scene(Scene const&) = delete;
+    Scene& operator=(Scene const&) = delete;
+
+    ml_status GetInfo(srt_scene_info* info) const;
+    size_t GetBvh(float* nodes, size_t max_nodes, int32_t* order, size_t max_order) const;
+
+    // Enqueues the render on `stream`; with `timed` the kernel is bracketed by
+    // the context's events (read back by GetStats).
+    ml_status RenderDevice(srt_camera const* camera, srt_light const* light,
+                           srt_render_params const* params, void* d_rgb, void* d_hit_id,
+                           void* d_hit_t, cudaStream_t stream, bool timed);
+    ml_status RenderHost(srt_camera const* camera, srt_light const* light,
+                         srt_render_params const* params, float* rgb, int32_t* hit_id,
+                         float* hit_t, srt_render_stats* stats);
+    ml_status GetStats(srt_render_stats* stats);
+
+    DeviceStatePtr const& Device() const { return m_device; }
+    char* GetError(char* buffer, size_t n) const { return FillBuffer(buffer, n, m_error); }
+    void SetError(std::string const& m) { m_error = m; }
+    bool HasBvh() const { return !m_nodes_host.empty(); }
+
+private:
+    bool Validate(srt_camera const* camera, srt_light const* light,
+                  srt_render_params const* params);
+    void EnsureStaging(size_t pixels);
+    void FreeStaging();
+
+    DeviceStatePtr m_device;
+    srt_scene_info m_info{};
+    DeviceSceneView m_view{};
+    void* m_d_tris = nullptr;     // one allocation: v0 | e1 | e2
+    void* m_d_albedo = nullptr;
+    void* m_d_nodes = nullptr;
+    unsigned long long* m_d_counters = nullptr; // primary, shadow, box, tri
+    std::vector<BvhNode> m_nodes_host;
+    std::vector<int32_t> m_order_host;
+    // staging for RenderHost (device band buffers + pinned host twins)
+    void* m_d_rgb = nullptr; void* m_d_id = nullptr; void* m_d_t = nullptr;
+    void* m_h_rgb = nullptr; void* m_h_id = nullptr; void* m_h_t = nullptr;
+    size_t m_stage_pixels = 0;
+    cudaStream_t m_timed_stream = nullptr;
+    bool m_timed_pending = false;
+    std::string m_error;
+};
+
+// Scene generators (host, scenes.cpp).
+size_t GenCornellBox(float* vertices, float* albedo, srt_camera* camera, srt_light* light,
+                     uint32_t width, uint32_t height);
+void GenMesh(uint32_t seed, size_t n_triangles, float* vertices, float* albedo,
+             srt_camera* camera, srt_light* light, uint32_t width, uint32_t height);
+
+// Kernel launchers (render_kernels.cu).
+struct RenderLaunch
+{
+    DeviceSceneView scene;
+    srt_camera camera;
+    srt_light light;
+    srt_render_params params;
+    float inv2w, inv2h, inv_spp;
+    float* d_rgb;
+    int32_t* d_hit_id;
+    float* d_hit_t;
+    unsigned long long* d_counters;
+};
+void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream);
+double MeasureFp32Peak(DeviceState const& device, int repeats);
+
+} // namespace ML
