@@ -1,0 +1,125 @@
+"""ctypes binding of oracle/liboracle.so (the CPU oracle).  Test infrastructure:
+imported only by tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs."""
+import ctypes as C
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+_SO = ROOT / "oracle" / "liboracle.so"
+
+
+class orc_camera(C.Structure):
+    _fields_ = [("origin", C.c_float * 3), ("forward", C.c_float * 3), ("right", C.c_float * 3),
+                ("up", C.c_float * 3), ("half_w", C.c_float), ("half_h", C.c_float)]
+
+
+class orc_light(C.Structure):
+    _fields_ = [("position", C.c_float * 3), ("intensity", C.c_float * 3)]
+
+
+class orc_params(C.Structure):
+    _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("x0", C.c_uint32), ("x1", C.c_uint32),
+                ("y0", C.c_uint32), ("y1", C.c_uint32), ("spp", C.c_uint32), ("jitter", C.c_uint32),
+                ("seed", C.c_uint32), ("shade", C.c_uint32), ("t_min", C.c_float),
+                ("shadow_eps", C.c_float), ("background", C.c_float * 3)]
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not _SO.exists():
+            subprocess.check_call(["make", "-C", str(ROOT / "oracle"), "liboracle.so"])
+        _lib = C.CDLL(str(_SO))
+        _lib.orc_render.restype = C.c_int
+        _lib.orc_render.argtypes = [C.c_uint64, C.c_void_p, C.c_void_p, C.POINTER(orc_camera),
+                                    C.POINTER(orc_light), C.POINTER(orc_params), C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        _lib.orc_intersect.restype = C.c_int
+        _lib.orc_intersect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_float)]
+        _lib.orc_conv2d.restype = C.c_int
+        _lib.orc_conv2d.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
+                                    C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float,
+                                    C.c_void_p, C.c_int]
+        _lib.orc_conv_geometry.restype = None
+        _lib.orc_conv_geometry.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        _lib.orc_add_bias_act.restype = None
+        _lib.orc_add_bias_act.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int,
+                                          C.c_float, C.c_void_p]
+    return _lib
+
+
+def _copy_struct(dst, src):
+    """Field-wise copy between the product's srt_* and the oracle's orc_* structs."""
+    for name, _ in dst._fields_:
+        if hasattr(src, name):
+            v = getattr(src, name)
+            if hasattr(v, "__len__"):
+                getattr(dst, name)[:] = list(v)
+            else:
+                setattr(dst, name, v)
+    return dst
+
+
+def render(vertices, albedo, camera, light, params, crop=None, threads=0, use_bvh=False):
+    """Oracle render of `crop` = (x0, x1, y0, y1) (default: rows [y0,y1) of params, all columns).
+    `camera`/`light`/`params` may be the product's ctypes structs; they are copied field by field."""
+    L = lib()
+    cam = _copy_struct(orc_camera(), camera)
+    lgt = _copy_struct(orc_light(), light)
+    p = _copy_struct(orc_params(), params)
+    if crop is None:
+        crop = (0, params.width, params.y0, params.y1)
+    p.x0, p.x1, p.y0, p.y1 = crop
+    h, w = p.y1 - p.y0, p.x1 - p.x0
+    v = np.ascontiguousarray(vertices, dtype=np.float32).reshape(-1, 9)
+    a = None if albedo is None else np.ascontiguousarray(albedo, dtype=np.float32).reshape(-1, 3)
+    rgb = np.zeros((h, w, 3), np.float32)
+    hid = np.zeros((h, w), np.int32)
+    ht = np.zeros((h, w), np.float32)
+    counts = np.zeros(2, np.uint64)
+    used = L.orc_render(len(v), v.ctypes.data, a.ctypes.data if a is not None else None, C.byref(cam),
+                        C.byref(lgt), C.byref(p), rgb.ctypes.data, hid.ctypes.data, ht.ctypes.data,
+                        counts.ctypes.data, threads, int(use_bvh))
+    return rgb, hid, ht, counts, used
+
+
+def intersect(o, d, tri):
+    o = np.asarray(o, np.float32); d = np.asarray(d, np.float32); tri = np.asarray(tri, np.float32).reshape(9)
+    t = C.c_float(0)
+    inside = lib().orc_intersect(o.ctypes.data, d.ctypes.data, tri.ctypes.data, C.byref(t))
+    return bool(inside), t.value
+
+
+ACTS = {None: 0, "Relu": 1, "LeakyRelu": 2, "Relu6": 3, "Sigmoid": 4, "Tanh": 5}
+
+
+def conv2d(x, w, bias=None, stride=1, dilation=1, padding="SAME", act=None, alpha=0.2, threads=0):
+    """x: HWC float32, w: HWIO.  Returns (OH, OW, Cout)."""
+    L = lib()
+    x = np.ascontiguousarray(x, np.float32); w = np.ascontiguousarray(w, np.float32)
+    H, W, Cin = x.shape
+    KH, KW, _, Cout = w.shape
+    oh, ow, pad = C.c_int(), C.c_int(), C.c_int()
+    same = int(padding == "SAME")
+    L.orc_conv_geometry(H, KH, stride, dilation, same, C.byref(oh), C.byref(pad))
+    L.orc_conv_geometry(W, KW, stride, dilation, same, C.byref(ow), C.byref(pad))
+    out = np.zeros((oh.value, ow.value, Cout), np.float32)
+    b = None if bias is None else np.ascontiguousarray(bias, np.float32)
+    L.orc_conv2d(x.ctypes.data, H, W, Cin, w.ctypes.data, KH, KW, Cout, b.ctypes.data if b is not None else None,
+                 stride, dilation, same, ACTS[act], alpha, out.ctypes.data, threads)
+    return out
+
+
+def run_denoiser(x, layers, residual=True, alpha=0.1, threads=0):
+    """Oracle forward pass of graphdef_writer.make_denoiser()."""
+    cur = np.ascontiguousarray(x, np.float32)
+    for w, b, act in layers:
+        cur = conv2d(cur, w, b, act=act, alpha=alpha, threads=threads)
+    if residual:
+        cur = (np.asarray(x, np.float32) + cur).astype(np.float32)
+    return cur
