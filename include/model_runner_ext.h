@@ -1,0 +1,38 @@
+/*
+ * model_runner_ext.h -- BUILD-DEFINED extensions next to the reference's C API
+ * (none of these exist in the reference; the 14 ml* entry points of
+ * model_runner.h are unchanged and sufficient for reference-style callers).
+ */
+#ifndef MODEL_RUNNER_EXT_H_B200
+#define MODEL_RUNNER_EXT_H_B200
+
+#include <stddef.h>
+#include "model_runner.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Parses a frozen GraphDef on the HOST only (no CUDA call) and writes a text
+ * description of what mlCreateModel would build: detected input/output nodes
+ * (reference model.cpp:94-120), dtype and dimensions (model.cpp:23-48) and the
+ * fused execution plan.  On failure the text is the message mlCreateModel
+ * would leave on the context.  Returns ML_OK / ML_FAIL; `buffer` always
+ * receives a NUL-terminated string (truncated to buffer_size-1). */
+ML_API_ENTRY ml_status mlxInspectModel(char const* model_path, char const* input_node,
+                                       char const* output_node, char* buffer, size_t buffer_size);
+
+/* Device pointer of an image's HBM twin, made current first (uploads the host
+ * copy if that is the valid one).  for_write != 0 declares that the caller will
+ * overwrite the whole image on `stream` and makes the device copy authoritative.
+ * Lets an external producer/consumer (e.g. a torch tensor) share the buffer. */
+ML_API_ENTRY void* mlxImageDevicePointer(ml_image image, int for_write, void* stream);
+
+/* Number of kernel launches one mlInfer() of this model enqueues. */
+ML_API_ENTRY size_t mlxModelLaunchCount(ml_model model);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* MODEL_RUNNER_EXT_H_B200 */

@@ -94,6 +94,9 @@ _PROTOTYPES = {
     "srtRenderToImage": (C.c_int, [C.c_void_p, C.POINTER(srt_camera), C.POINTER(srt_light),
                                    C.POINTER(srt_render_params), C.c_void_p, C.POINTER(srt_render_stats)]),
     "srtMeasureFp32Peak": (C.c_double, [C.c_void_p, C.c_int]),
+    "mlxInspectModel": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),
+    "mlxImageDevicePointer": (C.c_void_p, [C.c_void_p, C.c_int, C.c_void_p]),
+    "mlxModelLaunchCount": (C.c_size_t, [C.c_void_p]),
 }
 
 _lib = None
@@ -122,6 +125,15 @@ def load_library():
         fn.argtypes = argtypes
     _lib = lib
     return lib
+
+
+def inspect_model(path, input_node=None, output_node=None):
+    """mlxInspectModel: host-only parse; returns (ok, text)."""
+    lib = load_library()
+    buf = C.create_string_buffer(1 << 16)
+    st = lib.mlxInspectModel(os.fsencode(path) if path is not None else None, input_node.encode() if input_node else None,
+                             output_node.encode() if output_node else None, buf, len(buf))
+    return st == ML_OK, buf.value.decode(errors="replace")
 
 
 def _err(fn, handle) -> str:
@@ -205,6 +217,12 @@ class Image:
         if self.lib.mlUnmapImage(self.handle, ptr if ptr is not None else self._mapped) != ML_OK:
             raise MLError("mlUnmapImage failed")
 
+    def device_pointer(self, for_write=False, stream=0) -> int:
+        p = self.lib.mlxImageDevicePointer(self.handle, int(for_write), stream or None)
+        if not p:
+            raise MLError("mlxImageDevicePointer failed")
+        return int(p)
+
     def write(self, data: np.ndarray):
         view = self.map()
         np.copyto(view, np.asarray(data).reshape(view.shape))
@@ -240,6 +258,9 @@ class Model:
     def set_input_info(self, info: ml_image_info):
         if self.lib.mlSetModelInputInfo(self.handle, C.byref(info)) != ML_OK:
             raise MLError(self.error())
+
+    def launch_count(self) -> int:
+        return int(self.lib.mlxModelLaunchCount(self.handle))
 
     def infer(self, inp: Image, out: Image):
         if self.lib.mlInfer(self.handle, inp.handle, out.handle) != ML_OK:

@@ -7,6 +7,7 @@
 #include "image.h"
 
 #include "dtype.h"
+#include "model_runner_ext.h"
 
 namespace ML {
 
@@ -135,6 +136,29 @@ ML_API_ENTRY ml_status mlUnmapImage(ml_image image, void* data)
 ML_API_ENTRY void mlReleaseImage(ml_image image)
 {
     delete ML::Image::FromHandle(image);
+}
+
+ML_API_ENTRY void* mlxImageDevicePointer(ml_image image, int for_write, void* stream)
+{
+    ML::Image* img = ML::Image::FromHandle(image);
+    if (img == nullptr) return nullptr;
+    try
+    {
+        img->Device()->MakeCurrent();
+        cudaStream_t s = stream ? static_cast<cudaStream_t>(stream) : img->Device()->stream;
+        if (for_write)
+        {
+            void* p = img->DeviceWrite();
+            img->MarkDeviceAuthoritative();
+            return p;
+        }
+        return img->DeviceRead(s);
+    }
+    catch (std::exception const& e)
+    {
+        std::fprintf(stderr, "mlxImageDevicePointer: %s\n", e.what());
+        return nullptr;
+    }
 }
 
 } // extern "C"

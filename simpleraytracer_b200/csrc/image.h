@@ -36,6 +36,9 @@ public:
     // valid one.  If the host pointer has ever been handed out, the data is
     // copied back eagerly (asynchronously on `stream`; the caller syncs).
     void CommitDeviceWrite(cudaStream_t stream);
+    // An external writer owns the device copy now (mlxImageDevicePointer): the
+    // next Map() copies it back.
+    void MarkDeviceAuthoritative() { m_valid = kDeviceValid; }
     bool HostPointerEscaped() const { return m_host_escaped; }
 
 private:

@@ -16,6 +16,7 @@
 
 #include "dtype.h"
 #include "image.h"
+#include "model_runner_ext.h"
 
 #include <algorithm>
 #include <map>
@@ -102,16 +103,18 @@ Model::Model(DeviceStatePtr device, ml_model_params const* params) : m_device(st
     FusePlan();
 
     // Upload constants once; they stay resident in HBM for the model's life.
-    m_device->MakeCurrent();
+    // (m_device == nullptr: host-only inspection, mlxInspectModel.)
+    if (m_device) m_device->MakeCurrent();
     try
     {
         for (auto& c : m_consts)
+            if (m_device)
         {
             ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&c.dev), std::max<size_t>(c.host.size(), 1) * sizeof(float)));
             ML_CUDA_CHECK(cudaMemcpyAsync(c.dev, c.host.data(), c.host.size() * sizeof(float),
                                           cudaMemcpyHostToDevice, m_device->stream));
         }
-        ML_CUDA_CHECK(cudaStreamSynchronize(m_device->stream));
+        if (m_device) ML_CUDA_CHECK(cudaStreamSynchronize(m_device->stream));
     }
     catch (...)
     {
@@ -134,8 +137,11 @@ Model::Model(DeviceStatePtr device, ml_model_params const* params) : m_device(st
             m_output_info.height = static_cast<size_t>(out.H);
             m_output_info.width = static_cast<size_t>(out.W);
             m_output_info.channels = static_cast<size_t>(out.C);
-            AllocateBuffers();
-            m_ready = true;
+            if (m_device)
+            {
+                AllocateBuffers();
+                m_ready = true;
+            }
         }
     }
     catch (std::exception const& e)
@@ -147,6 +153,7 @@ Model::Model(DeviceStatePtr device, ml_model_params const* params) : m_device(st
 
 Model::~Model()
 {
+    if (!m_device) return;
     cudaSetDevice(m_device->device);
     cudaStreamSynchronize(m_device->stream);
     ReleaseBuffers();
@@ -575,6 +582,36 @@ void Model::AllocateBuffers()
     }
 }
 
+std::string Model::Describe() const
+{
+    static char const* const kinds[] = {"Conv", "BiasAct", "Add", "Concat", "Copy"};
+    static char const* const acts[] = {"none", "relu", "leaky_relu", "relu6", "sigmoid", "tanh"};
+    std::ostringstream os;
+    os << "input_node=" << m_input_node << " output_node=" << m_output_node << "\n";
+    os << "input dtype=" << m_input_info.dtype << " w=" << m_input_info.width << " h=" << m_input_info.height
+       << " c=" << m_input_info.channels << "\n";
+    os << "output dtype=" << m_output_info.dtype << " w=" << m_output_info.width << " h=" << m_output_info.height
+       << " c=" << m_output_info.channels << "\n";
+    os << "ops=" << m_ops.size() << " launches=" << LaunchesPerInfer() << "\n";
+    for (Op const& op : m_ops)
+    {
+        os << kinds[static_cast<int>(op.kind)] << " name=" << op.name << " in=";
+        for (size_t k = 0; k < op.in.size(); k++) os << (k ? "," : "") << "t" << op.in[k];
+        os << " out=t" << op.out << " cout=" << m_tensors[op.out].C;
+        if (op.kind == OpKind::Conv)
+        {
+            double sum = 0;
+            for (float v : m_consts[op.weights].host) sum += v;
+            os << " k=" << op.KH << "x" << op.KW << " stride=" << op.stride << " dilation=" << op.dilation
+               << " padding=" << (op.same_padding ? "SAME" : "VALID") << " wsum=" << sum;
+        }
+        os << " bias=" << (op.bias >= 0 ? "yes" : "no") << " act=" << acts[static_cast<int>(op.act)];
+        if (op.act == nn::Act::LeakyRelu) os << " alpha=" << op.alpha;
+        os << "\n";
+    }
+    return os.str();
+}
+
 size_t Model::LaunchesPerInfer() const
 {
     size_t n = 0;
@@ -859,6 +896,29 @@ ML_API_ENTRY ml_status mlInfer(ml_model model, ml_image input, ml_image output)
 ML_API_ENTRY void mlReleaseModel(ml_model model)
 {
     delete ML::Model::FromHandle(model);
+}
+
+ML_API_ENTRY ml_status mlxInspectModel(char const* model_path, char const* input_node,
+                                       char const* output_node, char* buffer, size_t buffer_size)
+{
+    try
+    {
+        ml_model_params params{model_path, input_node, output_node};
+        ML::Model model(nullptr, &params);
+        ML::FillBuffer(buffer, buffer_size, model.Describe());
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        ML::FillBuffer(buffer, buffer_size, e.what());
+        return ML_FAIL;
+    }
+}
+
+ML_API_ENTRY size_t mlxModelLaunchCount(ml_model model)
+{
+    if (ML::Model::FromHandle(model) == nullptr) return 0;
+    return ML::Model::FromHandle(model)->LaunchesPerInfer();
 }
 
 } // extern "C"

@@ -31,6 +31,8 @@ public:
 
     // Number of kernel launches one Infer() enqueues (bench bookkeeping).
     size_t LaunchesPerInfer() const;
+    // Text dump of the detected nodes, shapes and fused plan (mlxInspectModel).
+    std::string Describe() const;
 
 private:
     // ---- execution plan ---------------------------------------------------

@@ -1,0 +1,141 @@
+"""CPU: the GraphDef writer and the C++ wire-format reader, cross-checked
+against the protobuf runtime (an independent encoder/decoder)."""
+import numpy as np
+import pytest
+
+import tf_protos
+from simpleraytracer_b200 import api
+from simpleraytracer_b200 import graphdef_writer as gw
+
+P = tf_protos.build()
+
+
+def test_writer_bytes_parse_with_protobuf_runtime():
+    data, layers = gw.make_denoiser(channels=3, width=8, depth=3, seed=5)
+    g = P["GraphDef"]()
+    g.ParseFromString(data)
+    ops = [n.op for n in g.node]
+    assert ops[0] == "Placeholder" and ops[-1] == "Identity"
+    assert ops.count("Conv2D") == 3 and ops.count("BiasAdd") == 3 and ops.count("Relu") == 2
+    conv0 = next(n for n in g.node if n.name == "conv0")
+    assert list(conv0.input) == ["input", "conv0/kernel"]
+    assert conv0.attr["padding"].s == b"SAME"
+    assert list(conv0.attr["strides"].list.i) == [1, 1, 1, 1]
+    assert conv0.attr["T"].type == gw.DT_FLOAT
+    shp = conv0.attr["_output_shapes"].list.shape[0]
+    assert [d.size for d in shp.dim] == [-1, -1, -1, 8]
+    k = next(n for n in g.node if n.name == "conv0/kernel").attr["value"].tensor
+    assert [d.size for d in k.tensor_shape.dim] == [3, 3, 3, 8]
+    assert np.array_equal(np.frombuffer(k.tensor_content, "<f4").reshape(3, 3, 3, 8), layers[0][0])
+    # re-serialising with the runtime yields a graph the runtime parses identically
+    g2 = P["GraphDef"](); g2.ParseFromString(g.SerializeToString())
+    assert g2 == g
+
+
+def test_reader_inspects_writer_graph(tmp_path):
+    path = tmp_path / "m.pb"
+    gw.make_denoiser(path, channels=3, width=16, depth=4, seed=1, act="LeakyRelu")
+    ok, text = api.inspect_model(path)
+    assert ok, text
+    lines = text.splitlines()
+    assert lines[0] == "input_node=input output_node=output"
+    assert lines[1] == "input dtype=0 w=0 h=0 c=3"
+    assert lines[2] == "output dtype=0 w=0 h=0 c=3"
+    # Conv+BiasAdd+LeakyRelu fused: 4 convs + residual add (Identity is free)
+    assert lines[3] == "ops=5 launches=5"
+    assert lines[4].startswith("Conv name=conv0 ") and "bias=yes act=leaky_relu alpha=0.1" in lines[4]
+    assert "act=none" in lines[7] and lines[8].startswith("Add ")
+
+
+def runtime_graph(float_val=False, with_shapes=True):
+    """A graph built by the protobuf runtime with encodings our writer never
+    produces: float_val instead of tensor_content, device strings, versions,
+    control inputs, ':0' suffixes."""
+    rng = np.random.default_rng(3)
+    g = P["GraphDef"]()
+    g.versions.producer = 27
+
+    def add(name, op, inputs=()):
+        n = g.node.add(); n.name, n.op = name, op
+        n.input.extend(inputs)
+        n.device = "/device:CPU:0"
+        return n
+
+    x = add("x", "Placeholder")
+    x.attr["dtype"].type = 1
+    for d in (-1, 24, 32, 3):
+        x.attr["shape"].shape.dim.add().size = d
+    if with_shapes:
+        s = x.attr["_output_shapes"].list.shape.add()
+        for d in (-1, 24, 32, 3):
+            s.dim.add().size = d
+    w = rng.standard_normal((3, 3, 3, 4)).astype(np.float32)
+    k = add("k", "Const"); k.attr["dtype"].type = 1
+    t = k.attr["value"].tensor; t.dtype = 1
+    for d in w.shape:
+        t.tensor_shape.dim.add().size = d
+    if float_val:
+        t.float_val.extend(w.ravel().tolist())
+    else:
+        t.tensor_content = w.tobytes()
+    c = add("c", "Conv2D", ["x:0", "k", "^x"])
+    c.attr["T"].type = 1; c.attr["padding"].s = b"VALID"
+    c.attr["strides"].list.i.extend([1, 2, 2, 1])
+    b = add("b", "Const"); b.attr["dtype"].type = 1
+    tb = b.attr["value"].tensor; tb.dtype = 1; tb.tensor_shape.dim.add().size = 4
+    tb.float_val.append(0.5)                       # one value, broadcast to 4
+    ba = add("ba", "BiasAdd", ["c", "b"]); ba.attr["T"].type = 1
+    r = add("out", "Relu6", ["ba"]); r.attr["T"].type = 1
+    return g.SerializeToString(), w
+
+
+@pytest.mark.parametrize("float_val", [False, True])
+def test_reader_handles_runtime_encodings(tmp_path, float_val):
+    data, w = runtime_graph(float_val=float_val)
+    path = tmp_path / "r.pb"; path.write_bytes(data)
+    ok, text = api.inspect_model(path)
+    assert ok, text
+    lines = text.splitlines()
+    assert lines[0] == "input_node=x output_node=out"
+    assert lines[1] == "input dtype=0 w=32 h=24 c=3"
+    # static H,W,C known -> output shape known without mlSetModelInputInfo: VALID 3x3 stride 2
+    assert lines[2] == "output dtype=0 w=15 h=11 c=4"
+    assert lines[3] == "ops=1 launches=1"
+    assert "k=3x3 stride=2 dilation=1 padding=VALID" in lines[4] and "bias=yes act=relu6" in lines[4]
+    wsum = float(lines[4].split("wsum=")[1].split()[0])
+    assert abs(wsum - float(w.astype(np.float64).sum())) < 1e-4
+
+
+def test_reader_node_selection_and_errors(tmp_path):
+    data, _ = runtime_graph()
+    path = tmp_path / "r.pb"; path.write_bytes(data)
+    ok, text = api.inspect_model(path, None, "ba")        # explicit output node
+    assert ok and "output_node=ba" in text and "act=none" in text
+    ok, text = api.inspect_model(path, "x", "k")          # constant output
+    assert not ok and "Unable to detect" not in text and "constant" in text
+    ok, text = api.inspect_model(tmp_path / "missing.pb")
+    assert not ok and text.startswith("Error reading graph definition: ")
+    bad = tmp_path / "bad.pb"; bad.write_bytes(b"\x0a\xff\xff\xff")
+    ok, text = api.inspect_model(bad)
+    assert not ok and text.startswith("Error reading graph definition: ")
+    # unsupported op is refused loudly, never skipped
+    g = P["GraphDef"](); g.ParseFromString(data)
+    g.node[-1].op = "Softmax"
+    path2 = tmp_path / "u.pb"; path2.write_bytes(g.SerializeToString())
+    ok, text = api.inspect_model(path2)
+    assert not ok and "Unimplemented" in text and "Softmax" in text
+    # node without dtype/T: reference message (model.cpp:32)
+    g = P["GraphDef"](); g.ParseFromString(data)
+    del g.node[-1].attr["T"]
+    path3 = tmp_path / "d.pb"; path3.write_bytes(g.SerializeToString())
+    ok, text = api.inspect_model(path3)
+    assert not ok and text == "Unable to detect node dtype: out"
+    ok, text = api.inspect_model(None)
+    assert not ok and text == "Bad model_path model parameter value"
+
+
+def test_half_graph_dtype(tmp_path):
+    path = tmp_path / "h.pb"
+    gw.make_denoiser(path, channels=3, width=8, depth=2, seed=2, dtype=gw.DT_HALF)
+    ok, text = api.inspect_model(path)
+    assert ok and "input dtype=1 " in text and "output dtype=1 " in text

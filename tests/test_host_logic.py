@@ -1,0 +1,79 @@
+"""CPU: host-side logic -- generators, band sharding, the N>1 gather over gloo,
+and the no-fallback rule (without a GPU the product refuses to run)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+from simpleraytracer_b200 import api, sharding
+
+
+def test_generators_are_deterministic_and_exact():
+    v1, a1, cam, light = api.gen_mesh(9, 12345, 64, 36)
+    v2, a2, _, _ = api.gen_mesh(9, 12345, 64, 36)
+    assert v1.shape == (12345, 9) and np.array_equal(v1, v2) and np.array_equal(a1, a2)
+    v3, _, _, _ = api.gen_mesh(10, 12345, 64, 36)
+    assert not np.array_equal(v1, v3)
+    assert np.isfinite(v1).all() and (a1 >= 0).all() and (a1 <= 1).all()
+    f, r, u = (np.array(cam.forward[:]), np.array(cam.right[:]), np.array(cam.up[:]))
+    for x in (f, r, u):
+        assert abs(np.linalg.norm(x) - 1) < 1e-6
+    assert abs(f @ r) < 1e-6 and abs(f @ u) < 1e-6 and abs(r @ u) < 1e-6
+    assert abs(cam.half_w / cam.half_h - 64 / 36) < 1e-5
+    for n in (0, 1, 63, 64, 2000):
+        assert api.gen_mesh(1, n, 8, 8)[0].shape == (n, 9)
+    v, a, _, _ = api.gen_cornell_box(512, 512)
+    assert v.shape == (12, 9)
+
+
+@pytest.mark.parametrize("height,world", [(1080, 1), (1080, 2), (1080, 4), (1080, 8), (2160, 8), (27, 4), (5, 8)])
+def test_row_bands_cover_the_frame(height, world):
+    bands = sharding.row_bands(height, world)
+    assert len(bands) == world and bands[0][0] == 0 and bands[-1][1] == height
+    for (a0, a1), (b0, b1) in zip(bands, bands[1:]):
+        assert a1 == b0 and a0 <= a1
+    assert all(y0 % 8 == 0 for y0, _ in bands)
+    sizes = [b - a for a, b in bands]
+    assert max(sizes) - min(sizes) <= 8 or height < world * 8
+
+
+def _free_port():
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
+    return p
+
+
+def _gather_worker(rank, world, port, height, out):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        W = 6
+        bands = sharding.row_bands(height, world)
+        frame = torch.full((height, W, 3), -1.0)
+        y0, y1 = bands[rank]
+        ys = torch.arange(y0, y1, dtype=torch.float32)[:, None, None]
+        frame[y0:y1] = ys * 100 + torch.arange(W, dtype=torch.float32)[None, :, None] + torch.arange(3) * 0.25
+        sharding.gather_bands(frame, bands, rank)
+        if rank == 0:
+            torch.save(frame, out)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("height", [32, 27])   # equal bands (all_gather) and ragged bands (send/recv)
+def test_gather_bands_world_size_2_gloo(tmp_path, height):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "frame.pt")
+    mp.spawn(_gather_worker, args=(2, _free_port(), height, out), nprocs=2, join=True)
+    frame = torch.load(out)
+    ys = torch.arange(height, dtype=torch.float32)[:, None, None]
+    want = ys * 100 + torch.arange(6, dtype=torch.float32)[None, :, None] + torch.arange(3) * 0.25
+    assert torch.equal(frame, want)
+
+
+@pytest.mark.skipif(torch.cuda.is_available(), reason="only meaningful on a box without a GPU")
+def test_product_refuses_to_run_without_gpu():
+    with pytest.raises(api.MLError):
+        api.Context()

@@ -1,0 +1,230 @@
+"""GPU parity tests of the render loop: the CUDA path (through the C ABI,
+srtRender / srtRenderDevice / srtRenderToImage) against the CPU oracle and the
+committed golden fixtures.  Bar (BASELINE.json north_star): hit ids bit-exact,
+hit distance and radiance within 1e-5 relative."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from simpleraytracer_b200 import api
+from test_oracle_golden import load_cornell
+
+pytestmark = pytest.mark.gpu
+GOLD = Path(__file__).resolve().parent / "golden"
+REL = 1e-5  # tolerance on hit_t and rgb, relative
+
+
+def assert_parity(gpu, ref, what=""):
+    rgb, hid, ht = gpu[:3]
+    rrgb, rhid, rht = ref[:3]
+    assert np.array_equal(hid, rhid), f"{what}: {np.count_nonzero(hid != rhid)} hit ids differ"
+    finite = np.isfinite(rht)
+    assert np.array_equal(np.isfinite(ht), finite), what
+    np.testing.assert_allclose(ht[finite], rht[finite], rtol=REL, atol=0, err_msg=what)
+    np.testing.assert_allclose(rgb, rrgb, rtol=REL, atol=1e-7, err_msg=what)
+
+
+@pytest.mark.parametrize("name", ["cornell_8_shade0_spp1.npz", "cornell_64_shade0_spp1.npz",
+                                  "cornell_64_shade2_spp4.npz"])
+@pytest.mark.parametrize("accel", [api.SRT_ACCEL_BRUTE, api.SRT_ACCEL_BVH])
+def test_golden_cornell(ctx, name, accel):
+    g, cam, light, p = load_cornell(name)
+    p.accel = accel
+    scene = ctx.create_scene(g["vertices"], g["albedo"])
+    rgb, hid, ht, stats = scene.render(cam, light, p)
+    assert_parity((rgb, hid, ht), (g["rgb"], g["hit_id"], g["hit_t"]), name)
+    # in practice the spec makes the results bit-identical, not merely close
+    assert np.array_equal(ht, g["hit_t"]) and np.array_equal(rgb, g["rgb"])
+    assert stats.primary_rays == int(g["counts"][0]) and stats.shadow_rays == int(g["counts"][1])
+    scene.release()
+
+
+def test_config2_cornell_512_vs_oracle(ctx):
+    """BASELINE config 2: ~12-triangle Cornell box, 512x512, 1 spp, pixel-centre rays."""
+    v, a, cam, light = api.gen_cornell_box(512, 512)
+    scene = ctx.create_scene(v, a)
+    for shade in (api.SRT_SHADE_ALBEDO, api.SRT_SHADE_SHADOW):
+        p = api.make_params(512, 512, shade=shade)
+        ref = O.render(v, a, cam, light, p)
+        for accel in (api.SRT_ACCEL_BRUTE, api.SRT_ACCEL_BVH):
+            p.accel = accel
+            got = scene.render(cam, light, p)
+            assert_parity(got, ref, f"cornell512 shade{shade} accel{accel}")
+            assert got[3].primary_rays == 512 * 512
+            assert got[3].shadow_rays == int(ref[3][1])
+    scene.release()
+
+
+def test_golden_mesh_and_modes(ctx):
+    g = np.load(GOLD / "mesh_2000_48x27.npz")
+    w, h, spp, jitter, seed, shade, mesh_seed, n = [int(x) for x in g["params"]]
+    v, a, cam, light = api.gen_mesh(mesh_seed, n, w, h)
+    scene = ctx.create_scene(v, a)
+    p = api.make_params(w, h, spp=spp, jitter=jitter, seed=seed, shade=shade, background=(0.5, 0.7, 0.9))
+    for accel in (api.SRT_ACCEL_BRUTE, api.SRT_ACCEL_BVH):
+        p.accel = accel
+        got = scene.render(cam, light, p)
+        assert_parity(got, (g["rgb"], g["hit_id"], g["hit_t"]), f"mesh accel{accel}")
+        assert got[3].shadow_rays == int(g["counts"][1])
+    scene.release()
+
+
+@pytest.mark.parametrize("shade", [api.SRT_SHADE_ALBEDO, api.SRT_SHADE_LAMBERT, api.SRT_SHADE_SHADOW])
+def test_mesh_20k_brute_oracle_crop(ctx, shade):
+    """Brute-force oracle on a crop of a larger frame (the oracle is O(rays x triangles))."""
+    W, H = 320, 180
+    v, a, cam, light = api.gen_mesh(2, 20000, W, H)
+    scene = ctx.create_scene(v, a)
+    p = api.make_params(W, H, spp=2, jitter=1, seed=5, shade=shade, background=(0.2, 0.3, 0.4))
+    crop = (100, 164, 60, 100)
+    ref = O.render(v, a, cam, light, p, crop=crop)
+    for accel in (api.SRT_ACCEL_BRUTE, api.SRT_ACCEL_BVH):
+        p.accel = accel
+        rgb, hid, ht, _ = scene.render(cam, light, p)
+        x0, x1, y0, y1 = crop
+        assert_parity((rgb[y0:y1, x0:x1], hid[y0:y1, x0:x1], ht[y0:y1, x0:x1]), ref, f"accel{accel}")
+    scene.release()
+
+
+def test_bvh_equals_brute_force_100k(ctx):
+    """Size-independent property at a BASELINE-sized scene: the BVH only culls, so the
+    BVH render equals the brute-force render bit for bit (100K triangles, config 3 scene)."""
+    W, H = 480, 270
+    v, a, cam, light = api.gen_mesh(1, 100000, W, H)
+    scene = ctx.create_scene(v, a)
+    p = api.make_params(W, H, spp=2, jitter=1, seed=3, shade=api.SRT_SHADE_SHADOW, background=(0.5, 0.7, 0.9))
+    p.accel = api.SRT_ACCEL_BRUTE
+    brute = scene.render(cam, light, p)
+    p.accel = api.SRT_ACCEL_BVH
+    p.collect_stats = 1
+    bvh = scene.render(cam, light, p)
+    assert np.array_equal(brute[1], bvh[1])
+    assert np.array_equal(brute[2], bvh[2])
+    assert np.array_equal(brute[0], bvh[0])
+    assert brute[3].shadow_rays == bvh[3].shadow_rays > 0
+    assert bvh[3].tri_tests < brute[3].tri_tests / 100      # the BVH actually culls
+    # and the oracle's BVH path agrees on a band of the same frame
+    ref = O.render(v, a, cam, light, p, crop=(0, W, 128, 136), use_bvh=True)
+    assert_parity((bvh[0][128:136], bvh[1][128:136], bvh[2][128:136]), ref, "oracle band")
+    scene.release()
+
+
+def test_row_bands_compose_the_full_frame(ctx):
+    """Multi-GPU sharding contract: rendering bands separately equals rendering the frame."""
+    W, H = 200, 120
+    v, a, cam, light = api.gen_mesh(4, 5000, W, H)
+    scene = ctx.create_scene(v, a)
+    full_p = api.make_params(W, H, spp=2, jitter=1, seed=1, shade=api.SRT_SHADE_SHADOW, accel=api.SRT_ACCEL_BVH)
+    full = scene.render(cam, light, full_p)
+    rgb = np.zeros((H, W, 3), np.float32); hid = np.zeros((H, W), np.int32); ht = np.zeros((H, W), np.float32)
+    from simpleraytracer_b200.sharding import row_bands
+    rays = 0
+    for y0, y1 in row_bands(H, 3):
+        p = api.make_params(W, H, spp=2, jitter=1, seed=1, shade=api.SRT_SHADE_SHADOW, accel=api.SRT_ACCEL_BVH,
+                            y0=y0, y1=y1, buf_y0=y0)
+        r, i, t, st = scene.render(cam, light, p)
+        rgb[y0:y1], hid[y0:y1], ht[y0:y1] = r[: y1 - y0], i[: y1 - y0], t[: y1 - y0]
+        rays += st.primary_rays
+    assert rays == W * H * 2
+    assert np.array_equal(rgb, full[0]) and np.array_equal(hid, full[1]) and np.array_equal(ht, full[2])
+    scene.release()
+
+
+def test_degenerate_cases_on_gpu(ctx):
+    """Tie-breaks and rejections of the golden single-ray cases, through a 1x1 render."""
+    g = np.load(GOLD / "degenerate.npz")
+    for name in ["shared_edge", "shared_vertex", "parallel", "coplanar_dup", "miss", "behind", "backface"]:
+        tris, o, d = g[name + "_tris"], g[name + "_o"], g[name + "_d"]
+        cam = api.srt_camera()
+        cam.origin[:] = o; cam.forward[:] = d
+        # any orthonormal completion; with half_w = half_h = 0 the pixel-centre ray is exactly `forward`
+        right = np.cross(d, [0.0, 1.0, 0.0]); right = right if np.linalg.norm(right) > 0 else np.array([1.0, 0, 0])
+        cam.right[:] = right / np.linalg.norm(right)
+        cam.up[:] = np.cross(cam.right[:], d)
+        cam.half_w = cam.half_h = 0.0
+        p = api.make_params(1, 1, t_min=1e-4)
+        ref = O.render(tris, None, cam, api.srt_light(), p)
+        scene = ctx.create_scene(tris)
+        for accel in (api.SRT_ACCEL_BRUTE, api.SRT_ACCEL_BVH):
+            p.accel = accel
+            _, hid, ht, _ = scene.render(cam, api.srt_light(), p)
+            assert hid[0, 0] == ref[1][0, 0], name
+            assert (ht[0, 0] == ref[2][0, 0]) or (np.isinf(ht[0, 0]) and np.isinf(ref[2][0, 0])), name
+        inside, t = g[name + "_inside"], g[name + "_t"]
+        cands = [(t[i], i) for i in range(len(t)) if inside[i] and t[i] > 1e-4]
+        assert hid[0, 0] == (min(cands)[1] if cands else -1), name
+        scene.release()
+
+
+def test_empty_scene_and_tiny_frames(ctx):
+    cam = api.srt_camera(); cam.forward[:] = (0, 0, -1); cam.right[:] = (1, 0, 0); cam.up[:] = (0, 1, 0)
+    cam.half_w = cam.half_h = 0.5
+    scene = ctx.create_scene(np.zeros((0, 9), np.float32))
+    for accel in (api.SRT_ACCEL_BRUTE, api.SRT_ACCEL_BVH):
+        p = api.make_params(5, 3, background=(0.25, 0.5, 0.75), shade=api.SRT_SHADE_SHADOW, accel=accel)
+        rgb, hid, ht, st = scene.render(cam, api.srt_light(), p)
+        assert (hid == -1).all() and np.isinf(ht).all() and np.allclose(rgb, [0.25, 0.5, 0.75])
+        assert st.primary_rays == 15 and st.shadow_rays == 0
+    scene.release()
+    # ragged sizes: widths/heights that are not multiples of any tile
+    v, a, cam, light = api.gen_cornell_box(37, 19)
+    scene = ctx.create_scene(v, a)
+    for accel in (api.SRT_ACCEL_BRUTE, api.SRT_ACCEL_BVH):
+        p = api.make_params(37, 19, shade=api.SRT_SHADE_SHADOW, accel=accel, spp=3, jitter=1)
+        assert_parity(scene.render(cam, light, p), O.render(v, a, cam, light, p), f"ragged accel{accel}")
+    scene.release()
+
+
+def test_render_errors_are_reported(ctx):
+    v, a, cam, light = api.gen_cornell_box(16, 16)
+    scene = ctx.create_scene(v, a, build_bvh=False)
+    p = api.make_params(16, 16, accel=api.SRT_ACCEL_BVH)
+    with pytest.raises(api.MLError, match="without a BVH"):
+        scene.render(cam, light, p)
+    p = api.make_params(16, 16, y0=8, y1=4)
+    with pytest.raises(api.MLError, match="Bad row band"):
+        scene.render(cam, light, p)
+    p = api.make_params(16, 16, spp=0)
+    with pytest.raises(api.MLError, match="sample count"):
+        scene.render(cam, light, p)
+    scene.release()
+    bad = np.full((1, 9), np.nan, np.float32)
+    with pytest.raises(api.MLError, match="Non-finite"):
+        ctx.create_scene(bad)
+
+
+def test_render_to_image_stays_on_device_and_maps_back(ctx):
+    W, H = 96, 64
+    v, a, cam, light = api.gen_cornell_box(W, H)
+    scene = ctx.create_scene(v, a)
+    img = ctx.create_image(W, H, 3)
+    p = api.make_params(W, H, shade=api.SRT_SHADE_SHADOW, accel=api.SRT_ACCEL_BVH)
+    st = scene.render_to_image(cam, light, p, img)
+    assert st.primary_rays == W * H
+    ref = O.render(v, a, cam, light, p)
+    np.testing.assert_allclose(img.read(), ref[0], rtol=REL, atol=1e-7)
+    wrong = ctx.create_image(W, H, 4)
+    with pytest.raises(api.MLError, match="does not match"):
+        scene.render_to_image(cam, light, p, wrong)
+    for o in (wrong, img, scene):
+        o.release()
+
+
+def test_render_device_into_torch_tensor(ctx):
+    """srtRenderDevice with caller-owned device memory and stream (torch is plumbing)."""
+    import torch
+    W, H = 128, 72
+    v, a, cam, light = api.gen_mesh(6, 4000, W, H)
+    scene = ctx.create_scene(v, a)
+    p = api.make_params(W, H, spp=2, jitter=1, shade=api.SRT_SHADE_SHADOW, accel=api.SRT_ACCEL_BVH)
+    rgb = torch.zeros(H, W, 3, device="cuda"); hid = torch.zeros(H, W, dtype=torch.int32, device="cuda")
+    ht = torch.zeros(H, W, device="cuda")
+    stream = torch.cuda.current_stream()
+    scene.render_device(cam, light, p, rgb.data_ptr(), hid.data_ptr(), ht.data_ptr(), stream.cuda_stream)
+    st = scene.stats()
+    host = scene.render(cam, light, p)
+    assert np.array_equal(rgb.cpu().numpy(), host[0]) and np.array_equal(hid.cpu().numpy(), host[1])
+    assert st.primary_rays == W * H * 2 and st.kernel_ms > 0
+    scene.release()
