@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the render hot path (BASELINE.json metric:
+"Mrays/s (closest-hit+shade, 1080p)").
+
+Workload (BASELINE.json configs[2]): 1920x1080, 64 spp, Lambert + one shadow ray
+per lit hit, seeded synthetic 100,000-triangle mesh, BVH traversal kernel.
+One "step" = one full frame (132,710,400 primary rays + the shadow rays they
+spawn).  At N > 1 the frame is sharded by row bands over the ranks (scene
+replicated, no data-path collective) and the bands are gathered on rank 0
+inside the timed region, so total work is fixed: scaling = "strong".
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+`--impl reference` times the CPU implementation of the same path on the host
+cores.  The reference repository contains no renderer, so that
+arm is the build-authored CPU oracle ("port"), on a bounded sample of the same
+workload (the first spp_sample of the 64 samples of every pixel).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+WORKLOAD = dict(name="render_1080p_64spp_shadow_100k_tris", width=1920, height=1080, spp=64,
+                triangles=100_000, mesh_seed=1, sample_seed=1)
+CPU_SAMPLE_SPP = 2            # bounded CPU sample: first 2 of the 64 spp of every pixel
+FLOP_PER_TRI_TEST = 45        # SURVEY.md section 8d conventions
+FLOP_PER_BOX_TEST = 21
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--spp", type=int, default=WORKLOAD["spp"], help=argparse.SUPPRESS)  # debugging only
+    ap.add_argument("--no-cpu-baseline", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--no-brute", action="store_true", help=argparse.SUPPRESS)
+    return ap.parse_args()
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """Samples nvidia-smi clocks/throttle reasons while the timed region runs."""
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index: int):
+        self.index = device_index
+        self.samples = []
+        self._stop = threading.Event()
+        self._thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
+                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+                parts = [x.strip() for x in out.strip().split(",")]
+                if len(parts) >= 8:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._thread.start()
+        return self
+
+    def __exit__(self, *exc):
+        self._stop.set()
+        self._thread.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm = sorted(float(s[1]) for s in self.samples)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(s[4 + k].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(self.samples[0][2]),
+                "power_w_max": max(float(s[3]) for s in self.samples), "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+def physical_gpu_index(local_rank: int):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        try:
+            return vis.split(",")[local_rank].strip()      # index or UUID: nvidia-smi -i takes both
+        except IndexError:
+            pass
+    return local_rank
+
+
+def measured_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        return json.loads(p.read_text()), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+# --------------------------------------------------------------------------- CPU arm
+def scene_arrays(args):
+    from simpleraytracer_b200 import api
+    w = WORKLOAD
+    v, a, cam, light = api.gen_mesh(w["mesh_seed"], w["triangles"], w["width"], w["height"])
+    params = api.make_params(w["width"], w["height"], spp=args.spp, jitter=1, seed=w["sample_seed"],
+                             shade=api.SRT_SHADE_SHADOW, accel=api.SRT_ACCEL_BVH, background=(0.5, 0.7, 0.9))
+    return v, a, cam, light, params
+
+
+def cpu_sample(v, a, cam, light, params, spp):
+    """One bounded sample of the workload on the host cores through the oracle's BVH
+    path: the first `spp` samples of every pixel.  Returns (Mrays/s, seconds, rays, threads)."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle_lib as O   # bench.py's CPU-baseline leg is allowed to execute oracle/
+    from simpleraytracer_b200 import api
+    p = api.make_params(params.width, params.height, spp=spp, jitter=1, seed=params.seed,
+                        shade=params.shade, background=tuple(params.background))
+    t0 = time.perf_counter()
+    _, _, _, counts, threads = O.render(v, a, cam, light, p, threads=0, use_bvh=True)
+    dt = time.perf_counter() - t0
+    rays = int(counts[0]) + int(counts[1])
+    return rays / dt / 1e6, dt, rays, threads
+
+
+def run_reference_arm(args):
+    """`--impl reference`: the CPU implementation of the path, all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    v, a, cam, light, params = scene_arrays(args)
+    for _ in range(min(args.warmup, 1)):
+        cpu_sample(v, a, cam, light, params, 1)
+    total_rays, total_s, threads = 0, 0.0, 0
+    for _ in range(args.steps):
+        _, dt, rays, threads = cpu_sample(v, a, cam, light, params, CPU_SAMPLE_SPP)
+        total_rays += rays
+        total_s += dt
+    value = total_rays / total_s / 1e6
+    sample = (f"first {CPU_SAMPLE_SPP} of {args.spp} spp of every pixel of the 1920x1080 frame per step "
+              f"({total_rays // args.steps} rays), oracle BVH path incl. its BVH build")
+    line = {
+        "impl": "reference", "metric": "Mrays/s (closest-hit+shade, 1080p)", "value": value, "unit": "Mrays/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_s / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD["name"], "width": params.width, "height": params.height, "spp": args.spp,
+                   "triangles": WORKLOAD["triangles"], "note": "reference repo has no renderer; CPU oracle port"},
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- GPU arm
+def run_b200_arm(args):
+    import torch
+    import torch.distributed as dist
+    from simpleraytracer_b200 import api, sharding
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+
+    v, a, cam, light, params = scene_arrays(args)
+    W, H = params.width, params.height
+    ctx = api.Context()
+    scene = ctx.create_scene(v, a, build_bvh=True)
+    info = scene.info()
+
+    bands = sharding.row_bands(H, world)
+    y0, y1 = bands[rank]
+    params.y0, params.y1, params.buf_y0 = y0, y1, 0
+
+    frame = torch.zeros(H, W, 3, device=dev)             # full frame; this rank fills rows [y0,y1)
+    stream = torch.cuda.current_stream()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        scene.render_device(cam, light, params, frame.data_ptr(), 0, 0, stream.cuda_stream)
+        if world > 1:
+            sharding.gather_bands(frame, bands, rank)
+
+    # ---- one instrumented pass (not timed): ray and traversal counts for the roofline
+    params.collect_stats = 1
+    step()
+    st = scene.stats()
+    params.collect_stats = 0
+    counts = torch.tensor([st.primary_rays, st.shadow_rays, st.box_tests, st.tri_tests], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(counts)
+    primary, shadow, boxes, tris = [float(x) for x in counts.tolist()]
+    rays_per_step = primary + shadow
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+
+    # ---- timed region: K steps, each bracketed by CUDA events on the launching stream,
+    #      L2 flushed (untimed) between steps; kernel-only time from the library's own events
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kernel_ms = []
+    with ClockSampler(physical_gpu_index(local_rank)) as clocks:
+        t_wall = time.perf_counter()
+        for k in range(args.steps):
+            flush.zero_()
+            ev[k][0].record(stream)
+            step()
+            ev[k][1].record(stream)
+            torch.cuda.synchronize()
+            kernel_ms.append(scene.stats().kernel_ms)
+        barrier()
+        wall_s = time.perf_counter() - t_wall
+    step_ms = [s.elapsed_time(e) for s, e in ev]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    value = rays_per_step * args.steps / (total_ms * 1e-3) / 1e6
+
+    # ---- e2e: the public host-buffer call (srtRender), D2H of the band inside the timed region
+    host_params = api.make_params(W, H, spp=args.spp, jitter=1, seed=params.seed, shade=params.shade,
+                                  accel=api.SRT_ACCEL_BVH, background=tuple(params.background),
+                                  y0=y0, y1=y1, buf_y0=y0)
+    rows = y1 - y0
+    host_rgb = np.zeros((max(rows, 1), W, 3), np.float32)
+    import ctypes as C
+    def e2e_step():
+        stt = api.srt_render_stats()
+        rc = scene.lib.srtRender(scene.handle, C.byref(cam), C.byref(light), C.byref(host_params),
+                                 host_rgb.ctypes.data, None, None, C.byref(stt))
+        if rc != api.ML_OK:
+            raise RuntimeError(scene.error())
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = rays_per_step * args.steps / float(e2e_s.item()) / 1e6
+    d2h = torch.tensor([rows * W * 12], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(d2h)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- rank 0 only: FP32 peak, brute-force intersection roofline, CPU baseline, report
+    fp32_peak = ctx.measure_fp32_peak(5)
+    flops_per_step = boxes * FLOP_PER_BOX_TEST + tris * FLOP_PER_TRI_TEST
+    kern_ms = float(np.mean(kernel_ms))
+    # at N>1 this rank's kernel only did its band: scale the whole-frame flops by its share of the rays
+    share = (st.primary_rays + st.shadow_rays) / rays_per_step if rays_per_step else 1.0
+    achieved = flops_per_step * share / (kern_ms * 1e-3) / 1e12
+    scene_bytes = info.device_bytes
+    roofline = {"bound": "fp32", "kernel": "render_bvh_kernel", "achieved": achieved, "peak": fp32_peak,
+                "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None, "traffic": None,
+                "peak_source": "srtMeasureFp32Peak live FFMA microbenchmark (MEASURED_PEAKS.json has no FP32 figure)",
+                "algorithmic_flops_per_launch": flops_per_step * share,
+                "box_tests": boxes, "tri_tests": tris, "kernel_ms": kern_ms,
+                "algorithmic_bytes_per_launch": rows * W * 12 + scene_bytes,
+                "note": "BVH traversal is latency/divergence bound; flops = box_tests*21 + tri_tests*45 counted by "
+                        "the instrumented kernel variant on the same frame"}
+
+    brute = None
+    if not args.no_brute:
+        bp = api.make_params(W, H, spp=1, jitter=1, seed=params.seed, shade=api.SRT_SHADE_ALBEDO,
+                             accel=api.SRT_ACCEL_BRUTE, background=tuple(params.background))
+        scene.render_device(cam, light, bp, frame.data_ptr(), 0, 0, stream.cuda_stream)   # warm-up
+        scene.stats()
+        times = []
+        for _ in range(2):
+            flush.zero_()
+            scene.render_device(cam, light, bp, frame.data_ptr(), 0, 0, stream.cuda_stream)
+            times.append(scene.stats().kernel_ms)
+        ms = min(times)
+        tests = float(W) * H * WORKLOAD["triangles"]
+        tf = tests * FLOP_PER_TRI_TEST / (ms * 1e-3) / 1e12
+        brute = {"kernel": "render_brute_kernel<4>", "workload": "1920x1080 x 1 spp x 100000 triangles, closest hit",
+                 "ms": ms, "tests": tests, "achieved": tf, "peak": fp32_peak, "unit": "TFLOP/s",
+                 "frac": tf / fp32_peak if fp32_peak else None, "mrays_per_s": W * H / (ms * 1e-3) / 1e6,
+                 "bound": "fp32"}
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        cv, dt, crays, threads = cpu_sample(v, a, cam, light, params, CPU_SAMPLE_SPP)
+        cpu = {"value": cv, "unit": "Mrays/s", "cores": threads, "kind": "port",
+               "sample": f"first {CPU_SAMPLE_SPP} of {args.spp} spp of every pixel of the 1920x1080 frame "
+                         f"({crays} rays, {dt:.1f} s), oracle BVH path incl. its BVH build"}
+
+    line = {
+        "metric": "Mrays/s (closest-hit+shade, 1080p)", "value": value, "unit": "Mrays/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD["name"], "width": W, "height": H, "spp": args.spp,
+                   "triangles": WORKLOAD["triangles"], "shade": "lambert+shadow", "accel": "bvh",
+                   "parallelism": f"row_bands{world}", "l2_flush_between_steps": True,
+                   "rays_per_step": rays_per_step, "primary_rays": primary, "shadow_rays": shadow,
+                   "bvh_nodes": int(info.n_bvh_nodes), "bvh_build_ms": info.bvh_build_ms,
+                   "scene_upload_ms": info.upload_ms, "wall_s_timed_region": wall_s},
+        "roofline": roofline, "intersect_roofline": brute, "cpu_baseline": cpu,
+        "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(api.srt_render_params)
+                + C.sizeof(api.srt_camera) + C.sizeof(api.srt_light), "d2h_bytes_per_step": int(d2h.item())},
+        "gpu_launches": args.steps, "clocks": clocks.summary(),
+        "peaks": {"fp32_tflops_measured_live": fp32_peak, "hbm_gbs": measured_peaks()[0].get("hbm_gbs"),
+                  "source": measured_peaks()[1]},
+    }
+    print(json.dumps(line), flush=True)
+    scene.release()
+    ctx.release()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    main()
