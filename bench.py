@@ -34,7 +34,7 @@ sys.path.insert(0, str(ROOT))
 
 WORKLOAD = dict(name="render_1080p_64spp_shadow_100k_tris", width=1920, height=1080, spp=64,
                 triangles=100_000, mesh_seed=1, sample_seed=1)
-CPU_SAMPLE_SPP = 2            # bounded CPU sample: first 2 of the 64 spp of every pixel
+CPU_SAMPLE_SPP = 8            # bounded CPU sample: first 8 of the 64 spp of every pixel
 FLOP_PER_TRI_TEST = 45        # SURVEY.md section 8d conventions
 FLOP_PER_BOX_TEST = 21
 
@@ -193,7 +193,13 @@ def run_b200_arm(args):
     params.y0, params.y1, params.buf_y0 = y0, y1, 0
 
     frame = torch.zeros(H, W, 3, device=dev)             # full frame; this rank fills rows [y0,y1)
-    stream = torch.cuda.current_stream()
+    # A dedicated torch stream is made current for everything below: the render kernel is
+    # launched on it through the C ABI (a NULL stream would mean "the context's own stream"),
+    # torch.distributed's collectives order against it, and the timing events are recorded on it.
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    assert stream.cuda_stream != 0
+    torch.cuda.synchronize()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
     def barrier():
@@ -217,6 +223,8 @@ def run_b200_arm(args):
     primary, shadow, boxes, tris = [float(x) for x in counts.tolist()]
     rays_per_step = primary + shadow
 
+    sampler = ClockSampler(physical_gpu_index(local_rank))
+    sampler.__enter__()            # sampled from the warm-up on (same load as the timed steps)
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
@@ -225,17 +233,18 @@ def run_b200_arm(args):
     #      L2 flushed (untimed) between steps; kernel-only time from the library's own events
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     kernel_ms = []
-    with ClockSampler(physical_gpu_index(local_rank)) as clocks:
-        t_wall = time.perf_counter()
-        for k in range(args.steps):
-            flush.zero_()
-            ev[k][0].record(stream)
-            step()
-            ev[k][1].record(stream)
-            torch.cuda.synchronize()
-            kernel_ms.append(scene.stats().kernel_ms)
-        barrier()
-        wall_s = time.perf_counter() - t_wall
+    t_wall = time.perf_counter()
+    for k in range(args.steps):
+        flush.zero_()
+        ev[k][0].record(stream)
+        step()
+        ev[k][1].record(stream)
+        torch.cuda.synchronize()
+        kernel_ms.append(scene.stats().kernel_ms)
+    barrier()
+    wall_s = time.perf_counter() - t_wall
+    sampler.__exit__(None, None, None)
+    clocks = sampler
     step_ms = [s.elapsed_time(e) for s, e in ev]
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
     if world > 1:

@@ -290,20 +290,32 @@ __device__ __forceinline__ void brute_sweep(BruteSmem& sm, DeviceSceneView const
         for (int j = 0; j < kTriTile; j++)
         {
             float4 v0 = tv0[j], e1 = te1[j], e2 = te2[j];
+            // All R barycentric decisions first (straight-line, R independent
+            // dependency chains), then ONE rarely-taken branch for the division
+            // and the (t, id) update: hits are a ~1e-5 fraction of the tests.
+            float ts[R], adet[R];
+            bool in[R];
+            bool any = false;
 #pragma unroll
             for (int r = 0; r < R; r++)
             {
-                float ts, adet;
-                if (mt_inside(o[r], d[r], v0, e1, e2, ts, adet))
+                in[r] = mt_inside(o[r], d[r], v0, e1, e2, ts[r], adet[r]);
+                any |= in[r];
+            }
+            if (any)
+            {
+#pragma unroll
+                for (int r = 0; r < R; r++)
                 {
+                    if (!in[r]) continue;
                     if (ANY)
                     {
-                        float t = __fdiv_rn(ts, adet);
+                        float t = __fdiv_rn(ts[r], adet[r]);
                         if (t > 0.0f && t < 1.0f) occluded[r] = true;
                     }
                     else
                     {
-                        closest_update(best[r], ts, adet, __float_as_int(v0.w),
+                        closest_update(best[r], ts[r], adet[r], __float_as_int(v0.w),
                                        tile * kTriTile + static_cast<uint32_t>(j), t_min);
                     }
                 }

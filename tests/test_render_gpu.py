@@ -95,10 +95,10 @@ def test_bvh_equals_brute_force_100k(ctx):
     v, a, cam, light = api.gen_mesh(1, 100000, W, H)
     scene = ctx.create_scene(v, a)
     p = api.make_params(W, H, spp=2, jitter=1, seed=3, shade=api.SRT_SHADE_SHADOW, background=(0.5, 0.7, 0.9))
+    p.collect_stats = 1
     p.accel = api.SRT_ACCEL_BRUTE
     brute = scene.render(cam, light, p)
     p.accel = api.SRT_ACCEL_BVH
-    p.collect_stats = 1
     bvh = scene.render(cam, light, p)
     assert np.array_equal(brute[1], bvh[1])
     assert np.array_equal(brute[2], bvh[2])
