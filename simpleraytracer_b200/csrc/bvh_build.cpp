@@ -124,9 +124,11 @@ private:
     {
         float const p = m_pad;
         BvhNode& n = m_nodes[idx];
-        n.n0 = {b0.mn[0] - p, b0.mx[0] + p, b0.mn[1] - p, b0.mx[1] + p};
-        n.n1 = {b1.mn[0] - p, b1.mx[0] + p, b1.mn[1] - p, b1.mx[1] + p};
-        n.n2 = {b0.mn[2] - p, b0.mx[2] + p, b1.mn[2] - p, b1.mx[2] + p};
+        // per axis: (c0.min, c1.min, c0.max, c1.max) -- the two children side by
+        // side, so one packed f32x2 FMA handles both boxes
+        n.n0 = {b0.mn[0] - p, b1.mn[0] - p, b0.mx[0] + p, b1.mx[0] + p};
+        n.n1 = {b0.mn[1] - p, b1.mn[1] - p, b0.mx[1] + p, b1.mx[1] + p};
+        n.n2 = {b0.mn[2] - p, b1.mn[2] - p, b0.mx[2] + p, b1.mx[2] + p};
         n.n3 = {IntBitsToFloat(ref0), IntBitsToFloat(ref1), 0.f, 0.f};
     }
 

@@ -47,6 +47,29 @@ __device__ __forceinline__ V3 v3(float const* p) { return V3{p[0], p[1], p[2]}; 
 __device__ __forceinline__ V3 v3(float4 p) { return V3{p.x, p.y, p.z}; }
 __device__ __forceinline__ float pos_inf() { return __int_as_float(0x7f800000); }
 
+// Packed pair of fp32 in one 64-bit register (sm_100 f32x2 arithmetic).  Used
+// only where results do not enter the image (BVH culling).
+typedef unsigned long long F2;
+__device__ __forceinline__ F2 pack2(float a, float b)
+{
+    F2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ F2 pack2(float a) { return pack2(a, a); }
+__device__ __forceinline__ float2 unpack2(F2 v)
+{
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
+__device__ __forceinline__ F2 fma2(F2 a, F2 b, F2 c)
+{
+    F2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
 __device__ __forceinline__ uint32_t hash_sample(uint32_t pix, uint32_t s, uint32_t dim, uint32_t seed)
 {
     uint32_t h = (pix * 0x9E3779B1u) ^ (s * 0x85EBCA77u + dim * 0xC2B2AE3Du + seed * 0x27D4EB2Fu + 0x165667B1u);
@@ -96,7 +119,11 @@ __device__ __forceinline__ bool mt_inside(V3 o, V3 d, float4 v0, float4 e1, floa
     vs = __uint_as_float(__float_as_uint(vs) ^ sgn);
     ts = __uint_as_float(__float_as_uint(tsr) ^ sgn);
     adet = fabsf(det);
-    return (adet != 0.0f) & (us >= 0.0f) & (vs >= 0.0f) & (add(us, vs) <= adet);
+    // The spec's `det != 0` term is implied for every observable result and is
+    // not evaluated: with det == 0, t = ts/0 is +-inf or NaN, which neither the
+    // closest-hit rule (t < best.t, or t == best.t and id < best.id with
+    // best.id = -1 while best.t = +inf) nor the any-hit rule (0 < t < 1) accepts.
+    return (us >= 0.0f) & (vs >= 0.0f) & (add(us, vs) <= adet);
 }
 
 // Closest-hit record: t, original triangle id (tie-break + output) and the
@@ -462,8 +489,16 @@ __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d,
     float4 const* __restrict__ te1 = reinterpret_cast<float4 const*>(sc.tri_e1);
     float4 const* __restrict__ te2 = reinterpret_cast<float4 const*>(sc.tri_e2);
 
+    // Slab test of BOTH children at once with packed f32x2 FMAs (SASS FFMA2: one
+    // issue slot, two lanes of work).  The near/far plane of an axis is picked by
+    // the sign of the direction WITHOUT min/max: with idp = max(1/d,0) and
+    // idn = min(1/d,0) exactly one is non-zero, so
+    //     t_near = min_plane*idp + max_plane*idn - o/d ,  t_far = max_plane*idp + min_plane*idn - o/d
+    // which moves 12 FMNMX per node from the half-rate ALU pipe to 12 FFMA2.
     float const idx = safe_inv(d.x), idy = safe_inv(d.y), idz = safe_inv(d.z);
-    float const oodx = o.x * idx, oody = o.y * idy, oodz = o.z * idz;
+    F2 const idpx = pack2(fmaxf(idx, 0.f)), idnx = pack2(fminf(idx, 0.f)), noodx = pack2(-(o.x * idx));
+    F2 const idpy = pack2(fmaxf(idy, 0.f)), idny = pack2(fminf(idy, 0.f)), noody = pack2(-(o.y * idy));
+    F2 const idpz = pack2(fmaxf(idz, 0.f)), idnz = pack2(fminf(idz, 0.f)), noodz = pack2(-(o.z * idz));
     float const slack = 1.000244140625f; // 1 + 2^-12
     float t_far = ANY ? slack : pos_inf();
     float const t_near = fmaxf(t_min, 0.0f);
@@ -482,21 +517,21 @@ __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d,
             float4 n3 = __ldg(nodes + 4 * node + 3);
             if (STATS) n_box += 2;
 
-            float c0lox = fmaf(n0.x, idx, -oodx), c0hix = fmaf(n0.y, idx, -oodx);
-            float c0loy = fmaf(n0.z, idy, -oody), c0hiy = fmaf(n0.w, idy, -oody);
-            float c0loz = fmaf(n2.x, idz, -oodz), c0hiz = fmaf(n2.y, idz, -oodz);
-            float c1lox = fmaf(n1.x, idx, -oodx), c1hix = fmaf(n1.y, idx, -oodx);
-            float c1loy = fmaf(n1.z, idy, -oody), c1hiy = fmaf(n1.w, idy, -oody);
-            float c1loz = fmaf(n2.z, idz, -oodz), c1hiz = fmaf(n2.w, idz, -oodz);
+            // n = (c0.min, c1.min, c0.max, c1.max) per axis: .lo pair = mins, .hi pair = maxes
+            F2 const mnx = pack2(n0.x, n0.y), mxx = pack2(n0.z, n0.w);
+            F2 const mny = pack2(n1.x, n1.y), mxy = pack2(n1.z, n1.w);
+            F2 const mnz = pack2(n2.x, n2.y), mxz = pack2(n2.z, n2.w);
+            float2 const nx = unpack2(fma2(mnx, idpx, fma2(mxx, idnx, noodx)));
+            float2 const fx = unpack2(fma2(mxx, idpx, fma2(mnx, idnx, noodx)));
+            float2 const ny = unpack2(fma2(mny, idpy, fma2(mxy, idny, noody)));
+            float2 const fy = unpack2(fma2(mxy, idpy, fma2(mny, idny, noody)));
+            float2 const nz = unpack2(fma2(mnz, idpz, fma2(mxz, idnz, noodz)));
+            float2 const fz = unpack2(fma2(mxz, idpz, fma2(mnz, idnz, noodz)));
 
-            float c0min = fmaxf(fmaxf(fminf(c0lox, c0hix), fminf(c0loy, c0hiy)),
-                                fmaxf(fminf(c0loz, c0hiz), t_near));
-            float c0max = fminf(fminf(fmaxf(c0lox, c0hix), fmaxf(c0loy, c0hiy)),
-                                fminf(fmaxf(c0loz, c0hiz), t_far));
-            float c1min = fmaxf(fmaxf(fminf(c1lox, c1hix), fminf(c1loy, c1hiy)),
-                                fmaxf(fminf(c1loz, c1hiz), t_near));
-            float c1max = fminf(fminf(fmaxf(c1lox, c1hix), fmaxf(c1loy, c1hiy)),
-                                fminf(fmaxf(c1loz, c1hiz), t_far));
+            float c0min = fmaxf(fmaxf(nx.x, ny.x), fmaxf(nz.x, t_near));
+            float c0max = fminf(fminf(fx.x, fy.x), fminf(fz.x, t_far));
+            float c1min = fmaxf(fmaxf(nx.y, ny.y), fmaxf(nz.y, t_near));
+            float c1max = fminf(fminf(fx.y, fy.y), fminf(fz.y, t_far));
 
             // Slack on the entry distance as well (relative + box-scale absolute
             // error is already covered by the build-time padding).

@@ -29,9 +29,9 @@ constexpr int kLeafCountBits = 4;  // child ref: ~ref = (first << 4) | (count-1)
 constexpr int kBvhStackDepth = 64;
 
 // 64-byte inner node as stored in HBM:
-//   n0 = (c0.min.x, c0.max.x, c0.min.y, c0.max.y)
-//   n1 = (c1.min.x, c1.max.x, c1.min.y, c1.max.y)
-//   n2 = (c0.min.z, c0.max.z, c1.min.z, c1.max.z)
+//   n0 = (c0.min.x, c1.min.x, c0.max.x, c1.max.x)
+//   n1 = (c0.min.y, c1.min.y, c0.max.y, c1.max.y)
+//   n2 = (c0.min.z, c1.min.z, c0.max.z, c1.max.z)
 //   n3 = (bits(ref0), bits(ref1), 0, 0)
 struct BvhNode { F4 n0, n1, n2, n3; };
 
