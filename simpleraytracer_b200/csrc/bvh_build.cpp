@@ -88,7 +88,7 @@ public:
         BvhBuildResult out;
         size_t const n = m_prims.size();
         m_nodes.reserve(n / 2 + 2);
-        if (n <= static_cast<size_t>(kMaxLeafTris))
+        if (n <= static_cast<size_t>(m_leaf_size))
         {
             // Root must be an inner node: both children reference the one leaf
             // (for n == 0: the first padding triangle, which can never be hit).
@@ -137,7 +137,7 @@ private:
     int32_t BuildRange(int first, int count, int depth, Box& bounds)
     {
         m_max_depth = std::max(m_max_depth, depth);
-        if (count <= kMaxLeafTris)
+        if (count <= m_leaf_size)
         {
             for (int i = first; i < first + count; i++) bounds.Grow(m_prims[i].bmin, m_prims[i].bmax);
             return LeafRef(first, count);
@@ -250,6 +250,12 @@ private:
     std::vector<BvhNode> m_nodes;
     float m_pad = 0.f;
     int m_max_depth = 0;
+    // tuning knob for experiments only (SRT_BVH_LEAF=1..kMaxLeafTris)
+    int m_leaf_size = [] {
+        char const* e = std::getenv("SRT_BVH_LEAF");
+        int v = e ? std::atoi(e) : kDefaultLeafTris;
+        return v < 1 ? 1 : (v > kMaxLeafTris ? kMaxLeafTris : v);
+    }();
 };
 
 } // namespace
