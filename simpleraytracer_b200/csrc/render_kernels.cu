@@ -533,10 +533,10 @@ __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d,
             float c1min = fmaxf(fmaxf(nx.y, ny.y), fmaxf(nz.y, t_near));
             float c1max = fminf(fminf(fx.y, fy.y), fminf(fz.y, t_far));
 
-            // Slack on the entry distance as well (relative + box-scale absolute
-            // error is already covered by the build-time padding).
-            bool hit0 = c0max * slack >= c0min;
-            bool hit1 = c1max * slack >= c1min;
+            // No slack on the entry side: the build-time padding (2^-18 of the scene
+            // extent, absolute) exceeds the slab arithmetic's rounding by > 10x.
+            bool hit0 = c0max >= c0min;
+            bool hit1 = c1max >= c1min;
             int ref0 = __float_as_int(n3.x), ref1 = __float_as_int(n3.y);
 
             if (!hit0 && !hit1)
@@ -586,8 +586,9 @@ __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d,
     }
 }
 
-template <bool STATS>
-__global__ void __launch_bounds__(kBvhThreads) render_bvh_kernel(const __grid_constant__ RenderLaunch L)
+// MINB = minimum resident blocks per SM the register allocation must allow.
+template <bool STATS, int MINB>
+__global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __grid_constant__ RenderLaunch L)
 {
     uint32_t const W = L.params.width;
     uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -636,215 +637,6 @@ __global__ void __launch_bounds__(kBvhThreads) render_bvh_kernel(const __grid_co
 }
 
 // ---------------------------------------------------------------------------
-// BVH traversal, ray-stream variant (default).
-//
-// Same arithmetic as render_bvh_kernel, different control flow: every lane runs
-// ONE traversal loop through which all its rays flow (sample 0 primary, its
-// shadow ray, sample 1 primary, ...).  A lane whose ray has finished does not
-// wait for the slowest ray of the warp at every ray boundary; it parks until at
-// least kRefillLanes lanes of the warp are parked (or nothing else can run), then
-// those lanes shade / generate their next ray together and rejoin the loop.
-// Samples of a pixel are still accumulated in index order by the one lane that
-// owns the pixel, so the image is bit-identical to the simple kernel's.
-// ---------------------------------------------------------------------------
-constexpr int kSentinel = 0x7fffffff; // "stack empty": not an inner index, not a leaf ref
-constexpr int kRefillLanes = 8;
-
-template <bool STATS>
-__global__ void __launch_bounds__(kBvhThreads) render_bvh_stream_kernel(const __grid_constant__ RenderLaunch L)
-{
-    uint32_t const W = L.params.width;
-    uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint32_t const x = blockIdx.x * kBvhBlockW + (warp & 3u) * 8u + (lane & 7u);
-    uint32_t const y = L.params.y0 + blockIdx.y * kBvhBlockH + (warp >> 2) * 4u + (lane >> 3);
-    bool const valid = x < W && y < L.params.y1;
-
-    unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
-    if (valid)
-    {
-        DeviceSceneView const& sc = L.scene;
-        float4 const* __restrict__ nodes = reinterpret_cast<float4 const*>(sc.nodes);
-        float4 const* __restrict__ tv0 = reinterpret_cast<float4 const*>(sc.tri_v0);
-        float4 const* __restrict__ te1 = reinterpret_cast<float4 const*>(sc.tri_e1);
-        float4 const* __restrict__ te2 = reinterpret_cast<float4 const*>(sc.tri_e2);
-        float const slack = 1.000244140625f; // 1 + 2^-12
-        size_t const out = static_cast<size_t>(y * W + x) - static_cast<size_t>(L.params.buf_y0) * W;
-
-        // ---- per-lane ray state
-        V3 o, d;
-        F2 idpx, idnx, noodx, idpy, idny, noody, idpz, idnz, noodz;
-        float t_near, t_far;
-        Hit best;
-        bool shadow = false, occluded = false;
-        V3 pend = V3{0.f, 0.f, 0.f};  // unshadowed radiance while the shadow ray is in flight
-        V3 acc = V3{0.f, 0.f, 0.f};
-        uint32_t s = 0;
-        int stack[kBvhStackDepth];
-        int sp, node;
-
-        auto start_ray = [&](V3 ro, V3 rd, float tmin, float tfar) {
-            o = ro;
-            d = rd;
-            float const ix = safe_inv(rd.x), iy = safe_inv(rd.y), iz = safe_inv(rd.z);
-            idpx = pack2(fmaxf(ix, 0.f)); idnx = pack2(fminf(ix, 0.f)); noodx = pack2(-(ro.x * ix));
-            idpy = pack2(fmaxf(iy, 0.f)); idny = pack2(fminf(iy, 0.f)); noody = pack2(-(ro.y * iy));
-            idpz = pack2(fmaxf(iz, 0.f)); idnz = pack2(fminf(iz, 0.f)); noodz = pack2(-(ro.z * iz));
-            t_near = fmaxf(tmin, 0.0f);
-            t_far = tfar;
-            best = no_hit();
-            stack[0] = kSentinel;
-            sp = 1;
-            node = 0;
-        };
-        start_ray(v3(L.camera.origin), primary_dir(L, x, y, 0u), L.params.t_min, pos_inf());
-
-        while (true)
-        {
-            // ---- ray boundary: shade / spawn the shadow ray / next sample
-            bool const parked = node == kSentinel;
-            unsigned const mask = __activemask();
-            unsigned const parked_mask = __ballot_sync(mask, parked);
-            if (parked && (__popc(parked_mask) >= kRefillLanes || parked_mask == mask))
-            {
-                bool next_sample = true;
-                if (!shadow)
-                {
-                    n_primary++;
-                    if (s == 0)
-                    {
-                        if (L.d_hit_id) L.d_hit_id[out] = best.id;
-                        if (L.d_hit_t) L.d_hit_t[out] = best.t;
-                    }
-                    V3 rgb;
-                    if (best.id < 0)
-                    {
-                        rgb = v3(L.params.background);
-                    }
-                    else
-                    {
-                        ShadeOut sh = shade_hit(L, o, d, best);
-                        rgb = sh.rgb;
-                        if (sh.need_shadow)
-                        {
-                            n_shadow++;
-                            pend = rgb;
-                            shadow = true;
-                            occluded = false;
-                            start_ray(sh.so, sh.sd, 0.0f, slack);
-                            next_sample = false;
-                        }
-                    }
-                    if (next_sample)
-                    {
-                        acc.x = add(acc.x, rgb.x);
-                        acc.y = add(acc.y, rgb.y);
-                        acc.z = add(acc.z, rgb.z);
-                    }
-                }
-                else
-                {
-                    V3 rgb = occluded ? V3{0.f, 0.f, 0.f} : pend;
-                    acc.x = add(acc.x, rgb.x);
-                    acc.y = add(acc.y, rgb.y);
-                    acc.z = add(acc.z, rgb.z);
-                    shadow = false;
-                }
-                if (next_sample)
-                {
-                    if (++s == L.params.spp) break;
-                    start_ray(v3(L.camera.origin), primary_dir(L, x, y, s), L.params.t_min, pos_inf());
-                }
-            }
-
-            // ---- inner nodes
-            while (node >= 0 && node != kSentinel)
-            {
-                float4 n0 = __ldg(nodes + 4 * node + 0);
-                float4 n1 = __ldg(nodes + 4 * node + 1);
-                float4 n2 = __ldg(nodes + 4 * node + 2);
-                float4 n3 = __ldg(nodes + 4 * node + 3);
-                if (STATS) n_box += 2;
-
-                F2 const mnx = pack2(n0.x, n0.y), mxx = pack2(n0.z, n0.w);
-                F2 const mny = pack2(n1.x, n1.y), mxy = pack2(n1.z, n1.w);
-                F2 const mnz = pack2(n2.x, n2.y), mxz = pack2(n2.z, n2.w);
-                float2 const nx = unpack2(fma2(mnx, idpx, fma2(mxx, idnx, noodx)));
-                float2 const fx = unpack2(fma2(mxx, idpx, fma2(mnx, idnx, noodx)));
-                float2 const ny = unpack2(fma2(mny, idpy, fma2(mxy, idny, noody)));
-                float2 const fy = unpack2(fma2(mxy, idpy, fma2(mny, idny, noody)));
-                float2 const nz = unpack2(fma2(mnz, idpz, fma2(mxz, idnz, noodz)));
-                float2 const fz = unpack2(fma2(mxz, idpz, fma2(mnz, idnz, noodz)));
-
-                float c0min = fmaxf(fmaxf(nx.x, ny.x), fmaxf(nz.x, t_near));
-                float c0max = fminf(fminf(fx.x, fy.x), fminf(fz.x, t_far));
-                float c1min = fmaxf(fmaxf(nx.y, ny.y), fmaxf(nz.y, t_near));
-                float c1max = fminf(fminf(fx.y, fy.y), fminf(fz.y, t_far));
-                bool hit0 = c0max * slack >= c0min;
-                bool hit1 = c1max * slack >= c1min;
-                int ref0 = __float_as_int(n3.x), ref1 = __float_as_int(n3.y);
-
-                if (!hit0 && !hit1)
-                {
-                    node = stack[--sp];
-                }
-                else if (hit0 && hit1)
-                {
-                    bool swap = c1min < c0min;
-                    node = swap ? ref1 : ref0;
-                    stack[sp++] = swap ? ref0 : ref1;
-                }
-                else
-                {
-                    node = hit0 ? ref0 : ref1;
-                }
-            }
-
-            // ---- leaf
-            if (node < 0)
-            {
-                uint32_t enc = static_cast<uint32_t>(~node);
-                uint32_t first = enc >> kLeafCountBits;
-                uint32_t count = (enc & ((1u << kLeafCountBits) - 1u)) + 1u;
-                if (STATS) n_tri += count;
-                node = stack[--sp];
-                for (uint32_t i = first; i < first + count; i++)
-                {
-                    float4 v0 = __ldg(tv0 + i), e1 = __ldg(te1 + i), e2 = __ldg(te2 + i);
-                    float ts, adet;
-                    if (mt_inside(o, d, v0, e1, e2, ts, adet))
-                    {
-                        if (shadow)
-                        {
-                            float t = __fdiv_rn(ts, adet);
-                            if (t > 0.0f && t < 1.0f)
-                            {
-                                occluded = true;
-                                node = kSentinel; // any hit ends the shadow ray
-                                break;
-                            }
-                        }
-                        else
-                        {
-                            closest_update(best, ts, adet, __float_as_int(v0.w), i, L.params.t_min);
-                            t_far = best.t * slack;
-                        }
-                    }
-                }
-            }
-        }
-
-        if (L.d_rgb)
-        {
-            float* p = L.d_rgb + out * 3;
-            p[0] = mul(acc.x, L.inv_spp);
-            p[1] = mul(acc.y, L.inv_spp);
-            p[2] = mul(acc.z, L.inv_spp);
-        }
-    }
-    flush_counters(L, n_primary, n_shadow, n_box, n_tri);
-}
-
-// ---------------------------------------------------------------------------
 // FP32 peak microbenchmark: 8 independent FFMA chains per thread.
 // ---------------------------------------------------------------------------
 constexpr int kPeakIters = 4096;
@@ -881,25 +673,19 @@ void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
     if (p.accel == SRT_ACCEL_BVH)
     {
         dim3 grid((p.width + kBvhBlockW - 1) / kBvhBlockW, (rows + kBvhBlockH - 1) / kBvhBlockH);
-        // SRT_BVH_KERNEL=simple selects the per-ray-loop variant (A/B measurements).
-        static bool const simple = [] {
-            char const* e = std::getenv("SRT_BVH_KERNEL");
-            return e != nullptr && std::string(e) == "simple";
+        // SRT_BVH_MINB=4|5|6: occupancy experiment (register cap 64 / 48 / 40).
+        static int const minb = [] {
+            char const* e = std::getenv("SRT_BVH_MINB");
+            return e ? std::atoi(e) : 4;
         }();
-        if (simple)
-        {
-            if (p.collect_stats)
-                render_bvh_kernel<true><<<grid, kBvhThreads, 0, stream>>>(launch);
-            else
-                render_bvh_kernel<false><<<grid, kBvhThreads, 0, stream>>>(launch);
-        }
+        if (p.collect_stats)
+            render_bvh_kernel<true, 4><<<grid, kBvhThreads, 0, stream>>>(launch);
+        else if (minb == 6)
+            render_bvh_kernel<false, 6><<<grid, kBvhThreads, 0, stream>>>(launch);
+        else if (minb == 5)
+            render_bvh_kernel<false, 5><<<grid, kBvhThreads, 0, stream>>>(launch);
         else
-        {
-            if (p.collect_stats)
-                render_bvh_stream_kernel<true><<<grid, kBvhThreads, 0, stream>>>(launch);
-            else
-                render_bvh_stream_kernel<false><<<grid, kBvhThreads, 0, stream>>>(launch);
-        }
+            render_bvh_kernel<false, 4><<<grid, kBvhThreads, 0, stream>>>(launch);
     }
     else
     {
