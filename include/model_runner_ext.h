@@ -28,6 +28,18 @@ ML_API_ENTRY ml_status mlxInspectModel(char const* model_path, char const* input
  * Lets an external producer/consumer (e.g. a torch tensor) share the buffer. */
 ML_API_ENTRY void* mlxImageDevicePointer(ml_image image, int for_write, void* stream);
 
+/* Peer mapping of an image's HBM buffer into another PROCESS of the same node
+ * (one process per GPU): the owner exports a 64-byte handle, every other rank
+ * opens it and receives a device pointer that its kernels can store to over
+ * NVLink/NVSwitch.  This is how the multi-GPU render writes each rank's rows
+ * straight into rank 0's frame (no gather pass).  mlxIpcExportImage also makes
+ * the device copy authoritative (peers are about to overwrite it).
+ * mlxIpcOpen returns NULL on failure (message on the context). */
+#define MLX_IPC_HANDLE_BYTES 64
+ML_API_ENTRY ml_status mlxIpcExportImage(ml_image image, void* handle_out);
+ML_API_ENTRY void* mlxIpcOpen(ml_context context, void const* handle);
+ML_API_ENTRY void mlxIpcClose(ml_context context, void* device_pointer);
+
 /* Number of kernel launches one mlInfer() of this model enqueues. */
 ML_API_ENTRY size_t mlxModelLaunchCount(ml_model model);
 

@@ -64,6 +64,10 @@ struct srt_render_params
     uint32_t y0;         /* rows [y0,y1) are rendered (row-band sharding)         */
     uint32_t y1;
     uint32_t buf_y0;     /* frame row that the output pointers' first row holds   */
+    uint32_t row_block_stride; /* 0 or 1: every row of the band.  N > 1: only the  */
+    uint32_t row_block_phase;  /* 8-row blocks b = y/8 with b % N == phase are      */
+                               /* rendered (interleaved sharding over N GPUs for    */
+                               /* load balance); needs y0 % 8 == 0                  */
     uint32_t spp;        /* samples per pixel, accumulated in index order         */
     uint32_t jitter;     /* 0: pixel centre; 1: hashed sub-pixel jitter           */
     uint32_t seed;

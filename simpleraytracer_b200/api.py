@@ -43,7 +43,8 @@ class srt_light(C.Structure):
 
 class srt_render_params(C.Structure):
     _fields_ = [("width", C.c_uint32), ("height", C.c_uint32), ("y0", C.c_uint32), ("y1", C.c_uint32),
-                ("buf_y0", C.c_uint32), ("spp", C.c_uint32), ("jitter", C.c_uint32), ("seed", C.c_uint32),
+                ("buf_y0", C.c_uint32), ("row_block_stride", C.c_uint32), ("row_block_phase", C.c_uint32),
+                ("spp", C.c_uint32), ("jitter", C.c_uint32), ("seed", C.c_uint32),
                 ("shade", C.c_uint32), ("accel", C.c_uint32), ("collect_stats", C.c_uint32),
                 ("t_min", C.c_float), ("shadow_eps", C.c_float), ("background", C.c_float * 3)]
 
@@ -97,6 +98,9 @@ _PROTOTYPES = {
     "mlxInspectModel": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),
     "mlxImageDevicePointer": (C.c_void_p, [C.c_void_p, C.c_int, C.c_void_p]),
     "mlxModelLaunchCount": (C.c_size_t, [C.c_void_p]),
+    "mlxIpcExportImage": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "mlxIpcOpen": (C.c_void_p, [C.c_void_p, C.c_void_p]),
+    "mlxIpcClose": (None, [C.c_void_p, C.c_void_p]),
 }
 
 _lib = None
@@ -179,6 +183,17 @@ class Context:
             raise MLError(self.error())
         return Scene(self.lib, h)
 
+    def ipc_open(self, handle: bytes) -> int:
+        """mlxIpcOpen: maps another process's exported image buffer; returns a device pointer."""
+        buf = C.create_string_buffer(handle, 64)
+        p = self.lib.mlxIpcOpen(self.handle, buf)
+        if not p:
+            raise MLError(self.error())
+        return int(p)
+
+    def ipc_close(self, ptr: int):
+        self.lib.mlxIpcClose(self.handle, ptr)
+
     def measure_fp32_peak(self, repeats=5) -> float:
         return float(self.lib.srtMeasureFp32Peak(self.handle, repeats))
 
@@ -222,6 +237,13 @@ class Image:
         if not p:
             raise MLError("mlxImageDevicePointer failed")
         return int(p)
+
+    def ipc_export(self) -> bytes:
+        """mlxIpcExportImage: 64-byte handle other ranks pass to Context.ipc_open()."""
+        buf = C.create_string_buffer(64)
+        if self.lib.mlxIpcExportImage(self.handle, buf) != ML_OK:
+            raise MLError("mlxIpcExportImage failed")
+        return buf.raw
 
     def write(self, data: np.ndarray):
         view = self.map()
@@ -276,11 +298,12 @@ class Model:
 
 def make_params(width, height, spp=1, jitter=0, seed=0, shade=SRT_SHADE_ALBEDO, accel=SRT_ACCEL_BRUTE,
                 y0=0, y1=None, buf_y0=0, t_min=1e-4, shadow_eps=1e-3, background=(0.0, 0.0, 0.0),
-                collect_stats=0) -> srt_render_params:
+                collect_stats=0, row_block_stride=0, row_block_phase=0) -> srt_render_params:
     p = srt_render_params()
     p.width, p.height = width, height
     p.y0, p.y1 = y0, height if y1 is None else y1
     p.buf_y0 = buf_y0
+    p.row_block_stride, p.row_block_phase = row_block_stride, row_block_phase
     p.spp, p.jitter, p.seed = spp, jitter, seed
     p.shade, p.accel, p.collect_stats = shade, accel, collect_stats
     p.t_min, p.shadow_eps = t_min, shadow_eps

@@ -6,6 +6,7 @@
 // somebody maps them.
 #include "image.h"
 
+#include "context.h"
 #include "dtype.h"
 #include "model_runner_ext.h"
 
@@ -136,6 +137,56 @@ ML_API_ENTRY ml_status mlUnmapImage(ml_image image, void* data)
 ML_API_ENTRY void mlReleaseImage(ml_image image)
 {
     delete ML::Image::FromHandle(image);
+}
+
+ML_API_ENTRY ml_status mlxIpcExportImage(ml_image image, void* handle_out)
+{
+    ML::Image* img = ML::Image::FromHandle(image);
+    if (img == nullptr || handle_out == nullptr) return ML_FAIL;
+    static_assert(sizeof(cudaIpcMemHandle_t) == MLX_IPC_HANDLE_BYTES, "IPC handle size");
+    try
+    {
+        img->Device()->MakeCurrent();
+        cudaIpcMemHandle_t h;
+        ML_CUDA_CHECK(cudaIpcGetMemHandle(&h, img->DeviceWrite()));
+        std::memcpy(handle_out, &h, sizeof(h));
+        img->MarkDeviceAuthoritative();
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        std::fprintf(stderr, "mlxIpcExportImage: %s\n", e.what());
+        return ML_FAIL;
+    }
+}
+
+ML_API_ENTRY void* mlxIpcOpen(ml_context context, void const* handle)
+{
+    ML::Context* ctx = ML::Context::FromHandle(context);
+    if (ctx == nullptr || handle == nullptr) return nullptr;
+    ctx->ClearError();
+    try
+    {
+        ctx->Device()->MakeCurrent();
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handle, sizeof(h));
+        void* p = nullptr;
+        ML_CUDA_CHECK(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+        return p;
+    }
+    catch (std::exception const& e)
+    {
+        ctx->SetError(e.what());
+        return nullptr;
+    }
+}
+
+ML_API_ENTRY void mlxIpcClose(ml_context context, void* device_pointer)
+{
+    ML::Context* ctx = ML::Context::FromHandle(context);
+    if (ctx == nullptr || device_pointer == nullptr) return;
+    cudaSetDevice(ctx->Device()->device);
+    cudaIpcCloseMemHandle(device_pointer);
 }
 
 ML_API_ENTRY void* mlxImageDevicePointer(ml_image image, int for_write, void* stream)

@@ -366,8 +366,7 @@ __global__ void __launch_bounds__(kBruteThreads) render_brute_kernel(const __gri
     __syncthreads();
 
     uint32_t const W = L.params.width;
-    uint32_t const band_pixels = (L.params.y1 - L.params.y0) * W;
-    uint32_t const first_pixel = L.params.y0 * W;
+    uint32_t const owned_pixels = L.n_row_blocks * 8u * W; // rows past y1 are clipped below
     uint32_t const chunk = blockIdx.x * (kBruteThreads * R);
     V3 const cam_o = v3(L.camera.origin);
     DeviceSceneView const& sc = L.scene;
@@ -381,8 +380,11 @@ __global__ void __launch_bounds__(kBruteThreads) render_brute_kernel(const __gri
     for (int r = 0; r < R; r++)
     {
         uint32_t local = chunk + r * kBruteThreads + threadIdx.x;
-        valid[r] = local < band_pixels;
-        pix[r] = first_pixel + (valid[r] ? local : 0u);
+        // local pixel -> (owned row, x) -> frame row through the row-block map
+        uint32_t lrow = local / W, lx = local - lrow * W;
+        uint32_t fy = L.row_origin + (lrow >> 3) * L.row_block_step + (lrow & 7u);
+        valid[r] = local < owned_pixels && fy < L.params.y1;
+        pix[r] = valid[r] ? fy * W + lx : L.params.y0 * W;
         acc[r] = V3{0.f, 0.f, 0.f};
         first_hit[r] = no_hit();
     }
@@ -593,7 +595,7 @@ __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __g
     uint32_t const W = L.params.width;
     uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     uint32_t const x = blockIdx.x * kBvhBlockW + (warp & 3u) * 8u + (lane & 7u);
-    uint32_t const y = L.params.y0 + blockIdx.y * kBvhBlockH + (warp >> 2) * 4u + (lane >> 3);
+    uint32_t const y = L.row_origin + blockIdx.y * L.row_block_step + (warp >> 2) * 4u + (lane >> 3);
     bool const valid = x < W && y < L.params.y1;
 
     unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
@@ -669,10 +671,11 @@ __global__ void __launch_bounds__(256) fp32_peak_kernel(float* out, float a, flo
 void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
 {
     srt_render_params const& p = launch.params;
-    uint32_t const rows = p.y1 - p.y0;
+    uint32_t const rows = launch.n_row_blocks * 8u; // owned rows (last block may be clipped by y1)
     if (p.accel == SRT_ACCEL_BVH)
     {
-        dim3 grid((p.width + kBvhBlockW - 1) / kBvhBlockW, (rows + kBvhBlockH - 1) / kBvhBlockH);
+        static_assert(kBvhBlockH == 8, "row blocks are 8 rows");
+        dim3 grid((p.width + kBvhBlockW - 1) / kBvhBlockW, launch.n_row_blocks);
         // SRT_BVH_MINB=4|5|6: occupancy experiment (register cap 64 / 48 / 40).
         static int const minb = [] {
             char const* e = std::getenv("SRT_BVH_MINB");

@@ -21,6 +21,28 @@ inline float IntBitsToFloat(int32_t v)
     std::memcpy(&f, &v, 4);
     return f;
 }
+
+// The 8-row blocks a call owns: block k = 0..count-1 starts at frame row
+// origin + k*step (see RenderLaunch).  stride <= 1: the whole band from y0.
+void RowBlocks(srt_render_params const& p, uint32_t& origin, uint32_t& step, uint32_t& count)
+{
+    uint32_t const rows = p.y1 - p.y0;
+    uint32_t const blocks = (rows + 7u) / 8u;
+    uint32_t const stride = p.row_block_stride > 1 ? p.row_block_stride : 1u;
+    if (stride == 1)
+    {
+        origin = p.y0;
+        step = 8;
+        count = blocks;
+        return;
+    }
+    // frame block index b = y/8 (y0 % 8 == 0 is validated); owned: b % stride == phase
+    uint32_t const b0 = p.y0 / 8u;
+    uint32_t const first = b0 + (p.row_block_phase + stride - b0 % stride) % stride;
+    origin = first * 8u;
+    step = 8u * stride;
+    count = first < b0 + blocks ? (b0 + blocks - first + stride - 1) / stride : 0;
+}
 } // namespace
 
 Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const* albedo,
@@ -162,6 +184,9 @@ bool Scene::Validate(srt_camera const* camera, srt_light const* light, srt_rende
     else if (p->y0 > p->y1 || p->y1 > p->height)
         os << "Bad row band [" << p->y0 << ", " << p->y1 << ") for height " << p->height;
     else if (p->buf_y0 > p->y0) os << "Bad buffer row origin " << p->buf_y0 << " for band start " << p->y0;
+    else if (p->row_block_stride > 1 && (p->y0 % 8 != 0 || p->row_block_phase >= p->row_block_stride))
+        os << "Bad interleaved band: y0 " << p->y0 << " must be a multiple of 8 and phase "
+           << p->row_block_phase << " below stride " << p->row_block_stride;
     else if (p->spp == 0) os << "Unspecified sample count";
     else if (p->shade > SRT_SHADE_SHADOW) os << "Unsupported shade mode: " << p->shade;
     else if (p->accel > SRT_ACCEL_BVH) os << "Unsupported acceleration mode: " << p->accel;
@@ -191,9 +216,10 @@ ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
         launch.d_hit_id = static_cast<int32_t*>(d_hit_id);
         launch.d_hit_t = static_cast<float*>(d_hit_t);
         launch.d_counters = m_d_counters;
+        RowBlocks(*params, launch.row_origin, launch.row_block_step, launch.n_row_blocks);
         ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), stream));
         if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, stream));
-        if (params->y1 > params->y0)
+        if (launch.n_row_blocks > 0)
             LaunchRender(launch, m_device->prop.multiProcessorCount, stream);
         if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, stream));
         ML_CUDA_CHECK(cudaGetLastError());
@@ -258,7 +284,8 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         cudaStream_t s = m_device->stream;
         size_t const rows = params->y1 - params->y0;
         size_t const pixels = rows * params->width;
-        EnsureStaging(std::max<size_t>(pixels, 1));
+        // staging holds whole 8-row blocks so a clipped last block can be copied as a unit
+        EnsureStaging(std::max<size_t>((rows + 7) / 8 * 8 * params->width, 1));
 
         // Render the band into band-local device buffers (buf_y0 = y0) ...
         srt_render_params band = *params;
@@ -269,13 +296,54 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         // ... then D2H through pinned staging and into the caller's frame at
         // the rows' full-frame offsets (relative to the caller's buf_y0).
         size_t const row_off = static_cast<size_t>(params->y0 - params->buf_y0) * params->width;
-        if (rgb) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_rgb, m_d_rgb, pixels * 12, cudaMemcpyDeviceToHost, s));
-        if (hit_id) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_id, m_d_id, pixels * 4, cudaMemcpyDeviceToHost, s));
-        if (hit_t) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_t, m_d_t, pixels * 4, cudaMemcpyDeviceToHost, s));
+        uint32_t const stride = params->row_block_stride > 1 ? params->row_block_stride : 1u;
+        if (stride == 1)
+        {
+            if (rgb) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_rgb, m_d_rgb, pixels * 12, cudaMemcpyDeviceToHost, s));
+            if (hit_id) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_id, m_d_id, pixels * 4, cudaMemcpyDeviceToHost, s));
+            if (hit_t) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_t, m_d_t, pixels * 4, cudaMemcpyDeviceToHost, s));
+        }
+        else
+        {
+            // only the owned 8-row blocks cross PCIe: one strided 2-D copy per buffer
+            uint32_t origin, step, count;
+            RowBlocks(band, origin, step, count);
+            size_t const first = static_cast<size_t>(origin - params->y0) * params->width; // pixels
+            size_t const blk = 8 * static_cast<size_t>(params->width);                     // pixels per block
+            size_t const pitch = static_cast<size_t>(step) * params->width;                // pixels between blocks
+            auto copy = [&](void* h, void* d, size_t item) {
+                ML_CUDA_CHECK(cudaMemcpy2DAsync(static_cast<char*>(h) + first * item, pitch * item,
+                                                static_cast<char*>(d) + first * item, pitch * item,
+                                                blk * item, count, cudaMemcpyDeviceToHost, s));
+            };
+            if (count > 0)
+            {
+                if (rgb) copy(m_h_rgb, m_d_rgb, 12);
+                if (hit_id) copy(m_h_id, m_d_id, 4);
+                if (hit_t) copy(m_h_t, m_d_t, 4);
+            }
+        }
         ML_CUDA_CHECK(cudaStreamSynchronize(s));
-        if (rgb) std::memcpy(rgb + row_off * 3, m_h_rgb, pixels * 12);
-        if (hit_id) std::memcpy(hit_id + row_off, m_h_id, pixels * 4);
-        if (hit_t) std::memcpy(hit_t + row_off, m_h_t, pixels * 4);
+        if (stride == 1)
+        {
+            if (rgb) std::memcpy(rgb + row_off * 3, m_h_rgb, pixels * 12);
+            if (hit_id) std::memcpy(hit_id + row_off, m_h_id, pixels * 4);
+            if (hit_t) std::memcpy(hit_t + row_off, m_h_t, pixels * 4);
+        }
+        else
+        {
+            // interleaved sharding: only the 8-row blocks this call owns reach the caller's frame
+            size_t const W = params->width;
+            for (uint32_t y = params->y0; y < params->y1; y++)
+            {
+                if ((y / 8u) % stride != params->row_block_phase) continue;
+                size_t const src = static_cast<size_t>(y - params->y0) * W;
+                size_t const dst = static_cast<size_t>(y - params->buf_y0) * W;
+                if (rgb) std::memcpy(rgb + dst * 3, static_cast<float*>(m_h_rgb) + src * 3, W * 12);
+                if (hit_id) std::memcpy(hit_id + dst, static_cast<int32_t*>(m_h_id) + src, W * 4);
+                if (hit_t) std::memcpy(hit_t + dst, static_cast<float*>(m_h_t) + src, W * 4);
+            }
+        }
         if (stats) return GetStats(stats);
         return ML_OK;
     }

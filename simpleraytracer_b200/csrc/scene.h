@@ -129,6 +129,12 @@ struct RenderLaunch
     int32_t* d_hit_id;
     float* d_hit_t;
     unsigned long long* d_counters;
+    // Rows this launch owns: 8-row blocks k = 0..n_row_blocks-1 start at frame
+    // row  row_origin + k * row_block_step  (step 8: the whole band; step 8*N:
+    // every N-th block, interleaved multi-GPU sharding).  Rows >= y1 are clipped.
+    uint32_t row_origin;
+    uint32_t row_block_step;
+    uint32_t n_row_blocks;
 };
 void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream);
 double MeasureFp32Peak(DeviceState const& device, int repeats);

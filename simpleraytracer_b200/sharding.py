@@ -23,6 +23,23 @@ def row_bands(height: int, world_size: int, align: int = 8):
     return bands
 
 
+def interleaved_rows(height: int, world_size: int, rank: int, block: int = 8):
+    """Rows rank `rank` owns under interleaved sharding (srt_render_params.row_block_stride =
+    world_size, row_block_phase = rank): 8-row blocks b = y // 8 with b % world_size == rank.
+    Interleaving balances load when the cost per row varies over the frame (sky vs. geometry)."""
+    return [y for y in range(height) if (y // block) % world_size == rank]
+
+
+def reduce_interleaved(frame, rank, dst=0, group=None):
+    """Fallback exchange for interleaved sharding when peer (IPC) writes are unavailable:
+    every rank's frame holds its own rows and exact zeros elsewhere, so a sum-reduce onto
+    `dst` assembles the frame bit-exactly (x + 0 == x)."""
+    import torch.distributed as dist
+
+    dist.reduce(frame, dst=dst, op=dist.ReduceOp.SUM, group=group)
+    return frame
+
+
 def gather_bands(frame, bands, rank, dst=0, group=None):
     """Gathers every rank's band of `frame` (a [H, W, C] torch tensor whose rows
     [y0,y1) hold this rank's pixels) into rank `dst`'s frame, in place.

@@ -39,6 +39,41 @@ def test_row_bands_cover_the_frame(height, world):
     assert max(sizes) - min(sizes) <= 8 or height < world * 8
 
 
+@pytest.mark.parametrize("height,world", [(1080, 2), (1080, 8), (2160, 4), (13, 3), (8, 2)])
+def test_interleaved_rows_partition_the_frame(height, world):
+    owned = [sharding.interleaved_rows(height, world, r) for r in range(world)]
+    assert sorted(y for rows in owned for y in rows) == list(range(height))
+    for r, rows in enumerate(owned):
+        assert all((y // 8) % world == r for y in rows)
+    if height >= world * 64:
+        sizes = [len(rows) for rows in owned]
+        assert max(sizes) - min(sizes) <= 8
+
+
+def _reduce_worker(rank, world, port, height, out):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        frame = torch.zeros(height, 4, 3)
+        rows = sharding.interleaved_rows(height, world, rank)
+        frame[rows] = torch.tensor(rows, dtype=torch.float32)[:, None, None] + 0.5
+        sharding.reduce_interleaved(frame, rank)
+        if rank == 0:
+            torch.save(frame, out)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_reduce_interleaved_world_size_2_gloo(tmp_path):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "frame.pt")
+    mp.spawn(_reduce_worker, args=(2, _free_port(), 43, out), nprocs=2, join=True)
+    frame = torch.load(out)
+    want = (torch.arange(43, dtype=torch.float32) + 0.5)[:, None, None].expand(43, 4, 3)
+    assert torch.equal(frame, want)
+
+
 def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close()
     return p

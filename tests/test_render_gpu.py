@@ -132,6 +132,42 @@ def test_row_bands_compose_the_full_frame(ctx):
     scene.release()
 
 
+@pytest.mark.parametrize("accel", [api.SRT_ACCEL_BRUTE, api.SRT_ACCEL_BVH])
+def test_interleaved_row_blocks_compose_the_full_frame(ctx, accel):
+    """Interleaved multi-GPU sharding (row_block_stride/phase): N launches that each own every
+    N-th 8-row block write disjoint rows of ONE device frame and together equal the full render."""
+    import torch
+    from simpleraytracer_b200.sharding import interleaved_rows
+    W, H, N = 150, 77, 3            # ragged: 77 rows = 9 full blocks + 5 rows
+    v, a, cam, light = api.gen_mesh(4, 5000, W, H)
+    scene = ctx.create_scene(v, a)
+    common = dict(spp=2, jitter=1, seed=1, shade=api.SRT_SHADE_SHADOW, accel=accel)
+    full = scene.render(cam, light, api.make_params(W, H, **common))
+    frame = torch.full((H, W, 3), -7.0, device="cuda")
+    stream = torch.cuda.current_stream()
+    torch.cuda.synchronize()
+    rays = 0
+    for r in range(N):
+        p = api.make_params(W, H, row_block_stride=N, row_block_phase=r, **common)
+        scene.render_device(cam, light, p, frame.data_ptr(), 0, 0, 0)
+        rays += scene.stats().primary_rays
+        rows = interleaved_rows(H, N, r)
+        got = frame.cpu().numpy()
+        assert np.array_equal(got[rows], full[0][rows])
+    assert rays == W * H * 2
+    assert np.array_equal(frame.cpu().numpy(), full[0])
+    # host-buffer entry point: only the owned rows are written
+    host = scene.render(cam, light, api.make_params(W, H, row_block_stride=N, row_block_phase=1, **common))
+    rows = interleaved_rows(H, N, 1)
+    other = [y for y in range(H) if y not in set(rows)]
+    assert np.array_equal(host[0][rows], full[0][rows]) and np.array_equal(host[1][rows], full[1][rows])
+    assert (host[0][other] == 0).all() and (host[1][other] == -2).all()
+    p = api.make_params(W, H, y0=4, row_block_stride=2, row_block_phase=0, **common)
+    with pytest.raises(api.MLError, match="interleaved"):
+        scene.render(cam, light, p)
+    scene.release()
+
+
 def test_degenerate_cases_on_gpu(ctx):
     """Tie-breaks and rejections of the golden single-ray cases, through a 1x1 render."""
     g = np.load(GOLD / "degenerate.npz")
