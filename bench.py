@@ -184,7 +184,7 @@ def run_b200_arm(args):
 
     v, a, cam, light, params = scene_arrays(args)
     W, H = params.width, params.height
-    ctx = api.Context()
+    ctx = api.Context(device=local_rank)
     scene = ctx.create_scene(v, a, build_bvh=True)
     info = scene.info()
 

@@ -28,6 +28,13 @@ ML_API_ENTRY ml_status mlxInspectModel(char const* model_path, char const* input
  * Lets an external producer/consumer (e.g. a torch tensor) share the buffer. */
 ML_API_ENTRY void* mlxImageDevicePointer(ml_image image, int for_write, void* stream);
 
+/* mlCreateContext() on an explicit CUDA device ordinal (the reference API has
+ * no device argument; mlCreateContext uses MLB200_DEVICE or the CUDA runtime's
+ * current device).  One process per GPU passes its LOCAL_RANK here: the
+ * library links its own CUDA runtime, so another runtime's cudaSetDevice (for
+ * example torch's) is not visible to it. */
+ML_API_ENTRY ml_context mlxCreateContextOnDevice(int device);
+
 /* Peer mapping of an image's HBM buffer into another PROCESS of the same node
  * (one process per GPU): the owner exports a 64-byte handle, every other rank
  * opens it and receives a device pointer that its kernels can store to over

@@ -98,6 +98,7 @@ _PROTOTYPES = {
     "mlxInspectModel": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),
     "mlxImageDevicePointer": (C.c_void_p, [C.c_void_p, C.c_int, C.c_void_p]),
     "mlxModelLaunchCount": (C.c_size_t, [C.c_void_p]),
+    "mlxCreateContextOnDevice": (C.c_void_p, [C.c_int]),
     "mlxIpcExportImage": (C.c_int, [C.c_void_p, C.c_void_p]),
     "mlxIpcOpen": (C.c_void_p, [C.c_void_p, C.c_void_p]),
     "mlxIpcClose": (None, [C.c_void_p, C.c_void_p]),
@@ -147,9 +148,12 @@ def _err(fn, handle) -> str:
 
 
 class Context:
-    def __init__(self):
+    def __init__(self, device: int | None = None):
+        """device=None: mlCreateContext() (MLB200_DEVICE, else the library runtime's current device);
+        an int: mlxCreateContextOnDevice(device).  One process per GPU passes LOCAL_RANK: the
+        library links its own CUDA runtime and does not see torch.cuda.set_device()."""
         self.lib = load_library()
-        self.handle = self.lib.mlCreateContext()
+        self.handle = self.lib.mlCreateContext() if device is None else self.lib.mlxCreateContextOnDevice(device)
         if not self.handle:
             raise MLError("mlCreateContext failed (no usable CUDA device?)")
 

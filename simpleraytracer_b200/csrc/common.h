@@ -67,7 +67,7 @@ struct DeviceState
     cudaEvent_t ev_stop = nullptr;
     cudaDeviceProp prop{};
 
-    DeviceState();
+    explicit DeviceState(int requested_device = -1); // -1: MLB200_DEVICE, else current device
     ~DeviceState();
     DeviceState(DeviceState const&) = delete;
     DeviceState& operator=(DeviceState const&) = delete;

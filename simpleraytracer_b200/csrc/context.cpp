@@ -8,10 +8,11 @@
 
 #include "image.h"
 #include "model.h"
+#include "model_runner_ext.h"
 
 namespace ML {
 
-DeviceState::DeviceState()
+DeviceState::DeviceState(int requested_device)
 {
     int count = 0;
     cudaError_t err = cudaGetDeviceCount(&count);
@@ -21,7 +22,13 @@ DeviceState::DeviceState()
                                  + (err != cudaSuccess ? cudaGetErrorString(err) : "device count is 0")
                                  + " (this library has no CPU fallback)");
     }
-    if (char const* env = std::getenv("MLB200_DEVICE"))
+    if (requested_device >= 0)
+    {
+        device = requested_device;
+        if (device >= count)
+            throw std::runtime_error("CUDA device ordinal out of range: " + std::to_string(device));
+    }
+    else if (char const* env = std::getenv("MLB200_DEVICE"))
     {
         device = std::atoi(env);
         if (device < 0 || device >= count)
@@ -47,7 +54,7 @@ DeviceState::~DeviceState()
     if (stream) cudaStreamDestroy(stream);
 }
 
-Context::Context() : m_device(std::make_shared<DeviceState>()) {}
+Context::Context(int device) : m_device(std::make_shared<DeviceState>(device)) {}
 
 ml_image Context::CreateImage(ml_image_info const* info)
 {
@@ -102,6 +109,20 @@ ML_API_ENTRY ml_context mlCreateContext()
     }
     catch (...)
     {
+        return ML_INVALID_HANDLE;
+    }
+}
+
+ML_API_ENTRY ml_context mlxCreateContextOnDevice(int device)
+{
+    try
+    {
+        if (device < 0) throw std::runtime_error("negative device ordinal");
+        return ML::Context::MakeHandle(new ML::Context(device));
+    }
+    catch (std::exception const& e)
+    {
+        std::fprintf(stderr, "mlxCreateContextOnDevice: %s\n", e.what());
         return ML_INVALID_HANDLE;
     }
 }

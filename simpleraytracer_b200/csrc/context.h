@@ -9,7 +9,7 @@ namespace ML {
 class Context
 {
 public:
-    Context();
+    explicit Context(int device = -1);
 
     static ml_context MakeHandle(Context* c) { return reinterpret_cast<ml_context>(c); }
     static Context* FromHandle(ml_context c) { return reinterpret_cast<Context*>(c); }
