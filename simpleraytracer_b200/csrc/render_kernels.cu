@@ -638,6 +638,96 @@ __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __g
     flush_counters(L, n_primary, n_shadow, n_box, n_tri);
 }
 
+// Sample-parallel variant for spp >= 32/PIX.  A warp works on PIX pixels at a
+// time and spreads each pixel's samples over SPL = 32/PIX lanes, so the lanes
+// of a warp trace rays through (nearly) the same pixel: they walk the same BVH
+// path and diverge far less than 32 different pixels do, and a block is a
+// 1/32-th the work of the pixel-per-thread kernel (short tail).  Radiance is
+// still summed in sample order: each pass parks the SPL sample values of a
+// pixel in shared memory and ONE lane per (pixel, channel) adds them
+// sequentially onto its running sum, so the result is bit-identical to the
+// pixel-per-thread kernel and the oracle (docs/RENDER_SPEC.md section 5).
+constexpr int kSppTileW = 8; // block = 8 warps; warp w owns row w of an 8x8 pixel tile
+
+template <bool STATS, int PIX>
+__global__ void __launch_bounds__(256, 4) render_bvh_spp_kernel(const __grid_constant__ RenderLaunch L)
+{
+    constexpr uint32_t SPL = 32u / PIX; // sample lanes per pixel
+    static_assert(SPL >= 3, "one lane per (pixel, channel) does the ordered sum");
+    __shared__ float s_val[8][32][3];
+
+    uint32_t const W = L.params.width;
+    uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t const p = lane / SPL, sl = lane % SPL;
+    uint32_t const y = L.row_origin + blockIdx.y * L.row_block_step + warp;
+    uint32_t const spp = L.params.spp;
+    V3 const o = v3(L.camera.origin);
+    V3 const bg = v3(L.params.background);
+
+    unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
+    if (y < L.params.y1) // warp-uniform
+    {
+        for (uint32_t g = 0; g < kSppTileW / PIX; g++)
+        {
+            uint32_t const x = blockIdx.x * kSppTileW + g * PIX + p;
+            bool const in_frame = x < W;
+            float sum = 0.f; // running sum of channel `sl` of pixel p (lanes with sl < 3)
+            Hit first_hit = no_hit();
+            for (uint32_t s0 = 0; s0 < spp; s0 += SPL)
+            {
+                uint32_t const s = s0 + sl;
+                V3 rgb = V3{0.f, 0.f, 0.f};
+                if (in_frame && s < spp)
+                {
+                    V3 d = primary_dir(L, x, y, s);
+                    Hit best = no_hit();
+                    bool occ = false;
+                    n_primary++;
+                    bvh_trace<false, STATS>(L.scene, o, d, L.params.t_min, best, occ, n_box, n_tri);
+                    if (s == 0) first_hit = best;
+                    if (best.id < 0)
+                    {
+                        rgb = bg;
+                    }
+                    else
+                    {
+                        ShadeOut sh = shade_hit(L, o, d, best);
+                        rgb = sh.rgb;
+                        if (sh.need_shadow)
+                        {
+                            n_shadow++;
+                            Hit dummy = no_hit();
+                            bvh_trace<true, STATS>(L.scene, sh.so, sh.sd, 0.0f, dummy, occ, n_box, n_tri);
+                            if (occ) rgb = V3{0.f, 0.f, 0.f};
+                        }
+                    }
+                }
+                s_val[warp][lane][0] = rgb.x;
+                s_val[warp][lane][1] = rgb.y;
+                s_val[warp][lane][2] = rgb.z;
+                __syncwarp();
+                if (sl < 3)
+                {
+                    uint32_t const n = min(SPL, spp - s0);
+                    for (uint32_t j = 0; j < n; j++) sum = add(sum, s_val[warp][p * SPL + j][sl]);
+                }
+                __syncwarp();
+            }
+            if (in_frame)
+            {
+                size_t const out = static_cast<size_t>(y * W + x) - static_cast<size_t>(L.params.buf_y0) * W;
+                if (sl < 3 && L.d_rgb) L.d_rgb[out * 3 + sl] = mul(sum, L.inv_spp);
+                if (sl == 0) // this lane traced sample 0
+                {
+                    if (L.d_hit_id) L.d_hit_id[out] = first_hit.id;
+                    if (L.d_hit_t) L.d_hit_t[out] = first_hit.t;
+                }
+            }
+        }
+    }
+    flush_counters(L, n_primary, n_shadow, n_box, n_tri);
+}
+
 // ---------------------------------------------------------------------------
 // FP32 peak microbenchmark: 8 independent FFMA chains per thread.
 // ---------------------------------------------------------------------------
@@ -681,7 +771,30 @@ void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
             char const* e = std::getenv("SRT_BVH_MINB");
             return e ? std::atoi(e) : 4;
         }();
-        if (p.collect_stats)
+        // Sample-parallel kernel when there are enough samples per pixel to fill the
+        // lanes; SRT_BVH_PIX=1|2|4|8 pixels per warp pass (0 = pixel-per-thread kernel).
+        static int const pix_env = [] {
+            char const* e = std::getenv("SRT_BVH_PIX");
+            return e ? std::atoi(e) : -1;
+        }();
+        int pix = pix_env >= 0 ? pix_env : (p.spp >= 32 ? 1 : p.spp >= 16 ? 2 : p.spp >= 8 ? 4 : 0);
+        if (pix != 0 && pix != 1 && pix != 2 && pix != 4 && pix != 8) pix = 0;
+        if (pix != 0)
+        {
+            dim3 sgrid((p.width + kSppTileW - 1) / kSppTileW, launch.n_row_blocks);
+            bool const st = p.collect_stats != 0;
+#define SRT_SPP_LAUNCH(PIX)                                                                   \
+    do {                                                                                      \
+        if (st) render_bvh_spp_kernel<true, PIX><<<sgrid, 256, 0, stream>>>(launch);          \
+        else render_bvh_spp_kernel<false, PIX><<<sgrid, 256, 0, stream>>>(launch);            \
+    } while (0)
+            if (pix == 1) SRT_SPP_LAUNCH(1);
+            else if (pix == 2) SRT_SPP_LAUNCH(2);
+            else if (pix == 4) SRT_SPP_LAUNCH(4);
+            else SRT_SPP_LAUNCH(8);
+#undef SRT_SPP_LAUNCH
+        }
+        else if (p.collect_stats)
             render_bvh_kernel<true, 4><<<grid, kBvhThreads, 0, stream>>>(launch);
         else if (minb == 6)
             render_bvh_kernel<false, 6><<<grid, kBvhThreads, 0, stream>>>(launch);
