@@ -47,6 +47,18 @@ ML_API_ENTRY ml_status mlxIpcExportImage(ml_image image, void* handle_out);
 ML_API_ENTRY void* mlxIpcOpen(ml_context context, void const* handle);
 ML_API_ENTRY void mlxIpcClose(ml_context context, void* device_pointer);
 
+/* Arithmetic of the model's wide 3x3 convolution layers.  MLX_PRECISION_FP32 (default, or
+ * MLB200_PRECISION unset): fp32 on the CUDA cores.  MLX_PRECISION_BF16 (or
+ * MLB200_PRECISION=bf16 at mlCreateModel): bf16 operands, fp32 accumulation on the tensor
+ * cores (tcgen05 + TMEM) for every 3x3 / stride 1 / SAME layer with 16, 32 or 64k input
+ * channels; activations between such layers are stored as bf16.  Image I/O stays
+ * ML_FLOAT32 / ML_FLOAT16 as declared by the graph.  May be called before or after
+ * mlSetModelInputInfo.  mlxModelTensorCoreLayers reports how many layers use that path. */
+#define MLX_PRECISION_FP32 0
+#define MLX_PRECISION_BF16 1
+ML_API_ENTRY ml_status mlxSetModelPrecision(ml_model model, int precision);
+ML_API_ENTRY size_t mlxModelTensorCoreLayers(ml_model model);
+
 /* Number of kernel launches one mlInfer() of this model enqueues. */
 ML_API_ENTRY size_t mlxModelLaunchCount(ml_model model);
 

@@ -15,6 +15,7 @@ import numpy as np
 _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libModelRunner.so"
 
 ML_OK, ML_FAIL = 0, 1
+MLX_PRECISION_FP32, MLX_PRECISION_BF16 = 0, 1
 ML_FLOAT32, ML_FLOAT16 = 0, 1
 SRT_SHADE_ALBEDO, SRT_SHADE_LAMBERT, SRT_SHADE_SHADOW = 0, 1, 2
 SRT_ACCEL_BRUTE, SRT_ACCEL_BVH = 0, 1
@@ -98,6 +99,8 @@ _PROTOTYPES = {
     "mlxInspectModel": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),
     "mlxImageDevicePointer": (C.c_void_p, [C.c_void_p, C.c_int, C.c_void_p]),
     "mlxModelLaunchCount": (C.c_size_t, [C.c_void_p]),
+    "mlxSetModelPrecision": (C.c_int, [C.c_void_p, C.c_int]),
+    "mlxModelTensorCoreLayers": (C.c_size_t, [C.c_void_p]),
     "mlxCreateContextOnDevice": (C.c_void_p, [C.c_int]),
     "mlxIpcExportImage": (C.c_int, [C.c_void_p, C.c_void_p]),
     "mlxIpcOpen": (C.c_void_p, [C.c_void_p, C.c_void_p]),
@@ -287,6 +290,14 @@ class Model:
 
     def launch_count(self) -> int:
         return int(self.lib.mlxModelLaunchCount(self.handle))
+
+    def set_precision(self, precision: int):
+        """mlxSetModelPrecision: MLX_PRECISION_FP32 (0) or MLX_PRECISION_BF16 (1, tcgen05 layers)."""
+        if self.lib.mlxSetModelPrecision(self.handle, int(precision)) != ML_OK:
+            raise MLError(self.error())
+
+    def tensor_core_layers(self) -> int:
+        return int(self.lib.mlxModelTensorCoreLayers(self.handle))
 
     def infer(self, inp: Image, out: Image):
         if self.lib.mlInfer(self.handle, inp.handle, out.handle) != ML_OK:

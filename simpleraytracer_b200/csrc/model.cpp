@@ -101,6 +101,8 @@ Model::Model(DeviceStatePtr device, ml_model_params const* params) : m_device(st
 
     BuildPlan(graph, input_idx, output_idx);
     FusePlan();
+    if (char const* e = std::getenv("MLB200_PRECISION"))
+        m_precision = (std::string(e) == "bf16" || std::string(e) == "BF16") ? 1 : 0;
 
     // Upload constants once; they stay resident in HBM for the model's life.
     // (m_device == nullptr: host-only inspection, mlxInspectModel.)
@@ -157,6 +159,7 @@ Model::~Model()
     cudaSetDevice(m_device->device);
     cudaStreamSynchronize(m_device->stream);
     ReleaseBuffers();
+    for (void* p : m_packed) cudaFree(p);
     for (auto& c : m_consts) cudaFree(c.dev);
 }
 
@@ -518,10 +521,96 @@ void Model::InferShapes(size_t H, size_t W, size_t C)
                 break;
         }
     }
+    AssignPrecision();
+}
+
+// Decides which Conv ops run on the tensor cores and which tensors are stored as
+// bf16.  A tensor is bf16 iff a Conv produces it, every reader is a tensor-core
+// Conv and it is not the model's input/output; a Conv runs on the tensor cores
+// iff its shape is supported and its input tensor is bf16.  Fixpoint because
+// the two conditions feed each other.  The first layer of a chain (fp32 input,
+// e.g. 3 channels) stays on CUDA cores and writes bf16 directly.
+void Model::AssignPrecision()
+{
+    for (auto& t : m_tensors) t.bf16 = false;
+    std::vector<char> tc(m_ops.size(), 0);
+    auto plain3x3 = [](Op const& op) {
+        return op.KH == 3 && op.KW == 3 && op.stride == 1 && op.dilation == 1;
+    };
+    for (size_t i = 0; i < m_ops.size(); i++)
+    {
+        Op& op = m_ops[i];
+        op.tc = false;
+        if (m_precision != 1 || op.kind != OpKind::Conv) continue;
+        tc[i] = nn::ConvTcSupported(op.KH, op.KW, op.stride, op.dilation, op.same_padding,
+                                    m_tensors[op.in[0]].C, m_tensors[op.out].C);
+    }
+    bool changed = m_precision == 1;
+    std::vector<char> bf(m_tensors.size(), 0);
+    while (changed)
+    {
+        changed = false;
+        std::fill(bf.begin(), bf.end(), 0);
+        for (size_t i = 0; i < m_ops.size(); i++)
+        {
+            Op const& op = m_ops[i];
+            if (op.kind != OpKind::Conv || !(tc[i] || plain3x3(op))) continue;
+            if (op.out == m_output_tensor || op.out == m_input_tensor) continue;
+            if (m_tensors[op.out].C % 16 != 0) continue;
+            bool all_tc = false;
+            for (size_t j = 0; j < m_ops.size(); j++)
+                for (int t : m_ops[j].in)
+                    if (t == op.out) { all_tc = true; }
+            for (size_t j = 0; j < m_ops.size() && all_tc; j++)
+                for (int t : m_ops[j].in)
+                    if (t == op.out && !tc[j]) all_tc = false;
+            bf[op.out] = all_tc;
+        }
+        for (size_t i = 0; i < m_ops.size(); i++)
+            if (tc[i] && !bf[m_ops[i].in[0]]) { tc[i] = 0; changed = true; }
+    }
+    for (size_t i = 0; i < m_ops.size(); i++) m_ops[i].tc = tc[i] != 0;
+    for (size_t t = 0; t < m_tensors.size(); t++) m_tensors[t].bf16 = bf[t] != 0;
+}
+
+size_t Model::TensorCoreLayers() const
+{
+    size_t n = 0;
+    for (auto const& op : m_ops) n += op.tc ? 1 : 0;
+    return n;
+}
+
+ml_status Model::SetPrecision(int precision)
+{
+    m_error.clear();
+    if (precision != 0 && precision != 1)
+    {
+        m_error = "Unsupported precision: " + std::to_string(precision);
+        return ML_FAIL;
+    }
+    if (precision == m_precision) return ML_OK;
+    m_precision = precision;
+    try
+    {
+        AssignPrecision();
+        if (m_ready) AllocateBuffers();
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        m_ready = false;
+        m_error = std::string("Inference error: ") + e.what();
+        return ML_FAIL;
+    }
 }
 
 void Model::ReleaseBuffers()
 {
+    for (Op& op : m_ops)
+    {
+        nn::ConvTcDestroy(op.tc_op);
+        op.tc_op = nullptr;
+    }
     for (void* p : m_buffers) cudaFree(p);
     m_buffers.clear();
     m_buffer_bytes.clear();
@@ -544,7 +633,7 @@ void Model::AllocateBuffers()
         if (op.out != m_output_tensor)
         {
             TensorInfo& o = m_tensors[op.out];
-            size_t need = static_cast<size_t>(o.H) * o.W * o.C * sizeof(float);
+            size_t need = static_cast<size_t>(o.H) * o.W * o.C * (o.bf16 ? 2 : sizeof(float));
             int best = -1;
             for (size_t k = 0; k < free_list.size(); k++)
             {
@@ -572,6 +661,24 @@ void Model::AllocateBuffers()
                 bool dup = std::find(free_list.begin(), free_list.end(), m_tensors[t].buffer) != free_list.end();
                 if (!dup) free_list.push_back(m_tensors[t].buffer);
             }
+    }
+    // Tensor-core layers: repack the filter once, bind the TMA tensor maps to the (now fixed) buffers.
+    for (Op& op : m_ops)
+    {
+        if (!op.tc) continue;
+        TensorInfo const& a = m_tensors[op.in[0]];
+        TensorInfo const& o = m_tensors[op.out];
+        if (op.packed < 0)
+        {
+            std::vector<uint16_t> packed = nn::ConvTcPackWeights(m_consts[op.weights].host.data(), a.C, o.C);
+            void* d = nullptr;
+            ML_CUDA_CHECK(cudaMalloc(&d, packed.size() * 2));
+            m_packed.push_back(d);
+            op.packed = static_cast<int>(m_packed.size()) - 1;
+            ML_CUDA_CHECK(cudaMemcpy(d, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
+        }
+        op.tc_op = nn::ConvTcCreate(m_buffers[a.buffer], m_packed[op.packed], a.H, a.W, a.C, o.C, o.bf16,
+                                    op.act, op.alpha, m_device->prop.multiProcessorCount);
     }
     if (m_input_info.dtype == ML_FLOAT16)
     {
@@ -605,6 +712,8 @@ std::string Model::Describe() const
             os << " k=" << op.KH << "x" << op.KW << " stride=" << op.stride << " dilation=" << op.dilation
                << " padding=" << (op.same_padding ? "SAME" : "VALID") << " wsum=" << sum;
         }
+        if (op.tc) os << " engine=tcgen05_bf16";
+        if (m_tensors[op.out].bf16) os << " out=bf16";
         os << " bias=" << (op.bias >= 0 ? "yes" : "no") << " act=" << acts[static_cast<int>(op.act)];
         if (op.act == nn::Act::LeakyRelu) os << " alpha=" << op.alpha;
         os << "\n";
@@ -700,7 +809,7 @@ void Model::Run(float const* d_in, float* d_out, cudaStream_t stream)
     auto ptr = [&](int t) -> float* {
         if (t == m_input_tensor) return const_cast<float*>(d_in);
         if (t == m_output_tensor) return d_out;
-        return static_cast<float*>(m_buffers[m_tensors[t].buffer]);
+        return static_cast<float*>(m_buffers[m_tensors[t].buffer]); // bf16 tensors: same storage, 2-byte elements
     };
     for (Op const& op : m_ops)
     {
@@ -727,8 +836,13 @@ void Model::Run(float const* d_in, float* d_out, cudaStream_t stream)
                 }
                 d.act = op.act;
                 d.alpha = op.alpha;
-                nn::Conv2dFp32(ptr(op.in[0]), m_consts[op.weights].dev,
-                               op.bias >= 0 ? m_consts[op.bias].dev : nullptr, ptr(op.out), d, stream);
+                float const* bias = op.bias >= 0 ? m_consts[op.bias].dev : nullptr;
+                if (op.tc)
+                    nn::ConvTcRun(op.tc_op, bias, ptr(op.out), stream);
+                else if (o.bf16)
+                    nn::Conv2dFp32ToBf16(ptr(op.in[0]), m_consts[op.weights].dev, bias, ptr(op.out), d, stream);
+                else
+                    nn::Conv2dFp32(ptr(op.in[0]), m_consts[op.weights].dev, bias, ptr(op.out), d, stream);
                 break;
             }
             case OpKind::BiasAct:
@@ -913,6 +1027,20 @@ ML_API_ENTRY ml_status mlxInspectModel(char const* model_path, char const* input
         ML::FillBuffer(buffer, buffer_size, e.what());
         return ML_FAIL;
     }
+}
+
+ML_API_ENTRY ml_status mlxSetModelPrecision(ml_model model, int precision)
+{
+    ML::Model* m = ML::Model::FromHandle(model);
+    if (m == nullptr) return ML_FAIL;
+    try { return m->SetPrecision(precision); }
+    catch (...) { return ML_FAIL; }
+}
+
+ML_API_ENTRY size_t mlxModelTensorCoreLayers(ml_model model)
+{
+    ML::Model* m = ML::Model::FromHandle(model);
+    return m != nullptr ? m->TensorCoreLayers() : 0;
 }
 
 ML_API_ENTRY size_t mlxModelLaunchCount(ml_model model)

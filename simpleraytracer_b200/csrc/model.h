@@ -29,6 +29,13 @@ public:
     ml_status Infer(ml_image input, ml_image output);
     char* GetError(char* buffer, size_t buffer_size) const;
 
+    // Arithmetic of the wide 3x3 layers: 0 = fp32 on CUDA cores (default), 1 = bf16 on the
+    // tensor cores (tcgen05, fp32 accumulation) wherever conv_tc_kernels.cu supports the layer.
+    // Initial value from MLB200_PRECISION=bf16; mlxSetModelPrecision changes it later.
+    ml_status SetPrecision(int precision);
+    int Precision() const { return m_precision; }
+    size_t TensorCoreLayers() const;
+
     // Number of kernel launches one Infer() enqueues (bench bookkeeping).
     size_t LaunchesPerInfer() const;
     // Text dump of the detected nodes, shapes and fused plan (mlxInspectModel).
@@ -44,6 +51,7 @@ private:
         int H = 0, W = 0;      // set by shape inference
         int buffer = -1;       // index into m_buffers; -1 = external (input / output image)
         int last_use = -1;     // index of the last op reading it
+        bool bf16 = false;     // stored as bf16 NHWC (between tensor-core layers); else fp32
     };
 
     struct Op
@@ -59,6 +67,10 @@ private:
         nn::Act act = nn::Act::None;
         float alpha = 0.2f;
         std::string name;      // for error messages
+        // bf16 tensor-core execution (decided by AssignPrecision, bound by AllocateBuffers)
+        bool tc = false;
+        int packed = -1;       // index into m_packed (filter repacked [tap][co][ci] bf16)
+        nn::ConvTc* tc_op = nullptr;
     };
 
     struct DeviceConst
@@ -79,11 +91,13 @@ private:
                    std::vector<char>& state, int input_idx);
     void FusePlan();
     void InferShapes(size_t H, size_t W, size_t C); // throws on mismatch
+    void AssignPrecision();
     void AllocateBuffers();
     void ReleaseBuffers();
     int AddConst(std::vector<float> values);
     int NewTensor(int channels);
     void Run(float const* d_in, float* d_out, cudaStream_t stream);
+    nn::ConvDesc MakeConvDesc(Op const& op) const;
 
     DeviceStatePtr m_device;
     std::string m_input_node;
@@ -100,6 +114,8 @@ private:
     int m_input_tensor = -1;
     int m_output_tensor = -1;
 
+    int m_precision = 0;
+    std::vector<void*> m_packed;  // device copies of repacked bf16 filters
     std::vector<void*> m_buffers;
     std::vector<size_t> m_buffer_bytes;
     float* m_in_f32 = nullptr;   // staging when images are FLOAT16

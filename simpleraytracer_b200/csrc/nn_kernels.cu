@@ -13,6 +13,7 @@
 
 #include "common.h"
 
+#include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
 namespace ML {
@@ -32,10 +33,10 @@ __device__ __forceinline__ float apply_act(float v, Act act, float alpha)
     }
 }
 
-template <int KS, int TH, int TW, int PXT, int CG, int CI_T>
+template <int KS, int TH, int TW, int PXT, int CG, int CI_T, typename OutT>
 __global__ void __launch_bounds__(256)
 conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
-                   float const* __restrict__ bias, float* __restrict__ out, ConvDesc d)
+                   float const* __restrict__ bias, OutT* __restrict__ out, ConvDesc d)
 {
     constexpr int IH = TH + KS - 1, IW = TW + KS - 1;
     constexpr int CO_T = 4 * CG;
@@ -120,21 +121,30 @@ conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
     {
         int ox = tx0 + col0 + i;
         if (ox >= d.OW) continue;
-        float* o = out + (static_cast<size_t>(oy) * d.OW + ox) * d.Cout + co;
+        OutT* o = out + (static_cast<size_t>(oy) * d.OW + ox) * d.Cout + co;
         float r0 = apply_act(acc[i][0] + b[0], d.act, d.alpha);
         float r1 = apply_act(acc[i][1] + b[1], d.act, d.alpha);
         float r2 = apply_act(acc[i][2] + b[2], d.act, d.alpha);
         float r3 = apply_act(acc[i][3] + b[3], d.act, d.alpha);
         if (vec)
         {
-            *reinterpret_cast<float4*>(o) = make_float4(r0, r1, r2, r3);
+            if constexpr (sizeof(OutT) == 4)
+            {
+                *reinterpret_cast<float4*>(o) = make_float4(r0, r1, r2, r3);
+            }
+            else
+            {
+                __nv_bfloat162 lo = __floats2bfloat162_rn(r0, r1), hi = __floats2bfloat162_rn(r2, r3);
+                *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<uint32_t*>(&lo),
+                                                          *reinterpret_cast<uint32_t*>(&hi));
+            }
         }
         else
         {
-            if (co + 0 < d.Cout) o[0] = r0;
-            if (co + 1 < d.Cout) o[1] = r1;
-            if (co + 2 < d.Cout) o[2] = r2;
-            if (co + 3 < d.Cout) o[3] = r3;
+            if (co + 0 < d.Cout) o[0] = static_cast<OutT>(r0);
+            if (co + 1 < d.Cout) o[1] = static_cast<OutT>(r1);
+            if (co + 2 < d.Cout) o[2] = static_cast<OutT>(r2);
+            if (co + 3 < d.Cout) o[3] = static_cast<OutT>(r3);
         }
     }
 }
@@ -166,16 +176,16 @@ __global__ void conv2d_naive_kernel(float const* __restrict__ in, float const* _
     out[idx] = apply_act(acc, d.act, d.alpha);
 }
 
-template <int KS, int TH, int TW, int PXT, int CG, int CI_T>
-void LaunchTile(float const* in, float const* w, float const* bias, float* out, ConvDesc const& d,
+template <int KS, int TH, int TW, int PXT, int CG, int CI_T, typename OutT>
+void LaunchTile(float const* in, float const* w, float const* bias, OutT* out, ConvDesc const& d,
                 cudaStream_t stream)
 {
     dim3 grid((d.OW + TW - 1) / TW, (d.OH + TH - 1) / TH, (d.Cout + 4 * CG - 1) / (4 * CG));
-    conv2d_tile_kernel<KS, TH, TW, PXT, CG, CI_T><<<grid, 256, 0, stream>>>(in, w, bias, out, d);
+    conv2d_tile_kernel<KS, TH, TW, PXT, CG, CI_T, OutT><<<grid, 256, 0, stream>>>(in, w, bias, out, d);
 }
 
-template <int KS, int CI_T>
-void LaunchTileForCout(float const* in, float const* w, float const* bias, float* out,
+template <int KS, int CI_T, typename OutT>
+void LaunchTileForCout(float const* in, float const* w, float const* bias, OutT* out,
                        ConvDesc const& d, cudaStream_t stream)
 {
     if (d.Cout <= 4) LaunchTile<KS, 16, 16, 1, 1, CI_T>(in, w, bias, out, d, stream);
@@ -259,6 +269,16 @@ void Conv2dFp32(float const* in, float const* w, float const* bias, float* out, 
         unsigned const blocks = static_cast<unsigned>((total + 255) / 256);
         conv2d_naive_kernel<<<blocks, 256, 0, stream>>>(in, w, bias, out, d);
     }
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void Conv2dFp32ToBf16(float const* in, float const* w, float const* bias, void* out_bf16,
+                      ConvDesc const& d, cudaStream_t stream)
+{
+    // only the 3x3 stride-1 shape the tensor-core chain starts with
+    if (!(d.stride == 1 && d.dilation == 1 && d.KH == 3 && d.KW == 3))
+        throw std::runtime_error("Conv2dFp32ToBf16: only 3x3 stride 1");
+    LaunchTileForCout<3, 8>(in, w, bias, static_cast<__nv_bfloat16*>(out_bf16), d, stream);
     ML_CUDA_CHECK(cudaGetLastError());
 }
 

@@ -8,6 +8,7 @@
 
 #include <cstddef>
 #include <cstdint>
+#include <vector>
 
 namespace ML {
 namespace nn {
@@ -41,6 +42,21 @@ void AddAct(float const* a, float const* b, float* out, size_t n, Act act, float
 void ConcatChannels(float const* in, float* out, size_t pixels, int C, int Ctotal, int c0,
                     cudaStream_t stream);
 void HalfToFloat(void const* in, float* out, size_t n, cudaStream_t stream);
+// fp32 direct convolution writing bf16 NHWC (feeds the tensor-core layers).
+void Conv2dFp32ToBf16(float const* in, float const* w, float const* bias, void* out_bf16,
+                      ConvDesc const& d, cudaStream_t stream);
+
+// ---- bf16 tensor-core path (conv_tc_kernels.cu): 3x3, stride 1, SAME, tcgen05 + TMEM + TMA.
+// Activations bf16 NHWC, filter repacked [tap][Cout padded to 16][Cin] bf16, fp32 accumulation.
+struct ConvTc; // one planned layer: tensor maps bound to fixed device buffers
+bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding, int Cin, int Cout);
+int ConvTcPaddedCout(int Cout);
+std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout);
+// out_bf16: bf16 NHWC output (Cout % 16 == 0) for the next tensor-core layer; else fp32 NHWC.
+ConvTc* ConvTcCreate(void const* d_in_bf16, void const* d_w_packed, int H, int W, int Cin, int Cout,
+                     bool out_bf16, Act act, float alpha, int sm_count);
+void ConvTcRun(ConvTc const* op, float const* bias, void* out, cudaStream_t stream);
+void ConvTcDestroy(ConvTc* op);
 void FloatToHalf(float const* in, void* out, size_t n, cudaStream_t stream);
 
 } // namespace nn

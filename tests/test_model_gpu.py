@@ -340,3 +340,63 @@ def test_config1_reference_test_app_end_to_end(tmp_path):
     r = subprocess.run([str(exe), "-m", str(model), "-w", "128", "-h", "256", "-i", str(tmp_path / "in.bin")],
                        capture_output=True, text=True, timeout=300)
     assert r.returncode == 255 and "Bad input size" in r.stderr
+
+
+# --------------------------------------------------------------------------- bf16 tensor-core path
+BF16_VS_EMULATION = 4e-3   # of the output range, against an oracle that rounds to bf16 at the same points
+BF16_VS_FP32 = 3e-2        # stated bound of the bf16 path against the pure fp32 oracle (north_star)
+
+
+def _bf16(x):
+    import torch
+    return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).bfloat16().float().numpy()
+
+
+def bf16_emulated_denoiser(x, layers, tc_layers, alpha=0.1):
+    """The conv oracle with operands rounded to bf16 exactly where the CUDA path stores bf16:
+    filters of tensor-core layers, and every activation that feeds a tensor-core layer."""
+    cur = x
+    for k, (w, b, act) in enumerate(layers):
+        wk = _bf16(w) if k in tc_layers else w
+        cur = O.conv2d(cur, wk, b, act=act, alpha=alpha)
+        if k + 1 in tc_layers:
+            cur = _bf16(cur)
+    return x + cur
+
+
+@pytest.mark.parametrize("cfg", [
+    dict(width=64, depth=4, act="Relu", w=300, h=37, tc={1, 2, 3}),        # SW128 rows, ragged last tile
+    dict(width=32, depth=3, act="LeakyRelu", w=128, h=9, tc={1, 2}),       # SW64 rows
+    dict(width=16, depth=3, act="Relu", w=131, h=5, tc={1, 2}),            # SW32 rows
+    dict(width=128, depth=3, act="Relu", w=70, h=20, tc={2}),              # 128->128 too big for smem: fp32; 2 K-chunks
+    dict(width=64, depth=5, act="Relu", w=1000, h=150, tc={1, 2, 3, 4}),   # many tiles per CTA: ring + TMEM phases wrap
+])
+def test_bf16_tensor_core_denoiser(ctx, tmp_path, cfg):
+    path = tmp_path / "d.pb"
+    _, layers = gw.make_denoiser(path, channels=3, width=cfg["width"], depth=cfg["depth"], seed=11, act=cfg["act"])
+    w, h = cfg["w"], cfg["h"]
+    model, i, o = prepared_model(ctx, path, w, h)
+    x = np.random.default_rng(5).random((h, w, 3), dtype=np.float32)
+    inp = ctx.create_image(w, h, 3); out = ctx.create_image(w, h, 3)
+    inp.write(x)
+    model.infer(inp, out)
+    fp32 = out.read().copy()
+    assert model.tensor_core_layers() == 0
+    model.set_precision(api.MLX_PRECISION_BF16)
+    assert model.tensor_core_layers() == len(cfg["tc"])
+    model.infer(inp, out)
+    got = out.read().copy()
+    ref = O.run_denoiser(x, layers, alpha=0.1)
+    emu = bf16_emulated_denoiser(x, layers, cfg["tc"])
+    scale = float(np.abs(ref).max())
+    err_emu = float(np.abs(got - emu).max()) / scale
+    err_fp32 = float(np.abs(got - ref).max()) / scale
+    assert err_emu <= BF16_VS_EMULATION, f"{cfg}: {err_emu:.3e} vs the bf16-emulating oracle"
+    assert err_fp32 <= BF16_VS_FP32, f"{cfg}: {err_fp32:.3e} vs the fp32 oracle"
+    close(fp32, ref, "fp32 path")
+    # switching back restores the fp32 path bit for bit
+    model.set_precision(api.MLX_PRECISION_FP32)
+    model.infer(inp, out)
+    assert np.array_equal(out.read(), fp32)
+    for obj in (inp, out, model):
+        obj.release()
