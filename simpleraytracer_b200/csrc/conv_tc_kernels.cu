@@ -33,6 +33,7 @@
 #include <cudaTypedefs.h>
 #include <cuda_bf16.h>
 
+#include <cstdlib>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -62,6 +63,13 @@ struct TcParams
     int out_bf16;        // 1: bf16 NHWC with N == Cout channels; 0: fp32 NHWC with Cout channels
     Act act;
     float alpha;
+    int halo;            // 1: a stage is ONE box of 130 pixels (row y+kh-1, x0-1..x0+128) and the three
+                         //    kw taps are row-shifted views of it (KC == 64 only); 0: three 128-pixel boxes
+    int stage_bytes;     // bytes of one A stage (one kh row of one Cin chunk), multiple of 1024
+    int tap_stride;      // bytes from tap kw to tap kw+1 inside a stage: 128 (halo) or 128*KC*2
+    int stage_tx;        // bytes TMA delivers per stage
+    int base_offset_mode; // halo mode: fill the descriptor's base-offset field (MLB200_TC_BASEOFF, default 0: not needed)
+    int debug;           // MLB200_TC_DEBUG bit 0: no TMA loads of A, bit 1: no MMAs (timing experiments only)
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -192,7 +200,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     // 1024-byte alignment: the 128-byte swizzle pattern repeats every 1024 bytes
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~uintptr_t(1023u));
     uint32_t const b_tile_bytes = static_cast<uint32_t>(P.N) * P.KC * 2u;
-    uint32_t const a_stage_bytes = static_cast<uint32_t>(kTileM) * P.KC * 2u;
+    uint32_t const a_stage_bytes = static_cast<uint32_t>(P.stage_bytes);
     uint32_t const n_b_tiles = 9u * P.n_chunks;
     uint8_t* smem_b = smem;
     uint8_t* smem_a = smem + n_b_tiles * b_tile_bytes;
@@ -205,6 +213,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
 
     uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // bias (zero beyond Cout) staged once; the epilogue reads it as broadcast LDS.128
+    __shared__ __align__(16) float s_bias[256];
+    for (int c = threadIdx.x; c < P.N; c += kTcThreads) s_bias[c] = (bias != nullptr && c < P.Cout) ? bias[c] : 0.f;
+    bool const simple_act = P.act == Act::None || P.act == Act::Relu || P.act == Act::LeakyRelu;
+    float const neg_slope = P.act == Act::None ? 1.f : (P.act == Act::LeakyRelu ? P.alpha : 0.f);
 
     if (warp == 0 && lane == 0)
     {
@@ -241,17 +255,26 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
             {
                 int const y = tile / P.tiles_per_row;
                 int const x0 = (tile - y * P.tiles_per_row) * kTileM;
-                for (int tap = 0; tap < 9; tap++)
+                for (int kh = 0; kh < 3; kh++)
                 {
-                    int const kh = tap / 3, kw = tap - kh * 3;
                     for (int ch = 0; ch < P.n_chunks; ch++, it++)
                     {
                         uint32_t const s = it % P.stages, ph = (it / P.stages) & 1u;
                         bar_wait(&empty[s], ph ^ 1u);
-                        bar_expect_tx(&full[s], a_stage_bytes);
+                        if (P.debug & 1) { bar_arrive(&full[s]); continue; }
+                        bar_expect_tx(&full[s], static_cast<uint32_t>(P.stage_tx));
                         // rows/pixels outside the image are zero-filled by TMA = SAME padding
-                        tma_load_3d(smem_a + s * a_stage_bytes, &in_map, ch * P.KC, x0 + kw - 1, y + kh - 1,
-                                    &full[s]);
+                        uint8_t* dst = smem_a + s * a_stage_bytes;
+                        if (P.halo)
+                        {
+                            tma_load_3d(dst, &in_map, ch * P.KC, x0 - 1, y + kh - 1, &full[s]);
+                        }
+                        else
+                        {
+                            for (int kw = 0; kw < 3; kw++)
+                                tma_load_3d(dst + kw * P.tap_stride, &in_map, ch * P.KC, x0 + kw - 1, y + kh - 1,
+                                            &full[s]);
+                        }
                     }
                 }
             }
@@ -276,23 +299,36 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                 tc_fence_after();
                 uint32_t const d_tmem = tmem_base + acc * static_cast<uint32_t>(P.N);
                 uint32_t first = 0;
-                for (uint32_t tap = 0; tap < 9u; tap++)
+                for (uint32_t kh = 0; kh < 3u; kh++)
                 {
                     for (int ch = 0; ch < P.n_chunks; ch++, it++)
                     {
                         uint32_t const s = it % P.stages, ph = (it / P.stages) & 1u;
                         bar_wait(&full[s], ph);
                         tc_fence_after();
-                        uint64_t const a_desc = umma_desc(smem_addr(smem_a + s * a_stage_bytes), P.sbo, P.layout_type);
-                        uint64_t const b_desc = umma_desc(smem_addr(smem_b + (tap * P.n_chunks + ch) * b_tile_bytes),
-                                                          P.sbo, P.layout_type);
-                        for (int k = 0; k < P.KC / 16; k++)
+                        uint32_t const a_base = smem_addr(smem_a + s * a_stage_bytes);
+                        for (uint32_t kw = 0; kw < 3u; kw++)
                         {
-                            // +32 bytes along K inside the swizzle row = +2 in the (addr >> 4) field
-                            tc_mma_bf16(d_tmem, a_desc + 2u * k, b_desc + 2u * k, idesc, first);
-                            first = 1;
+                            // halo mode: tap kw = the same box read from pixel row kw on.  The start is then
+                            // kw * 128 bytes into the 1024-byte swizzle pattern.  Measured on B200: the MMA
+                            // applies the 128B swizzle XOR to the ABSOLUTE shared-memory address bits (as TMA
+                            // does), so a row-shifted start needs NO base offset (bits [49,52) stay 0; setting
+                            // them to (start >> 7) & 7 gives wrong results).  MLB200_TC_BASEOFF=1 re-enables
+                            // the field for that experiment.
+                            uint32_t const a_addr = a_base + kw * static_cast<uint32_t>(P.tap_stride);
+                            uint64_t a_desc = umma_desc(a_addr, P.sbo, P.layout_type);
+                            if (P.halo && P.base_offset_mode) a_desc |= static_cast<uint64_t>((a_addr >> 7) & 7u) << 49;
+                            uint64_t const b_desc =
+                                umma_desc(smem_addr(smem_b + ((kh * 3u + kw) * P.n_chunks + ch) * b_tile_bytes), P.sbo,
+                                          P.layout_type);
+                            for (int k = 0; k < P.KC / 16 && !(P.debug & 2); k++)
+                            {
+                                // +32 bytes along K inside the swizzle row = +2 in the (addr >> 4) field
+                                tc_mma_bf16(d_tmem, a_desc + 2u * k, b_desc + 2u * k, idesc, first);
+                                first = 1;
+                            }
                         }
-                        tc_commit(&empty[s]);       // stage reusable once these MMAs have read it
+                        tc_commit(&empty[s]);       // ONE commit per stage (12 MMAs at Cin = 64)
                     }
                 }
                 tc_commit(&acc_full[acc]);          // accumulator complete
@@ -314,34 +350,58 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
             tc_fence_after();
             uint32_t const taddr = tmem_base + acc * static_cast<uint32_t>(P.N) + ((q * 32u) << 16);
             size_t const pixel = static_cast<size_t>(y) * P.W + x;
-            for (int c0 = 0; c0 < P.N; c0 += 16)
+            for (int c0 = 0; c0 < P.N; c0 += 32)
             {
-                uint32_t r[16];
-                tc_ld16(taddr + static_cast<uint32_t>(c0), r);
+                // two 16-column loads in flight, one wait (N is a multiple of 16: the second
+                // half is warp-uniformly skipped on the last odd chunk)
+                uint32_t r[32];
+                bool const two = c0 + 16 < P.N;
+                tc_ld16(taddr + static_cast<uint32_t>(c0), *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
+                if (two) tc_ld16(taddr + static_cast<uint32_t>(c0 + 16), *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
                 tc_ld_wait();
-                float v[16];
 #pragma unroll
-                for (int j = 0; j < 16; j++)
+                for (int h = 0; h < 2; h++)
                 {
-                    float b = (bias != nullptr && c0 + j < P.Cout) ? __ldg(bias + c0 + j) : 0.f;
-                    v[j] = tc_act(__uint_as_float(r[j]) + b, P.act, P.alpha);
-                }
-                if (x < P.W)
-                {
-                    if (P.out_bf16)
+                    if (h == 1 && !two) break;
+                    int const cb = c0 + 16 * h;
+                    float v[16];
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; j4++)
                     {
-                        uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(out) + pixel * P.N + c0);
-                        o[0] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
-                                          pack_bf16(v[6], v[7]));
-                        o[1] = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
-                                          pack_bf16(v[14], v[15]));
+                        float4 const b = *reinterpret_cast<float4 const*>(&s_bias[cb + 4 * j4]); // broadcast LDS.128
+                        v[4 * j4 + 0] = __uint_as_float(r[16 * h + 4 * j4 + 0]) + b.x;
+                        v[4 * j4 + 1] = __uint_as_float(r[16 * h + 4 * j4 + 1]) + b.y;
+                        v[4 * j4 + 2] = __uint_as_float(r[16 * h + 4 * j4 + 2]) + b.z;
+                        v[4 * j4 + 3] = __uint_as_float(r[16 * h + 4 * j4 + 3]) + b.w;
+                    }
+                    if (simple_act)
+                    {
+                        // None / Relu / LeakyRelu without branches: max(v,0) + slope * min(v,0)
+#pragma unroll
+                        for (int j = 0; j < 16; j++) v[j] = fmaf(neg_slope, fminf(v[j], 0.f), fmaxf(v[j], 0.f));
                     }
                     else
                     {
-                        float* o = static_cast<float*>(out) + pixel * P.Cout;
 #pragma unroll
-                        for (int j = 0; j < 16; j++)
-                            if (c0 + j < P.Cout) o[c0 + j] = v[j];
+                        for (int j = 0; j < 16; j++) v[j] = tc_act(v[j], P.act, P.alpha);
+                    }
+                    if (x < P.W)
+                    {
+                        if (P.out_bf16)
+                        {
+                            uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(out) + pixel * P.N + cb);
+                            o[0] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                                              pack_bf16(v[6], v[7]));
+                            o[1] = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]),
+                                              pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
+                        }
+                        else
+                        {
+                            float* o = static_cast<float*>(out) + pixel * P.Cout;
+#pragma unroll
+                            for (int j = 0; j < 16; j++)
+                                if (cb + j < P.Cout) o[cb + j] = v[j];
+                        }
                     }
                 }
             }
@@ -392,10 +452,22 @@ void Encode(CUtensorMap* map, void const* base, int rank, cuuint64_t const* dims
         throw std::runtime_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(r)));
 }
 
+bool HaloMode(int KC)
+{
+    static int const env = std::getenv("MLB200_TC_HALO") ? std::atoi(std::getenv("MLB200_TC_HALO")) : 1;
+    return KC == 64 && env != 0;
+}
+
+size_t StageBytes(int KC)
+{
+    // halo: 130 pixels x 128 B = 16640 B, rounded up to the 1024-byte swizzle pattern; else 3 boxes
+    return HaloMode(KC) ? 17u * 1024u : static_cast<size_t>(3) * kTileM * KC * 2;
+}
+
 size_t SmemBytes(int N, int Cin, int KC, int stages)
 {
     size_t b = static_cast<size_t>(9) * N * Cin * 2;
-    size_t a = static_cast<size_t>(stages) * kTileM * KC * 2;
+    size_t a = static_cast<size_t>(stages) * StageBytes(KC);
     return 1024 /*alignment slack*/ + b + a + (2 * kMaxStages + 5) * sizeof(uint64_t) + 16;
 }
 
@@ -419,7 +491,7 @@ bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding
     int const N = ConvTcPaddedCout(Cout);
     if (Cout < 1 || N > 256) return false;
     int const KC = Cin < 64 ? Cin : 64;
-    return SmemBytes(N, Cin, KC, 3) <= 227u * 1024u;
+    return SmemBytes(N, Cin, KC, 2) <= 226u * 1024u;
 }
 
 std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout)
@@ -456,17 +528,23 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, int H, int W, int
     p.out_bf16 = out_bf16 ? 1 : 0;
     p.act = act;
     p.alpha = alpha;
+    p.debug = std::getenv("MLB200_TC_DEBUG") ? std::atoi(std::getenv("MLB200_TC_DEBUG")) : 0;
+    p.halo = HaloMode(p.KC) ? 1 : 0;
+    p.stage_bytes = static_cast<int>(StageBytes(p.KC));
+    p.tap_stride = p.halo ? 128 : kTileM * p.KC * 2;
+    p.stage_tx = p.halo ? (kTileM + 2) * 128 : 3 * kTileM * p.KC * 2;
+    p.base_offset_mode = std::getenv("MLB200_TC_BASEOFF") ? std::atoi(std::getenv("MLB200_TC_BASEOFF")) : 0;
     p.stages = kMaxStages;
-    while (p.stages > 3 && SmemBytes(p.N, Cin, p.KC, p.stages) > 227u * 1024u) p.stages--;
+    while (p.stages > 2 && SmemBytes(p.N, Cin, p.KC, p.stages) > 226u * 1024u) p.stages--;
     op->smem = SmemBytes(p.N, Cin, p.KC, p.stages);
-    if (op->smem > 227u * 1024u) throw std::runtime_error("filter does not fit in shared memory");
+    if (op->smem > 226u * 1024u) throw std::runtime_error("filter does not fit in shared memory");
     op->grid = p.n_tiles < sm_count ? p.n_tiles : sm_count;
 
     // activation: [H][W][Cin] bf16, box = KC channels x 128 pixels x 1 row
     {
         cuuint64_t dims[3] = {static_cast<cuuint64_t>(Cin), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H)};
         cuuint64_t strides[2] = {static_cast<cuuint64_t>(Cin) * 2, static_cast<cuuint64_t>(W) * Cin * 2};
-        cuuint32_t box[3] = {static_cast<cuuint32_t>(p.KC), kTileM, 1};
+        cuuint32_t box[3] = {static_cast<cuuint32_t>(p.KC), static_cast<cuuint32_t>(p.halo ? kTileM + 2 : kTileM), 1};
         Encode(&op->in_map, d_in, 3, dims, strides, box, SwizzleFor(p.KC));
     }
     // filter: [9 * N][Cin] bf16, box = KC channels x N rows
@@ -477,7 +555,7 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, int H, int W, int
         Encode(&op->w_map, d_w_packed, 2, dims, strides, box, SwizzleFor(p.KC));
     }
     // per device: the attribute belongs to the function in the current context
-    ML_CUDA_CHECK(cudaFuncSetAttribute(conv3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    ML_CUDA_CHECK(cudaFuncSetAttribute(conv3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
     return op.release();
 }
 
