@@ -33,6 +33,7 @@
 #include <cudaTypedefs.h>
 #include <cuda_bf16.h>
 
+#include <cstdio>
 #include <cstdlib>
 #include <memory>
 #include <stdexcept>
@@ -46,6 +47,7 @@ namespace {
 constexpr int kTileM = 128;          // output pixels per tile = TMEM lanes
 constexpr int kTcThreads = 192;      // 6 warps
 constexpr int kMaxStages = 8;
+constexpr int kMaxAcc = 4;
 
 struct TcParams
 {
@@ -59,16 +61,20 @@ struct TcParams
     int n_tiles;
     int layout_type;     // UMMA LayoutType: 2 = SW128, 4 = SW64, 6 = SW32
     int sbo;             // bytes between 8-row groups = 8 * KC * 2
-    int tmem_cols;       // allocated TMEM columns (power of two >= 32, holds 2 accumulators)
+    int n_acc;           // accumulators kept in TMEM (2 or 4): tile i's epilogue overlaps later tiles' MMAs
+    int tmem_cols;       // allocated TMEM columns (power of two >= 32) = n_acc * N rounded up
     int out_bf16;        // 1: bf16 NHWC with N == Cout channels; 0: fp32 NHWC with Cout channels
     Act act;
     float alpha;
     int halo;            // 1: a stage is ONE box of 130 pixels (row y+kh-1, x0-1..x0+128) and the three
                          //    kw taps are row-shifted views of it (KC == 64 only); 0: three 128-pixel boxes
-    int stage_bytes;     // bytes of one A stage (one kh row of one Cin chunk), multiple of 1024
+    int rps;             // filter rows per A stage: 3 (whole tile in one stage: one wait/fence/commit per
+                         //    36 MMAs) when two such stages fit next to the filter, else 1
+    int row_bytes;       // bytes of one filter row inside a stage, multiple of 1024
+    int stage_bytes;     // bytes of one A stage = rps * row_bytes
     int tap_stride;      // bytes from tap kw to tap kw+1 inside a stage: 128 (halo) or 128*KC*2
     int stage_tx;        // bytes TMA delivers per stage
-    int base_offset_mode; // halo mode: fill the descriptor's base-offset field (MLB200_TC_BASEOFF, default 0: not needed)
+    unsigned long long* prof; // MLB200_TC_PROF=1: 8 cycle counters summed over CTAs (see ConvTcRun)
     int debug;           // MLB200_TC_DEBUG bit 0: no TMA loads of A, bit 1: no MMAs (timing experiments only)
 };
 
@@ -115,6 +121,13 @@ __device__ __forceinline__ void tma_load_3d(void* dst, CUtensorMap const* map, i
         ::"r"(smem_addr(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(smem_addr(bar))
         : "memory");
 }
+__device__ __forceinline__ void tma_store_3d(CUtensorMap const* map, void const* src, int c0, int c1, int c2)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
+        ::"l"(map), "r"(smem_addr(src)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
 __device__ __forceinline__ void tma_load_2d(void* dst, CUtensorMap const* map, int c0, int c1, uint64_t* bar)
 {
     asm volatile(
@@ -122,6 +135,23 @@ __device__ __forceinline__ void tma_load_2d(void* dst, CUtensorMap const* map, i
         " [%0], [%1, {%2, %3}], [%4];"
         ::"r"(smem_addr(dst)), "l"(map), "r"(c0), "r"(c1), "r"(smem_addr(bar))
         : "memory");
+}
+// One lane of a fully active warp (the lowest): the role loops below run with ALL lanes of their
+// warp in uniform control flow and only the asynchronous instructions sit under this predicate, so
+// the compiler keeps descriptors and addresses in uniform registers (a loop under `if (lane == 0)`
+// costs an ELECT/R2UR/branch sequence per UTCHMMA and makes the issuing thread the bottleneck).
+__device__ __forceinline__ bool elect_one()
+{
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .b32 rx;\n"
+        ".reg .pred px;\n"
+        "elect.sync rx|px, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, px;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -191,26 +221,34 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
     return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// MLB200_TC_PROF instrumentation: cycles a role spends in a region, summed over CTAs.
+#define TC_PROF_T0() long long t0__ = P.prof ? clock64() : 0
+#define TC_PROF_ADD(slot) do { if (P.prof) { long long t1__ = clock64(); prof_acc[slot] += t1__ - t0__; t0__ = t1__; } } while (0)
+
 // ---------------------------------------------------------------- the kernel
+template <int KC>
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap w_map,
-                  float const* __restrict__ bias, void* __restrict__ out, TcParams const P)
+                  const __grid_constant__ CUtensorMap out_map, float const* __restrict__ bias,
+                  void* __restrict__ out, TcParams const P)
 {
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment: the 128-byte swizzle pattern repeats every 1024 bytes
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~uintptr_t(1023u));
-    uint32_t const b_tile_bytes = static_cast<uint32_t>(P.N) * P.KC * 2u;
+    uint32_t const b_tile_bytes = static_cast<uint32_t>(P.N) * KC * 2u;
     uint32_t const a_stage_bytes = static_cast<uint32_t>(P.stage_bytes);
     uint32_t const n_b_tiles = 9u * P.n_chunks;
-    uint8_t* smem_b = smem;
-    uint8_t* smem_a = smem + n_b_tiles * b_tile_bytes;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_a + static_cast<uint32_t>(P.stages) * a_stage_bytes);
+    uint32_t const out_tile_bytes = P.out_bf16 ? static_cast<uint32_t>(kTileM) * P.N * 2u : 0u;
+    uint8_t* smem_b = smem;                                       // filter, resident
+    uint8_t* smem_a = smem_b + n_b_tiles * b_tile_bytes;           // A ring
+    uint8_t* smem_o = smem_a + static_cast<uint32_t>(P.stages) * a_stage_bytes;   // 2 output staging tiles
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_o + 2u * out_tile_bytes);
     uint64_t* full = bars;                       // [stages]   TMA -> MMA
     uint64_t* empty = bars + kMaxStages;         // [stages]   MMA -> TMA
     uint64_t* w_full = bars + 2 * kMaxStages;    // filter resident
-    uint64_t* acc_full = w_full + 1;             // [2]        MMA -> epilogue
-    uint64_t* acc_empty = acc_full + 2;          // [2]        epilogue -> MMA
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+    uint64_t* acc_full = w_full + 1;             // [n_acc]    MMA -> epilogue
+    uint64_t* acc_empty = acc_full + kMaxAcc;    // [n_acc]    epilogue -> MMA
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + kMaxAcc);
 
     uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -224,9 +262,10 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     {
         asm volatile("prefetch.tensormap [%0];" ::"l"(&in_map) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&w_map) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&out_map) : "memory");
         for (int s = 0; s < P.stages; s++) { bar_init(&full[s], 1); bar_init(&empty[s], 1); }
         bar_init(w_full, 1);
-        for (int a = 0; a < 2; a++) { bar_init(&acc_full[a], 1); bar_init(&acc_empty[a], 4); }
+        for (int a = 0; a < P.n_acc; a++) { bar_init(&acc_full[a], 1); bar_init(&acc_empty[a], 4); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1)
@@ -239,118 +278,191 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     __syncthreads();
     tc_fence_after();
     uint32_t const tmem_base = *tmem_slot;
+    long long prof_acc[5] = {0, 0, 0, 0, 0};
 
+    // All three role loops run with every lane of their warp in uniform control flow; ring slot and
+    // phase are carried incrementally (no division / modulo per stage) because each loop is a single
+    // instruction stream whose length per tile bounds the kernel.
     if (warp == 0)
     {
-        if (lane == 0)
+        // ---- TMA producer
+        if (elect_one())
         {
-            // ---- TMA producer
             bar_expect_tx(w_full, n_b_tiles * b_tile_bytes);
             for (uint32_t t = 0; t < 9u; t++)
                 for (int ch = 0; ch < P.n_chunks; ch++)
-                    tma_load_2d(smem_b + (t * P.n_chunks + ch) * b_tile_bytes, &w_map, ch * P.KC,
+                    tma_load_2d(smem_b + (t * P.n_chunks + ch) * b_tile_bytes, &w_map, ch * KC,
                                 static_cast<int>(t) * P.N, w_full);
-            uint32_t it = 0;
-            for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x)
+        }
+        __syncwarp();
+        uint32_t s = 0, ph = 0;
+        int y = blockIdx.x / P.tiles_per_row, tx = blockIdx.x - y * P.tiles_per_row;
+        int const dy = gridDim.x / P.tiles_per_row, dtx = gridDim.x - dy * P.tiles_per_row;
+        TC_PROF_T0();
+        for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x)
+        {
+            int const x0 = tx * kTileM;
+            for (int kh0 = 0; kh0 < 3; kh0 += P.rps)
             {
-                int const y = tile / P.tiles_per_row;
-                int const x0 = (tile - y * P.tiles_per_row) * kTileM;
-                for (int kh = 0; kh < 3; kh++)
+                for (int ch = 0; ch < P.n_chunks; ch++)
                 {
-                    for (int ch = 0; ch < P.n_chunks; ch++, it++)
+                    TC_PROF_ADD(1);
+                    bar_wait(&empty[s], ph ^ 1u);
+                    TC_PROF_ADD(0);
+                    if (elect_one())
                     {
-                        uint32_t const s = it % P.stages, ph = (it / P.stages) & 1u;
-                        bar_wait(&empty[s], ph ^ 1u);
-                        if (P.debug & 1) { bar_arrive(&full[s]); continue; }
-                        bar_expect_tx(&full[s], static_cast<uint32_t>(P.stage_tx));
-                        // rows/pixels outside the image are zero-filled by TMA = SAME padding
-                        uint8_t* dst = smem_a + s * a_stage_bytes;
-                        if (P.halo)
+                        if (P.debug & 1)
                         {
-                            tma_load_3d(dst, &in_map, ch * P.KC, x0 - 1, y + kh - 1, &full[s]);
+                            bar_arrive(&full[s]);
                         }
                         else
                         {
-                            for (int kw = 0; kw < 3; kw++)
-                                tma_load_3d(dst + kw * P.tap_stride, &in_map, ch * P.KC, x0 + kw - 1, y + kh - 1,
-                                            &full[s]);
+                            bar_expect_tx(&full[s], static_cast<uint32_t>(P.stage_tx));
+                            for (int r = 0; r < P.rps; r++)
+                            {
+                                // rows/pixels outside the image are zero-filled by TMA = SAME padding
+                                uint8_t* dst = smem_a + s * a_stage_bytes + r * P.row_bytes;
+                                int const iy = y + kh0 + r - 1;
+                                if (P.halo)
+                                {
+                                    tma_load_3d(dst, &in_map, ch * KC, x0 - 1, iy, &full[s]);
+                                }
+                                else
+                                {
+                                    for (int kw = 0; kw < 3; kw++)
+                                        tma_load_3d(dst + kw * P.tap_stride, &in_map, ch * KC, x0 + kw - 1, iy,
+                                                    &full[s]);
+                                }
+                            }
                         }
                     }
+                    __syncwarp();
+                    if (++s == static_cast<uint32_t>(P.stages)) { s = 0; ph ^= 1u; }
                 }
             }
+            y += dy; tx += dtx;
+            if (tx >= P.tiles_per_row) { tx -= P.tiles_per_row; y++; }
+        }
+        TC_PROF_ADD(1);
+        if (P.prof && lane == 0)
+        {
+            atomicAdd(P.prof + 0, static_cast<unsigned long long>(prof_acc[0]));
+            atomicAdd(P.prof + 1, static_cast<unsigned long long>(prof_acc[1]));
         }
     }
     else if (warp == 1)
     {
-        if (lane == 0)
+        // ---- MMA issuer.  Instruction descriptor (cute::UMMA::InstrDescriptor): D = fp32 [4,6),
+        // A = B = bf16 [7,10) [10,13), both K-major, N>>3 at [17,23), M>>4 at [24,29).
+        uint32_t const idesc = (1u << 4) | (1u << 7) | (1u << 10)
+                             | (static_cast<uint32_t>(P.N >> 3) << 17)
+                             | (static_cast<uint32_t>(kTileM >> 4) << 24);
+        bar_wait(w_full, 0);
+        tc_fence_after();
+        // Everything of the two shared-memory descriptors except the start address is constant;
+        // (addr >> 4) stays below 2^14 for any address inside the 227 KB window, so stages, taps and
+        // K steps are plain additions to the low word.
+        uint64_t const desc_hi = umma_desc(0u, P.sbo, P.layout_type);
+        uint32_t const a_lo0 = smem_addr(smem_a) >> 4, b_lo0 = smem_addr(smem_b) >> 4;
+        uint32_t const stage_u = a_stage_bytes >> 4, tap_u = static_cast<uint32_t>(P.tap_stride) >> 4;
+        uint32_t const b_tile_u = b_tile_bytes >> 4, row_u = static_cast<uint32_t>(P.row_bytes) >> 4;
+        uint32_t const rps = static_cast<uint32_t>(P.rps), n_chunks = static_cast<uint32_t>(P.n_chunks);
+        uint32_t s = 0, ph = 0, acc = 0, aph = 0;
+        TC_PROF_T0();
+        for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x)
         {
-            // ---- MMA issuer.  Instruction descriptor (cute::UMMA::InstrDescriptor): D = fp32 [4,6),
-            // A = B = bf16 [7,10) [10,13), both K-major, N>>3 at [17,23), M>>4 at [24,29).
-            uint32_t const idesc = (1u << 4) | (1u << 7) | (1u << 10)
-                                 | (static_cast<uint32_t>(P.N >> 3) << 17)
-                                 | (static_cast<uint32_t>(kTileM >> 4) << 24);
-            bar_wait(w_full, 0);
+            TC_PROF_ADD(2);
+            bar_wait(&acc_empty[acc], aph ^ 1u);
+            TC_PROF_ADD(0);
             tc_fence_after();
-            uint32_t it = 0, tcount = 0;
-            for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, tcount++)
+            uint32_t const d_tmem = tmem_base + acc * static_cast<uint32_t>(P.N);
+            for (uint32_t kh0 = 0; kh0 < 3u; kh0 += rps)
             {
-                uint32_t const acc = tcount & 1u, aph = (tcount >> 1) & 1u;
-                bar_wait(&acc_empty[acc], aph ^ 1u);
-                tc_fence_after();
-                uint32_t const d_tmem = tmem_base + acc * static_cast<uint32_t>(P.N);
-                uint32_t first = 0;
-                for (uint32_t kh = 0; kh < 3u; kh++)
+                for (uint32_t ch = 0; ch < n_chunks; ch++)
                 {
-                    for (int ch = 0; ch < P.n_chunks; ch++, it++)
+                    TC_PROF_ADD(2);
+                    bar_wait(&full[s], ph);
+                    TC_PROF_ADD(1);
+                    tc_fence_after();
+                    if (elect_one())
                     {
-                        uint32_t const s = it % P.stages, ph = (it / P.stages) & 1u;
-                        bar_wait(&full[s], ph);
-                        tc_fence_after();
-                        uint32_t const a_base = smem_addr(smem_a + s * a_stage_bytes);
-                        for (uint32_t kw = 0; kw < 3u; kw++)
+                        if (!(P.debug & 2))
                         {
-                            // halo mode: tap kw = the same box read from pixel row kw on.  The start is then
-                            // kw * 128 bytes into the 1024-byte swizzle pattern.  Measured on B200: the MMA
-                            // applies the 128B swizzle XOR to the ABSOLUTE shared-memory address bits (as TMA
-                            // does), so a row-shifted start needs NO base offset (bits [49,52) stay 0; setting
-                            // them to (start >> 7) & 7 gives wrong results).  MLB200_TC_BASEOFF=1 re-enables
-                            // the field for that experiment.
-                            uint32_t const a_addr = a_base + kw * static_cast<uint32_t>(P.tap_stride);
-                            uint64_t a_desc = umma_desc(a_addr, P.sbo, P.layout_type);
-                            if (P.halo && P.base_offset_mode) a_desc |= static_cast<uint64_t>((a_addr >> 7) & 7u) << 49;
-                            uint64_t const b_desc =
-                                umma_desc(smem_addr(smem_b + ((kh * 3u + kw) * P.n_chunks + ch) * b_tile_bytes), P.sbo,
-                                          P.layout_type);
-                            for (int k = 0; k < P.KC / 16 && !(P.debug & 2); k++)
+                            for (uint32_t r = 0; r < rps; r++)
                             {
-                                // +32 bytes along K inside the swizzle row = +2 in the (addr >> 4) field
-                                tc_mma_bf16(d_tmem, a_desc + 2u * k, b_desc + 2u * k, idesc, first);
-                                first = 1;
+                                uint32_t const kh = kh0 + r;
+                                uint32_t const a_lo = a_lo0 + s * stage_u + r * row_u;
+                                uint32_t const b_lo = b_lo0 + (kh * 3u * n_chunks + ch) * b_tile_u;
+#pragma unroll
+                                for (uint32_t kw = 0; kw < 3u; kw++)
+                                {
+                                    // halo mode: tap kw = the same box read from pixel row kw on (start kw * 128
+                                    // bytes into the 1024-byte swizzle pattern).  Measured on B200: the MMA
+                                    // applies the swizzle XOR to the ABSOLUTE shared-memory address bits, as TMA
+                                    // does, so a row-shifted start needs no base offset (descriptor bits [49,52)
+                                    // stay 0; setting them to (start >> 7) & 7 gives wrong results).
+#pragma unroll
+                                    for (uint32_t k = 0; k < KC / 16; k++)
+                                    {
+                                        // +32 bytes along K inside the swizzle row = +2 in the (addr >> 4) field
+                                        uint64_t const a_desc = desc_hi | (a_lo + kw * tap_u + 2u * k);
+                                        uint64_t const b_desc = desc_hi | (b_lo + kw * n_chunks * b_tile_u + 2u * k);
+                                        tc_mma_bf16(d_tmem, a_desc, b_desc, idesc, (kh | kw | k | ch) != 0u);
+                                    }
+                                }
                             }
                         }
-                        tc_commit(&empty[s]);       // ONE commit per stage (12 MMAs at Cin = 64)
+                        TC_PROF_ADD(2);
+                        tc_commit(&empty[s]);       // ONE commit per stage (12 or 36 MMAs at Cin = 64)
+                        TC_PROF_ADD(3);
                     }
+                    __syncwarp();
+                    if (++s == static_cast<uint32_t>(P.stages)) { s = 0; ph ^= 1u; }
+                    TC_PROF_ADD(4);
                 }
-                tc_commit(&acc_full[acc]);          // accumulator complete
             }
+            if (elect_one()) tc_commit(&acc_full[acc]);   // accumulator complete
+            __syncwarp();
+            if (++acc == static_cast<uint32_t>(P.n_acc)) { acc = 0; aph ^= 1u; }
+        }
+        TC_PROF_ADD(4);
+        if (P.prof && lane == 0)
+        {
+            for (int k = 0; k < 3; k++) atomicAdd(P.prof + 2 + k, static_cast<unsigned long long>(prof_acc[k]));
+            atomicAdd(P.prof + 7, static_cast<unsigned long long>(prof_acc[3]));
+            atomicAdd(P.prof + 8, static_cast<unsigned long long>(prof_acc[4]));
         }
     }
     else
     {
-        // ---- epilogue warps 2..5: warp w may touch TMEM lanes 32*(w%4) .. +31
+        // ---- epilogue warps 2..5: warp w may touch TMEM lanes 32*(w%4) .. +31 = tile rows (pixels).
+        // bf16 output: each thread packs its pixel's channels and parks them in a swizzled staging tile
+        // (conflict-free STS.128), then ONE thread hands the whole 128-pixel tile to TMA
+        // (cp.async.bulk.tensor store: coalesced, asynchronous, clipped at the image edge).  Two staging
+        // tiles alternate, so tile i's store drains while tile i+1 is being packed.
         uint32_t const q = warp & 3u;
         uint32_t const row = q * 32u + lane;
-        uint32_t tcount = 0;
-        for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, tcount++)
+        bool const issuer = threadIdx.x == 64;               // warp 2, lane 0
+        int const OC = P.N < 64 ? P.N : 64;                  // channels per output box / staging chunk
+        uint32_t const row_bytes = static_cast<uint32_t>(OC) * 2u;
+        uint32_t const swz_mask = row_bytes == 128u ? 7u : (row_bytes == 64u ? 3u : 1u);
+        uint32_t const chunk_bytes = static_cast<uint32_t>(kTileM) * row_bytes;
+        uint32_t acc = 0, aph = 0, buf = 0;
+        int y = blockIdx.x / P.tiles_per_row, tx = blockIdx.x - y * P.tiles_per_row;
+        int const dy = gridDim.x / P.tiles_per_row, dtx = gridDim.x - dy * P.tiles_per_row;
+        TC_PROF_T0();
+        for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x)
         {
-            uint32_t const acc = tcount & 1u, aph = (tcount >> 1) & 1u;
-            int const y = tile / P.tiles_per_row;
-            int const x = (tile - y * P.tiles_per_row) * kTileM + static_cast<int>(row);
+            int const x0 = tx * kTileM;
+            TC_PROF_ADD(1);
             bar_wait(&acc_full[acc], aph);
+            TC_PROF_ADD(0);
             tc_fence_after();
             uint32_t const taddr = tmem_base + acc * static_cast<uint32_t>(P.N) + ((q * 32u) << 16);
+            uint8_t* const stg = smem_o + buf * out_tile_bytes;
+            int const x = x0 + static_cast<int>(row);
             size_t const pixel = static_cast<size_t>(y) * P.W + x;
-            for (int c0 = 0; c0 < P.N; c0 += 32)
+            for (int c0 = 0; c0 < P.N && !(P.debug & 4); c0 += 32)
             {
                 // two 16-column loads in flight, one wait (N is a multiple of 16: the second
                 // half is warp-uniformly skipped on the last odd chunk)
@@ -385,29 +497,63 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
 #pragma unroll
                         for (int j = 0; j < 16; j++) v[j] = tc_act(v[j], P.act, P.alpha);
                     }
-                    if (x < P.W)
+                    if (P.out_bf16)
                     {
-                        if (P.out_bf16)
-                        {
-                            uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(out) + pixel * P.N + cb);
-                            o[0] = make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
-                                              pack_bf16(v[6], v[7]));
-                            o[1] = make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]),
-                                              pack_bf16(v[12], v[13]), pack_bf16(v[14], v[15]));
-                        }
-                        else
-                        {
-                            float* o = static_cast<float*>(out) + pixel * P.Cout;
+                        // 16 channels = two 16-byte units of this pixel's row in staging chunk cb / 64
+                        uint32_t const oc = static_cast<uint32_t>(cb) >> 6;
+                        uint32_t const unit = (static_cast<uint32_t>(cb) & 63u) >> 3;
+                        uint32_t off0 = row * row_bytes + unit * 16u;
+                        uint32_t off1 = off0 + 16u;
+                        off0 ^= ((off0 >> 7) & swz_mask) << 4;   // the swizzle TMA expects (address bits, 1024-aligned base)
+                        off1 ^= ((off1 >> 7) & swz_mask) << 4;
+                        uint8_t* const base = stg + oc * chunk_bytes;
+                        *reinterpret_cast<uint4*>(base + off0) =
+                            make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                                       pack_bf16(v[6], v[7]));
+                        *reinterpret_cast<uint4*>(base + off1) =
+                            make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
+                                       pack_bf16(v[14], v[15]));
+                    }
+                    else if (x < P.W)
+                    {
+                        float* o = static_cast<float*>(out) + pixel * P.Cout;
 #pragma unroll
-                            for (int j = 0; j < 16; j++)
-                                if (cb + j < P.Cout) o[cb + j] = v[j];
-                        }
+                        for (int j = 0; j < 16; j++)
+                            if (cb + j < P.Cout) o[cb + j] = v[j];
                     }
                 }
             }
+            // TMEM accumulator is free as soon as it has been read
             tc_fence_before();
             __syncwarp();
             if (lane == 0) bar_arrive(&acc_empty[acc]);
+            if (++acc == static_cast<uint32_t>(P.n_acc)) { acc = 0; aph ^= 1u; }
+
+            if (P.out_bf16)
+            {
+                // generic-proxy writes -> visible to the async proxy (TMA) ; the issuer first makes sure
+                // the store that last read the OTHER staging tile is done, so that after the barrier
+                // every thread may start overwriting it for the next tile
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (issuer)
+                {
+                    for (int oc = 0; oc * 64 < P.N; oc++)
+                        tma_store_3d(&out_map, stg + oc * chunk_bytes, oc * 64, x0, y);
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+                buf ^= 1u;
+            }
+            y += dy; tx += dtx;
+            if (tx >= P.tiles_per_row) { tx -= P.tiles_per_row; y++; }
+        }
+        if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        TC_PROF_ADD(1);
+        if (P.prof && warp == 2 && lane == 0)
+        {
+            atomicAdd(P.prof + 5, static_cast<unsigned long long>(prof_acc[0]));
+            atomicAdd(P.prof + 6, static_cast<unsigned long long>(prof_acc[1]));
         }
     }
 
@@ -464,11 +610,12 @@ size_t StageBytes(int KC)
     return HaloMode(KC) ? 17u * 1024u : static_cast<size_t>(3) * kTileM * KC * 2;
 }
 
-size_t SmemBytes(int N, int Cin, int KC, int stages)
+size_t SmemBytes(int N, int Cin, int KC, int stages, bool out_bf16, int rps = 1)
 {
     size_t b = static_cast<size_t>(9) * N * Cin * 2;
-    size_t a = static_cast<size_t>(stages) * StageBytes(KC);
-    return 1024 /*alignment slack*/ + b + a + (2 * kMaxStages + 5) * sizeof(uint64_t) + 16;
+    size_t a = static_cast<size_t>(stages) * StageBytes(KC) * rps;
+    size_t o = out_bf16 ? static_cast<size_t>(2) * kTileM * N * 2 : 0;   // two staging tiles for the TMA store
+    return 1024 /*alignment slack*/ + b + a + o + (2 * kMaxStages + 1 + 2 * kMaxAcc) * sizeof(uint64_t) + 16;
 }
 
 } // namespace
@@ -477,6 +624,7 @@ struct ConvTc
 {
     CUtensorMap in_map;
     CUtensorMap w_map;
+    CUtensorMap out_map;
     TcParams p;
     size_t smem;
     int grid;
@@ -491,25 +639,25 @@ bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding
     int const N = ConvTcPaddedCout(Cout);
     if (Cout < 1 || N > 256) return false;
     int const KC = Cin < 64 ? Cin : 64;
-    return SmemBytes(N, Cin, KC, 2) <= 226u * 1024u;
+    return SmemBytes(N, Cin, KC, 2, true) <= 226u * 1024u;
 }
 
-std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout)
+std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout, int Cin_pad)
 {
     int const N = ConvTcPaddedCout(Cout);
-    std::vector<uint16_t> packed(static_cast<size_t>(9) * N * Cin, 0);
+    std::vector<uint16_t> packed(static_cast<size_t>(9) * N * Cin_pad, 0);
     for (int t = 0; t < 9; t++)
         for (int co = 0; co < Cout; co++)
             for (int ci = 0; ci < Cin; ci++)
             {
                 __nv_bfloat16 b = __float2bfloat16_rn(hwio[(static_cast<size_t>(t) * Cin + ci) * Cout + co]);
-                packed[(static_cast<size_t>(t) * N + co) * Cin + ci] = *reinterpret_cast<uint16_t*>(&b);
+                packed[(static_cast<size_t>(t) * N + co) * Cin_pad + ci] = *reinterpret_cast<uint16_t*>(&b);
             }
     return packed;
 }
 
-ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, int H, int W, int Cin, int Cout, bool out_bf16,
-                     Act act, float alpha, int sm_count)
+ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16, int H, int W, int Cin, int Cout,
+                     bool out_bf16, Act act, float alpha, int sm_count)
 {
     auto op = std::make_unique<ConvTc>();
     TcParams& p = op->p;
@@ -522,21 +670,28 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, int H, int W, int
     p.sbo = 8 * p.KC * 2;
     p.tiles_per_row = (W + kTileM - 1) / kTileM;
     p.n_tiles = p.tiles_per_row * H;
+    int const want_acc = std::getenv("MLB200_TC_ACC") ? std::atoi(std::getenv("MLB200_TC_ACC")) : kMaxAcc;
+    p.n_acc = (want_acc >= 4 && 4 * p.N <= 512) ? 4 : 2;
     int cols = 32;
-    while (cols < 2 * p.N) cols *= 2;
+    while (cols < p.n_acc * p.N) cols *= 2;
     p.tmem_cols = cols;
     p.out_bf16 = out_bf16 ? 1 : 0;
     p.act = act;
     p.alpha = alpha;
     p.debug = std::getenv("MLB200_TC_DEBUG") ? std::atoi(std::getenv("MLB200_TC_DEBUG")) : 0;
     p.halo = HaloMode(p.KC) ? 1 : 0;
-    p.stage_bytes = static_cast<int>(StageBytes(p.KC));
+    p.row_bytes = static_cast<int>(StageBytes(p.KC));
+    int const want_rps = std::getenv("MLB200_TC_RPS") ? std::atoi(std::getenv("MLB200_TC_RPS")) : 3;
+    p.rps = (want_rps == 3 && SmemBytes(p.N, Cin, p.KC, 2, out_bf16, 3) <= 226u * 1024u) ? 3 : 1;
+    p.stage_bytes = p.rps * p.row_bytes;
     p.tap_stride = p.halo ? 128 : kTileM * p.KC * 2;
-    p.stage_tx = p.halo ? (kTileM + 2) * 128 : 3 * kTileM * p.KC * 2;
-    p.base_offset_mode = std::getenv("MLB200_TC_BASEOFF") ? std::atoi(std::getenv("MLB200_TC_BASEOFF")) : 0;
+    p.stage_tx = p.rps * (p.halo ? (kTileM + 2) * 128 : 3 * kTileM * p.KC * 2);
+    p.prof = nullptr;
+    if (std::getenv("MLB200_TC_PROF") != nullptr)
+        ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&p.prof), 12 * sizeof(unsigned long long)));
     p.stages = kMaxStages;
-    while (p.stages > 2 && SmemBytes(p.N, Cin, p.KC, p.stages) > 226u * 1024u) p.stages--;
-    op->smem = SmemBytes(p.N, Cin, p.KC, p.stages);
+    while (p.stages > 2 && SmemBytes(p.N, Cin, p.KC, p.stages, out_bf16, p.rps) > 226u * 1024u) p.stages--;
+    op->smem = SmemBytes(p.N, Cin, p.KC, p.stages, out_bf16, p.rps);
     if (op->smem > 226u * 1024u) throw std::runtime_error("filter does not fit in shared memory");
     op->grid = p.n_tiles < sm_count ? p.n_tiles : sm_count;
 
@@ -554,18 +709,56 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, int H, int W, int
         cuuint32_t box[2] = {static_cast<cuuint32_t>(p.KC), static_cast<cuuint32_t>(p.N)};
         Encode(&op->w_map, d_w_packed, 2, dims, strides, box, SwizzleFor(p.KC));
     }
+    // bf16 output: [H][W][N] bf16, box = min(N, 64) channels x 128 pixels (the TMA store clips at W)
+    if (out_bf16)
+    {
+        if (d_out_bf16 == nullptr) throw std::runtime_error("bf16 output buffer missing");
+        int const OC = p.N < 64 ? p.N : 64;
+        cuuint64_t dims[3] = {static_cast<cuuint64_t>(p.N), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H)};
+        cuuint64_t strides[2] = {static_cast<cuuint64_t>(p.N) * 2, static_cast<cuuint64_t>(W) * p.N * 2};
+        cuuint32_t box[3] = {static_cast<cuuint32_t>(OC), kTileM, 1};
+        Encode(&op->out_map, d_out_bf16, 3, dims, strides, box, SwizzleFor(OC));
+    }
+    else
+    {
+        op->out_map = op->in_map; // unused by the fp32-output epilogue
+    }
     // per device: the attribute belongs to the function in the current context
-    ML_CUDA_CHECK(cudaFuncSetAttribute(conv3x3_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+    auto set = [](auto* k) { ML_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024)); };
+    if (p.KC == 64) set(conv3x3_tc_kernel<64>);
+    else if (p.KC == 32) set(conv3x3_tc_kernel<32>);
+    else set(conv3x3_tc_kernel<16>);
     return op.release();
 }
 
 void ConvTcRun(ConvTc const* op, float const* bias, void* out, cudaStream_t stream)
 {
-    conv3x3_tc_kernel<<<op->grid, kTcThreads, op->smem, stream>>>(op->in_map, op->w_map, bias, out, op->p);
+    if (op->p.prof) ML_CUDA_CHECK(cudaMemsetAsync(op->p.prof, 0, 12 * sizeof(unsigned long long), stream));
+    if (op->p.KC == 64)
+        conv3x3_tc_kernel<64><<<op->grid, kTcThreads, op->smem, stream>>>(op->in_map, op->w_map, op->out_map, bias, out, op->p);
+    else if (op->p.KC == 32)
+        conv3x3_tc_kernel<32><<<op->grid, kTcThreads, op->smem, stream>>>(op->in_map, op->w_map, op->out_map, bias, out, op->p);
+    else
+        conv3x3_tc_kernel<16><<<op->grid, kTcThreads, op->smem, stream>>>(op->in_map, op->w_map, op->out_map, bias, out, op->p);
     ML_CUDA_CHECK(cudaGetLastError());
+    if (op->p.prof)
+    {
+        unsigned long long h[12];
+        ML_CUDA_CHECK(cudaStreamSynchronize(stream));
+        ML_CUDA_CHECK(cudaMemcpy(h, op->p.prof, sizeof(h), cudaMemcpyDeviceToHost));
+        double const per = 1.0 / (static_cast<double>(op->grid) * ((op->p.n_tiles + op->grid - 1) / op->grid));
+        std::fprintf(stderr, "[tc prof] N=%d cycles/tile: producer wait_empty %.0f other %.0f | mma wait_acc_empty %.0f "
+                     "wait_full %.0f issue %.0f commit %.0f rest %.0f | epilogue wait_acc_full %.0f body %.0f\n", op->p.N,
+                     h[0] * per, h[1] * per, h[2] * per, h[3] * per, h[4] * per, h[7] * per, h[8] * per, h[5] * per,
+                     h[6] * per);
+    }
 }
 
-void ConvTcDestroy(ConvTc* op) { delete op; }
+void ConvTcDestroy(ConvTc* op)
+{
+    if (op != nullptr) cudaFree(op->p.prof);
+    delete op;
+}
 
 } // namespace nn
 } // namespace ML

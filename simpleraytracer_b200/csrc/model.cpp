@@ -541,9 +541,13 @@ void Model::AssignPrecision()
     {
         Op& op = m_ops[i];
         op.tc = false;
+        op.pad_in = false;
         if (m_precision != 1 || op.kind != OpKind::Conv) continue;
+        int const cin = m_tensors[op.in[0]].C;
+        // a thin first layer (e.g. RGB) runs on the tensor cores too, on a 16-channel zero-padded bf16 copy
+        op.pad_in = cin > 0 && cin < 16;
         tc[i] = nn::ConvTcSupported(op.KH, op.KW, op.stride, op.dilation, op.same_padding,
-                                    m_tensors[op.in[0]].C, m_tensors[op.out].C);
+                                    op.pad_in ? 16 : cin, m_tensors[op.out].C);
     }
     bool changed = m_precision == 1;
     std::vector<char> bf(m_tensors.size(), 0);
@@ -567,7 +571,7 @@ void Model::AssignPrecision()
             bf[op.out] = all_tc;
         }
         for (size_t i = 0; i < m_ops.size(); i++)
-            if (tc[i] && !bf[m_ops[i].in[0]]) { tc[i] = 0; changed = true; }
+            if (tc[i] && !m_ops[i].pad_in && !bf[m_ops[i].in[0]]) { tc[i] = 0; changed = true; }
     }
     for (size_t i = 0; i < m_ops.size(); i++) m_ops[i].tc = tc[i] != 0;
     for (size_t t = 0; t < m_tensors.size(); t++) m_tensors[t].bf16 = bf[t] != 0;
@@ -610,6 +614,8 @@ void Model::ReleaseBuffers()
     {
         nn::ConvTcDestroy(op.tc_op);
         op.tc_op = nullptr;
+        cudaFree(op.pad_buffer);
+        op.pad_buffer = nullptr;
     }
     for (void* p : m_buffers) cudaFree(p);
     m_buffers.clear();
@@ -668,16 +674,20 @@ void Model::AllocateBuffers()
         if (!op.tc) continue;
         TensorInfo const& a = m_tensors[op.in[0]];
         TensorInfo const& o = m_tensors[op.out];
+        int const cin = op.pad_in ? 16 : a.C;
+        if (op.pad_in)
+            ML_CUDA_CHECK(cudaMalloc(&op.pad_buffer, static_cast<size_t>(a.H) * a.W * 16 * 2));
         if (op.packed < 0)
         {
-            std::vector<uint16_t> packed = nn::ConvTcPackWeights(m_consts[op.weights].host.data(), a.C, o.C);
+            std::vector<uint16_t> packed = nn::ConvTcPackWeights(m_consts[op.weights].host.data(), a.C, o.C, cin);
             void* d = nullptr;
             ML_CUDA_CHECK(cudaMalloc(&d, packed.size() * 2));
             m_packed.push_back(d);
             op.packed = static_cast<int>(m_packed.size()) - 1;
             ML_CUDA_CHECK(cudaMemcpy(d, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
         }
-        op.tc_op = nn::ConvTcCreate(m_buffers[a.buffer], m_packed[op.packed], a.H, a.W, a.C, o.C, o.bf16,
+        op.tc_op = nn::ConvTcCreate(op.pad_in ? op.pad_buffer : m_buffers[a.buffer], m_packed[op.packed],
+                                    o.bf16 ? m_buffers[o.buffer] : nullptr, a.H, a.W, cin, o.C, o.bf16,
                                     op.act, op.alpha, m_device->prop.multiProcessorCount);
     }
     if (m_input_info.dtype == ML_FLOAT16)
@@ -724,7 +734,7 @@ std::string Model::Describe() const
 size_t Model::LaunchesPerInfer() const
 {
     size_t n = 0;
-    for (auto const& op : m_ops) n += op.kind == OpKind::Concat ? op.in.size() : 1;
+    for (auto const& op : m_ops) n += op.kind == OpKind::Concat ? op.in.size() : ((op.tc && op.pad_in) ? 2 : 1);
     if (m_input_info.dtype == ML_FLOAT16) n += 2;
     return n;
 }
@@ -838,7 +848,11 @@ void Model::Run(float const* d_in, float* d_out, cudaStream_t stream)
                 d.alpha = op.alpha;
                 float const* bias = op.bias >= 0 ? m_consts[op.bias].dev : nullptr;
                 if (op.tc)
+                {
+                    if (op.pad_in)
+                        nn::PadToBf16x16(ptr(op.in[0]), op.pad_buffer, static_cast<size_t>(a.H) * a.W, a.C, stream);
                     nn::ConvTcRun(op.tc_op, bias, ptr(op.out), stream);
+                }
                 else if (o.bf16)
                     nn::Conv2dFp32ToBf16(ptr(op.in[0]), m_consts[op.weights].dev, bias, ptr(op.out), d, stream);
                 else

@@ -71,6 +71,8 @@ private:
         bool tc = false;
         int packed = -1;       // index into m_packed (filter repacked [tap][co][ci] bf16)
         nn::ConvTc* tc_op = nullptr;
+        bool pad_in = false;   // fp32 input with < 16 channels: zero-padded to 16 bf16 channels first
+        void* pad_buffer = nullptr;
     };
 
     struct DeviceConst

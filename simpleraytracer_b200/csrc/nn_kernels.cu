@@ -243,6 +243,29 @@ __global__ void float_to_half_kernel(float const* __restrict__ in, __half* __res
     for (; i < n; i += stride) out[i] = __float2half_rn(in[i]);
 }
 
+// fp32 [pixels][C] -> bf16 [pixels][16], channels >= C zero: the tensor-core layer's K-major rows
+// are at least 16 channels (32 bytes, one 32B-swizzle row).
+__global__ void pad_to_bf16x16_kernel(float const* __restrict__ in, uint4* __restrict__ out, size_t pixels, int C)
+{
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < pixels; i += stride)
+    {
+        float v[16];
+#pragma unroll
+        for (int c = 0; c < 16; c++) v[c] = c < C ? in[i * C + c] : 0.f;
+        uint32_t w[8];
+#pragma unroll
+        for (int c = 0; c < 8; c++)
+        {
+            __nv_bfloat162 b = __floats2bfloat162_rn(v[2 * c], v[2 * c + 1]);
+            w[c] = *reinterpret_cast<uint32_t*>(&b);
+        }
+        out[2 * i + 0] = make_uint4(w[0], w[1], w[2], w[3]);
+        out[2 * i + 1] = make_uint4(w[4], w[5], w[6], w[7]);
+    }
+}
+
 inline unsigned EltGrid(size_t n)
 {
     size_t blocks = (n + 255) / 256;
@@ -279,6 +302,14 @@ void Conv2dFp32ToBf16(float const* in, float const* w, float const* bias, void* 
     if (!(d.stride == 1 && d.dilation == 1 && d.KH == 3 && d.KW == 3))
         throw std::runtime_error("Conv2dFp32ToBf16: only 3x3 stride 1");
     LaunchTileForCout<3, 8>(in, w, bias, static_cast<__nv_bfloat16*>(out_bf16), d, stream);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void PadToBf16x16(float const* in, void* out_bf16, size_t pixels, int C, cudaStream_t stream)
+{
+    if (pixels == 0) return;
+    if (C < 1 || C > 16) throw std::runtime_error("PadToBf16x16: 1..16 channels");
+    pad_to_bf16x16_kernel<<<EltGrid(pixels), 256, 0, stream>>>(in, static_cast<uint4*>(out_bf16), pixels, C);
     ML_CUDA_CHECK(cudaGetLastError());
 }
 

@@ -51,10 +51,15 @@ void Conv2dFp32ToBf16(float const* in, float const* w, float const* bias, void* 
 struct ConvTc; // one planned layer: tensor maps bound to fixed device buffers
 bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding, int Cin, int Cout);
 int ConvTcPaddedCout(int Cout);
-std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout);
+// Cin_pad >= Cin: input channels beyond Cin get zero filter taps (3-channel first layer padded to 16).
+std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout, int Cin_pad);
+// fp32 [pixels][C <= 16] -> bf16 [pixels][16], zero padded (input of a padded first layer).
+void PadToBf16x16(float const* in, void* out_bf16, size_t pixels, int C, cudaStream_t stream);
 // out_bf16: bf16 NHWC output (Cout % 16 == 0) for the next tensor-core layer; else fp32 NHWC.
-ConvTc* ConvTcCreate(void const* d_in_bf16, void const* d_w_packed, int H, int W, int Cin, int Cout,
-                     bool out_bf16, Act act, float alpha, int sm_count);
+// d_out_bf16: the (fixed) bf16 output buffer the TMA store is bound to; ignored for fp32 output,
+// whose pointer is given to ConvTcRun.
+ConvTc* ConvTcCreate(void const* d_in_bf16, void const* d_w_packed, void* d_out_bf16, int H, int W, int Cin,
+                     int Cout, bool out_bf16, Act act, float alpha, int sm_count);
 void ConvTcRun(ConvTc const* op, float const* bias, void* out, cudaStream_t stream);
 void ConvTcDestroy(ConvTc* op);
 void FloatToHalf(float const* in, void* out, size_t n, cudaStream_t stream);

@@ -355,7 +355,7 @@ def _bf16(x):
 def bf16_emulated_denoiser(x, layers, tc_layers, alpha=0.1):
     """The conv oracle with operands rounded to bf16 exactly where the CUDA path stores bf16:
     filters of tensor-core layers, and every activation that feeds a tensor-core layer."""
-    cur = x
+    cur = _bf16(x) if 0 in tc_layers else x      # a thin first layer reads a 16-channel bf16 copy of the image
     for k, (w, b, act) in enumerate(layers):
         wk = _bf16(w) if k in tc_layers else w
         cur = O.conv2d(cur, wk, b, act=act, alpha=alpha)
@@ -365,11 +365,12 @@ def bf16_emulated_denoiser(x, layers, tc_layers, alpha=0.1):
 
 
 @pytest.mark.parametrize("cfg", [
-    dict(width=64, depth=4, act="Relu", w=300, h=37, tc={1, 2, 3}),        # SW128 rows, ragged last tile
-    dict(width=32, depth=3, act="LeakyRelu", w=128, h=9, tc={1, 2}),       # SW64 rows
-    dict(width=16, depth=3, act="Relu", w=131, h=5, tc={1, 2}),            # SW32 rows
-    dict(width=128, depth=3, act="Relu", w=70, h=20, tc={2}),              # 128->128 too big for smem: fp32; 2 K-chunks
-    dict(width=64, depth=5, act="Relu", w=1000, h=150, tc={1, 2, 3, 4}),   # many tiles per CTA: ring + TMEM phases wrap
+    dict(width=64, depth=4, act="Relu", w=300, h=37, tc={0, 1, 2, 3}),     # SW128 rows, ragged last tile
+    dict(width=32, depth=3, act="LeakyRelu", w=128, h=9, tc={0, 1, 2}),    # SW64 rows
+    dict(width=16, depth=3, act="Relu", w=131, h=5, tc={0, 1, 2}),         # SW32 rows
+    dict(width=128, depth=3, act="Relu", w=70, h=20, tc={0, 2}),           # 128->128 too big for smem: fp32; 2 K-chunks
+    dict(width=64, depth=5, act="Relu", w=1000, h=150, tc={0, 1, 2, 3, 4}),  # many tiles per CTA: ring + TMEM phases wrap
+    dict(width=64, depth=3, act="Tanh", w=257, h=11, tc={0, 1, 2}),        # slow-path activation
 ])
 def test_bf16_tensor_core_denoiser(ctx, tmp_path, cfg):
     path = tmp_path / "d.pb"
