@@ -15,12 +15,12 @@
 // row length Cin * 2 bytes, so the TMA box lands in exactly the canonical
 // layout the UMMA shared-memory descriptor describes.
 //
-// Persistent kernel, one CTA per SM, 6 warps:
+// Persistent kernel, one CTA per SM, 10 warps:
 //   warp 0 (one lane)   TMA producer: the filter (once, stays resident in smem),
 //                       then a ring of A stages, one per (tile, tap, Cin chunk)
 //   warp 1 (one lane)   MMA issuer: Cin/16 tcgen05.mma per stage, tcgen05.commit
 //                       frees the stage / publishes the accumulator
-//   warps 2-5           epilogue: tcgen05.ld 32 lanes x 16 columns at a time,
+//   warps 2-9           epilogue: tcgen05.ld 32 lanes x 16 columns at a time,
 //                       + bias, activation, pack to bf16 (or fp32 for the last
 //                       layer), 16-byte stores; the accumulator is double
 //                       buffered in TMEM so tile i's epilogue overlaps tile
@@ -45,7 +45,8 @@ namespace nn {
 namespace {
 
 constexpr int kTileM = 128;          // output pixels per tile = TMEM lanes
-constexpr int kTcThreads = 192;      // 6 warps
+constexpr int kEpiWarps = 8;         // two per TMEM lane quarter, each takes half of the columns
+constexpr int kTcThreads = 64 + 32 * kEpiWarps;   // TMA warp + MMA warp + epilogue warps
 constexpr int kMaxStages = 8;
 constexpr int kMaxAcc = 4;
 
@@ -255,6 +256,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     // bias (zero beyond Cout) staged once; the epilogue reads it as broadcast LDS.128
     __shared__ __align__(16) float s_bias[256];
     for (int c = threadIdx.x; c < P.N; c += kTcThreads) s_bias[c] = (bias != nullptr && c < P.Cout) ? bias[c] : 0.f;
+    bool const relu_act = P.act == Act::Relu;
     bool const simple_act = P.act == Act::None || P.act == Act::Relu || P.act == Act::LeakyRelu;
     float const neg_slope = P.act == Act::None ? 1.f : (P.act == Act::LeakyRelu ? P.alpha : 0.f);
 
@@ -265,7 +267,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
         asm volatile("prefetch.tensormap [%0];" ::"l"(&out_map) : "memory");
         for (int s = 0; s < P.stages; s++) { bar_init(&full[s], 1); bar_init(&empty[s], 1); }
         bar_init(w_full, 1);
-        for (int a = 0; a < P.n_acc; a++) { bar_init(&acc_full[a], 1); bar_init(&acc_empty[a], 4); }
+        for (int a = 0; a < P.n_acc; a++) { bar_init(&acc_full[a], 1); bar_init(&acc_empty[a], kEpiWarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1)
@@ -435,7 +437,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     }
     else
     {
-        // ---- epilogue warps 2..5: warp w may touch TMEM lanes 32*(w%4) .. +31 = tile rows (pixels).
+        // ---- epilogue warps 2..9: warp w may touch TMEM lanes 32*(w%4) .. +31 = tile rows (pixels).
         // bf16 output: each thread packs its pixel's channels and parks them in a swizzled staging tile
         // (conflict-free STS.128), then ONE thread hands the whole 128-pixel tile to TMA
         // (cp.async.bulk.tensor store: coalesced, asynchronous, clipped at the image edge).  Two staging
@@ -443,6 +445,10 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
         uint32_t const q = warp & 3u;
         uint32_t const row = q * 32u + lane;
         bool const issuer = threadIdx.x == 64;               // warp 2, lane 0
+        // the two warps of a lane quarter split the N/16 column units: [c_begin, c_end)
+        int const units = P.N >> 4, half = static_cast<int>(warp - 2u) >> 2;
+        int const c_begin = half == 0 ? 0 : ((units + 1) >> 1) << 4;
+        int const c_end = half == 0 ? ((units + 1) >> 1) << 4 : P.N;
         int const OC = P.N < 64 ? P.N : 64;                  // channels per output box / staging chunk
         uint32_t const row_bytes = static_cast<uint32_t>(OC) * 2u;
         uint32_t const swz_mask = row_bytes == 128u ? 7u : (row_bytes == 64u ? 3u : 1u);
@@ -462,12 +468,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
             uint8_t* const stg = smem_o + buf * out_tile_bytes;
             int const x = x0 + static_cast<int>(row);
             size_t const pixel = static_cast<size_t>(y) * P.W + x;
-            for (int c0 = 0; c0 < P.N && !(P.debug & 4); c0 += 32)
+            for (int c0 = c_begin; c0 < c_end && !(P.debug & 4); c0 += 32)
             {
                 // two 16-column loads in flight, one wait (N is a multiple of 16: the second
                 // half is warp-uniformly skipped on the last odd chunk)
                 uint32_t r[32];
-                bool const two = c0 + 16 < P.N;
+                bool const two = c0 + 16 < c_end;
                 tc_ld16(taddr + static_cast<uint32_t>(c0), *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
                 if (two) tc_ld16(taddr + static_cast<uint32_t>(c0 + 16), *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
                 tc_ld_wait();
@@ -486,9 +492,14 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                         v[4 * j4 + 2] = __uint_as_float(r[16 * h + 4 * j4 + 2]) + b.z;
                         v[4 * j4 + 3] = __uint_as_float(r[16 * h + 4 * j4 + 3]) + b.w;
                     }
-                    if (simple_act)
+                    if (relu_act)
                     {
-                        // None / Relu / LeakyRelu without branches: max(v,0) + slope * min(v,0)
+#pragma unroll
+                        for (int j = 0; j < 16; j++) v[j] = fmaxf(v[j], 0.f);
+                    }
+                    else if (simple_act)
+                    {
+                        // None / LeakyRelu without per-element branches: max(v,0) + slope * min(v,0)
 #pragma unroll
                         for (int j = 0; j < 16; j++) v[j] = fmaf(neg_slope, fminf(v[j], 0.f), fmaxf(v[j], 0.f));
                     }
@@ -523,6 +534,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                     }
                 }
             }
+            TC_PROF_ADD(2);
             // TMEM accumulator is free as soon as it has been read
             tc_fence_before();
             __syncwarp();
@@ -535,8 +547,11 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                 // the store that last read the OTHER staging tile is done, so that after the barrier
                 // every thread may start overwriting it for the next tile
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                TC_PROF_ADD(1);
                 if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                TC_PROF_ADD(3);
+                asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+                TC_PROF_ADD(4);
                 if (issuer)
                 {
                     for (int oc = 0; oc * 64 < P.N; oc++)
@@ -554,6 +569,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
         {
             atomicAdd(P.prof + 5, static_cast<unsigned long long>(prof_acc[0]));
             atomicAdd(P.prof + 6, static_cast<unsigned long long>(prof_acc[1]));
+            for (int k = 2; k < 5; k++) atomicAdd(P.prof + 7 + k, static_cast<unsigned long long>(prof_acc[k]));
         }
     }
 
@@ -748,9 +764,9 @@ void ConvTcRun(ConvTc const* op, float const* bias, void* out, cudaStream_t stre
         ML_CUDA_CHECK(cudaMemcpy(h, op->p.prof, sizeof(h), cudaMemcpyDeviceToHost));
         double const per = 1.0 / (static_cast<double>(op->grid) * ((op->p.n_tiles + op->grid - 1) / op->grid));
         std::fprintf(stderr, "[tc prof] N=%d cycles/tile: producer wait_empty %.0f other %.0f | mma wait_acc_empty %.0f "
-                     "wait_full %.0f issue %.0f commit %.0f rest %.0f | epilogue wait_acc_full %.0f body %.0f\n", op->p.N,
+                     "wait_full %.0f issue %.0f commit %.0f rest %.0f | epilogue wait_acc_full %.0f other %.0f ld+math+sts %.0f wait_store %.0f barrier %.0f\n", op->p.N,
                      h[0] * per, h[1] * per, h[2] * per, h[3] * per, h[4] * per, h[7] * per, h[8] * per, h[5] * per,
-                     h[6] * per);
+                     h[6] * per, h[9] * per, h[10] * per, h[11] * per);
     }
 }
 
