@@ -48,6 +48,7 @@ def parse_args():
     ap.add_argument("--spp", type=int, default=WORKLOAD["spp"], help=argparse.SUPPRESS)  # debugging only
     ap.add_argument("--no-cpu-baseline", action="store_true", help=argparse.SUPPRESS)
     ap.add_argument("--no-brute", action="store_true", help=argparse.SUPPRESS)
+    ap.add_argument("--no-inference", action="store_true", help=argparse.SUPPRESS)
     return ap.parse_args()
 
 
@@ -164,6 +165,126 @@ def run_reference_arm(args):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- inference leg (config 5)
+NET = dict(name="denoiser_conv3x3_w64_d6_residual", width=64, depth=6, batch=8)
+
+
+def cpu_inference_sample(layers, threads=0):
+    """Oracle (fp32 direct conv, all host threads) on a 768x768 crop; scaled to 1080p images/s by pixels."""
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle_lib as O
+    x = np.random.default_rng(3).random((768, 768, 3), dtype=np.float32)
+    t0 = time.perf_counter()
+    O.run_denoiser(x, layers, alpha=0.1, threads=threads)
+    dt = time.perf_counter() - t0
+    return (768 * 768) / (WORKLOAD["width"] * WORKLOAD["height"]) / dt, dt
+
+
+def inference_leg(ctx, scene, cam, light, params, rank, world, dist, torch, dev, no_cpu):
+    """BASELINE config 5: the rendered 1080p frame feeds the image-to-image conv net, batch 8, bf16 on
+    the tensor cores.  images/s device-resident, end to end from host buffers (mlxInferBatch), the
+    dominant kernel against the tensor roofline, and render -> infer with no host bounce."""
+    import tempfile
+    from simpleraytracer_b200 import api, graphdef_writer as gw
+    W, H = params.width, params.height
+    with tempfile.TemporaryDirectory() as d:
+        path = Path(d) / "net.pb"
+        _, layers = gw.make_denoiser(path, channels=3, width=NET["width"], depth=NET["depth"], seed=0)
+        model = ctx.create_model(path)
+    i, o = model.info()
+    i.width, i.height = W, H
+    model.set_input_info(i)
+    n_img = max(NET["batch"] // world, 1)
+    rng = np.random.default_rng(10 + rank)
+    ins = [ctx.create_image(W, H, 3) for _ in range(n_img)]
+    outs = [ctx.create_image(W, H, 3) for _ in range(n_img)]
+    x = rng.random((H, W, 3), dtype=np.float32)
+    for a in ins:
+        a.write(x)                    # host copy authoritative: every infer uploads it (reference semantics)
+    res = {}
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, reps):
+        fn()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fn()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        return float(dt.item()) / reps
+
+    for prec, key in ((api.MLX_PRECISION_FP32, "fp32"), (api.MLX_PRECISION_BF16, "bf16")):
+        model.set_precision(prec)
+        # e2e: host buffers in, host buffers out (outputs' host pointers were handed out by read())
+        for b in outs:
+            b.read()
+        t = timed(lambda: model.infer_batch(ins, outs), 3 if key == "bf16" else 1)
+        res[key + "_e2e_images_per_s"] = n_img * world / t
+        # device resident: inputs and outputs stay in HBM
+        for a in ins:
+            a.device_pointer(False); a.device_pointer(True)
+        fresh = [ctx.create_image(W, H, 3) for _ in range(n_img)]   # host pointer never handed out: no D2H
+        t = timed(lambda: model.infer_batch(ins, fresh), 5 if key == "bf16" else 1)
+        res[key + "_images_per_s"] = n_img * world / t
+        if rank == 0:
+            res[key + "_ops"] = model.profile(ins[0], fresh[0])
+        for f in fresh:
+            f.release()
+        for a in ins:
+            a.write(x)
+    res["tc_layers"] = model.tensor_core_layers()
+    res["launches_per_image"] = model.launch_count()
+
+    # render -> infer on the device (full frame on every rank: replicas, no exchange)
+    frame = ctx.create_image(W, H, 3)
+    den = ctx.create_image(W, H, 3)
+    p1 = api.make_params(W, H, spp=params.spp, jitter=1, seed=params.seed, shade=params.shade,
+                         accel=api.SRT_ACCEL_BVH, background=tuple(params.background))
+    def render_infer():
+        scene.render_to_image(cam, light, p1, frame)
+        model.infer(frame, den)
+    res["render_plus_infer_ms"] = timed(render_infer, 2) * 1e3
+    cpu = None
+    if rank == 0 and not no_cpu:
+        v, dt = cpu_inference_sample(layers)
+        cpu = {"value": v, "unit": "images/s", "cores": os.cpu_count(), "kind": "port",
+               "sample": f"fp32 conv oracle on one 768x768 crop ({dt:.1f} s), scaled to 1920x1080 by pixel count"}
+    for obj in ins + outs + [frame, den, model]:
+        obj.release()
+    if rank != 0:
+        return None
+    peaks, src = measured_peaks()
+    ops = res.pop("bf16_ops")
+    fp32_ops = res.pop("fp32_ops")
+    k = max(range(len(ops)), key=lambda j: ops[j][0])
+    ms, fl, by = ops[k]
+    conv_ms = sum(o[0] for o in ops)
+    roof = {"bound": "tensor", "kernel": f"conv3x3_tc_kernel<64> (op {k}: 3x3 conv 64->64 + bias + relu, bf16 in/out)",
+            "achieved": fl / (ms * 1e-3) / 1e12, "peak": peaks.get("bf16_tflops"), "unit": "TFLOP/s",
+            "frac": fl / (ms * 1e-3) / 1e12 / peaks["bf16_tflops"] if peaks.get("bf16_tflops") else None,
+            "peak_source": f"MEASURED_PEAKS.json bf16_tflops (burst: kernel timed alone), {src}",
+            "kernel_ms": ms, "algorithmic_flops_per_launch": fl, "algorithmic_bytes_per_launch": by,
+            "hbm_gbs_achieved": by / (ms * 1e-3) / 1e9, "hbm_frac": by / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
+            "traffic": None, "all_ops_ms": [round(o[0], 4) for o in ops], "sum_ops_ms": conv_ms,
+            "fp32_all_ops_ms": [round(o[0], 4) for o in fp32_ops]}
+    return {"metric": "images/s (1080p image-to-image conv net, batch 8)", "unit": "images/s",
+            "config": {"workload": "infer_1080p_" + NET["name"], "batch": NET["batch"], "images_per_rank": n_img,
+                       "width": W, "height": H, "net": NET["name"], "weights": "random-init (He), seed 0",
+                       "parallelism": f"images_dp{world}" if world > 1 else "single_gpu"},
+            "dtype": "bf16", "value": res["bf16_images_per_s"],
+            "e2e": {"value": res["bf16_e2e_images_per_s"], "unit": "images/s",
+                    "h2d_bytes_per_step": NET["batch"] * W * H * 12, "d2h_bytes_per_step": NET["batch"] * W * H * 12},
+            "fp32": {"value": res["fp32_images_per_s"], "e2e": res["fp32_e2e_images_per_s"]},
+            "tensor_core_layers": res["tc_layers"], "launches_per_image": res["launches_per_image"],
+            "render_plus_infer_ms": res["render_plus_infer_ms"], "roofline": roof, "cpu_baseline": cpu}
 
 
 # --------------------------------------------------------------------------- GPU arm
@@ -310,6 +431,14 @@ def run_b200_arm(args):
     if world > 1:
         dist.all_reduce(d2h)
 
+    inference = None
+    if not args.no_inference:
+        try:
+            inference = inference_leg(ctx, scene, cam, light, params, rank, world, dist, torch, dev,
+                                      args.no_cpu_baseline)
+        except Exception as e:  # noqa: BLE001  -- the headline render numbers must still be reported
+            inference = {"error": f"{type(e).__name__}: {e}"}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -369,7 +498,7 @@ def run_b200_arm(args):
                    "rays_per_step": rays_per_step, "primary_rays": primary, "shadow_rays": shadow,
                    "bvh_nodes": int(info.n_bvh_nodes), "bvh_build_ms": info.bvh_build_ms,
                    "scene_upload_ms": info.upload_ms, "wall_s_timed_region": wall_s},
-        "roofline": roofline, "intersect_roofline": brute, "cpu_baseline": cpu,
+        "roofline": roofline, "intersect_roofline": brute, "cpu_baseline": cpu, "inference": inference,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(api.srt_render_params)
                 + C.sizeof(api.srt_camera) + C.sizeof(api.srt_light), "d2h_bytes_per_step": int(d2h.item())},
         "gpu_launches": args.steps, "clocks": clocks.summary(),

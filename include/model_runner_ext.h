@@ -59,6 +59,20 @@ ML_API_ENTRY void mlxIpcClose(ml_context context, void* device_pointer);
 ML_API_ENTRY ml_status mlxSetModelPrecision(ml_model model, int precision);
 ML_API_ENTRY size_t mlxModelTensorCoreLayers(ml_model model);
 
+/* `count` independent mlInfer() calls as one pipelined batch (the reference API is batch-1 only,
+ * model.cpp:208-213): the host->device copy of image i+1 and the device->host copy of result i-1
+ * run on copy streams while the kernels of image i execute.  Per-image checks and error messages
+ * are those of mlInfer, prefixed "Image <i>: ".  Synchronous like mlInfer: on ML_OK every output
+ * is complete. */
+ML_API_ENTRY ml_status mlxInferBatch(ml_model model, ml_image const* inputs, ml_image const* outputs, size_t count);
+
+/* One mlInfer() with every fused op of the plan timed on the device (CUDA events, op by op).
+ * op_ms / op_flops / op_bytes (each may be NULL) receive, for the first max_ops ops in execution
+ * order (the order mlxInspectModel lists them), the duration in ms and the ALGORITHMIC flops and
+ * bytes of the op; *n_ops receives the number of ops.  Measurement aid for roofline reports. */
+ML_API_ENTRY ml_status mlxProfileModel(ml_model model, ml_image input, ml_image output, float* op_ms,
+                                       double* op_flops, double* op_bytes, size_t max_ops, size_t* n_ops);
+
 /* Number of kernel launches one mlInfer() of this model enqueues. */
 ML_API_ENTRY size_t mlxModelLaunchCount(ml_model model);
 

@@ -100,6 +100,9 @@ _PROTOTYPES = {
     "mlxImageDevicePointer": (C.c_void_p, [C.c_void_p, C.c_int, C.c_void_p]),
     "mlxModelLaunchCount": (C.c_size_t, [C.c_void_p]),
     "mlxSetModelPrecision": (C.c_int, [C.c_void_p, C.c_int]),
+    "mlxProfileModel": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                  C.c_void_p]),
+    "mlxInferBatch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t]),
     "mlxModelTensorCoreLayers": (C.c_size_t, [C.c_void_p]),
     "mlxCreateContextOnDevice": (C.c_void_p, [C.c_int]),
     "mlxIpcExportImage": (C.c_int, [C.c_void_p, C.c_void_p]),
@@ -301,6 +304,22 @@ class Model:
 
     def infer(self, inp: Image, out: Image):
         if self.lib.mlInfer(self.handle, inp.handle, out.handle) != ML_OK:
+            raise MLError(self.error())
+
+    def profile(self, inp: Image, out: Image, max_ops=256):
+        """mlxProfileModel: [(ms, algorithmic flops, algorithmic bytes)] per fused op, device-timed."""
+        ms = (C.c_float * max_ops)(); fl = (C.c_double * max_ops)(); by = (C.c_double * max_ops)()
+        n = C.c_size_t(0)
+        if self.lib.mlxProfileModel(self.handle, inp.handle, out.handle, ms, fl, by, max_ops, C.byref(n)) != ML_OK:
+            raise MLError(self.error())
+        return [(float(ms[k]), float(fl[k]), float(by[k])) for k in range(min(n.value, max_ops))]
+
+    def infer_batch(self, inputs, outputs):
+        """mlxInferBatch: pipelined batch of independent inferences."""
+        n = len(inputs)
+        ia = (C.c_void_p * n)(*[i.handle for i in inputs])
+        oa = (C.c_void_p * n)(*[o.handle for o in outputs])
+        if self.lib.mlxInferBatch(self.handle, ia, oa, n) != ML_OK:
             raise MLError(self.error())
 
     def release(self):

@@ -63,6 +63,8 @@ struct DeviceState
 {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_in = nullptr;   // H2D of the next image while the current one computes (mlxInferBatch)
+    cudaStream_t copy_out = nullptr;  // D2H of the previous result
     cudaEvent_t ev_start = nullptr;
     cudaEvent_t ev_stop = nullptr;
     cudaDeviceProp prop{};

@@ -41,6 +41,8 @@ DeviceState::DeviceState(int requested_device)
     ML_CUDA_CHECK(cudaSetDevice(device));
     ML_CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
     ML_CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    ML_CUDA_CHECK(cudaStreamCreateWithFlags(&copy_in, cudaStreamNonBlocking));
+    ML_CUDA_CHECK(cudaStreamCreateWithFlags(&copy_out, cudaStreamNonBlocking));
     ML_CUDA_CHECK(cudaEventCreate(&ev_start));
     ML_CUDA_CHECK(cudaEventCreate(&ev_stop));
 }
@@ -51,6 +53,8 @@ DeviceState::~DeviceState()
     cudaSetDevice(device);
     if (ev_start) cudaEventDestroy(ev_start);
     if (ev_stop) cudaEventDestroy(ev_stop);
+    if (copy_in) cudaStreamDestroy(copy_in);
+    if (copy_out) cudaStreamDestroy(copy_out);
     if (stream) cudaStreamDestroy(stream);
 }
 

@@ -160,6 +160,7 @@ Model::~Model()
     cudaStreamSynchronize(m_device->stream);
     ReleaseBuffers();
     for (void* p : m_packed) cudaFree(p);
+    for (cudaEvent_t e : m_events) cudaEventDestroy(e);
     for (auto& c : m_consts) cudaFree(c.dev);
 }
 
@@ -816,12 +817,16 @@ ml_status Model::SetInputInfo(ml_image_info const* info)
 
 void Model::Run(float const* d_in, float* d_out, cudaStream_t stream)
 {
+    for (Op const& op : m_ops) RunOp(op, d_in, d_out, stream);
+}
+
+void Model::RunOp(Op const& op, float const* d_in, float* d_out, cudaStream_t stream)
+{
     auto ptr = [&](int t) -> float* {
         if (t == m_input_tensor) return const_cast<float*>(d_in);
         if (t == m_output_tensor) return d_out;
         return static_cast<float*>(m_buffers[m_tensors[t].buffer]); // bf16 tensors: same storage, 2-byte elements
     };
-    for (Op const& op : m_ops)
     {
         TensorInfo const& a = m_tensors[op.in[0]];
         TensorInfo const& o = m_tensors[op.out];
@@ -885,20 +890,19 @@ void Model::Run(float const* d_in, float* d_out, cudaStream_t stream)
     }
 }
 
-ml_status Model::Infer(ml_image input, ml_image output)
+bool Model::CheckInferArgs(ml_image input, ml_image output)
 {
-    m_error.clear();
     Image* in = Image::FromHandle(input);
     Image* out = Image::FromHandle(output);
     if (in == nullptr)
     {
         m_error = "Bad input image handle";
-        return ML_FAIL;
+        return false;
     }
     if (out == nullptr)
     {
         m_error = "Bad output image handle";
-        return ML_FAIL;
+        return false;
     }
 
     ml_image_info const& oi = out->Info();
@@ -913,7 +917,7 @@ ml_status Model::Infer(ml_image input, ml_image output)
         }
         return true;
     });
-    if (!ok) return ML_FAIL;
+    if (!ok) return false;
 
     ok = ForEachDim([&](auto dim, char const* name) {
         if (m_input_info.*dim == 0)
@@ -923,7 +927,7 @@ ml_status Model::Infer(ml_image input, ml_image output)
         }
         return true;
     });
-    if (!ok) return ML_FAIL;
+    if (!ok) return false;
 
     size_t const item = DataTypeSize(m_input_info.dtype);
     size_t const in_bytes = m_input_info.width * m_input_info.height * m_input_info.channels * item;
@@ -933,15 +937,27 @@ ml_status Model::Infer(ml_image input, ml_image output)
         std::ostringstream os;
         os << "Internal error: input size does not match: " << in->Bytes() << " vs " << in_bytes;
         m_error = os.str();
-        return ML_FAIL;
+        return false;
     }
     if (out->Bytes() != out_bytes)
     {
         std::ostringstream os;
         os << "Internal error: output size does not match: " << out->Bytes() << " vs " << out_bytes;
         m_error = os.str();
-        return ML_FAIL;
+        return false;
     }
+    return true;
+}
+
+ml_status Model::Infer(ml_image input, ml_image output)
+{
+    m_error.clear();
+    if (!CheckInferArgs(input, output)) return ML_FAIL;
+    Image* in = Image::FromHandle(input);
+    Image* out = Image::FromHandle(output);
+    size_t const item = DataTypeSize(m_input_info.dtype);
+    size_t const in_bytes = in->Bytes();
+    size_t const out_bytes = out->Bytes();
 
     try
     {
@@ -961,6 +977,127 @@ ml_status Model::Infer(ml_image input, ml_image output)
         else
         {
             Run(static_cast<float const*>(d_in), static_cast<float*>(d_out), s);
+        }
+        out->CommitDeviceWrite(s);
+        ML_CUDA_CHECK(cudaStreamSynchronize(s));
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        m_error = std::string("Inference error: ") + e.what();
+        return ML_FAIL;
+    }
+}
+
+ml_status Model::InferBatch(ml_image const* inputs, ml_image const* outputs, size_t n)
+{
+    m_error.clear();
+    if ((inputs == nullptr || outputs == nullptr) && n != 0)
+    {
+        m_error = "Bad image array argument";
+        return ML_FAIL;
+    }
+    for (size_t i = 0; i < n; i++)
+        if (!CheckInferArgs(inputs[i], outputs[i]))
+        {
+            m_error = "Image " + std::to_string(i) + ": " + m_error;
+            return ML_FAIL;
+        }
+    if (m_input_info.dtype == ML_FLOAT16)
+    {
+        // the fp16 <-> fp32 staging buffers are single: run one after the other
+        for (size_t i = 0; i < n; i++)
+            if (Infer(inputs[i], outputs[i]) != ML_OK) return ML_FAIL;
+        return ML_OK;
+    }
+    try
+    {
+        if (!m_ready) throw std::runtime_error("model input shape has not been set");
+        m_device->MakeCurrent();
+        cudaStream_t const s_in = m_device->copy_in, s_run = m_device->stream, s_out = m_device->copy_out;
+        while (m_events.size() < 2 * n)
+        {
+            cudaEvent_t e = nullptr;
+            ML_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            m_events.push_back(e);
+        }
+        for (size_t i = 0; i < n; i++)
+        {
+            Image* in = Image::FromHandle(inputs[i]);
+            Image* out = Image::FromHandle(outputs[i]);
+            if (in->Device()->device != m_device->device || out->Device()->device != m_device->device)
+                throw std::runtime_error("images and model live on different devices");
+            // upload (if the host copy is the valid one) on the copy-in stream, ahead of the kernels
+            void* d_in = in->DeviceRead(s_in);
+            ML_CUDA_CHECK(cudaEventRecord(m_events[2 * i], s_in));
+            ML_CUDA_CHECK(cudaStreamWaitEvent(s_run, m_events[2 * i], 0));
+            void* d_out = out->DeviceWrite();
+            Run(static_cast<float const*>(d_in), static_cast<float*>(d_out), s_run);
+            ML_CUDA_CHECK(cudaEventRecord(m_events[2 * i + 1], s_run));
+            // read-back (if the caller holds the host pointer) on the copy-out stream, behind the kernels
+            ML_CUDA_CHECK(cudaStreamWaitEvent(s_out, m_events[2 * i + 1], 0));
+            out->CommitDeviceWrite(s_out);
+        }
+        ML_CUDA_CHECK(cudaStreamSynchronize(s_in));
+        ML_CUDA_CHECK(cudaStreamSynchronize(s_run));
+        ML_CUDA_CHECK(cudaStreamSynchronize(s_out));
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        cudaStreamSynchronize(m_device->copy_in);
+        cudaStreamSynchronize(m_device->stream);
+        cudaStreamSynchronize(m_device->copy_out);
+        m_error = std::string("Inference error: ") + e.what();
+        return ML_FAIL;
+    }
+}
+
+// One inference with every op bracketed by CUDA events on the compute stream (op by op, so the
+// numbers are kernel durations, not a pipeline).  flops/bytes are the ALGORITHMIC figures of
+// conv 2*OH*OW*KH*KW*Cin*Cout and (in + out) elements in their stored width + filter.
+ml_status Model::Profile(ml_image input, ml_image output, float* op_ms, double* op_flops, double* op_bytes,
+                         size_t max_ops, size_t* n_ops)
+{
+    m_error.clear();
+    if (n_ops != nullptr) *n_ops = m_ops.size();
+    if (!CheckInferArgs(input, output)) return ML_FAIL;
+    try
+    {
+        if (!m_ready) throw std::runtime_error("model input shape has not been set");
+        if (m_input_info.dtype != ML_FLOAT32) throw std::runtime_error("profiling needs ML_FLOAT32 images");
+        Image* in = Image::FromHandle(input);
+        Image* out = Image::FromHandle(output);
+        m_device->MakeCurrent();
+        cudaStream_t s = m_device->stream;
+        float const* d_in = static_cast<float const*>(in->DeviceRead(s));
+        float* d_out = static_cast<float*>(out->DeviceWrite());
+        ML_CUDA_CHECK(cudaStreamSynchronize(s));
+        for (size_t i = 0; i < m_ops.size(); i++)
+        {
+            Op const& op = m_ops[i];
+            ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s));
+            RunOp(op, d_in, d_out, s);
+            ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, s));
+            ML_CUDA_CHECK(cudaStreamSynchronize(s));
+            float ms = 0.f;
+            ML_CUDA_CHECK(cudaEventElapsedTime(&ms, m_device->ev_start, m_device->ev_stop));
+            if (i >= max_ops) continue;
+            TensorInfo const& o = m_tensors[op.out];
+            double const out_elems = static_cast<double>(o.H) * o.W * o.C;
+            double flops = out_elems, bytes = 0;
+            for (int t : op.in)
+                bytes += static_cast<double>(m_tensors[t].H) * m_tensors[t].W * m_tensors[t].C * (m_tensors[t].bf16 ? 2 : 4);
+            bytes += out_elems * (o.bf16 ? 2 : 4);
+            if (op.kind == OpKind::Conv)
+            {
+                TensorInfo const& a = m_tensors[op.in[0]];
+                flops = 2.0 * out_elems * op.KH * op.KW * a.C;
+                bytes += static_cast<double>(op.KH) * op.KW * a.C * o.C * (op.tc ? 2 : 4);
+            }
+            if (op_ms != nullptr) op_ms[i] = ms;
+            if (op_flops != nullptr) op_flops[i] = flops;
+            if (op_bytes != nullptr) op_bytes[i] = bytes;
         }
         out->CommitDeviceWrite(s);
         ML_CUDA_CHECK(cudaStreamSynchronize(s));
@@ -1014,6 +1151,33 @@ ML_API_ENTRY ml_status mlInfer(ml_model model, ml_image input, ml_image output)
     try
     {
         return ML::Model::FromHandle(model)->Infer(input, output);
+    }
+    catch (...)
+    {
+        return ML_FAIL;
+    }
+}
+
+ML_API_ENTRY ml_status mlxInferBatch(ml_model model, ml_image const* inputs, ml_image const* outputs, size_t count)
+{
+    if (ML::Model::FromHandle(model) == nullptr) return ML_FAIL;
+    try
+    {
+        return ML::Model::FromHandle(model)->InferBatch(inputs, outputs, count);
+    }
+    catch (...)
+    {
+        return ML_FAIL;
+    }
+}
+
+ML_API_ENTRY ml_status mlxProfileModel(ml_model model, ml_image input, ml_image output, float* op_ms,
+                                       double* op_flops, double* op_bytes, size_t max_ops, size_t* n_ops)
+{
+    if (ML::Model::FromHandle(model) == nullptr) return ML_FAIL;
+    try
+    {
+        return ML::Model::FromHandle(model)->Profile(input, output, op_ms, op_flops, op_bytes, max_ops, n_ops);
     }
     catch (...)
     {

@@ -27,7 +27,12 @@ public:
     ml_status GetInfo(ml_image_info* input_info, ml_image_info* output_info);
     ml_status SetInputInfo(ml_image_info const* info);
     ml_status Infer(ml_image input, ml_image output);
+    // n independent inferences, pipelined: H2D of image i+1 and D2H of result i-1 overlap the
+    // kernels of image i (three streams).  Same checks and messages as Infer, per image.
+    ml_status InferBatch(ml_image const* inputs, ml_image const* outputs, size_t n);
     char* GetError(char* buffer, size_t buffer_size) const;
+    ml_status Profile(ml_image input, ml_image output, float* op_ms, double* op_flops, double* op_bytes,
+                      size_t max_ops, size_t* n_ops);
 
     // Arithmetic of the wide 3x3 layers: 0 = fp32 on CUDA cores (default), 1 = bf16 on the
     // tensor cores (tcgen05, fp32 accumulation) wherever conv_tc_kernels.cu supports the layer.
@@ -99,6 +104,8 @@ private:
     int AddConst(std::vector<float> values);
     int NewTensor(int channels);
     void Run(float const* d_in, float* d_out, cudaStream_t stream);
+    void RunOp(Op const& op, float const* d_in, float* d_out, cudaStream_t stream);
+    bool CheckInferArgs(ml_image input, ml_image output); // sets m_error, false on failure
     nn::ConvDesc MakeConvDesc(Op const& op) const;
 
     DeviceStatePtr m_device;
@@ -117,6 +124,7 @@ private:
     int m_output_tensor = -1;
 
     int m_precision = 0;
+    std::vector<cudaEvent_t> m_events; // pool for InferBatch
     std::vector<void*> m_packed;  // device copies of repacked bf16 filters
     std::vector<void*> m_buffers;
     std::vector<size_t> m_buffer_bytes;

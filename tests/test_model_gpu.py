@@ -401,3 +401,34 @@ def test_bf16_tensor_core_denoiser(ctx, tmp_path, cfg):
     assert np.array_equal(out.read(), fp32)
     for obj in (inp, out, model):
         obj.release()
+
+
+@pytest.mark.parametrize("precision", [api.MLX_PRECISION_FP32, api.MLX_PRECISION_BF16])
+def test_infer_batch_equals_single_infers(ctx, tmp_path, precision):
+    """mlxInferBatch (SURVEY N4): pipelined batch == the same mlInfer calls one by one, bit for bit;
+    host-written inputs are uploaded inside the call, mapped outputs are read back inside the call."""
+    path = tmp_path / "d.pb"
+    gw.make_denoiser(path, channels=3, width=32, depth=3, seed=2)
+    w, h, n = 200, 64, 5
+    model, i, o = prepared_model(ctx, path, w, h)
+    model.set_precision(precision)
+    rng = np.random.default_rng(8)
+    xs = [rng.random((h, w, 3), dtype=np.float32) for _ in range(n)]
+    ins = [ctx.create_image(w, h, 3) for _ in range(n)]
+    outs = [ctx.create_image(w, h, 3) for _ in range(n)]
+    single = []
+    for x, a, b in zip(xs, ins, outs):
+        a.write(x)
+        model.infer(a, b)
+        single.append(b.read().copy())
+        b.write(np.zeros_like(x))            # host pointer handed out + stale content
+    model.infer_batch(ins, outs)
+    for k in range(n):
+        assert np.array_equal(outs[k].read(), single[k]), f"image {k}"
+    # per-image checks keep mlInfer's messages
+    bad = ctx.create_image(w + 1, h, 3)
+    with pytest.raises(api.MLError, match=r"Image 1: Output image width dimension 201 does not match 200"):
+        model.infer_batch(ins[:2], [outs[0], bad])
+    model.infer_batch([], [])
+    for obj in ins + outs + [bad, model]:
+        obj.release()
