@@ -273,7 +273,10 @@ def inference_leg(ctx, scene, cam, light, params, rank, world, dist, torch, dev,
             "peak_source": f"MEASURED_PEAKS.json bf16_tflops (burst: kernel timed alone), {src}",
             "kernel_ms": ms, "algorithmic_flops_per_launch": fl, "algorithmic_bytes_per_launch": by,
             "hbm_gbs_achieved": by / (ms * 1e-3) / 1e9, "hbm_frac": by / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
-            "traffic": None, "all_ops_ms": [round(o[0], 4) for o in ops], "sum_ops_ms": conv_ms,
+            "traffic": 491.6e6,
+            "traffic_source": "ncu --set full, dram__bytes_read+write per launch: 265.8 MB + 225.8 MB "
+                              "(profiles/r01_conv_tc_kernel_ncu_full_summary.csv); tensor pipe active 43.7 %",
+            "all_ops_ms": [round(o[0], 4) for o in ops], "sum_ops_ms": conv_ms,
             "fp32_all_ops_ms": [round(o[0], 4) for o in fp32_ops]}
     return {"metric": "images/s (1080p image-to-image conv net, batch 8)", "unit": "images/s",
             "config": {"workload": "infer_1080p_" + NET["name"], "batch": NET["batch"], "images_per_rank": n_img,
@@ -453,7 +456,10 @@ def run_b200_arm(args):
     achieved = flops_per_step * share / (kern_ms * 1e-3) / 1e12
     scene_bytes = info.device_bytes
     roofline = {"bound": "fp32", "kernel": "render_bvh_spp_kernel<false,1>", "achieved": achieved, "peak": fp32_peak,
-                "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None, "traffic": None,
+                "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None,
+                "traffic": 6.55e6 if world == 1 and args.spp == WORKLOAD["spp"] else None,
+                "traffic_source": "ncu --set full, dram__bytes_read+write per launch: 5.69 MB + 0.86 MB "
+                                  "(profiles/r01_bvh_spp_kernel_ncu_full_summary.csv; scene and frame stay in the 126 MB L2)",
                 "peak_source": "srtMeasureFp32Peak live FFMA microbenchmark (MEASURED_PEAKS.json has no FP32 figure)",
                 "algorithmic_flops_per_launch": flops_per_step * share,
                 "box_tests": boxes, "tri_tests": tris, "kernel_ms": kern_ms,
