@@ -25,7 +25,7 @@ struct F4 { float x, y, z, w; };
 
 constexpr int kTriTile = 256;      // triangles per shared-memory tile (12 KB)
 constexpr int kMaxLeafTris = 8;    // largest BVH leaf the encoding is used with
-constexpr int kDefaultLeafTris = 4; // BVH leaf size
+constexpr int kDefaultLeafTris = 2; // BVH leaf size
 constexpr int kLeafCountBits = 4;  // child ref: ~ref = (first << 4) | (count-1)
 constexpr int kBvhStackDepth = 64;
 

@@ -18,7 +18,7 @@ def main():
     for v in values:
         env = dict(os.environ)
         env[knob] = v
-        r = subprocess.run([sys.executable, str(ROOT / "bench.py")] + bench_args, env=env, capture_output=True, text=True)
+        r = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--no-inference"] + bench_args, env=env, capture_output=True, text=True)
         try:
             d = json.loads(r.stdout.strip().splitlines()[-1])
             rl = d["roofline"]
