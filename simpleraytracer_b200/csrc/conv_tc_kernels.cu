@@ -164,18 +164,43 @@ __device__ __forceinline__ void tc_commit(uint64_t* bar)
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                  ::"r"(smem_addr(bar)) : "memory");
 }
-// D[tmem] (+)= A[smem] * B[smem], bf16 x bf16 -> fp32, issued by ONE thread for the CTA.
-__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                            uint32_t accumulate)
+// D[tmem] (+)= A[smem] * B[smem], bf16 x bf16 -> fp32, issued by ONE thread for the CTA.  The
+// descriptors are given as 32-bit halves: both share the constant high word, the low words are
+// base + compile-time offset, so the single issuing warp spends ~3 uniform-datapath instructions per
+// MMA (8 with 64-bit descriptor arithmetic and a run-time predicate -- that bounded the issue rate
+// at N = 64).  ALWAYS_ACCUMULATE = false: D is overwritten when `accumulate` is 0 (a tile's first MMA).
+template <bool ALWAYS_ACCUMULATE>
+__device__ __forceinline__ void tc_mma_bf16_lohi(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t hi,
+                                                 uint32_t idesc, uint32_t accumulate)
 {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-        "}\n"
-        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
+    if (ALWAYS_ACCUMULATE)
+    {
+        asm volatile(
+            "{\n"
+            ".reg .b64 da, db;\n"
+            ".reg .pred p;\n"
+            "setp.eq.b32 p, 0, 0;\n"
+            "mov.b64 da, {%1, %3};\n"
+            "mov.b64 db, {%2, %3};\n"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n"
+            "}\n"
+            ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc)
+            : "memory");
+    }
+    else
+    {
+        asm volatile(
+            "{\n"
+            ".reg .b64 da, db;\n"
+            ".reg .pred p;\n"
+            "setp.ne.b32 p, %5, 0;\n"
+            "mov.b64 da, {%1, %3};\n"
+            "mov.b64 db, {%2, %3};\n"
+            "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n"
+            "}\n"
+            ::"r"(d_tmem), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(accumulate)
+            : "memory");
+    }
 }
 // 32 lanes x 16 consecutive fp32 columns of TMEM -> 16 registers per thread.
 __device__ __forceinline__ void tc_ld16(uint32_t taddr, uint32_t (&r)[16])
@@ -364,11 +389,14 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
         // Everything of the two shared-memory descriptors except the start address is constant;
         // (addr >> 4) stays below 2^14 for any address inside the 227 KB window, so stages, taps and
         // K steps are plain additions to the low word.
-        uint64_t const desc_hi = umma_desc(0u, P.sbo, P.layout_type);
-        uint32_t const a_lo0 = smem_addr(smem_a) >> 4, b_lo0 = smem_addr(smem_b) >> 4;
+        uint64_t const desc0 = umma_desc(0u, P.sbo, P.layout_type);
+        uint32_t const desc_hi = static_cast<uint32_t>(desc0 >> 32);
+        uint32_t const lo_flags = static_cast<uint32_t>(desc0);          // LBO field; start address added below
+        uint32_t const a_lo0 = (smem_addr(smem_a) >> 4) + lo_flags, b_lo0 = (smem_addr(smem_b) >> 4) + lo_flags;
         uint32_t const stage_u = a_stage_bytes >> 4, tap_u = static_cast<uint32_t>(P.tap_stride) >> 4;
         uint32_t const b_tile_u = b_tile_bytes >> 4, row_u = static_cast<uint32_t>(P.row_bytes) >> 4;
         uint32_t const rps = static_cast<uint32_t>(P.rps), n_chunks = static_cast<uint32_t>(P.n_chunks);
+        uint32_t const b_tap_u = n_chunks * b_tile_u, b_row_u = 3u * b_tap_u;
         uint32_t s = 0, ph = 0, acc = 0, aph = 0;
         TC_PROF_T0();
         for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x)
@@ -390,26 +418,33 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                     {
                         if (!(P.debug & 2))
                         {
-                            for (uint32_t r = 0; r < rps; r++)
+                            uint32_t const a_st = a_lo0 + s * stage_u;
+                            uint32_t const b_st = b_lo0 + kh0 * b_row_u + ch * b_tile_u;
+#pragma unroll
+                            for (uint32_t r = 0; r < 3u; r++)
                             {
-                                uint32_t const kh = kh0 + r;
-                                uint32_t const a_lo = a_lo0 + s * stage_u + r * row_u;
-                                uint32_t const b_lo = b_lo0 + (kh * 3u * n_chunks + ch) * b_tile_u;
-#pragma unroll
-                                for (uint32_t kw = 0; kw < 3u; kw++)
+                                if (r < rps)
                                 {
-                                    // halo mode: tap kw = the same box read from pixel row kw on (start kw * 128
-                                    // bytes into the 1024-byte swizzle pattern).  Measured on B200: the MMA
-                                    // applies the swizzle XOR to the ABSOLUTE shared-memory address bits, as TMA
-                                    // does, so a row-shifted start needs no base offset (descriptor bits [49,52)
-                                    // stay 0; setting them to (start >> 7) & 7 gives wrong results).
 #pragma unroll
-                                    for (uint32_t k = 0; k < KC / 16; k++)
+                                    for (uint32_t kw = 0; kw < 3u; kw++)
                                     {
-                                        // +32 bytes along K inside the swizzle row = +2 in the (addr >> 4) field
-                                        uint64_t const a_desc = desc_hi | (a_lo + kw * tap_u + 2u * k);
-                                        uint64_t const b_desc = desc_hi | (b_lo + kw * n_chunks * b_tile_u + 2u * k);
-                                        tc_mma_bf16(d_tmem, a_desc, b_desc, idesc, (kh | kw | k | ch) != 0u);
+                                        // halo mode: tap kw = the same box read from pixel row kw on (start
+                                        // kw * 128 bytes into the 1024-byte swizzle pattern).  Measured on
+                                        // B200: the MMA applies the swizzle XOR to the ABSOLUTE shared-memory
+                                        // address bits, as TMA does, so a row-shifted start needs no base
+                                        // offset (descriptor bits [49,52) stay 0; setting them to
+                                        // (start >> 7) & 7 gives wrong results).
+#pragma unroll
+                                        for (uint32_t k = 0; k < KC / 16; k++)
+                                        {
+                                            // +32 bytes along K inside the swizzle row = +2 in (addr >> 4)
+                                            uint32_t const a_lo = a_st + r * row_u + kw * tap_u + 2u * k;
+                                            uint32_t const b_lo = b_st + r * b_row_u + kw * b_tap_u + 2u * k;
+                                            if (r == 0 && kw == 0 && k == 0)   // the tile's first MMA overwrites D
+                                                tc_mma_bf16_lohi<false>(d_tmem, a_lo, b_lo, desc_hi, idesc, kh0 | ch);
+                                            else
+                                                tc_mma_bf16_lohi<true>(d_tmem, a_lo, b_lo, desc_hi, idesc, 1u);
+                                        }
                                     }
                                 }
                             }
