@@ -432,3 +432,33 @@ def test_infer_batch_equals_single_infers(ctx, tmp_path, precision):
     model.infer_batch([], [])
     for obj in ins + outs + [bad, model]:
         obj.release()
+
+
+def test_render_cli_pipes_into_reference_test_app(ctx, tmp_path):
+    """srt_render writes the headerless HWC fp32 wire format of test_app.cpp:137-192, so a
+    rendered frame can be piped straight into the reference's (unmodified) client."""
+    cli = ROOT / "simpleraytracer_b200" / "bin" / "srt_render"
+    exe = ROOT / "oracle" / "_ref" / "test_app"
+    if not cli.exists() or not exe.exists():
+        pytest.skip("srt_render / oracle/_ref/test_app not built")
+    W, H, n, spp = 160, 96, 3000, 8
+    r = subprocess.run([str(cli), "-s", "mesh", "-n", str(n), "-seed", "3", "-w", str(W), "-h", str(H),
+                        "-spp", str(spp)], capture_output=True, timeout=300)
+    assert r.returncode == 0, r.stderr
+    frame = np.frombuffer(r.stdout, np.float32).reshape(H, W, 3)
+    # the same frame through the library API
+    v, a, cam, light = api.gen_mesh(3, n, W, H)
+    scene = ctx.create_scene(v, a)
+    p = api.make_params(W, H, spp=spp, jitter=1, seed=3, shade=api.SRT_SHADE_SHADOW, accel=api.SRT_ACCEL_BVH,
+                        background=(0.5, 0.7, 0.9))
+    assert np.array_equal(frame, scene.render(cam, light, p)[0])
+    scene.release()
+    model = tmp_path / "denoiser.pb"
+    _, layers = gw.make_denoiser(model, channels=3, width=16, depth=3, seed=5)
+    out = subprocess.run([str(exe), "-m", str(model), "-w", str(W), "-h", str(H)], input=r.stdout,
+                         capture_output=True, timeout=300)
+    assert out.returncode == 0, out.stderr
+    y = np.frombuffer(out.stdout, np.float32).reshape(H, W, 3)
+    close(y, O.run_denoiser(frame, layers), "srt_render | test_app")
+    # CLI errors: status 255 like test_app
+    assert subprocess.run([str(cli), "-s", "mesh"], capture_output=True).returncode == 255
