@@ -154,7 +154,7 @@ def run_reference_arm(args):
         total_rays += rays
         total_s += dt
     value = total_rays / total_s / 1e6
-    sample = (f"first {min(CPU_SAMPLE_SPP, args.spp)} of {args.spp} spp of every pixel of the 1920x1080 frame per step "
+    sample = (f"first {min(CPU_SAMPLE_SPP, args.spp)} of {args.spp} spp of every pixel of the {params.width}x{params.height} frame per step "
               f"({total_rays // args.steps} rays), oracle BVH path incl. its BVH build")
     line = {
         "impl": "reference", "metric": "Mrays/s (closest-hit+shade, 1080p)", "value": value, "unit": "Mrays/s",
@@ -492,7 +492,7 @@ def run_b200_arm(args):
     if not args.no_cpu_baseline:
         cv, dt, crays, threads = cpu_sample(v, a, cam, light, params, min(CPU_SAMPLE_SPP, args.spp))
         cpu = {"value": cv, "unit": "Mrays/s", "cores": threads, "kind": "port",
-               "sample": f"first {min(CPU_SAMPLE_SPP, args.spp)} of {args.spp} spp of every pixel of the 1920x1080 frame "
+               "sample": f"first {min(CPU_SAMPLE_SPP, args.spp)} of {args.spp} spp of every pixel of the {params.width}x{params.height} frame "
                          f"({crays} rays, {dt:.1f} s), oracle BVH path incl. its BVH build"}
 
     line = {
