@@ -481,10 +481,20 @@ __device__ __forceinline__ float safe_inv(float d)
 
 // Culling only (docs/RENDER_SPEC.md section 6): boxes are padded at build time and
 // `t_far` carries a relative slack, so rounding here can only visit too much.
+//
+// `hint` (kNoHint = none) is the slot of a triangle a neighbouring ray hit: it is tested BEFORE the
+// traversal.  Closest hit: the traversal then starts with a tight t_far and culls every subtree
+// behind it; any hit: a still-valid occluder ends the query without touching the BVH.  The result
+// is unchanged -- the closest-hit winner is the lexicographic minimum of (t, id) whatever the test
+// order, occlusion is a boolean -- only the number of nodes visited drops.  On return best.slot
+// holds the occluder's slot when ANY found one (the next ray's hint).
+constexpr uint32_t kNoHint = 0xffffffffu;
+
 template <bool ANY, bool STATS>
 __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d, float t_min,
                                           Hit& best, bool& occluded,
-                                          unsigned long long& n_box, unsigned long long& n_tri)
+                                          unsigned long long& n_box, unsigned long long& n_tri,
+                                          uint32_t hint = kNoHint)
 {
     float4 const* __restrict__ nodes = reinterpret_cast<float4 const*>(sc.nodes);
     float4 const* __restrict__ tv0 = reinterpret_cast<float4 const*>(sc.tri_v0);
@@ -504,6 +514,25 @@ __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d,
     float const slack = 1.000244140625f; // 1 + 2^-12
     float t_far = ANY ? slack : pos_inf();
     float const t_near = fmaxf(t_min, 0.0f);
+
+    if (!STATS && hint != kNoHint)
+    {
+        float4 v0 = __ldg(tv0 + hint), e1 = __ldg(te1 + hint), e2 = __ldg(te2 + hint);
+        float ts, adet;
+        if (mt_inside(o, d, v0, e1, e2, ts, adet))
+        {
+            if (ANY)
+            {
+                float t = __fdiv_rn(ts, adet);
+                if (t > 0.0f && t < 1.0f) { occluded = true; best.slot = hint; return; }
+            }
+            else
+            {
+                closest_update(best, ts, adet, __float_as_int(v0.w), hint, t_min);
+                t_far = best.t * slack; // +inf * slack = +inf when the hint was rejected
+            }
+        }
+    }
 
     int stack[kBvhStackDepth];
     int sp = 0;
@@ -573,7 +602,7 @@ __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d,
                     if (ANY)
                     {
                         float t = __fdiv_rn(ts, adet);
-                        if (t > 0.0f && t < 1.0f) { occluded = true; return; }
+                        if (t > 0.0f && t < 1.0f) { occluded = true; best.slot = i; return; }
                     }
                     else
                     {
@@ -665,6 +694,10 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
     V3 const bg = v3(L.params.background);
 
     unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
+    // triangle this lane's previous primary / shadow ray ended on: the next ray of the same (or the
+    // neighbouring) pixel almost always ends on it too
+    uint32_t hint_hit = kNoHint, hint_occ = kNoHint;
+    bool const use_hints = L.hints != 0;
     if (y < L.params.y1) // warp-uniform
     {
         for (uint32_t g = 0; g < kSppTileW / PIX; g++)
@@ -683,7 +716,7 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                     Hit best = no_hit();
                     bool occ = false;
                     n_primary++;
-                    bvh_trace<false, STATS>(L.scene, o, d, L.params.t_min, best, occ, n_box, n_tri);
+                    bvh_trace<false, STATS>(L.scene, o, d, L.params.t_min, best, occ, n_box, n_tri, hint_hit);
                     if (s == 0) first_hit = best;
                     if (best.id < 0)
                     {
@@ -697,9 +730,14 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                         {
                             n_shadow++;
                             Hit dummy = no_hit();
-                            bvh_trace<true, STATS>(L.scene, sh.so, sh.sd, 0.0f, dummy, occ, n_box, n_tri);
-                            if (occ) rgb = V3{0.f, 0.f, 0.f};
+                            bvh_trace<true, STATS>(L.scene, sh.so, sh.sd, 0.0f, dummy, occ, n_box, n_tri, hint_occ);
+                            if (occ)
+                            {
+                                rgb = V3{0.f, 0.f, 0.f};
+                                if (use_hints) hint_occ = dummy.slot;
+                            }
                         }
+                        if (use_hints) hint_hit = best.slot;
                     }
                 }
                 s_val[warp][lane][0] = rgb.x;

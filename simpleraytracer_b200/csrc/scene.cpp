@@ -5,6 +5,8 @@
 // object (model.cpp:161-176).
 #include "scene.h"
 
+#include <cstdlib>
+
 #include "context.h"
 #include "image.h"
 
@@ -153,6 +155,7 @@ Scene::~Scene()
     cudaSetDevice(m_device->device);
     cudaStreamSynchronize(m_device->stream);
     FreeStaging();
+    for (cudaEvent_t e : m_chunk_events) cudaEventDestroy(e);
     cudaFree(m_d_tris); cudaFree(m_d_albedo); cudaFree(m_d_nodes); cudaFree(m_d_counters);
 }
 
@@ -204,6 +207,27 @@ ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
     {
         m_device->MakeCurrent();
         if (stream == nullptr) stream = m_device->stream;
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), stream));
+        if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, stream));
+        EnqueueBand(camera, light, params, d_rgb, d_hit_id, d_hit_t, stream);
+        if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, stream));
+        ML_CUDA_CHECK(cudaGetLastError());
+        m_timed_pending = timed;
+        m_timed_stream = stream;
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        m_error = e.what();
+        return ML_FAIL;
+    }
+}
+
+// One kernel launch for the rows params->[y0, y1) (already validated); counters accumulate.
+void Scene::EnqueueBand(srt_camera const* camera, srt_light const* light, srt_render_params const* params,
+                        void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream)
+{
+    {
         RenderLaunch launch{};
         launch.scene = m_view;
         launch.camera = *camera;
@@ -217,20 +241,10 @@ ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
         launch.d_hit_t = static_cast<float*>(d_hit_t);
         launch.d_counters = m_d_counters;
         RowBlocks(*params, launch.row_origin, launch.row_block_step, launch.n_row_blocks);
-        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), stream));
-        if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, stream));
+        static int const hints = std::getenv("SRT_BVH_HINTS") ? std::atoi(std::getenv("SRT_BVH_HINTS")) : 1;
+        launch.hints = static_cast<uint32_t>(hints);
         if (launch.n_row_blocks > 0)
             LaunchRender(launch, m_device->prop.multiProcessorCount, stream);
-        if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, stream));
-        ML_CUDA_CHECK(cudaGetLastError());
-        m_timed_pending = timed;
-        m_timed_stream = stream;
-        return ML_OK;
-    }
-    catch (std::exception const& e)
-    {
-        m_error = e.what();
-        return ML_FAIL;
     }
 }
 
@@ -287,9 +301,71 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         // staging holds whole 8-row blocks so a clipped last block can be copied as a unit
         EnsureStaging(std::max<size_t>((rows + 7) / 8 * 8 * params->width, 1));
 
-        // Render the band into band-local device buffers (buf_y0 = y0) ...
         srt_render_params band = *params;
         band.buf_y0 = params->y0;
+        size_t const row_off0 = static_cast<size_t>(params->y0 - params->buf_y0) * params->width;
+        if ((params->row_block_stride <= 1) && rows >= 64)
+        {
+            // Contiguous band: render it as up to 8 chunks of whole 8-row blocks; chunk k's D2H (copy
+            // stream) and its copy from the pinned staging into the caller's (pageable) buffer run
+            // while chunk k+1 renders, so only the last chunk's transfer is exposed.
+            size_t const n_chunks = std::min<size_t>(8, rows / 32);
+            size_t const chunk_rows = ((rows + n_chunks - 1) / n_chunks + 7) / 8 * 8;
+            cudaStream_t const sc = m_device->copy_out;
+            while (m_chunk_events.size() < 2 * n_chunks + 2)
+            {
+                cudaEvent_t e = nullptr;
+                ML_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+                m_chunk_events.push_back(e);
+            }
+            ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), s));
+            ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s));
+            // chunks alternate between two streams so that chunk k+1's blocks fill the SMs that
+            // chunk k's last wave leaves idle (one stream would serialise the tails: +3 ms per frame)
+            cudaStream_t const s2 = m_device->copy_in;
+            cudaEvent_t const ev_begin = m_chunk_events[2 * n_chunks], ev_s2_done = m_chunk_events[2 * n_chunks + 1];
+            ML_CUDA_CHECK(cudaEventRecord(ev_begin, s));
+            ML_CUDA_CHECK(cudaStreamWaitEvent(s2, ev_begin, 0));
+            size_t used = 0;
+            for (size_t k = 0; k < n_chunks; k++)
+            {
+                cudaStream_t const s = (k & 1) ? s2 : m_device->stream; // shadows the outer `s` on purpose
+                size_t const r0 = k * chunk_rows, r1 = std::min(rows, r0 + chunk_rows);
+                if (r0 >= r1) break;
+                srt_render_params c = band;
+                c.y0 = params->y0 + static_cast<uint32_t>(r0);
+                c.y1 = params->y0 + static_cast<uint32_t>(r1);
+                EnqueueBand(camera, light, &c, m_d_rgb, m_d_id, m_d_t, s);
+                ML_CUDA_CHECK(cudaEventRecord(m_chunk_events[2 * k], s));
+                ML_CUDA_CHECK(cudaStreamWaitEvent(sc, m_chunk_events[2 * k], 0));
+                size_t const p0 = r0 * params->width, np = (r1 - r0) * params->width;
+                if (rgb) ML_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(m_h_rgb) + p0 * 12, static_cast<char*>(m_d_rgb) + p0 * 12, np * 12, cudaMemcpyDeviceToHost, sc));
+                if (hit_id) ML_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(m_h_id) + p0 * 4, static_cast<char*>(m_d_id) + p0 * 4, np * 4, cudaMemcpyDeviceToHost, sc));
+                if (hit_t) ML_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(m_h_t) + p0 * 4, static_cast<char*>(m_d_t) + p0 * 4, np * 4, cudaMemcpyDeviceToHost, sc));
+                ML_CUDA_CHECK(cudaEventRecord(m_chunk_events[2 * k + 1], sc));
+                used = k + 1;
+            }
+            ML_CUDA_CHECK(cudaEventRecord(ev_s2_done, s2));
+            ML_CUDA_CHECK(cudaStreamWaitEvent(s, ev_s2_done, 0));
+            ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, s));
+            ML_CUDA_CHECK(cudaGetLastError());
+            m_timed_pending = true;
+            m_timed_stream = s;
+            for (size_t k = 0; k < used; k++)
+            {
+                size_t const r0 = k * chunk_rows, r1 = std::min(rows, r0 + chunk_rows);
+                size_t const p0 = r0 * params->width, np = (r1 - r0) * params->width;
+                ML_CUDA_CHECK(cudaEventSynchronize(m_chunk_events[2 * k + 1]));
+                if (rgb) std::memcpy(rgb + (row_off0 + p0) * 3, static_cast<float*>(m_h_rgb) + p0 * 3, np * 12);
+                if (hit_id) std::memcpy(hit_id + row_off0 + p0, static_cast<int32_t*>(m_h_id) + p0, np * 4);
+                if (hit_t) std::memcpy(hit_t + row_off0 + p0, static_cast<float*>(m_h_t) + p0, np * 4);
+            }
+            ML_CUDA_CHECK(cudaStreamSynchronize(s));
+            if (stats) return GetStats(stats);
+            return ML_OK;
+        }
+
+        // Render the band into band-local device buffers (buf_y0 = y0) ...
         ml_status st = RenderDevice(camera, light, &band, m_d_rgb, m_d_id, m_d_t, s, true);
         if (st != ML_OK) return st;
 

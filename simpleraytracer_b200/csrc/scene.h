@@ -90,6 +90,8 @@ public:
 private:
     bool Validate(srt_camera const* camera, srt_light const* light,
                   srt_render_params const* params);
+    void EnqueueBand(srt_camera const* camera, srt_light const* light, srt_render_params const* params,
+                     void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream);
     void EnsureStaging(size_t pixels);
     void FreeStaging();
 
@@ -106,6 +108,7 @@ private:
     void* m_d_rgb = nullptr; void* m_d_id = nullptr; void* m_d_t = nullptr;
     void* m_h_rgb = nullptr; void* m_h_id = nullptr; void* m_h_t = nullptr;
     size_t m_stage_pixels = 0;
+    std::vector<cudaEvent_t> m_chunk_events; // RenderHost pipeline
     cudaStream_t m_timed_stream = nullptr;
     bool m_timed_pending = false;
     std::string m_error;
@@ -135,6 +138,7 @@ struct RenderLaunch
     uint32_t row_origin;
     uint32_t row_block_step;
     uint32_t n_row_blocks;
+    uint32_t hints;  // 1: rays first test the triangle the lane's previous ray ended on (SRT_BVH_HINTS=0 disables)
 };
 void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream);
 double MeasureFp32Peak(DeviceState const& device, int repeats);
