@@ -139,3 +139,28 @@ def test_half_graph_dtype(tmp_path):
     gw.make_denoiser(path, channels=3, width=8, depth=2, seed=2, dtype=gw.DT_HALF)
     ok, text = api.inspect_model(path)
     assert ok and "input dtype=1 " in text and "output dtype=1 " in text
+
+
+def test_bf16_plan_is_decided_on_the_host(tmp_path, monkeypatch):
+    """MLB200_PRECISION=bf16: which layers go to the tensor cores (and which tensors are stored as
+    bf16) is host logic -- visible through mlxInspectModel without a GPU."""
+    path = tmp_path / "m.pb"
+    gw.make_denoiser(path, channels=3, width=64, depth=4, seed=1)
+    ok, text = api.inspect_model(path)
+    assert ok and "tcgen05" not in text                      # default precision: fp32 CUDA-core kernels
+    monkeypatch.setenv("MLB200_PRECISION", "bf16")
+    ok, text = api.inspect_model(path)
+    assert ok, text
+    convs = [l for l in text.splitlines() if l.startswith("Conv ")]
+    assert len(convs) == 4 and all("engine=tcgen05_bf16" in l for l in convs)
+    assert all("out=bf16" in l for l in convs[:3]) and "out=bf16" not in convs[3]   # last layer writes fp32
+    assert "launches=6" in text                              # + pad-to-16-channels pass + residual add
+    # a 5x5 net has no tensor-core layer; a 128->128 layer does not fit in shared memory
+    gw.make_denoiser(path, channels=3, width=32, depth=3, seed=1, kernel=5)
+    ok, text = api.inspect_model(path)
+    assert ok and "tcgen05" not in text
+    gw.make_denoiser(path, channels=3, width=128, depth=3, seed=1)
+    ok, text = api.inspect_model(path)
+    convs = [l for l in text.splitlines() if l.startswith("Conv ")]
+    assert ["engine=tcgen05_bf16" in l for l in convs] == [True, False, True]
+    assert "out=bf16" in convs[1]                            # the fp32 layer feeds a tensor-core layer in bf16
