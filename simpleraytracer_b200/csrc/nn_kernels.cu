@@ -33,17 +33,40 @@ __device__ __forceinline__ float apply_act(float v, Act act, float alpha)
     }
 }
 
-template <int KS, int TH, int TW, int PXT, int CG, int CI_T, typename OutT>
+// Packed pair of fp32 in one 64-bit register: sm_100 fma.rn.f32x2 (SASS FFMA2) does two FMAs per
+// issue slot, which leaves issue slots for the shared-memory loads of a direct convolution.
+typedef unsigned long long F2;
+__device__ __forceinline__ F2 pack2(float a, float b)
+{
+    F2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ float2 unpack2(F2 v)
+{
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
+__device__ __forceinline__ F2 fma2(F2 a, F2 b, F2 c)
+{
+    F2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
+template <int KS, int TH, int TW, int PXT, int CG, int CI_T, typename OutT, int CPT = 4>
 __global__ void __launch_bounds__(256)
 conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
                    float const* __restrict__ bias, OutT* __restrict__ out, ConvDesc d)
 {
     constexpr int IH = TH + KS - 1, IW = TW + KS - 1;
-    constexpr int CO_T = 4 * CG;
+    constexpr int CO_T = CPT * CG;   // CPT = 4 or 8 output channels per thread
     constexpr int GROUPS_PER_ROW = TW / PXT;
+    static_assert(CPT == 4 || CPT == 8, "channels per thread");
     static_assert((TH * TW / PXT) * CG == 256, "thread mapping must cover 256 threads");
 
-    __shared__ float s_in[IH][IW][CI_T];
+    __shared__ float s_in[IH][IW][CI_T + 1]; // +1: pixel groups of a warp land in different banks
     __shared__ __align__(16) float s_w[KS * KS][CI_T][CO_T];
 
     int const tid = threadIdx.x;
@@ -54,11 +77,11 @@ conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
     int const ty0 = blockIdx.y * TH, tx0 = blockIdx.x * TW;
     int const cot0 = blockIdx.z * CO_T;
 
-    float acc[PXT][4];
+    F2 acc2[PXT][CPT / 2]; // channel pairs (0,1), (2,3), ... of every pixel
 #pragma unroll
     for (int i = 0; i < PXT; i++)
 #pragma unroll
-        for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+        for (int j = 0; j < CPT / 2; j++) acc2[i][j] = pack2(0.f, 0.f);
 
     for (int c0 = 0; c0 < d.Cin; c0 += CI_T)
     {
@@ -88,20 +111,27 @@ conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
 #pragma unroll 2
             for (int ci = 0; ci < CI_T; ci++)
             {
-                float xin[PXT + KS - 1];
+                F2 xin[PXT + KS - 1]; // (x, x)
 #pragma unroll
-                for (int j = 0; j < PXT + KS - 1; j++) xin[j] = s_in[row + kh][col0 + j][ci];
+                for (int j = 0; j < PXT + KS - 1; j++)
+                {
+                    float const x = s_in[row + kh][col0 + j][ci];
+                    xin[j] = pack2(x, x);
+                }
 #pragma unroll
                 for (int kw = 0; kw < KS; kw++)
                 {
-                    float4 wv = *reinterpret_cast<float4 const*>(&s_w[kh * KS + kw][ci][cg * 4]);
 #pragma unroll
-                    for (int i = 0; i < PXT; i++)
+                    for (int q = 0; q < CPT / 4; q++)
                     {
-                        acc[i][0] = fmaf(xin[i + kw], wv.x, acc[i][0]);
-                        acc[i][1] = fmaf(xin[i + kw], wv.y, acc[i][1]);
-                        acc[i][2] = fmaf(xin[i + kw], wv.z, acc[i][2]);
-                        acc[i][3] = fmaf(xin[i + kw], wv.w, acc[i][3]);
+                        float4 wv = *reinterpret_cast<float4 const*>(&s_w[kh * KS + kw][ci][cg * CPT + 4 * q]);
+                        F2 const w01 = pack2(wv.x, wv.y), w23 = pack2(wv.z, wv.w);
+#pragma unroll
+                        for (int i = 0; i < PXT; i++)
+                        {
+                            acc2[i][2 * q + 0] = fma2(xin[i + kw], w01, acc2[i][2 * q + 0]);
+                            acc2[i][2 * q + 1] = fma2(xin[i + kw], w23, acc2[i][2 * q + 1]);
+                        }
                     }
                 }
             }
@@ -111,40 +141,45 @@ conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
 
     int const oy = ty0 + row;
     if (oy >= d.OH) return;
-    int const co = cot0 + cg * 4;
-    float b[4];
 #pragma unroll
-    for (int j = 0; j < 4; j++) b[j] = (bias != nullptr && co + j < d.Cout) ? bias[co + j] : 0.f;
-    bool const vec = (d.Cout % 4 == 0) && (co + 3 < d.Cout);
-#pragma unroll
-    for (int i = 0; i < PXT; i++)
+    for (int q = 0; q < CPT / 4; q++)
     {
-        int ox = tx0 + col0 + i;
-        if (ox >= d.OW) continue;
-        OutT* o = out + (static_cast<size_t>(oy) * d.OW + ox) * d.Cout + co;
-        float r0 = apply_act(acc[i][0] + b[0], d.act, d.alpha);
-        float r1 = apply_act(acc[i][1] + b[1], d.act, d.alpha);
-        float r2 = apply_act(acc[i][2] + b[2], d.act, d.alpha);
-        float r3 = apply_act(acc[i][3] + b[3], d.act, d.alpha);
-        if (vec)
+        int const co = cot0 + cg * CPT + 4 * q;
+        float b[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) b[j] = (bias != nullptr && co + j < d.Cout) ? bias[co + j] : 0.f;
+        bool const vec = (d.Cout % 4 == 0) && (co + 3 < d.Cout);
+#pragma unroll
+        for (int i = 0; i < PXT; i++)
         {
-            if constexpr (sizeof(OutT) == 4)
+            float2 const a01 = unpack2(acc2[i][2 * q]), a23 = unpack2(acc2[i][2 * q + 1]);
+            int ox = tx0 + col0 + i;
+            if (ox >= d.OW) continue;
+            OutT* o = out + (static_cast<size_t>(oy) * d.OW + ox) * d.Cout + co;
+            float r0 = apply_act(a01.x + b[0], d.act, d.alpha);
+            float r1 = apply_act(a01.y + b[1], d.act, d.alpha);
+            float r2 = apply_act(a23.x + b[2], d.act, d.alpha);
+            float r3 = apply_act(a23.y + b[3], d.act, d.alpha);
+            if (vec)
             {
-                *reinterpret_cast<float4*>(o) = make_float4(r0, r1, r2, r3);
+                if constexpr (sizeof(OutT) == 4)
+                {
+                    *reinterpret_cast<float4*>(o) = make_float4(r0, r1, r2, r3);
+                }
+                else
+                {
+                    __nv_bfloat162 lo = __floats2bfloat162_rn(r0, r1), hi = __floats2bfloat162_rn(r2, r3);
+                    *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<uint32_t*>(&lo),
+                                                              *reinterpret_cast<uint32_t*>(&hi));
+                }
             }
             else
             {
-                __nv_bfloat162 lo = __floats2bfloat162_rn(r0, r1), hi = __floats2bfloat162_rn(r2, r3);
-                *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<uint32_t*>(&lo),
-                                                          *reinterpret_cast<uint32_t*>(&hi));
+                if (co + 0 < d.Cout) o[0] = static_cast<OutT>(r0);
+                if (co + 1 < d.Cout) o[1] = static_cast<OutT>(r1);
+                if (co + 2 < d.Cout) o[2] = static_cast<OutT>(r2);
+                if (co + 3 < d.Cout) o[3] = static_cast<OutT>(r3);
             }
-        }
-        else
-        {
-            if (co + 0 < d.Cout) o[0] = static_cast<OutT>(r0);
-            if (co + 1 < d.Cout) o[1] = static_cast<OutT>(r1);
-            if (co + 2 < d.Cout) o[2] = static_cast<OutT>(r2);
-            if (co + 3 < d.Cout) o[3] = static_cast<OutT>(r3);
         }
     }
 }
@@ -176,21 +211,23 @@ __global__ void conv2d_naive_kernel(float const* __restrict__ in, float const* _
     out[idx] = apply_act(acc, d.act, d.alpha);
 }
 
-template <int KS, int TH, int TW, int PXT, int CG, int CI_T, typename OutT>
+template <int KS, int TH, int TW, int PXT, int CG, int CI_T, int CPT = 4, typename OutT>
 void LaunchTile(float const* in, float const* w, float const* bias, OutT* out, ConvDesc const& d,
                 cudaStream_t stream)
 {
-    dim3 grid((d.OW + TW - 1) / TW, (d.OH + TH - 1) / TH, (d.Cout + 4 * CG - 1) / (4 * CG));
-    conv2d_tile_kernel<KS, TH, TW, PXT, CG, CI_T, OutT><<<grid, 256, 0, stream>>>(in, w, bias, out, d);
+    dim3 grid((d.OW + TW - 1) / TW, (d.OH + TH - 1) / TH, (d.Cout + CPT * CG - 1) / (CPT * CG));
+    conv2d_tile_kernel<KS, TH, TW, PXT, CG, CI_T, OutT, CPT><<<grid, 256, 0, stream>>>(in, w, bias, out, d);
 }
 
 template <int KS, int CI_T, typename OutT>
 void LaunchTileForCout(float const* in, float const* w, float const* bias, OutT* out,
                        ConvDesc const& d, cudaStream_t stream)
 {
-    if (d.Cout <= 4) LaunchTile<KS, 16, 16, 1, 1, CI_T>(in, w, bias, out, d, stream);
+    if (d.Cout <= 4 && KS == 3) LaunchTile<KS, 16, 64, 4, 1, CI_T>(in, w, bias, out, d, stream); // 4 px x 4 ch
+    else if (d.Cout <= 4) LaunchTile<KS, 16, 16, 1, 1, CI_T>(in, w, bias, out, d, stream);
     else if (d.Cout <= 16) LaunchTile<KS, 16, 32, 8, 4, CI_T>(in, w, bias, out, d, stream);
     else if (d.Cout <= 32) LaunchTile<KS, 16, 16, 8, 8, CI_T>(in, w, bias, out, d, stream);
+    else if (KS == 3) LaunchTile<KS, 16, 16, 8, 8, CI_T, 8>(in, w, bias, out, d, stream); // 8 px x 8 ch per thread
     else LaunchTile<KS, 8, 16, 8, 16, CI_T>(in, w, bias, out, d, stream);
 }
 
