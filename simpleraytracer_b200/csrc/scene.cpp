@@ -295,131 +295,110 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
     try
     {
         m_device->MakeCurrent();
-        cudaStream_t s = m_device->stream;
+        cudaStream_t const s0 = m_device->stream, s1 = m_device->copy_in, sc = m_device->copy_out;
+        size_t const W = params->width;
         size_t const rows = params->y1 - params->y0;
-        size_t const pixels = rows * params->width;
+        uint32_t const stride = params->row_block_stride > 1 ? params->row_block_stride : 1u;
         // staging holds whole 8-row blocks so a clipped last block can be copied as a unit
-        EnsureStaging(std::max<size_t>((rows + 7) / 8 * 8 * params->width, 1));
+        EnsureStaging(std::max<size_t>((rows + 7) / 8 * 8 * W, 1));
 
+        // The band is rendered into band-local device buffers (buf_y0 = y0) as up to 8 chunks of whole
+        // (8 * stride)-row groups.  Chunk kernels alternate between two streams (chunk k+1's blocks fill
+        // the SMs chunk k's last wave leaves idle); chunk k's D2H (copy stream, pinned staging) and its
+        // copy into the caller's pageable frame run while later chunks render, so only the last chunk's
+        // transfer is exposed.  With interleaved sharding only the owned 8-row blocks cross PCIe.
         srt_render_params band = *params;
         band.buf_y0 = params->y0;
-        size_t const row_off0 = static_cast<size_t>(params->y0 - params->buf_y0) * params->width;
-        if ((params->row_block_stride <= 1) && rows >= 64)
+        size_t const group = 8u * stride;
+        size_t n_chunks = rows >= 64 ? std::min<size_t>(8, rows / 32) : 1;
+        size_t const chunk_rows = ((rows + n_chunks - 1) / n_chunks + group - 1) / group * group;
+        n_chunks = (rows + chunk_rows - 1) / chunk_rows;
+        while (m_chunk_events.size() < 2 * n_chunks + 2)
         {
-            // Contiguous band: render it as up to 8 chunks of whole 8-row blocks; chunk k's D2H (copy
-            // stream) and its copy from the pinned staging into the caller's (pageable) buffer run
-            // while chunk k+1 renders, so only the last chunk's transfer is exposed.
-            size_t const n_chunks = std::min<size_t>(8, rows / 32);
-            size_t const chunk_rows = ((rows + n_chunks - 1) / n_chunks + 7) / 8 * 8;
-            cudaStream_t const sc = m_device->copy_out;
-            while (m_chunk_events.size() < 2 * n_chunks + 2)
-            {
-                cudaEvent_t e = nullptr;
-                ML_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-                m_chunk_events.push_back(e);
-            }
-            ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), s));
-            ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s));
-            // chunks alternate between two streams so that chunk k+1's blocks fill the SMs that
-            // chunk k's last wave leaves idle (one stream would serialise the tails: +3 ms per frame)
-            cudaStream_t const s2 = m_device->copy_in;
-            cudaEvent_t const ev_begin = m_chunk_events[2 * n_chunks], ev_s2_done = m_chunk_events[2 * n_chunks + 1];
-            ML_CUDA_CHECK(cudaEventRecord(ev_begin, s));
-            ML_CUDA_CHECK(cudaStreamWaitEvent(s2, ev_begin, 0));
-            size_t used = 0;
-            for (size_t k = 0; k < n_chunks; k++)
-            {
-                cudaStream_t const s = (k & 1) ? s2 : m_device->stream; // shadows the outer `s` on purpose
-                size_t const r0 = k * chunk_rows, r1 = std::min(rows, r0 + chunk_rows);
-                if (r0 >= r1) break;
-                srt_render_params c = band;
-                c.y0 = params->y0 + static_cast<uint32_t>(r0);
-                c.y1 = params->y0 + static_cast<uint32_t>(r1);
-                EnqueueBand(camera, light, &c, m_d_rgb, m_d_id, m_d_t, s);
-                ML_CUDA_CHECK(cudaEventRecord(m_chunk_events[2 * k], s));
-                ML_CUDA_CHECK(cudaStreamWaitEvent(sc, m_chunk_events[2 * k], 0));
-                size_t const p0 = r0 * params->width, np = (r1 - r0) * params->width;
-                if (rgb) ML_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(m_h_rgb) + p0 * 12, static_cast<char*>(m_d_rgb) + p0 * 12, np * 12, cudaMemcpyDeviceToHost, sc));
-                if (hit_id) ML_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(m_h_id) + p0 * 4, static_cast<char*>(m_d_id) + p0 * 4, np * 4, cudaMemcpyDeviceToHost, sc));
-                if (hit_t) ML_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(m_h_t) + p0 * 4, static_cast<char*>(m_d_t) + p0 * 4, np * 4, cudaMemcpyDeviceToHost, sc));
-                ML_CUDA_CHECK(cudaEventRecord(m_chunk_events[2 * k + 1], sc));
-                used = k + 1;
-            }
-            ML_CUDA_CHECK(cudaEventRecord(ev_s2_done, s2));
-            ML_CUDA_CHECK(cudaStreamWaitEvent(s, ev_s2_done, 0));
-            ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, s));
-            ML_CUDA_CHECK(cudaGetLastError());
-            m_timed_pending = true;
-            m_timed_stream = s;
-            for (size_t k = 0; k < used; k++)
-            {
-                size_t const r0 = k * chunk_rows, r1 = std::min(rows, r0 + chunk_rows);
-                size_t const p0 = r0 * params->width, np = (r1 - r0) * params->width;
-                ML_CUDA_CHECK(cudaEventSynchronize(m_chunk_events[2 * k + 1]));
-                if (rgb) std::memcpy(rgb + (row_off0 + p0) * 3, static_cast<float*>(m_h_rgb) + p0 * 3, np * 12);
-                if (hit_id) std::memcpy(hit_id + row_off0 + p0, static_cast<int32_t*>(m_h_id) + p0, np * 4);
-                if (hit_t) std::memcpy(hit_t + row_off0 + p0, static_cast<float*>(m_h_t) + p0, np * 4);
-            }
-            ML_CUDA_CHECK(cudaStreamSynchronize(s));
-            if (stats) return GetStats(stats);
-            return ML_OK;
+            cudaEvent_t e = nullptr;
+            ML_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            m_chunk_events.push_back(e);
         }
-
-        // Render the band into band-local device buffers (buf_y0 = y0) ...
-        ml_status st = RenderDevice(camera, light, &band, m_d_rgb, m_d_id, m_d_t, s, true);
-        if (st != ML_OK) return st;
-
-        // ... then D2H through pinned staging and into the caller's frame at
-        // the rows' full-frame offsets (relative to the caller's buf_y0).
-        size_t const row_off = static_cast<size_t>(params->y0 - params->buf_y0) * params->width;
-        uint32_t const stride = params->row_block_stride > 1 ? params->row_block_stride : 1u;
-        if (stride == 1)
+        cudaEvent_t const ev_begin = m_chunk_events[2 * n_chunks], ev_s1_done = m_chunk_events[2 * n_chunks + 1];
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), s0));
+        ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s0));
+        ML_CUDA_CHECK(cudaEventRecord(ev_begin, s0));
+        ML_CUDA_CHECK(cudaStreamWaitEvent(s1, ev_begin, 0));
+        for (size_t k = 0; k < n_chunks; k++)
         {
-            if (rgb) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_rgb, m_d_rgb, pixels * 12, cudaMemcpyDeviceToHost, s));
-            if (hit_id) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_id, m_d_id, pixels * 4, cudaMemcpyDeviceToHost, s));
-            if (hit_t) ML_CUDA_CHECK(cudaMemcpyAsync(m_h_t, m_d_t, pixels * 4, cudaMemcpyDeviceToHost, s));
-        }
-        else
-        {
-            // only the owned 8-row blocks cross PCIe: one strided 2-D copy per buffer
-            uint32_t origin, step, count;
-            RowBlocks(band, origin, step, count);
-            size_t const first = static_cast<size_t>(origin - params->y0) * params->width; // pixels
-            size_t const blk = 8 * static_cast<size_t>(params->width);                     // pixels per block
-            size_t const pitch = static_cast<size_t>(step) * params->width;                // pixels between blocks
-            auto copy = [&](void* h, void* d, size_t item) {
-                ML_CUDA_CHECK(cudaMemcpy2DAsync(static_cast<char*>(h) + first * item, pitch * item,
-                                                static_cast<char*>(d) + first * item, pitch * item,
-                                                blk * item, count, cudaMemcpyDeviceToHost, s));
-            };
-            if (count > 0)
+            cudaStream_t const s = (k & 1) ? s1 : s0;
+            size_t const r0 = k * chunk_rows, r1 = std::min(rows, r0 + chunk_rows);
+            srt_render_params c = band;
+            c.y0 = params->y0 + static_cast<uint32_t>(r0);
+            c.y1 = params->y0 + static_cast<uint32_t>(r1);
+            EnqueueBand(camera, light, &c, m_d_rgb, m_d_id, m_d_t, s);
+            ML_CUDA_CHECK(cudaEventRecord(m_chunk_events[2 * k], s));
+            ML_CUDA_CHECK(cudaStreamWaitEvent(sc, m_chunk_events[2 * k], 0));
+            if (stride == 1)
             {
+                size_t const p0 = r0 * W, np = (r1 - r0) * W;
+                auto copy = [&](void* h, void* d, size_t item) {
+                    ML_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(h) + p0 * item, static_cast<char*>(d) + p0 * item,
+                                                  np * item, cudaMemcpyDeviceToHost, sc));
+                };
                 if (rgb) copy(m_h_rgb, m_d_rgb, 12);
                 if (hit_id) copy(m_h_id, m_d_id, 4);
                 if (hit_t) copy(m_h_t, m_d_t, 4);
             }
-        }
-        ML_CUDA_CHECK(cudaStreamSynchronize(s));
-        if (stride == 1)
-        {
-            if (rgb) std::memcpy(rgb + row_off * 3, m_h_rgb, pixels * 12);
-            if (hit_id) std::memcpy(hit_id + row_off, m_h_id, pixels * 4);
-            if (hit_t) std::memcpy(hit_t + row_off, m_h_t, pixels * 4);
-        }
-        else
-        {
-            // interleaved sharding: only the 8-row blocks this call owns reach the caller's frame
-            size_t const W = params->width;
-            for (uint32_t y = params->y0; y < params->y1; y++)
+            else
             {
-                if ((y / 8u) % stride != params->row_block_phase) continue;
-                size_t const src = static_cast<size_t>(y - params->y0) * W;
+                // the chunk's owned 8-row blocks: one strided 2-D copy per buffer
+                uint32_t origin, step, count;
+                RowBlocks(c, origin, step, count);
+                size_t const first = static_cast<size_t>(origin - params->y0) * W; // pixels
+                size_t const blk = 8 * W;                                           // pixels per block
+                size_t const pitch = static_cast<size_t>(step) * W;                 // pixels between blocks
+                auto copy = [&](void* h, void* d, size_t item) {
+                    ML_CUDA_CHECK(cudaMemcpy2DAsync(static_cast<char*>(h) + first * item, pitch * item,
+                                                    static_cast<char*>(d) + first * item, pitch * item,
+                                                    blk * item, count, cudaMemcpyDeviceToHost, sc));
+                };
+                if (count > 0)
+                {
+                    if (rgb) copy(m_h_rgb, m_d_rgb, 12);
+                    if (hit_id) copy(m_h_id, m_d_id, 4);
+                    if (hit_t) copy(m_h_t, m_d_t, 4);
+                }
+            }
+            ML_CUDA_CHECK(cudaEventRecord(m_chunk_events[2 * k + 1], sc));
+        }
+        ML_CUDA_CHECK(cudaEventRecord(ev_s1_done, s1));
+        ML_CUDA_CHECK(cudaStreamWaitEvent(s0, ev_s1_done, 0));
+        ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, s0));
+        ML_CUDA_CHECK(cudaGetLastError());
+        m_timed_pending = true;
+        m_timed_stream = s0;
+
+        // host side: as each chunk lands in the pinned staging, move its (owned) rows into the caller's
+        // frame at their full-frame offsets (relative to the caller's buf_y0)
+        for (size_t k = 0; k < n_chunks; k++)
+        {
+            size_t const r0 = k * chunk_rows, r1 = std::min(rows, r0 + chunk_rows);
+            ML_CUDA_CHECK(cudaEventSynchronize(m_chunk_events[2 * k + 1]));
+            for (size_t r = r0; r < r1;)
+            {
+                uint32_t const y = params->y0 + static_cast<uint32_t>(r);
+                size_t run = r1 - r; // rows to copy in one go
+                if (stride > 1)
+                {
+                    size_t const to_block_end = 8u - (y & 7u);
+                    if ((y / 8u) % stride != params->row_block_phase) { r += to_block_end; continue; }
+                    run = std::min(run, to_block_end);
+                }
+                size_t const src = r * W;
                 size_t const dst = static_cast<size_t>(y - params->buf_y0) * W;
-                if (rgb) std::memcpy(rgb + dst * 3, static_cast<float*>(m_h_rgb) + src * 3, W * 12);
-                if (hit_id) std::memcpy(hit_id + dst, static_cast<int32_t*>(m_h_id) + src, W * 4);
-                if (hit_t) std::memcpy(hit_t + dst, static_cast<float*>(m_h_t) + src, W * 4);
+                if (rgb) std::memcpy(rgb + dst * 3, static_cast<float*>(m_h_rgb) + src * 3, run * W * 12);
+                if (hit_id) std::memcpy(hit_id + dst, static_cast<int32_t*>(m_h_id) + src, run * W * 4);
+                if (hit_t) std::memcpy(hit_t + dst, static_cast<float*>(m_h_t) + src, run * W * 4);
+                r += run;
             }
         }
+        ML_CUDA_CHECK(cudaStreamSynchronize(s0));
         if (stats) return GetStats(stats);
         return ML_OK;
     }
