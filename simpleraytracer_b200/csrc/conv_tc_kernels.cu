@@ -76,6 +76,8 @@ struct TcParams
     int tap_stride;      // bytes from tap kw to tap kw+1 inside a stage: 128 (halo) or 128*KC*2
     int stage_tx;        // bytes TMA delivers per stage
     unsigned long long* prof; // MLB200_TC_PROF=1: 8 cycle counters summed over CTAs (see ConvTcRun)
+    int wait_ns;         // suspend-time hint of the mbarrier waits in the rows kernel (0: none)
+    int rows_mode;       // 1: conv3x3_tc_rows_kernel (filter rows stacked along N), 0: conv3x3_tc_kernel
     int debug;           // MLB200_TC_DEBUG bit 0: no TMA loads of A, bit 1: no MMAs (timing experiments only)
 };
 
@@ -110,6 +112,25 @@ __device__ __forceinline__ void bar_wait(uint64_t* bar, uint32_t parity)
             "}\n"
             : "=r"(done)
             : "r"(smem_addr(bar)), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+// The same with a suspend-time hint (ns): the thread may stay suspended in hardware that long before
+// try_wait returns false, so a waiting warp polls less often (MLB200_TC_WAIT_NS; 0 = no hint).
+__device__ __forceinline__ void bar_wait(uint64_t* bar, uint32_t parity, uint32_t hint_ns)
+{
+    if (hint_ns == 0u) { bar_wait(bar, parity); return; }
+    uint32_t done;
+    do
+    {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(done)
+            : "r"(smem_addr(bar)), "r"(parity), "r"(hint_ns)
             : "memory");
     } while (!done);
 }
@@ -229,7 +250,9 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t sbo, uint
     return d;
 }
 
-__device__ __forceinline__ float tc_act(float v, Act act, float alpha)
+// The transcendental activations stay out of line: inlined 16x per column group they made the
+// epilogue loop body ~70 KB of SASS and the common ReLU path paid for it in instruction-cache misses.
+__device__ __noinline__ float tc_act(float v, Act act, float alpha)
 {
     switch (act)
     {
@@ -618,6 +641,417 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     }
 }
 
+// ---------------------------------------------------------------- the row-stacked kernel
+// Same convolution, organised around INPUT rows.  Input row r contributes to the three output rows
+// r+1, r, r-1 through the filter rows kh = 0, 1, 2, so ONE MMA with the three filter rows stacked
+// along N (N3 = 3 * N columns of TMEM = three output-row accumulators side by side) does the work
+// of three MMAs of the tile-per-stage kernel above while reading the A operand from shared memory
+// once instead of three times: 10 KB of operand reads per 128 x 192 x 16 MMA instead of 18 KB.
+// The kernel above is bound by exactly that shared-memory bandwidth.
+//
+// A CTA walks DOWN a strip of 128-pixel tiles, one TMA box (one input row) per stage.  The
+// accumulator of output row y lives in TMEM slot y mod 3; for input row r the stacked B operand
+// must present filter rows (kh for slot 0, 1, 2) = a cyclic rotation of (1, 0, 2) that depends on
+// r mod 3, so each kw tap keeps FIVE filter blocks [W1 W0 W2 W1 W0] in shared memory and the
+// descriptor start picks the window.  Output row r+1 starts at input row r: the first K step of a
+// row is issued as three N-wide MMAs whose accumulate flags differ per slot, the rest N3-wide.
+// Output row r-1 is complete after input row r and is drained by the epilogue warps while the MMA
+// pipe works on the CTA's second, independent strip ("pipe" 0 / 1, TMEM columns [0,3N) / [3N,6N)).
+struct RowWalk
+{
+    int t, t_end, H;             // this pipe's share [t, t_end) of the tile sequence t = strip * H + y
+    int strip, ya, yb;           // current segment: output rows [ya, yb) of one strip
+    int r, r_last;               // current / last input row of the segment
+    bool first;                  // r is the segment's first input row: every slot starts afresh
+
+    __device__ __forceinline__ void Open()
+    {
+        if (t >= t_end) return;
+        strip = t / H;
+        ya = t - strip * H;
+        yb = min(H, ya + (t_end - t));
+        r = ya > 0 ? ya - 1 : 0;             // rows above / below the image contribute nothing (SAME padding)
+        r_last = yb < H ? yb : H - 1;
+        first = true;
+    }
+    __device__ __forceinline__ void Init(int q, int n_pipes, int n_tiles, int H_)
+    {
+        H = H_;
+        t = static_cast<int>(static_cast<long long>(n_tiles) * q / n_pipes);
+        t_end = static_cast<int>(static_cast<long long>(n_tiles) * (q + 1) / n_pipes);
+        Open();
+    }
+    __device__ __forceinline__ bool Valid() const { return t < t_end; }
+    __device__ __forceinline__ void Next()
+    {
+        first = false;
+        if (++r > r_last) { t += yb - ya; Open(); }
+    }
+};
+
+// EPI selects the epilogue at compile time (one straight-line loop body per variant keeps it inside the
+// instruction cache): bit 0 = bf16 output through the TMA store (else fp32 direct stores), bits 1-2 =
+// activation class 0 ReLU, 1 none / LeakyReLU, 2 anything else (out of line).
+template <int KC, int EPI>
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_constant__ CUtensorMap w_map,
+                       const __grid_constant__ CUtensorMap out_map, float const* __restrict__ bias,
+                       void* __restrict__ out, TcParams const P)
+{
+    constexpr bool kOutBf16 = (EPI & 1) != 0;
+    constexpr int kActClass = EPI >> 1;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~uintptr_t(1023u));
+    uint32_t const b_blk_bytes = static_cast<uint32_t>(P.N) * KC * 2u;      // one filter row of one kw tap
+    uint32_t const a_stage_bytes = static_cast<uint32_t>(P.stage_bytes);
+    uint32_t const out_tile_bytes = kOutBf16 ? static_cast<uint32_t>(kTileM) * P.N * 2u : 0u;
+    uint8_t* smem_b = smem;                                       // [kw][W1 W0 W2 W1 W0] filter blocks, resident
+    uint8_t* smem_a = smem_b + 15u * b_blk_bytes;                 // ring of input rows
+    uint8_t* smem_o = smem_a + static_cast<uint32_t>(P.stages) * a_stage_bytes;   // 2 output staging tiles
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_o + 2u * out_tile_bytes);
+    uint64_t* full = bars;                       // [stages]   TMA -> MMA
+    uint64_t* empty = bars + kMaxStages;         // [stages]   MMA -> TMA
+    uint64_t* w_full = bars + 2 * kMaxStages;    // filter resident
+    uint64_t* row_done = w_full + 1;             // [2 pipes]  MMA -> epilogue: an input row has been accumulated
+    uint64_t* slot_free = row_done + kMaxAcc;    // [2 pipes]  epilogue -> MMA: the rows it completed are drained
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(slot_free + kMaxAcc);
+
+    uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __shared__ __align__(16) float s_bias[256];
+    for (int c = threadIdx.x; c < P.N; c += kTcThreads) s_bias[c] = (bias != nullptr && c < P.Cout) ? bias[c] : 0.f;
+    float const neg_slope = P.act == Act::None ? 1.f : (P.act == Act::LeakyRelu ? P.alpha : 0.f);
+
+    if (warp == 0 && lane == 0)
+    {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&in_map) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&w_map) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&out_map) : "memory");
+        for (int s = 0; s < P.stages; s++) { bar_init(&full[s], 1); bar_init(&empty[s], 1); }
+        bar_init(w_full, 1);
+        for (int a = 0; a < 2; a++) { bar_init(&row_done[a], 1); bar_init(&slot_free[a], kEpiWarps); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1)
+    {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;"
+                     ::"r"(smem_addr(tmem_slot)), "r"(static_cast<uint32_t>(P.tmem_cols)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t const tmem_base = *tmem_slot;
+    long long prof_acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+
+    // Every role steps identical copies of the two pipes' walks, alternating pipe 0 / pipe 1.
+    RowWalk walk[2];
+    walk[0].Init(2 * blockIdx.x, 2 * gridDim.x, P.n_tiles, P.H);
+    walk[1].Init(2 * blockIdx.x + 1, 2 * gridDim.x, P.n_tiles, P.H);
+    uint32_t const N = static_cast<uint32_t>(P.N);
+    uint32_t const wait_ns = static_cast<uint32_t>(P.wait_ns);
+
+    if (warp == 0)
+    {
+        // ---- TMA producer: the filter blocks once, then one input row per stage
+        if (elect_one())
+        {
+            bar_expect_tx(w_full, 15u * b_blk_bytes);
+            for (int kw = 0; kw < 3; kw++)
+                for (int j = 0; j < 5; j++)
+                {
+                    int const kh = j == 0 || j == 3 ? 1 : (j == 1 || j == 4 ? 0 : 2);
+                    tma_load_2d(smem_b + (kw * 5 + j) * b_blk_bytes, &w_map, 0, (kh * 3 + kw) * P.N, w_full);
+                }
+        }
+        __syncwarp();
+        uint32_t s = 0, ph = 0;
+        TC_PROF_T0();
+        while (walk[0].Valid() || walk[1].Valid())
+        {
+#pragma unroll
+            for (int p = 0; p < 2; p++)
+            {
+                if (!walk[p].Valid()) continue;
+                TC_PROF_ADD(1);
+                bar_wait(&empty[s], ph ^ 1u, wait_ns);
+                TC_PROF_ADD(0);
+                if (elect_one())
+                {
+                    if (P.debug & 1)
+                    {
+                        bar_arrive(&full[s]);
+                    }
+                    else
+                    {
+                        bar_expect_tx(&full[s], static_cast<uint32_t>(P.stage_tx));
+                        uint8_t* dst = smem_a + s * a_stage_bytes;
+                        int const x0 = walk[p].strip * kTileM, iy = walk[p].r;
+                        if (P.halo)
+                        {
+                            tma_load_3d(dst, &in_map, 0, x0 - 1, iy, &full[s]);   // pixels outside the row: zeros
+                        }
+                        else
+                        {
+                            for (int kw = 0; kw < 3; kw++)
+                                tma_load_3d(dst + kw * P.tap_stride, &in_map, 0, x0 + kw - 1, iy, &full[s]);
+                        }
+                    }
+                }
+                __syncwarp();
+                if (++s == static_cast<uint32_t>(P.stages)) { s = 0; ph ^= 1u; }
+                walk[p].Next();
+            }
+        }
+        TC_PROF_ADD(1);
+        if (P.prof && lane == 0)
+        {
+            atomicAdd(P.prof + 0, static_cast<unsigned long long>(prof_acc[0]));
+            atomicAdd(P.prof + 1, static_cast<unsigned long long>(prof_acc[1]));
+        }
+    }
+    else if (warp == 1)
+    {
+        // ---- MMA issuer
+        uint32_t const idesc_base = (1u << 4) | (1u << 7) | (1u << 10) | (static_cast<uint32_t>(kTileM >> 4) << 24);
+        uint32_t const idesc1 = idesc_base | ((N >> 3) << 17);            // one slot
+        uint32_t const idesc3 = idesc_base | (((3u * N) >> 3) << 17);     // the three slots of a pipe
+        bar_wait(w_full, 0);
+        tc_fence_after();
+        uint64_t const desc0 = umma_desc(0u, P.sbo, P.layout_type);
+        uint32_t const desc_hi = static_cast<uint32_t>(desc0 >> 32);
+        uint32_t const lo_flags = static_cast<uint32_t>(desc0);
+        uint32_t const a_lo0 = (smem_addr(smem_a) >> 4) + lo_flags, b_lo0 = (smem_addr(smem_b) >> 4) + lo_flags;
+        uint32_t const stage_u = a_stage_bytes >> 4, tap_u = static_cast<uint32_t>(P.tap_stride) >> 4;
+        uint32_t const b_blk_u = b_blk_bytes >> 4, b_kw_u = 5u * b_blk_u;
+        uint32_t s = 0, ph = 0;
+        uint32_t ev[2] = {0u, 0u};       // input rows issued per pipe (= barrier phases)
+        TC_PROF_T0();
+        while (walk[0].Valid() || walk[1].Valid())
+        {
+#pragma unroll
+            for (int p = 0; p < 2; p++)
+            {
+                if (!walk[p].Valid()) continue;
+                TC_PROF_ADD(2);
+                // the slot this row starts afresh held output row r-2, completed by the pipe's previous row
+                if (ev[p] > 0) bar_wait(&slot_free[p], (ev[p] - 1u) & 1u, wait_ns);
+                TC_PROF_ADD(0);
+                bar_wait(&full[s], ph, wait_ns);
+                TC_PROF_ADD(1);
+                tc_fence_after();
+                uint32_t const c = static_cast<uint32_t>(walk[p].r) % 3u;
+                uint32_t const win = c == 0u ? 0u : (c == 1u ? 2u : 1u);      // window start in [W1 W0 W2 W1 W0]
+                uint32_t const fresh = c == 2u ? 0u : c + 1u;                  // slot of output row r+1
+                uint32_t const all_fresh = walk[p].first ? 1u : 0u;
+                if (elect_one())
+                {
+                    if (!(P.debug & 2))
+                    {
+                        uint32_t const a_st = a_lo0 + s * stage_u;
+                        uint32_t const b_st = b_lo0 + win * b_blk_u;
+                        uint32_t const d_tmem = tmem_base + static_cast<uint32_t>(p) * 3u * N;
+#pragma unroll
+                        for (uint32_t sl = 0; sl < 3u; sl++)
+                            tc_mma_bf16_lohi<false>(d_tmem + sl * N, a_st, b_st + sl * b_blk_u, desc_hi, idesc1,
+                                                    (all_fresh | (sl == fresh ? 1u : 0u)) ^ 1u);
+#pragma unroll
+                        for (uint32_t kw = 0; kw < 3u; kw++)
+                        {
+#pragma unroll
+                            for (uint32_t k = 0; k < KC / 16; k++)
+                            {
+                                if (kw == 0 && k == 0) continue;
+                                tc_mma_bf16_lohi<true>(d_tmem, a_st + kw * tap_u + 2u * k, b_st + kw * b_kw_u + 2u * k,
+                                                       desc_hi, idesc3, 1u);
+                            }
+                        }
+                    }
+                    TC_PROF_ADD(2);
+                    tc_commit(&empty[s]);
+                    tc_commit(&row_done[p]);
+                    TC_PROF_ADD(3);
+                }
+                __syncwarp();
+                if (++s == static_cast<uint32_t>(P.stages)) { s = 0; ph ^= 1u; }
+                ev[p]++;
+                walk[p].Next();
+                TC_PROF_ADD(4);
+            }
+        }
+        TC_PROF_ADD(4);
+        if (P.prof && lane == 0)
+        {
+            for (int k = 0; k < 3; k++) atomicAdd(P.prof + 2 + k, static_cast<unsigned long long>(prof_acc[k]));
+            atomicAdd(P.prof + 7, static_cast<unsigned long long>(prof_acc[3]));
+            atomicAdd(P.prof + 8, static_cast<unsigned long long>(prof_acc[4]));
+        }
+    }
+    else
+    {
+        // ---- epilogue warps 2..9 (lane quarter q = warp % 4, two warps per quarter split the columns)
+        uint32_t const q = warp & 3u;
+        uint32_t const row = q * 32u + lane;
+        bool const issuer = threadIdx.x == 64;
+        int const units = P.N >> 4, half = static_cast<int>(warp - 2u) >> 2;
+        int const c_begin = half == 0 ? 0 : ((units + 1) >> 1) << 4;
+        int const c_end = half == 0 ? ((units + 1) >> 1) << 4 : P.N;
+        int const OC = P.N < 64 ? P.N : 64;
+        uint32_t const row_bytes = static_cast<uint32_t>(OC) * 2u;
+        uint32_t const swz_mask = row_bytes == 128u ? 7u : (row_bytes == 64u ? 3u : 1u);
+        uint32_t const chunk_bytes = static_cast<uint32_t>(kTileM) * row_bytes;
+        uint32_t buf = 0;
+        uint32_t ev[2] = {0u, 0u};
+        // this warp's bias values live in registers (its columns never change); only a warp with more
+        // than 32 columns (N = 80) reloads them per 32-column step
+        bool const bias_fixed = c_end - c_begin <= 32;
+        float breg[32];
+#pragma unroll
+        for (int j = 0; j < 32; j++) breg[j] = c_begin + j < c_end ? s_bias[c_begin + j] : 0.f;
+        TC_PROF_T0();
+        while (walk[0].Valid() || walk[1].Valid())
+        {
+#pragma unroll
+            for (int p = 0; p < 2; p++)
+            {
+                if (!walk[p].Valid()) continue;
+                // output rows this input row completes: r-1, and r itself on the image's last row
+                int const r = walk[p].r;
+                bool const above = r - 1 >= walk[p].ya;
+                int const y_begin = above ? r - 1 : r;           // the completed rows are consecutive
+                int const nd = (above ? 1 : 0) + ((r == P.H - 1 && r < walk[p].yb) ? 1 : 0);
+                int const x0 = walk[p].strip * kTileM;
+                int const x = x0 + static_cast<int>(row);
+                TC_PROF_ADD(1);
+                bar_wait(&row_done[p], ev[p] & 1u, wait_ns);
+                TC_PROF_ADD(0);
+                tc_fence_after();
+                for (int d = 0; d < nd; d++)
+                {
+                    int const y = y_begin + d;
+                    uint32_t const slot = static_cast<uint32_t>(y) % 3u;
+                    uint32_t const taddr = tmem_base + (static_cast<uint32_t>(p) * 3u + slot) * N + ((q * 32u) << 16);
+                    uint8_t* const stg = smem_o + buf * out_tile_bytes;
+                    size_t const pixel = static_cast<size_t>(y) * P.W + x;
+                    for (int c0 = c_begin; c0 < c_end && !(P.debug & 4); c0 += 32)
+                    {
+                        uint32_t v32[32];
+                        bool const two = c0 + 16 < c_end;
+                        if (!bias_fixed)
+                        {
+#pragma unroll
+                            for (int j = 0; j < 32; j++) breg[j] = c0 + j < c_end ? s_bias[c0 + j] : 0.f;
+                        }
+                        tc_ld16(taddr + static_cast<uint32_t>(c0), *reinterpret_cast<uint32_t(*)[16]>(&v32[0]));
+                        if (two) tc_ld16(taddr + static_cast<uint32_t>(c0 + 16), *reinterpret_cast<uint32_t(*)[16]>(&v32[16]));
+                        tc_ld_wait();
+                        TC_PROF_ADD(5);
+#pragma unroll
+                        for (int h = 0; h < 2; h++)
+                        {
+                            if (h == 1 && !two) break;
+                            int const cb = c0 + 16 * h;
+                            float v[16];
+#pragma unroll
+                            for (int j = 0; j < 16; j++) v[j] = __uint_as_float(v32[16 * h + j]) + breg[16 * h + j];
+                            if constexpr (kActClass == 0)
+                            {
+#pragma unroll
+                                for (int j = 0; j < 16; j++) v[j] = fmaxf(v[j], 0.f);
+                            }
+                            else if constexpr (kActClass == 1)
+                            {
+#pragma unroll
+                                for (int j = 0; j < 16; j++) v[j] = fmaf(neg_slope, fminf(v[j], 0.f), fmaxf(v[j], 0.f));
+                            }
+                            else
+                            {
+#pragma unroll
+                                for (int j = 0; j < 16; j++) v[j] = tc_act(v[j], P.act, P.alpha);
+                            }
+                            if constexpr (kOutBf16)
+                            {
+                                uint32_t const oc = static_cast<uint32_t>(cb) >> 6;
+                                uint32_t const unit = (static_cast<uint32_t>(cb) & 63u) >> 3;
+                                uint32_t off0 = row * row_bytes + unit * 16u;
+                                uint32_t off1 = off0 + 16u;
+                                off0 ^= ((off0 >> 7) & swz_mask) << 4;
+                                off1 ^= ((off1 >> 7) & swz_mask) << 4;
+                                uint8_t* const base = stg + oc * chunk_bytes;
+                                *reinterpret_cast<uint4*>(base + off0) =
+                                    make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                                               pack_bf16(v[6], v[7]));
+                                *reinterpret_cast<uint4*>(base + off1) =
+                                    make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
+                                               pack_bf16(v[14], v[15]));
+                            }
+                            else
+                            {
+                              if (x < P.W)
+                              {
+                                float* o = static_cast<float*>(out) + pixel * P.Cout;
+#pragma unroll
+                                for (int j = 0; j < 16; j++)
+                                    if (cb + j < P.Cout) o[cb + j] = v[j];
+                              }
+                            }
+                        }
+                    }
+                    TC_PROF_ADD(2);
+                    if (d == nd - 1)
+                    {
+                        // every completed row of this event has been read out of TMEM
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) bar_arrive(&slot_free[p]);
+                    }
+                    TC_PROF_ADD(6);
+                    if constexpr (kOutBf16)
+                    {
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                        TC_PROF_ADD(7);
+                        if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                        TC_PROF_ADD(3);
+                        asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
+                        TC_PROF_ADD(4);
+                        if (issuer)
+                        {
+                            for (int oc = 0; oc * 64 < P.N; oc++)
+                                tma_store_3d(&out_map, stg + oc * chunk_bytes, oc * 64, x0, y);
+                            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                        }
+                        buf ^= 1u;
+                    }
+                }
+                if (nd == 0)
+                {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) bar_arrive(&slot_free[p]);
+                }
+                ev[p]++;
+                walk[p].Next();
+            }
+        }
+        if (issuer) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        TC_PROF_ADD(1);
+        if (P.prof && warp == 2 && lane == 0)
+        {
+            atomicAdd(P.prof + 5, static_cast<unsigned long long>(prof_acc[0]));
+            atomicAdd(P.prof + 6, static_cast<unsigned long long>(prof_acc[1]));
+            for (int k = 2; k < 8; k++) atomicAdd(P.prof + 7 + k, static_cast<unsigned long long>(prof_acc[k]));
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1)
+    {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;"
+                     ::"r"(tmem_base), "r"(static_cast<uint32_t>(P.tmem_cols)) : "memory");
+    }
+}
+
 // ---------------------------------------------------------------- host side
 PFN_cuTensorMapEncodeTiled_v12000 EncodeTiled()
 {
@@ -649,16 +1083,24 @@ void Encode(CUtensorMap* map, void const* base, int rank, cuuint64_t const* dims
         throw std::runtime_error("cuTensorMapEncodeTiled failed with CUresult " + std::to_string(static_cast<int>(r)));
 }
 
-bool HaloMode(int KC)
+int EnvInt(char const* name, int fallback)
 {
-    static int const env = std::getenv("MLB200_TC_HALO") ? std::atoi(std::getenv("MLB200_TC_HALO")) : 1;
-    return KC == 64 && env != 0;
+    char const* v = std::getenv(name);
+    return v != nullptr ? std::atoi(v) : fallback;
+}
+
+// Halo mode: one box of 130 pixels per input row, the kw taps are row-shifted views of it.
+// Works under all three swizzles (128/64/32-byte rows).  MLB200_TC_HALO=0: three 128-pixel boxes instead.
+bool HaloMode(int /*KC*/)
+{
+    return EnvInt("MLB200_TC_HALO", 1) != 0;
 }
 
 size_t StageBytes(int KC)
 {
-    // halo: 130 pixels x 128 B = 16640 B, rounded up to the 1024-byte swizzle pattern; else 3 boxes
-    return HaloMode(KC) ? 17u * 1024u : static_cast<size_t>(3) * kTileM * KC * 2;
+    // halo: 130 pixels x KC*2 B, rounded up to the 1024-byte swizzle pattern; else 3 boxes of 128 pixels
+    size_t const halo = (static_cast<size_t>(kTileM + 2) * KC * 2 + 1023) / 1024 * 1024;
+    return HaloMode(KC) ? halo : static_cast<size_t>(3) * kTileM * KC * 2;
 }
 
 size_t SmemBytes(int N, int Cin, int KC, int stages, bool out_bf16, int rps = 1)
@@ -667,6 +1109,45 @@ size_t SmemBytes(int N, int Cin, int KC, int stages, bool out_bf16, int rps = 1)
     size_t a = static_cast<size_t>(stages) * StageBytes(KC) * rps;
     size_t o = out_bf16 ? static_cast<size_t>(2) * kTileM * N * 2 : 0;   // two staging tiles for the TMA store
     return 1024 /*alignment slack*/ + b + a + o + (2 * kMaxStages + 1 + 2 * kMaxAcc) * sizeof(uint64_t) + 16;
+}
+
+size_t SmemBytesRows(int N, int KC, int stages, bool out_bf16)
+{
+    size_t b = static_cast<size_t>(15) * N * KC * 2;                    // 3 kw taps x [W1 W0 W2 W1 W0]
+    size_t a = static_cast<size_t>(stages) * StageBytes(KC);            // one input row per stage
+    size_t o = out_bf16 ? static_cast<size_t>(2) * kTileM * N * 2 : 0;
+    return 1024 + b + a + o + (2 * kMaxStages + 1 + 2 * kMaxAcc) * sizeof(uint64_t) + 16;
+}
+
+// The row-stacked kernel needs the whole Cin in one swizzle row and three accumulators of a pipe
+// inside one MMA's N range; MLB200_TC_ROWS=0 keeps the tile-per-stage kernel (for comparison).
+bool RowsModeFits(int N, int Cin, bool out_bf16)
+{
+    if (EnvInt("MLB200_TC_ROWS", 1) == 0 || Cin > 64 || 3 * N > 256) return false;
+    return SmemBytesRows(N, Cin, 3, out_bf16) <= 226u * 1024u;
+}
+
+using RowsKernel = void (*)(CUtensorMap, CUtensorMap, CUtensorMap, float const*, void*, TcParams);
+
+template <int KC>
+RowsKernel RowsKernelForKc(int epi)
+{
+    switch (epi)
+    {
+        case 0: return conv3x3_tc_rows_kernel<KC, 0>;
+        case 1: return conv3x3_tc_rows_kernel<KC, 1>;
+        case 2: return conv3x3_tc_rows_kernel<KC, 2>;
+        case 3: return conv3x3_tc_rows_kernel<KC, 3>;
+        case 4: return conv3x3_tc_rows_kernel<KC, 4>;
+        default: return conv3x3_tc_rows_kernel<KC, 5>;
+    }
+}
+
+RowsKernel RowsKernelFor(TcParams const& p)
+{
+    int const act_class = p.act == Act::Relu ? 0 : (p.act == Act::None || p.act == Act::LeakyRelu) ? 1 : 2;
+    int const epi = (act_class << 1) | (p.out_bf16 ? 1 : 0);
+    return p.KC == 64 ? RowsKernelForKc<64>(epi) : p.KC == 32 ? RowsKernelForKc<32>(epi) : RowsKernelForKc<16>(epi);
 }
 
 } // namespace
@@ -735,16 +1216,35 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     int const want_rps = std::getenv("MLB200_TC_RPS") ? std::atoi(std::getenv("MLB200_TC_RPS")) : 3;
     p.rps = (want_rps == 3 && SmemBytes(p.N, Cin, p.KC, 2, out_bf16, 3) <= 226u * 1024u) ? 3 : 1;
     p.stage_bytes = p.rps * p.row_bytes;
-    p.tap_stride = p.halo ? 128 : kTileM * p.KC * 2;
-    p.stage_tx = p.rps * (p.halo ? (kTileM + 2) * 128 : 3 * kTileM * p.KC * 2);
+    p.tap_stride = p.halo ? p.KC * 2 : kTileM * p.KC * 2;
+    p.stage_tx = p.rps * (p.halo ? (kTileM + 2) * p.KC * 2 : 3 * kTileM * p.KC * 2);
     p.prof = nullptr;
     if (std::getenv("MLB200_TC_PROF") != nullptr)
-        ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&p.prof), 12 * sizeof(unsigned long long)));
+        ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&p.prof), 16 * sizeof(unsigned long long)));
+    p.rows_mode = RowsModeFits(p.N, Cin, out_bf16) ? 1 : 0;
+    p.wait_ns = EnvInt("MLB200_TC_WAIT_NS", 0);
     p.stages = kMaxStages;
-    while (p.stages > 2 && SmemBytes(p.N, Cin, p.KC, p.stages, out_bf16, p.rps) > 226u * 1024u) p.stages--;
-    op->smem = SmemBytes(p.N, Cin, p.KC, p.stages, out_bf16, p.rps);
+    if (p.rows_mode)
+    {
+        p.rps = 1;
+        p.stage_bytes = p.row_bytes;
+        p.stage_tx = p.halo ? (kTileM + 2) * p.KC * 2 : 3 * kTileM * p.KC * 2;
+        p.n_acc = 2;                                  // two pipes of three slots
+        cols = 32;
+        while (cols < 6 * p.N) cols *= 2;
+        p.tmem_cols = cols;
+        while (p.stages > 3 && SmemBytesRows(p.N, p.KC, p.stages, out_bf16) > 226u * 1024u) p.stages--;
+        op->smem = SmemBytesRows(p.N, p.KC, p.stages, out_bf16);
+        int const want = (p.n_tiles + 1) / 2;        // two pipes per CTA
+        op->grid = want < sm_count ? want : sm_count;
+    }
+    else
+    {
+        while (p.stages > 2 && SmemBytes(p.N, Cin, p.KC, p.stages, out_bf16, p.rps) > 226u * 1024u) p.stages--;
+        op->smem = SmemBytes(p.N, Cin, p.KC, p.stages, out_bf16, p.rps);
+        op->grid = p.n_tiles < sm_count ? p.n_tiles : sm_count;
+    }
     if (op->smem > 226u * 1024u) throw std::runtime_error("filter does not fit in shared memory");
-    op->grid = p.n_tiles < sm_count ? p.n_tiles : sm_count;
 
     // activation: [H][W][Cin] bf16, box = KC channels x 128 pixels x 1 row
     {
@@ -776,16 +1276,24 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     }
     // per device: the attribute belongs to the function in the current context
     auto set = [](auto* k) { ML_CUDA_CHECK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024)); };
-    if (p.KC == 64) set(conv3x3_tc_kernel<64>);
-    else if (p.KC == 32) set(conv3x3_tc_kernel<32>);
-    else set(conv3x3_tc_kernel<16>);
+    if (p.rows_mode) set(RowsKernelFor(p));
+    else
+    {
+        if (p.KC == 64) set(conv3x3_tc_kernel<64>);
+        else if (p.KC == 32) set(conv3x3_tc_kernel<32>);
+        else set(conv3x3_tc_kernel<16>);
+    }
     return op.release();
 }
 
 void ConvTcRun(ConvTc const* op, float const* bias, void* out, cudaStream_t stream)
 {
-    if (op->p.prof) ML_CUDA_CHECK(cudaMemsetAsync(op->p.prof, 0, 12 * sizeof(unsigned long long), stream));
-    if (op->p.KC == 64)
+    if (op->p.prof) ML_CUDA_CHECK(cudaMemsetAsync(op->p.prof, 0, 16 * sizeof(unsigned long long), stream));
+    if (op->p.rows_mode)
+    {
+        RowsKernelFor(op->p)<<<op->grid, kTcThreads, op->smem, stream>>>(op->in_map, op->w_map, op->out_map, bias, out, op->p);
+    }
+    else if (op->p.KC == 64)
         conv3x3_tc_kernel<64><<<op->grid, kTcThreads, op->smem, stream>>>(op->in_map, op->w_map, op->out_map, bias, out, op->p);
     else if (op->p.KC == 32)
         conv3x3_tc_kernel<32><<<op->grid, kTcThreads, op->smem, stream>>>(op->in_map, op->w_map, op->out_map, bias, out, op->p);
@@ -794,14 +1302,17 @@ void ConvTcRun(ConvTc const* op, float const* bias, void* out, cudaStream_t stre
     ML_CUDA_CHECK(cudaGetLastError());
     if (op->p.prof)
     {
-        unsigned long long h[12];
+        unsigned long long h[16];
         ML_CUDA_CHECK(cudaStreamSynchronize(stream));
         ML_CUDA_CHECK(cudaMemcpy(h, op->p.prof, sizeof(h), cudaMemcpyDeviceToHost));
         double const per = 1.0 / (static_cast<double>(op->grid) * ((op->p.n_tiles + op->grid - 1) / op->grid));
-        std::fprintf(stderr, "[tc prof] N=%d cycles/tile: producer wait_empty %.0f other %.0f | mma wait_acc_empty %.0f "
-                     "wait_full %.0f issue %.0f commit %.0f rest %.0f | epilogue wait_acc_full %.0f other %.0f ld+math+sts %.0f wait_store %.0f barrier %.0f\n", op->p.N,
+        std::fprintf(stderr, "[tc prof] N=%d rows_mode=%d cycles/tile: producer wait_empty %.0f other %.0f | mma wait_acc_empty %.0f "
+                     "wait_full %.0f issue %.0f commit %.0f rest %.0f | epilogue wait_acc_full %.0f other %.0f ld+math+sts %.0f wait_store %.0f barrier %.0f\n", op->p.N, op->p.rows_mode,
                      h[0] * per, h[1] * per, h[2] * per, h[3] * per, h[4] * per, h[7] * per, h[8] * per, h[5] * per,
                      h[6] * per, h[9] * per, h[10] * per, h[11] * per);
+        if (op->p.rows_mode)
+            std::fprintf(stderr, "[tc prof]   epilogue detail: tcgen05.ld+wait %.0f (excluded from ld+math+sts above) | slot_free arrive %.0f fence.proxy.async %.0f\n",
+                         h[12] * per, h[13] * per, h[14] * per);
     }
 }
 

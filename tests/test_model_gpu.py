@@ -371,8 +371,16 @@ def bf16_emulated_denoiser(x, layers, tc_layers, alpha=0.1):
     dict(width=128, depth=3, act="Relu", w=70, h=20, tc={0, 2}),           # 128->128 too big for smem: fp32; 2 K-chunks
     dict(width=64, depth=5, act="Relu", w=1000, h=150, tc={0, 1, 2, 3, 4}),  # many tiles per CTA: ring + TMEM phases wrap
     dict(width=64, depth=3, act="Tanh", w=257, h=11, tc={0, 1, 2}),        # slow-path activation
+    dict(width=64, depth=3, act="Relu", w=140, h=1, tc={0, 1, 2}),         # one image row: no row above or below
+    dict(width=48, depth=3, act="Relu", w=129, h=2, tc={0}),               # Cin = 48 is not a tensor-core shape: only layer 0
+    dict(width=64, depth=3, act="LeakyRelu", w=100, h=700, tc={0, 1, 2}),       # one strip, many short row segments per CTA
 ])
-def test_bf16_tensor_core_denoiser(ctx, tmp_path, cfg):
+@pytest.mark.parametrize("kernel", ["rows", "tile", "rows-3-boxes"])
+def test_bf16_tensor_core_denoiser(ctx, tmp_path, cfg, kernel, monkeypatch):
+    # both tensor-core kernels: the row-stacked one (default where it fits) and the tile-per-stage one
+    # (Cin > 64 or Cout > 80, or MLB200_TC_ROWS=0); the library reads the switches when the plan is built
+    monkeypatch.setenv("MLB200_TC_ROWS", "0" if kernel == "tile" else "1")
+    monkeypatch.setenv("MLB200_TC_HALO", "0" if kernel == "rows-3-boxes" else "1")
     path = tmp_path / "d.pb"
     _, layers = gw.make_denoiser(path, channels=3, width=cfg["width"], depth=cfg["depth"], seed=11, act=cfg["act"])
     w, h = cfg["w"], cfg["h"]

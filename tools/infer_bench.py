@@ -47,6 +47,10 @@ def main():
     flop = px * 2 * 9 * (3 * a.width + (a.depth - 2) * a.width * a.width + a.width * 3)
     print(f"{a.precision} width={a.width} depth={a.depth} {a.w}x{a.h}: {dt*1e3:.3f} ms/image, {1/dt:.1f} images/s, "
           f"{flop/dt/1e12:.1f} TFLOP/s algorithmic, tc_layers={model.tensor_core_layers()} launches={model.launch_count()}")
+    prof = model.profile(inp, out)
+    print("per op ms:", " ".join(f"{ms:.4f}" for ms, _, _ in prof),
+          "| TFLOP/s:", " ".join(f"{fl/ms/1e9:.0f}" for ms, fl, _ in prof if ms > 0),
+          "| GB/s:", " ".join(f"{by/ms/1e6:.0f}" for ms, _, by in prof if ms > 0))
 
 
 if __name__ == "__main__":
