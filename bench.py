@@ -269,15 +269,16 @@ def inference_leg(ctx, scene, cam, light, params, rank, world, dist, torch, dev,
     k = max(range(len(ops)), key=lambda j: ops[j][0])
     ms, fl, by = ops[k]
     conv_ms = sum(o[0] for o in ops)
-    roof = {"bound": "tensor", "kernel": f"conv3x3_tc_kernel<64> (op {k}: 3x3 conv 64->64 + bias + relu, bf16 in/out)",
+    roof = {"bound": "tensor", "kernel": f"conv3x3_tc_rows_kernel<64,1> (op {k}: 3x3 conv 64->64 + bias + relu, bf16 in/out)",
             "achieved": fl / (ms * 1e-3) / 1e12, "peak": peaks.get("bf16_tflops"), "unit": "TFLOP/s",
             "frac": fl / (ms * 1e-3) / 1e12 / peaks["bf16_tflops"] if peaks.get("bf16_tflops") else None,
             "peak_source": f"MEASURED_PEAKS.json bf16_tflops (burst: kernel timed alone), {src}",
             "kernel_ms": ms, "algorithmic_flops_per_launch": fl, "algorithmic_bytes_per_launch": by,
             "hbm_gbs_achieved": by / (ms * 1e-3) / 1e9, "hbm_frac": by / (ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
-            "traffic": 491.6e6,
-            "traffic_source": "ncu --set full, dram__bytes_read+write per launch: 265.8 MB + 225.8 MB "
-                              "(profiles/r01_conv_tc_kernel_ncu_full_summary.csv); tensor pipe active 43.7 %",
+            "traffic": 502.2e6,
+            "traffic_source": "ncu --set full, dram__bytes_read+write per launch: 281.3 MB + 220.9 MB "
+                              "(profiles/r01_conv_tc_rows_kernel_ncu_full_summary.csv); tensor pipe active 70.5 %, "
+                              "shared-memory data pipe: 58 % MMA operands + 24 % LSU + TMA",
             "all_ops_ms": [round(o[0], 4) for o in ops], "sum_ops_ms": conv_ms,
             "fp32_all_ops_ms": [round(o[0], 4) for o in fp32_ops]}
     return {"metric": "images/s (1080p image-to-image conv net, batch 8)", "unit": "images/s",

@@ -78,7 +78,8 @@ struct TcParams
     unsigned long long* prof; // MLB200_TC_PROF=1: 8 cycle counters summed over CTAs (see ConvTcRun)
     int wait_ns;         // suspend-time hint of the mbarrier waits in the rows kernel (0: none)
     int rows_mode;       // 1: conv3x3_tc_rows_kernel (filter rows stacked along N), 0: conv3x3_tc_kernel
-    int debug;           // MLB200_TC_DEBUG bit 0: no TMA loads of A, bit 1: no MMAs (timing experiments only)
+    int debug;           // MLB200_TC_DEBUG bit 0: no TMA loads of A, bit 1: no MMAs, bit 2: no epilogue math,
+                         // bit 3: no TMA stores (timing experiments only; results are garbage)
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -263,6 +264,12 @@ __device__ __noinline__ float tc_act(float v, Act act, float alpha)
         case Act::Tanh: return tanhf(v);
         default: return v;
     }
+}
+// 16-byte store to a shared-memory address (the compiler loses the address space of pointers derived
+// from the dynamic shared-memory base and would emit generic ST.E.128)
+__device__ __forceinline__ void sts128(uint32_t saddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+{
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi)
 {
@@ -901,12 +908,6 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
         uint32_t const chunk_bytes = static_cast<uint32_t>(kTileM) * row_bytes;
         uint32_t buf = 0;
         uint32_t ev[2] = {0u, 0u};
-        // this warp's bias values live in registers (its columns never change); only a warp with more
-        // than 32 columns (N = 80) reloads them per 32-column step
-        bool const bias_fixed = c_end - c_begin <= 32;
-        float breg[32];
-#pragma unroll
-        for (int j = 0; j < 32; j++) breg[j] = c_begin + j < c_end ? s_bias[c_begin + j] : 0.f;
         TC_PROF_T0();
         while (walk[0].Valid() || walk[1].Valid())
         {
@@ -936,11 +937,6 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
                     {
                         uint32_t v32[32];
                         bool const two = c0 + 16 < c_end;
-                        if (!bias_fixed)
-                        {
-#pragma unroll
-                            for (int j = 0; j < 32; j++) breg[j] = c0 + j < c_end ? s_bias[c0 + j] : 0.f;
-                        }
                         tc_ld16(taddr + static_cast<uint32_t>(c0), *reinterpret_cast<uint32_t(*)[16]>(&v32[0]));
                         if (two) tc_ld16(taddr + static_cast<uint32_t>(c0 + 16), *reinterpret_cast<uint32_t(*)[16]>(&v32[16]));
                         tc_ld_wait();
@@ -952,7 +948,14 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
                             int const cb = c0 + 16 * h;
                             float v[16];
 #pragma unroll
-                            for (int j = 0; j < 16; j++) v[j] = __uint_as_float(v32[16 * h + j]) + breg[16 * h + j];
+                            for (int j4 = 0; j4 < 4; j4++)
+                            {
+                                float4 const b = *reinterpret_cast<float4 const*>(&s_bias[cb + 4 * j4]);   // broadcast LDS.128
+                                v[4 * j4 + 0] = __uint_as_float(v32[16 * h + 4 * j4 + 0]) + b.x;
+                                v[4 * j4 + 1] = __uint_as_float(v32[16 * h + 4 * j4 + 1]) + b.y;
+                                v[4 * j4 + 2] = __uint_as_float(v32[16 * h + 4 * j4 + 2]) + b.z;
+                                v[4 * j4 + 3] = __uint_as_float(v32[16 * h + 4 * j4 + 3]) + b.w;
+                            }
                             if constexpr (kActClass == 0)
                             {
 #pragma unroll
@@ -976,13 +979,11 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
                                 uint32_t off1 = off0 + 16u;
                                 off0 ^= ((off0 >> 7) & swz_mask) << 4;
                                 off1 ^= ((off1 >> 7) & swz_mask) << 4;
-                                uint8_t* const base = stg + oc * chunk_bytes;
-                                *reinterpret_cast<uint4*>(base + off0) =
-                                    make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
-                                               pack_bf16(v[6], v[7]));
-                                *reinterpret_cast<uint4*>(base + off1) =
-                                    make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
-                                               pack_bf16(v[14], v[15]));
+                                uint32_t const base = smem_addr(stg) + oc * chunk_bytes;
+                                sts128(base + off0, pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                                       pack_bf16(v[6], v[7]));
+                                sts128(base + off1, pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
+                                       pack_bf16(v[14], v[15]));
                             }
                             else
                             {
@@ -1013,7 +1014,7 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
                         TC_PROF_ADD(3);
                         asm volatile("bar.sync 1, %0;" ::"n"(32 * kEpiWarps) : "memory");
                         TC_PROF_ADD(4);
-                        if (issuer)
+                        if (issuer && !(P.debug & 8))
                         {
                             for (int oc = 0; oc * 64 < P.N; oc++)
                                 tma_store_3d(&out_map, stg + oc * chunk_bytes, oc * 64, x0, y);
