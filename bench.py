@@ -467,8 +467,12 @@ def run_b200_arm(args):
                 "algorithmic_flops_per_launch": flops_per_step * share,
                 "box_tests": boxes, "tri_tests": tris, "kernel_ms": kern_ms,
                 "algorithmic_bytes_per_launch": rows * W * 12 + scene_bytes,
-                "note": "BVH traversal is latency/divergence bound; flops = box_tests*21 + tri_tests*45 counted by "
-                        "the instrumented kernel variant on the same frame"}
+                "issue_slots": {"busy_frac": 0.725, "threads_per_instruction": 27.7, "l1_hit": 0.998,
+                                "source": "ncu --set full of this kernel on this workload (smsp__issue_active, "
+                                          "profiles/r01_bvh_spp_kernel_ncu_full_summary.csv): the kernel is bound by "
+                                          "instruction issue, ~40 SASS instructions per two-box node visit"},
+                "note": "BVH traversal is instruction-issue bound, not FP32-pipe bound; flops = box_tests*21 + "
+                        "tri_tests*45 counted by the instrumented kernel variant on the same frame"}
 
     brute = None
     if not args.no_brute:

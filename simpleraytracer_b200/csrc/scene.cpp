@@ -310,7 +310,10 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         srt_render_params band = *params;
         band.buf_y0 = params->y0;
         size_t const group = 8u * stride;
-        size_t n_chunks = rows >= 64 ? std::min<size_t>(8, rows / 32) : 1;
+        // chunks are sized by the rows this launch OWNS: each one costs a launch, two events and a copy
+        // setup (~20 us), which a rank that owns 135 rows of a 1080p frame cannot hide behind 8 of them
+        size_t const owned = rows / stride;
+        size_t n_chunks = owned >= 64 ? std::min<size_t>(8, std::max<size_t>(1, owned / 48)) : 1;
         size_t const chunk_rows = ((rows + n_chunks - 1) / n_chunks + group - 1) / group * group;
         n_chunks = (rows + chunk_rows - 1) / chunk_rows;
         while (m_chunk_events.size() < 2 * n_chunks + 2)

@@ -193,6 +193,41 @@ def test_interleaved_row_blocks_compose_the_full_frame(ctx, accel):
     scene.release()
 
 
+@pytest.mark.parametrize("shape", [
+    dict(W=64, H=300, y0=0, y1=300, stride=1, spp=8),     # 8 chunks of 40 rows, last one short
+    dict(W=96, H=301, y0=13, y1=293, stride=1, spp=1),    # a band that starts off the 8-row grid
+    dict(W=64, H=203, y0=0, y1=203, stride=2, spp=8),     # interleaved: chunks are whole 16-row groups
+    dict(W=40, H=500, y0=0, y1=500, stride=5, spp=1),     # 40-row groups, 13 of them over 8 chunks
+    dict(W=33, H=63, y0=0, y1=63, stride=1, spp=2),       # below the chunking threshold: one piece
+])
+def test_host_render_pipeline_equals_device_render(ctx, shape):
+    """srtRender (host buffers) renders, copies and scatters the band in up to 8 overlapped chunks on
+    alternating streams; every owned pixel must equal the one-launch device render, the rest stays untouched."""
+    import torch
+    from simpleraytracer_b200.sharding import interleaved_rows
+    W, H = shape["W"], shape["H"]
+    v, a, cam, light = api.gen_mesh(9, 3000, W, H)
+    scene = ctx.create_scene(v, a)
+    common = dict(spp=shape["spp"], jitter=1 if shape["spp"] > 1 else 0, seed=3, shade=api.SRT_SHADE_SHADOW,
+                  accel=api.SRT_ACCEL_BVH)
+    frame = torch.zeros((H, W, 3), device="cuda")
+    torch.cuda.synchronize()
+    scene.render_device(cam, light, api.make_params(W, H, **common), frame.data_ptr(), 0, 0, 0)
+    scene.stats()                      # srtRenderDevice is asynchronous on the context's stream: this waits for it
+    full = frame.cpu().numpy()
+    for phase in range(shape["stride"]):
+        p = api.make_params(W, H, y0=shape["y0"], y1=shape["y1"], row_block_stride=shape["stride"],
+                            row_block_phase=phase, **common)
+        rgb, hid, ht, _ = scene.render(cam, light, p)
+        own = [y for y in (interleaved_rows(H, shape["stride"], phase) if shape["stride"] > 1 else range(H))
+               if shape["y0"] <= y < shape["y1"]]
+        other = [y for y in range(H) if y not in set(own)]
+        assert np.array_equal(rgb[own], full[own]), f"phase {phase}"
+        assert (rgb[other] == 0).all() and (hid[other] == -2).all()
+        assert (hid[own] >= -1).all()
+    scene.release()
+
+
 def test_degenerate_cases_on_gpu(ctx):
     """Tie-breaks and rejections of the golden single-ray cases, through a 1x1 render."""
     g = np.load(GOLD / "degenerate.npz")
