@@ -116,6 +116,7 @@ def measured_peaks():
 
 
 # --------------------------------------------------------------------------- CPU arm
+REFERENCE_ARM_BUDGET_S = 150.0   # CPU seconds the timed steps of `--impl reference` may take in total
 def scene_arrays(args):
     from simpleraytracer_b200 import api
     w = WORKLOAD
@@ -146,15 +147,18 @@ def run_reference_arm(args):
     if rank != 0:
         return
     v, a, cam, light, params = scene_arrays(args)
-    for _ in range(min(args.warmup, 1)):
-        cpu_sample(v, a, cam, light, params, 1)
+    # One untimed calibration pass (2 spp) sizes the per-step sample so that the whole run stays within
+    # ~150 s of CPU time whatever --steps is: the first n of the frame's spp samples of every pixel.
+    _, cal_s, _, _ = cpu_sample(v, a, cam, light, params, min(2, args.spp))
+    per_spp = max(cal_s / min(2, args.spp), 1e-3)
+    sample_spp = int(max(1, min(CPU_SAMPLE_SPP, args.spp, REFERENCE_ARM_BUDGET_S / (max(args.steps, 1) * per_spp))))
     total_rays, total_s, threads = 0, 0.0, 0
     for _ in range(args.steps):
-        _, dt, rays, threads = cpu_sample(v, a, cam, light, params, min(CPU_SAMPLE_SPP, args.spp))
+        _, dt, rays, threads = cpu_sample(v, a, cam, light, params, sample_spp)
         total_rays += rays
         total_s += dt
     value = total_rays / total_s / 1e6
-    sample = (f"first {min(CPU_SAMPLE_SPP, args.spp)} of {args.spp} spp of every pixel of the {params.width}x{params.height} frame per step "
+    sample = (f"first {sample_spp} of {args.spp} spp of every pixel of the {params.width}x{params.height} frame per step "
               f"({total_rays // args.steps} rays), oracle BVH path incl. its BVH build")
     line = {
         "impl": "reference", "metric": "Mrays/s (closest-hit+shade, 1080p)", "value": value, "unit": "Mrays/s",
