@@ -717,11 +717,12 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
     uint8_t* smem_o = smem_a + static_cast<uint32_t>(P.stages) * a_stage_bytes;   // 2 output staging tiles
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem_o + 2u * out_tile_bytes);
     uint64_t* full = bars;                       // [stages]   TMA -> MMA
-    uint64_t* empty = bars + kMaxStages;         // [stages]   MMA -> TMA
+    uint64_t* done = bars + kMaxStages;          // [stages]   MMA -> TMA and MMA -> epilogue: the stage's input row has been
+                                                 //            accumulated (ONE tcgen05.commit per row: the stage is free for
+                                                 //            the producer AND the rows it completed can be drained)
     uint64_t* w_full = bars + 2 * kMaxStages;    // filter resident
-    uint64_t* row_done = w_full + 1;             // [2 pipes]  MMA -> epilogue: an input row has been accumulated
-    uint64_t* slot_free = row_done + kMaxAcc;    // [2 pipes]  epilogue -> MMA: the rows it completed are drained
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(slot_free + kMaxAcc);
+    uint64_t* slot_free = w_full + 1;            // [2 pipes]  epilogue -> MMA: the rows it completed are drained
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(slot_free + 2 * kMaxAcc);
 
     uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     __shared__ __align__(16) float s_bias[256];
@@ -733,9 +734,9 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
         asm volatile("prefetch.tensormap [%0];" ::"l"(&in_map) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&w_map) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&out_map) : "memory");
-        for (int s = 0; s < P.stages; s++) { bar_init(&full[s], 1); bar_init(&empty[s], 1); }
+        for (int s = 0; s < P.stages; s++) { bar_init(&full[s], 1); bar_init(&done[s], 1); }
         bar_init(w_full, 1);
-        for (int a = 0; a < 2; a++) { bar_init(&row_done[a], 1); bar_init(&slot_free[a], kEpiWarps); }
+        for (int a = 0; a < 2; a++) bar_init(&slot_free[a], kEpiWarps);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1)
@@ -780,7 +781,7 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
             {
                 if (!walk[p].Valid()) continue;
                 TC_PROF_ADD(1);
-                bar_wait(&empty[s], ph ^ 1u, wait_ns);
+                bar_wait(&done[s], ph ^ 1u, wait_ns);
                 TC_PROF_ADD(0);
                 if (elect_one())
                 {
@@ -874,8 +875,7 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
                         }
                     }
                     TC_PROF_ADD(2);
-                    tc_commit(&empty[s]);
-                    tc_commit(&row_done[p]);
+                    tc_commit(&done[s]);
                     TC_PROF_ADD(3);
                 }
                 __syncwarp();
@@ -907,7 +907,7 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
         uint32_t const swz_mask = row_bytes == 128u ? 7u : (row_bytes == 64u ? 3u : 1u);
         uint32_t const chunk_bytes = static_cast<uint32_t>(kTileM) * row_bytes;
         uint32_t buf = 0;
-        uint32_t ev[2] = {0u, 0u};
+        uint32_t s = 0, ph = 0;          // the stage ring, stepped exactly like the producer and the MMA warp do
         TC_PROF_T0();
         while (walk[0].Valid() || walk[1].Valid())
         {
@@ -923,7 +923,7 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
                 int const x0 = walk[p].strip * kTileM;
                 int const x = x0 + static_cast<int>(row);
                 TC_PROF_ADD(1);
-                bar_wait(&row_done[p], ev[p] & 1u, wait_ns);
+                bar_wait(&done[s], ph, wait_ns);
                 TC_PROF_ADD(0);
                 tc_fence_after();
                 for (int d = 0; d < nd; d++)
@@ -1029,7 +1029,7 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
                     __syncwarp();
                     if (lane == 0) bar_arrive(&slot_free[p]);
                 }
-                ev[p]++;
+                if (++s == static_cast<uint32_t>(P.stages)) { s = 0; ph ^= 1u; }
                 walk[p].Next();
             }
         }
