@@ -116,6 +116,21 @@ __device__ __forceinline__ void bar_wait(uint64_t* bar, uint32_t parity)
             : "memory");
     } while (!done);
 }
+// One probe of the phase without suspending: true when it has completed.
+__device__ __forceinline__ bool bar_test(uint64_t* bar, uint32_t parity)
+{
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(smem_addr(bar)), "r"(parity)
+        : "memory");
+    return done != 0;
+}
 // The same with a suspend-time hint (ns): the thread may stay suspended in hardware that long before
 // try_wait returns false, so a waiting warp polls less often (MLB200_TC_WAIT_NS; 0 = no hint).
 __device__ __forceinline__ void bar_wait(uint64_t* bar, uint32_t parity, uint32_t hint_ns)
@@ -833,6 +848,11 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
         uint32_t const b_blk_u = b_blk_bytes >> 4, b_kw_u = 5u * b_blk_u;
         uint32_t s = 0, ph = 0;
         uint32_t ev[2] = {0u, 0u};       // input rows issued per pipe (= barrier phases)
+        // The waits of step k+1 (its stage landed, the slot it starts afresh drained) are taken in the MIDDLE of
+        // step k's MMAs, while the tensor pipe still has the first ten queued: the MMA queue is short, and
+        // every cycle this thread spends between the last MMA of one row and the first of the next (barrier
+        // latency, fence, loop bookkeeping) is a cycle the pipe runs dry.
+        bool pre_waited = false;
         TC_PROF_T0();
         while (walk[0].Valid() || walk[1].Valid())
         {
@@ -841,48 +861,75 @@ conv3x3_tc_rows_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_
             {
                 if (!walk[p].Valid()) continue;
                 TC_PROF_ADD(2);
-                // the slot this row starts afresh held output row r-2, completed by the pipe's previous row
-                if (ev[p] > 0) bar_wait(&slot_free[p], (ev[p] - 1u) & 1u, wait_ns);
+                if (!pre_waited)
+                {
+                    // the slot this row starts afresh held output row r-2, completed by the pipe's previous row
+                    if (ev[p] > 0) bar_wait(&slot_free[p], (ev[p] - 1u) & 1u, wait_ns);
+                    bar_wait(&full[s], ph, wait_ns);
+                    tc_fence_after();
+                }
                 TC_PROF_ADD(0);
-                bar_wait(&full[s], ph, wait_ns);
-                TC_PROF_ADD(1);
-                tc_fence_after();
                 uint32_t const c = static_cast<uint32_t>(walk[p].r) % 3u;
                 uint32_t const win = c == 0u ? 0u : (c == 1u ? 2u : 1u);      // window start in [W1 W0 W2 W1 W0]
                 uint32_t const fresh = c == 2u ? 0u : c + 1u;                  // slot of output row r+1
                 uint32_t const all_fresh = walk[p].first ? 1u : 0u;
-                if (elect_one())
+                uint32_t const a_st = a_lo0 + s * stage_u;
+                uint32_t const b_st = b_lo0 + win * b_blk_u;
+                uint32_t const d_tmem = tmem_base + static_cast<uint32_t>(p) * 3u * N;
+                uint64_t* const done_bar = &done[s];
+                bool const mma_on = !(P.debug & 2);
+                if (elect_one() && mma_on)
                 {
-                    if (!(P.debug & 2))
+#pragma unroll
+                    for (uint32_t sl = 0; sl < 3u; sl++)
+                        tc_mma_bf16_lohi<false>(d_tmem + sl * N, a_st, b_st + sl * b_blk_u, desc_hi, idesc1,
+                                                (all_fresh | (sl == fresh ? 1u : 0u)) ^ 1u);
+#pragma unroll
+                    for (uint32_t kw = 0; kw < 2u; kw++)
                     {
-                        uint32_t const a_st = a_lo0 + s * stage_u;
-                        uint32_t const b_st = b_lo0 + win * b_blk_u;
-                        uint32_t const d_tmem = tmem_base + static_cast<uint32_t>(p) * 3u * N;
 #pragma unroll
-                        for (uint32_t sl = 0; sl < 3u; sl++)
-                            tc_mma_bf16_lohi<false>(d_tmem + sl * N, a_st, b_st + sl * b_blk_u, desc_hi, idesc1,
-                                                    (all_fresh | (sl == fresh ? 1u : 0u)) ^ 1u);
-#pragma unroll
-                        for (uint32_t kw = 0; kw < 3u; kw++)
+                        for (uint32_t k = 0; k < KC / 16; k++)
                         {
-#pragma unroll
-                            for (uint32_t k = 0; k < KC / 16; k++)
-                            {
-                                if (kw == 0 && k == 0) continue;
-                                tc_mma_bf16_lohi<true>(d_tmem, a_st + kw * tap_u + 2u * k, b_st + kw * b_kw_u + 2u * k,
-                                                       desc_hi, idesc3, 1u);
-                            }
+                            if (kw == 0 && k == 0) continue;
+                            tc_mma_bf16_lohi<true>(d_tmem, a_st + kw * tap_u + 2u * k, b_st + kw * b_kw_u + 2u * k,
+                                                   desc_hi, idesc3, 1u);
                         }
                     }
-                    TC_PROF_ADD(2);
-                    tc_commit(&done[s]);
-                    TC_PROF_ADD(3);
                 }
                 __syncwarp();
+                TC_PROF_ADD(2);
+                // bookkeeping and a probe of the next step's barriers, under cover of the queued MMAs.  The next
+                // step is the other pipe's unless that one is exhausted; a step on the SAME pipe depends on this
+                // row's own commit (its slot_free follows from it), so it is never probed early.
                 if (++s == static_cast<uint32_t>(P.stages)) { s = 0; ph ^= 1u; }
                 ev[p]++;
                 walk[p].Next();
-                TC_PROF_ADD(4);
+                pre_waited = false;
+                if (walk[1 - p].Valid())
+                {
+                    // only if both have already happened: blocking here would hold this row's last MMAs back
+                    bool ok = ev[1 - p] == 0 || bar_test(&slot_free[1 - p], (ev[1 - p] - 1u) & 1u);
+                    ok = ok && bar_test(&full[s], ph);
+                    if (ok)
+                    {
+                        tc_fence_after();
+                        pre_waited = true;
+                    }
+                }
+                TC_PROF_ADD(1);
+                if (elect_one())
+                {
+                    if (mma_on)
+                    {
+#pragma unroll
+                        for (uint32_t k = 0; k < KC / 16; k++)
+                            tc_mma_bf16_lohi<true>(d_tmem, a_st + 2u * tap_u + 2u * k, b_st + 2u * b_kw_u + 2u * k,
+                                                   desc_hi, idesc3, 1u);
+                    }
+                    tc_commit(done_bar);
+                }
+                __syncwarp();
+                TC_PROF_ADD(3);
             }
         }
         TC_PROF_ADD(4);
