@@ -425,6 +425,7 @@ void Model::FusePlan()
             if (p < 0 || uses[src] != 1) continue;
             Op& prod = m_ops[p];
             if (prod.act != nn::Act::None) continue; // activation already applied: order matters
+            if (prod.residual >= 0) continue;        // the residual is added after the activation
             bool const has_bias = op.bias >= 0;
             if (prod.kind == OpKind::Conv || prod.kind == OpKind::BiasAct)
             {
@@ -448,6 +449,30 @@ void Model::FusePlan()
             prod.out = op.out;
             m_ops.erase(m_ops.begin() + static_cast<long>(i));
             changed = true;
+        }
+        // Add(conv(...), r) -> the convolution's epilogue adds r (a global residual costs no pass of its
+        // own).  Only when nothing else reads the conv result, r exists before the conv runs, and no
+        // activation sits on the Add (the fused order is act(conv + bias) + r, exactly the graph's).
+        for (size_t i = 0; i < m_ops.size() && !changed; i++)
+        {
+            Op& op = m_ops[i];
+            if (op.kind != OpKind::Add || op.in.size() != 2 || op.in[0] == op.in[1]) continue;
+            if (op.act != nn::Act::None) continue;
+            for (int k = 0; k < 2 && !changed; k++)
+            {
+                int const conv_t = op.in[k], res_t = op.in[1 - k];
+                int const p = producer[conv_t];
+                if (p < 0 || uses[conv_t] != 1) continue;
+                Op& prod = m_ops[p];
+                if (prod.kind != OpKind::Conv || prod.residual >= 0) continue;
+                if (res_t != m_input_tensor && (producer[res_t] < 0 || producer[res_t] > p)) continue;
+                prod.residual = res_t;
+                prod.in.push_back(res_t);
+                prod.add_name = op.name;
+                prod.out = op.out;
+                m_ops.erase(m_ops.begin() + static_cast<long>(i));
+                changed = true;
+            }
         }
     }
 }
@@ -495,6 +520,12 @@ void Model::InferShapes(size_t H, size_t W, size_t C)
                 if ((a.H && !o.H) || (a.W && !o.W))
                     throw std::runtime_error("Conv2D '" + op.name + "' output is empty for a "
                                              + std::to_string(a.W) + " x " + std::to_string(a.H) + " input");
+                if (op.residual >= 0)
+                {
+                    TensorInfo const& r = m_tensors[op.residual];
+                    if (r.C != o.C || r.H != o.H || r.W != o.W)
+                        throw std::runtime_error("'" + op.add_name + "' operands differ in shape");
+                }
                 break;
             }
             case OpKind::BiasAct:
@@ -562,13 +593,14 @@ void Model::AssignPrecision()
             if (op.kind != OpKind::Conv || !(tc[i] || plain3x3(op))) continue;
             if (op.out == m_output_tensor || op.out == m_input_tensor) continue;
             if (m_tensors[op.out].C % 16 != 0) continue;
+            if (op.residual >= 0) continue;          // conv + residual writes fp32
             bool all_tc = false;
             for (size_t j = 0; j < m_ops.size(); j++)
                 for (int t : m_ops[j].in)
                     if (t == op.out) { all_tc = true; }
             for (size_t j = 0; j < m_ops.size() && all_tc; j++)
                 for (int t : m_ops[j].in)
-                    if (t == op.out && !tc[j]) all_tc = false;
+                    if (t == op.out && (!tc[j] || m_ops[j].residual == t)) all_tc = false;   // a residual is read as fp32
             bf[op.out] = all_tc;
         }
         for (size_t i = 0; i < m_ops.size(); i++)
@@ -723,6 +755,7 @@ std::string Model::Describe() const
             os << " k=" << op.KH << "x" << op.KW << " stride=" << op.stride << " dilation=" << op.dilation
                << " padding=" << (op.same_padding ? "SAME" : "VALID") << " wsum=" << sum;
         }
+        if (op.residual >= 0) os << " residual=t" << op.residual;
         if (op.tc) os << " engine=tcgen05_bf16";
         if (m_tensors[op.out].bf16) os << " out=bf16";
         os << " bias=" << (op.bias >= 0 ? "yes" : "no") << " act=" << acts[static_cast<int>(op.act)];
@@ -735,7 +768,8 @@ std::string Model::Describe() const
 size_t Model::LaunchesPerInfer() const
 {
     size_t n = 0;
-    for (auto const& op : m_ops) n += op.kind == OpKind::Concat ? op.in.size() : ((op.tc && op.pad_in) ? 2 : 1);
+    for (auto const& op : m_ops)
+        n += op.kind == OpKind::Concat ? op.in.size() : (1 + (op.tc && op.pad_in ? 1 : 0) + (op.tc && op.residual >= 0 ? 1 : 0));
     if (m_input_info.dtype == ML_FLOAT16) n += 2;
     return n;
 }
@@ -852,11 +886,17 @@ void Model::RunOp(Op const& op, float const* d_in, float* d_out, cudaStream_t st
                 d.act = op.act;
                 d.alpha = op.alpha;
                 float const* bias = op.bias >= 0 ? m_consts[op.bias].dev : nullptr;
+                d.residual = op.residual >= 0 ? ptr(op.residual) : nullptr;
                 if (op.tc)
                 {
                     if (op.pad_in)
                         nn::PadToBf16x16(ptr(op.in[0]), op.pad_buffer, static_cast<size_t>(a.H) * a.W, a.C, stream);
                     nn::ConvTcRun(op.tc_op, bias, ptr(op.out), stream);
+                    // The folded Add runs as its own in-place pass here: inside the tensor-core epilogue the
+                    // residual's global loads sit in the serial per-tile drain (measured on the 64->3 layer
+                    // at 1080p: 0.135 ms fused, even prefetched, against 0.091 + 0.022 ms as two launches).
+                    if (d.residual != nullptr)
+                        nn::AddAct(ptr(op.out), d.residual, ptr(op.out), n_out, nn::Act::None, 0.f, stream);
                 }
                 else if (o.bf16)
                     nn::Conv2dFp32ToBf16(ptr(op.in[0]), m_consts[op.weights].dev, bias, ptr(op.out), d, stream);

@@ -71,6 +71,8 @@ private:
         int bias = -1;         // index into m_consts or -1
         nn::Act act = nn::Act::None;
         float alpha = 0.2f;
+        int residual = -1;     // Conv: tensor added after the activation (a following Add folded in); also in `in`
+        std::string add_name;  // name of the folded Add node, for its error message
         std::string name;      // for error messages
         // bf16 tensor-core execution (decided by AssignPrecision, bound by AllocateBuffers)
         bool tc = false;

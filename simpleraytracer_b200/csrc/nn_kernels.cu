@@ -160,6 +160,26 @@ conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
             float r1 = apply_act(a01.y + b[1], d.act, d.alpha);
             float r2 = apply_act(a23.x + b[2], d.act, d.alpha);
             float r3 = apply_act(a23.y + b[3], d.act, d.alpha);
+            if constexpr (sizeof(OutT) == 4)
+            {
+                if (d.residual != nullptr)
+                {
+                    // fused Add: same fp32 additions, in the same order, as the separate add kernel made
+                    float const* res = d.residual + (static_cast<size_t>(oy) * d.OW + ox) * d.Cout + co;
+                    if (vec)
+                    {
+                        float4 const rv = *reinterpret_cast<float4 const*>(res);
+                        r0 += rv.x; r1 += rv.y; r2 += rv.z; r3 += rv.w;
+                    }
+                    else
+                    {
+                        if (co + 0 < d.Cout) r0 += res[0];
+                        if (co + 1 < d.Cout) r1 += res[1];
+                        if (co + 2 < d.Cout) r2 += res[2];
+                        if (co + 3 < d.Cout) r3 += res[3];
+                    }
+                }
+            }
             if (vec)
             {
                 if constexpr (sizeof(OutT) == 4)
@@ -208,7 +228,9 @@ __global__ void conv2d_naive_kernel(float const* __restrict__ in, float const* _
         }
     }
     if (bias) acc += bias[co];
-    out[idx] = apply_act(acc, d.act, d.alpha);
+    acc = apply_act(acc, d.act, d.alpha);
+    if (d.residual != nullptr) acc += d.residual[idx];
+    out[idx] = acc;
 }
 
 template <int KS, int TH, int TW, int PXT, int CG, int CI_T, int CPT = 4, typename OutT>
@@ -244,8 +266,8 @@ __global__ void bias_act_kernel(float const* __restrict__ in, float const* __res
     }
 }
 
-__global__ void add_act_kernel(float const* __restrict__ a, float const* __restrict__ b,
-                               float* __restrict__ out, size_t n, Act act, float alpha)
+// no __restrict__: `out` may be `a` or `b` (in-place inference, or the residual pass after a tensor-core layer)
+__global__ void add_act_kernel(float const* a, float const* b, float* out, size_t n, Act act, float alpha)
 {
     size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;

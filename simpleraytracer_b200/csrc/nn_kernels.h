@@ -25,6 +25,7 @@ struct ConvDesc
     int pad_top, pad_left;
     Act act;
     float alpha;        // LeakyRelu slope
+    float const* residual; // fp32 [OH*OW*Cout] added AFTER the activation (a fused Add), or nullptr
 };
 
 // fp32 direct convolution + bias + activation, one launch.

@@ -41,10 +41,10 @@ def test_reader_inspects_writer_graph(tmp_path):
     assert lines[0] == "input_node=input output_node=output"
     assert lines[1] == "input dtype=0 w=0 h=0 c=3"
     assert lines[2] == "output dtype=0 w=0 h=0 c=3"
-    # Conv+BiasAdd+LeakyRelu fused: 4 convs + residual add (Identity is free)
-    assert lines[3] == "ops=5 launches=5"
+    # Conv+BiasAdd+LeakyRelu fused: 4 launches; the residual add is folded into the last conv (Identity is free)
+    assert lines[3] == "ops=4 launches=4"
     assert lines[4].startswith("Conv name=conv0 ") and "bias=yes act=leaky_relu alpha=0.1" in lines[4]
-    assert "act=none" in lines[7] and lines[8].startswith("Add ")
+    assert "act=none" in lines[7] and "residual=t0" in lines[7] and len(lines) == 8
 
 
 def runtime_graph(float_val=False, with_shapes=True):
@@ -154,7 +154,7 @@ def test_bf16_plan_is_decided_on_the_host(tmp_path, monkeypatch):
     convs = [l for l in text.splitlines() if l.startswith("Conv ")]
     assert len(convs) == 4 and all("engine=tcgen05_bf16" in l for l in convs)
     assert all("out=bf16" in l for l in convs[:3]) and "out=bf16" not in convs[3]   # last layer writes fp32
-    assert "launches=6" in text                              # + pad-to-16-channels pass + residual add
+    assert "launches=6" in text                              # + the pad-to-16-channels pass + the residual add (its own pass after a tensor-core layer)
     # a 5x5 net has no tensor-core layer; a 128->128 layer does not fit in shared memory
     gw.make_denoiser(path, channels=3, width=32, depth=3, seed=1, kernel=5)
     ok, text = api.inspect_model(path)
@@ -164,3 +164,43 @@ def test_bf16_plan_is_decided_on_the_host(tmp_path, monkeypatch):
     convs = [l for l in text.splitlines() if l.startswith("Conv ")]
     assert ["engine=tcgen05_bf16" in l for l in convs] == [True, False, True]
     assert "out=bf16" in convs[1]                            # the fp32 layer feeds a tensor-core layer in bf16
+
+
+def test_add_is_folded_into_the_conv_only_when_the_order_allows(tmp_path):
+    """Add(conv, r) -> conv epilogue (host logic, visible through mlxInspectModel).  Not folded: an
+    activation on the sum, a conv result with a second reader, a residual that is computed later."""
+    rng = np.random.default_rng(0)
+    k = lambda ci, co: (rng.standard_normal((3, 3, ci, co)) * 0.1).astype(np.float32)
+
+    def build(fn):
+        g = gw.GraphBuilder()
+        x = g.placeholder("input", (-1, -1, -1, 4))
+        out = fn(g, x)
+        g.unary("Identity", out, name="output", out_shape=(-1, -1, -1, 4))
+        path = tmp_path / "g.pb"
+        path.write_bytes(g.finish())
+        ok, text = api.inspect_model(path)
+        assert ok, text
+        return [l for l in text.splitlines()[4:]]
+
+    # relu(conv(x) + x): the activation belongs to the sum -> the Add stays (with the Relu folded into it)
+    ops = build(lambda g, x: g.unary("Relu", g.add(g.conv2d(x, k(4, 4), name="c", out_shape=(-1, -1, -1, 4)), x,
+                                                   out_shape=(-1, -1, -1, 4)), out_shape=(-1, -1, -1, 4)))
+    assert [o.split()[0] for o in ops] == ["Conv", "Add"] and "act=relu" in ops[1] and "residual" not in ops[0]
+
+    # t = conv(x); u = conv(t); t + u: t has two readers, u is folded with t as its residual
+    def two(g, x):
+        t = g.conv2d(x, k(4, 4), name="t", out_shape=(-1, -1, -1, 4))
+        u = g.conv2d(t, k(4, 4), name="u", out_shape=(-1, -1, -1, 4))
+        return g.add(t, u, out_shape=(-1, -1, -1, 4))
+    ops = build(two)
+    assert [o.split()[0] for o in ops] == ["Conv", "Conv"] and "residual" not in ops[0] and "residual=t" in ops[1]
+
+    # a = conv(x); b = conv(x); a + b: only the LATER conv can take the other as a residual
+    def par(g, x):
+        a = g.conv2d(x, k(4, 4), name="a", out_shape=(-1, -1, -1, 4))
+        b = g.conv2d(x, k(4, 4), name="b", out_shape=(-1, -1, -1, 4))
+        return g.add(a, b, out_shape=(-1, -1, -1, 4))
+    ops = build(par)
+    assert [o.split()[0] for o in ops] == ["Conv", "Conv"]
+    assert "residual" not in ops[0] and "name=b " in ops[1] and "residual=t" in ops[1]

@@ -63,7 +63,7 @@ def test_denoiser_matches_oracle(ctx, tmp_path, cfg):
     inp.write(x)
     model.infer(inp, out)
     close(out.read(), O.run_denoiser(x, layers, alpha=0.1), str(cfg))
-    assert model.launch_count() == cfg["depth"] + 1   # fused conv+bias+act per layer + residual add
+    assert model.launch_count() == cfg["depth"]       # conv+bias+act per layer; the residual add rides in the last one
     for obj in (inp, out, model):
         obj.release()
 
@@ -131,6 +131,41 @@ def test_concat_and_unfused_ops(ctx, tmp_path):
     close(out.read(), ref, "concat")
     for obj in (inp, out, model):
         obj.release()
+
+
+def test_residual_adds_fused_and_unfused(ctx, tmp_path):
+    """Add(conv, r) rides in the conv's epilogue when the order allows (test_graphdef checks the plan);
+    the numbers must not care, nor about inferring in place (input image == output image)."""
+    rng = np.random.default_rng(13)
+    k = lambda ci, co: (rng.standard_normal((3, 3, ci, co)) * 0.2).astype(np.float32)
+    w1, w2 = k(4, 4), k(4, 4)
+    cases = {
+        "relu(conv(x)+x)": (lambda g, x: g.unary("Relu", g.add(g.conv2d(x, w1, name="c"), x)),
+                            lambda x: np.maximum(O.conv2d(x, w1) + x, 0)),
+        "t+conv(t)": (lambda g, x: (lambda t: g.add(t, g.conv2d(t, w2, name="u")))(g.conv2d(x, w1, name="t")),
+                      lambda x: (lambda t: t + O.conv2d(t, w2))(O.conv2d(x, w1))),
+        "conv_a(x)+conv_b(x)": (lambda g, x: g.add(g.conv2d(x, w1, name="a"), g.conv2d(x, w2, name="b")),
+                                lambda x: O.conv2d(x, w1) + O.conv2d(x, w2)),
+        "x+conv(x)": (lambda g, x: g.add(x, g.conv2d(x, w1, name="c")),
+                      lambda x: x + O.conv2d(x, w1)),
+    }
+    W, H = 37, 19
+    xin = rng.standard_normal((H, W, 4)).astype(np.float32)
+    for name, (build, ref_fn) in cases.items():
+        g = gw.GraphBuilder()
+        x = g.placeholder("input", (-1, -1, -1, 4))
+        g.unary("Identity", build(g, x), name="output", out_shape=(-1, -1, -1, 4))
+        path = tmp_path / "r.pb"; path.write_bytes(g.finish())
+        model, i, o = prepared_model(ctx, path, W, H)
+        inp = ctx.create_image(W, H, 4); out = ctx.create_image(W, H, 4)
+        inp.write(xin)
+        model.infer(inp, out)
+        ref = ref_fn(xin)
+        close(out.read(), ref, name)
+        model.infer(inp, inp)                      # in place
+        close(inp.read(), ref, name + " in place")
+        for obj in (inp, out, model):
+            obj.release()
 
 
 def test_float16_images(ctx, tmp_path):
