@@ -438,6 +438,19 @@ def run_b200_arm(args):
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     e2e_value = rays_per_step * args.steps / float(e2e_s.item()) / 1e6
+    # the same call into a page-locked frame: srtRender copies the chunks straight from the device
+    pinned = torch.zeros((H, W, 3), dtype=torch.float32).pin_memory()
+    host_rgb = pinned.numpy()
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_pin_s = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_pin_s, op=dist.ReduceOp.MAX)
+    e2e_pinned_value = rays_per_step * args.steps / float(e2e_pin_s.item()) / 1e6
     d2h = torch.tensor([rows * W * 12], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(d2h)
@@ -519,7 +532,9 @@ def run_b200_arm(args):
                    "scene_upload_ms": info.upload_ms, "wall_s_timed_region": wall_s},
         "roofline": roofline, "intersect_roofline": brute, "cpu_baseline": cpu, "inference": inference,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": C.sizeof(api.srt_render_params)
-                + C.sizeof(api.srt_camera) + C.sizeof(api.srt_light), "d2h_bytes_per_step": int(d2h.item())},
+                + C.sizeof(api.srt_camera) + C.sizeof(api.srt_light), "d2h_bytes_per_step": int(d2h.item()),
+                "host_buffer": "pageable (a reference-style caller's std::vector / numpy array)",
+                "value_page_locked_buffer": e2e_pinned_value},
         "gpu_launches": args.steps, "clocks": clocks.summary(),
         "peaks": {"fp32_tflops_measured_live": fp32_peak, "hbm_gbs": measured_peaks()[0].get("hbm_gbs"),
                   "source": measured_peaks()[1]},

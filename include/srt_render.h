@@ -136,7 +136,10 @@ ML_API_ENTRY ml_status srtGenMesh(uint32_t seed, size_t n_triangles,
 /* Host-buffer entry point: renders rows [y0,y1) and copies them into the
  * caller's buffers (any of rgb/hit_id/hit_t may be NULL).  Synchronous.
  * rgb: H*W*3 floats (HWC); hit_id: H*W int32 (-1 = miss); hit_t: H*W floats
- * (+inf = miss).  With spp > 1, hit_id/hit_t are those of sample 0. */
+ * (+inf = miss).  With spp > 1, hit_id/hit_t are those of sample 0.
+ * The band is rendered, copied and scattered in overlapped chunks; buffers that
+ * are page-locked as a whole (cudaHostAlloc / cudaHostRegister) are filled
+ * straight from the device, pageable ones through pinned staging. */
 ML_API_ENTRY ml_status srtRender(srt_scene scene, srt_camera const* camera,
                                  srt_light const* light, srt_render_params const* params,
                                  float* rgb, int32_t* hit_id, float* hit_t,

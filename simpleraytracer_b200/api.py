@@ -365,12 +365,18 @@ class Scene:
         self.lib.srtGetSceneBvh(self.handle, nodes.ctypes.data, n, order.ctypes.data, len(order))
         return nodes, order
 
-    def render(self, camera, light, params, want_rgb=True, want_aov=True):
-        """srtRender: host buffers; returns (rgb, hit_id, hit_t, stats) for rows [buf_y0, y1)."""
+    def render(self, camera, light, params, want_rgb=True, want_aov=True, buffers=None):
+        """srtRender: host buffers; returns (rgb, hit_id, hit_t, stats) for rows [buf_y0, y1).
+        `buffers` = (rgb, hit_id, hit_t) numpy arrays to render into (e.g. views of page-locked memory,
+        which srtRender fills straight from the device) instead of fresh pageable arrays."""
         rows = params.height - params.buf_y0
-        rgb = np.zeros((rows, params.width, 3), dtype=np.float32) if want_rgb else None
-        hid = np.full((rows, params.width), -2, dtype=np.int32) if want_aov else None
-        ht = np.zeros((rows, params.width), dtype=np.float32) if want_aov else None
+        if buffers is not None:
+            rgb, hid, ht = buffers
+            want_rgb, want_aov = rgb is not None, hid is not None and ht is not None
+        else:
+            rgb = np.zeros((rows, params.width, 3), dtype=np.float32) if want_rgb else None
+            hid = np.full((rows, params.width), -2, dtype=np.int32) if want_aov else None
+            ht = np.zeros((rows, params.width), dtype=np.float32) if want_aov else None
         stats = srt_render_stats()
         st = self.lib.srtRender(self.handle, C.byref(camera), C.byref(light), C.byref(params),
                                 rgb.ctypes.data if want_rgb else None,

@@ -309,6 +309,20 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         // transfer is exposed.  With interleaved sharding only the owned 8-row blocks cross PCIe.
         srt_render_params band = *params;
         band.buf_y0 = params->y0;
+        // Caller buffers that are page-locked (cudaHostAlloc / cudaHostRegister, as a whole) take the chunks
+        // straight from the device: no staging copy, no host-side scatter.
+        auto page_locked = [](void const* ptr) {
+            if (ptr == nullptr) return true;
+            cudaPointerAttributes at{};
+            if (cudaPointerGetAttributes(&at, ptr) != cudaSuccess) { cudaGetLastError(); return false; }
+            return at.type == cudaMemoryTypeHost;
+        };
+        bool const direct = (rgb || hit_id || hit_t) && page_locked(rgb) && page_locked(hit_id) && page_locked(hit_t);
+        // band-local pixel p of the device buffers is pixel `to_caller + p` of the caller's frame
+        size_t const to_caller = static_cast<size_t>(params->y0 - params->buf_y0) * W;
+        void* const h_rgb = direct ? static_cast<void*>(rgb ? rgb + to_caller * 3 : nullptr) : m_h_rgb;
+        void* const h_id = direct ? static_cast<void*>(hit_id ? hit_id + to_caller : nullptr) : m_h_id;
+        void* const h_t = direct ? static_cast<void*>(hit_t ? hit_t + to_caller : nullptr) : m_h_t;
         size_t const group = 8u * stride;
         // chunks are sized by the rows this launch OWNS: each one costs a launch, two events and a copy
         // setup (~20 us), which a rank that owns 135 rows of a 1080p frame cannot hide behind 8 of them
@@ -344,9 +358,9 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
                     ML_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(h) + p0 * item, static_cast<char*>(d) + p0 * item,
                                                   np * item, cudaMemcpyDeviceToHost, sc));
                 };
-                if (rgb) copy(m_h_rgb, m_d_rgb, 12);
-                if (hit_id) copy(m_h_id, m_d_id, 4);
-                if (hit_t) copy(m_h_t, m_d_t, 4);
+                if (rgb) copy(h_rgb, m_d_rgb, 12);
+                if (hit_id) copy(h_id, m_d_id, 4);
+                if (hit_t) copy(h_t, m_d_t, 4);
             }
             else
             {
@@ -356,16 +370,27 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
                 size_t const first = static_cast<size_t>(origin - params->y0) * W; // pixels
                 size_t const blk = 8 * W;                                           // pixels per block
                 size_t const pitch = static_cast<size_t>(step) * W;                 // pixels between blocks
+                // the staging buffers hold whole blocks; the caller's frame may end inside the last one
+                size_t const last_y = static_cast<size_t>(origin) + static_cast<size_t>(count ? count - 1 : 0) * step;
+                bool const clipped = direct && count > 0 && last_y + 8 > c.y1;
+                size_t const whole = clipped ? count - 1 : count;
                 auto copy = [&](void* h, void* d, size_t item) {
-                    ML_CUDA_CHECK(cudaMemcpy2DAsync(static_cast<char*>(h) + first * item, pitch * item,
-                                                    static_cast<char*>(d) + first * item, pitch * item,
-                                                    blk * item, count, cudaMemcpyDeviceToHost, sc));
+                    if (whole > 0)
+                        ML_CUDA_CHECK(cudaMemcpy2DAsync(static_cast<char*>(h) + first * item, pitch * item,
+                                                        static_cast<char*>(d) + first * item, pitch * item,
+                                                        blk * item, whole, cudaMemcpyDeviceToHost, sc));
+                    if (clipped)
+                    {
+                        size_t const off = (last_y - params->y0) * W, n = (c.y1 - last_y) * W;
+                        ML_CUDA_CHECK(cudaMemcpyAsync(static_cast<char*>(h) + off * item, static_cast<char*>(d) + off * item,
+                                                      n * item, cudaMemcpyDeviceToHost, sc));
+                    }
                 };
                 if (count > 0)
                 {
-                    if (rgb) copy(m_h_rgb, m_d_rgb, 12);
-                    if (hit_id) copy(m_h_id, m_d_id, 4);
-                    if (hit_t) copy(m_h_t, m_d_t, 4);
+                    if (rgb) copy(h_rgb, m_d_rgb, 12);
+                    if (hit_id) copy(h_id, m_d_id, 4);
+                    if (hit_t) copy(h_t, m_d_t, 4);
                 }
             }
             ML_CUDA_CHECK(cudaEventRecord(m_chunk_events[2 * k + 1], sc));
@@ -379,7 +404,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
 
         // host side: as each chunk lands in the pinned staging, move its (owned) rows into the caller's
         // frame at their full-frame offsets (relative to the caller's buf_y0)
-        for (size_t k = 0; k < n_chunks; k++)
+        for (size_t k = 0; k < n_chunks && !direct; k++)
         {
             size_t const r0 = k * chunk_rows, r1 = std::min(rows, r0 + chunk_rows);
             ML_CUDA_CHECK(cudaEventSynchronize(m_chunk_events[2 * k + 1]));
@@ -401,6 +426,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
                 r += run;
             }
         }
+        if (direct) ML_CUDA_CHECK(cudaStreamSynchronize(sc));
         ML_CUDA_CHECK(cudaStreamSynchronize(s0));
         if (stats) return GetStats(stats);
         return ML_OK;

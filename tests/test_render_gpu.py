@@ -225,6 +225,12 @@ def test_host_render_pipeline_equals_device_render(ctx, shape):
         assert np.array_equal(rgb[own], full[own]), f"phase {phase}"
         assert (rgb[other] == 0).all() and (hid[other] == -2).all()
         assert (hid[own] >= -1).all()
+        # the same into page-locked buffers: filled straight from the device, no staging / host scatter
+        pin = [torch.zeros(s_, dtype=t_).pin_memory() for s_, t_ in
+               (((H, W, 3), torch.float32), ((H, W), torch.int32), ((H, W), torch.float32))]
+        pin[1].fill_(-2)
+        prgb, phid, pht, _ = scene.render(cam, light, p, buffers=tuple(t.numpy() for t in pin))
+        assert np.array_equal(prgb, rgb) and np.array_equal(phid, hid) and np.array_equal(pht, ht), f"phase {phase}"
     scene.release()
 
 
