@@ -1,5 +1,8 @@
+#!/usr/bin/env python
+"""Wall time of srtRender (host buffers) against the device-resident render of the benchmark frame."""
 import sys, time, ctypes as C
-sys.path.insert(0, '/root/repo')
+from pathlib import Path
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 import numpy as np
 from simpleraytracer_b200 import api
 W,H=1920,1080
