@@ -446,6 +446,30 @@ def test_bf16_tensor_core_denoiser(ctx, tmp_path, cfg, kernel, monkeypatch):
         obj.release()
 
 
+@pytest.mark.parametrize("shape", [(1, 1), (127, 3), (128, 4), (129, 5), (255, 31), (256, 32), (257, 33), (3, 200),
+                                   (385, 7), (640, 360), (37, 1080), (1025, 2)])
+def test_bf16_row_stacked_kernel_tiles_any_frame(ctx, tmp_path, shape):
+    """The row-stacked kernel cuts the (strip, row) tile sequence into 2 x 148 contiguous ranges that may
+    start and end anywhere, cross strip boundaries, or be empty: frames around the 128-pixel tile width,
+    shorter than the pipes, one pixel wide, one row high."""
+    w, h = shape
+    path = tmp_path / "d.pb"
+    _, layers = gw.make_denoiser(path, channels=3, width=64, depth=3, seed=21, act="Relu")
+    model, i, o = prepared_model(ctx, path, w, h)
+    x = np.random.default_rng(w * 131 + h).random((h, w, 3), dtype=np.float32)
+    inp = ctx.create_image(w, h, 3); out = ctx.create_image(w, h, 3)
+    inp.write(x)
+    model.set_precision(api.MLX_PRECISION_BF16)
+    assert model.tensor_core_layers() == 3
+    model.infer(inp, out)
+    emu = bf16_emulated_denoiser(x, layers, {0, 1, 2})
+    scale = max(float(np.abs(emu).max()), 1e-6)
+    err = float(np.abs(out.read() - emu).max()) / scale
+    assert err <= BF16_VS_EMULATION, f"{shape}: {err:.3e}"
+    for obj in (inp, out, model):
+        obj.release()
+
+
 @pytest.mark.parametrize("precision", [api.MLX_PRECISION_FP32, api.MLX_PRECISION_BF16])
 def test_infer_batch_equals_single_infers(ctx, tmp_path, precision):
     """mlxInferBatch (SURVEY N4): pipelined batch == the same mlInfer calls one by one, bit for bit;
