@@ -56,7 +56,7 @@ __device__ __forceinline__ F2 fma2(F2 a, F2 b, F2 c)
 }
 
 template <int KS, int TH, int TW, int PXT, int CG, int CI_T, typename OutT, int CPT = 4>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 2)
 conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
                    float const* __restrict__ bias, OutT* __restrict__ out, ConvDesc d)
 {
@@ -83,27 +83,106 @@ conv2d_tile_kernel(float const* __restrict__ in, float const* __restrict__ w,
 #pragma unroll
         for (int j = 0; j < CPT / 2; j++) acc2[i][j] = pack2(0.f, 0.f);
 
+    // Staging is software-pipelined through registers: the next channel slice is fetched from global
+    // memory (float4 wherever the layout allows) BEFORE the FMAs of the current slice, and written to
+    // shared memory after them, so the global-load latency hides behind ~2300 FFMA2 per thread.
+    constexpr int VI = CI_T % 4 == 0 ? 4 : 1;                  // input channels per fetch
+    constexpr int VW = CO_T % 4 == 0 ? 4 : 1;                  // filter output channels per fetch
+    constexpr int IN_ITEMS = IH * IW * (CI_T / VI), W_ITEMS = KS * KS * CI_T * (CO_T / VW);
+    constexpr int IN_PER = (IN_ITEMS + 255) / 256, W_PER = (W_ITEMS + 255) / 256;
+    bool const vec_in = VI == 4 && d.Cin % 4 == 0;            // 16-byte aligned pixels, no ragged channel tail
+    bool const vec_w = VW == 4 && d.Cout % 4 == 0;
+    float4 rin[IN_PER], rw[W_PER];
+    auto fetch = [&](int c0) {
+#pragma unroll
+        for (int k = 0; k < IN_PER; k++)
+        {
+            int const idx = tid + 256 * k;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (idx < IN_ITEMS)
+            {
+                int const cv = idx % (CI_T / VI), px = idx / (CI_T / VI);
+                int const r = px / IW, c = px % IW;
+                int const y = ty0 + r - d.pad_top, x = tx0 + c - d.pad_left;
+                if (y >= 0 && y < d.H && x >= 0 && x < d.W)
+                {
+                    float const* src = in + (static_cast<size_t>(y) * d.W + x) * d.Cin + c0 + cv * VI;
+                    if (vec_in)
+                    {
+                        if (c0 + cv * VI < d.Cin) v = __ldg(reinterpret_cast<float4 const*>(src));
+                    }
+                    else
+                    {
+                        if (c0 + cv * VI + 0 < d.Cin) v.x = __ldg(src + 0);
+                        if (VI == 4 && c0 + cv * VI + 1 < d.Cin) v.y = __ldg(src + 1);
+                        if (VI == 4 && c0 + cv * VI + 2 < d.Cin) v.z = __ldg(src + 2);
+                        if (VI == 4 && c0 + cv * VI + 3 < d.Cin) v.w = __ldg(src + 3);
+                    }
+                }
+            }
+            rin[k] = v;
+        }
+#pragma unroll
+        for (int k = 0; k < W_PER; k++)
+        {
+            int const idx = tid + 256 * k;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (idx < W_ITEMS)
+            {
+                int const cov = idx % (CO_T / VW), ci = (idx / (CO_T / VW)) % CI_T, kk = idx / ((CO_T / VW) * CI_T);
+                int const co = cot0 + cov * VW;
+                if (c0 + ci < d.Cin)
+                {
+                    float const* src = w + (static_cast<size_t>(kk) * d.Cin + c0 + ci) * d.Cout + co;
+                    if (vec_w)
+                    {
+                        if (co < d.Cout) v = __ldg(reinterpret_cast<float4 const*>(src));
+                    }
+                    else
+                    {
+                        if (co + 0 < d.Cout) v.x = __ldg(src + 0);
+                        if (VW == 4 && co + 1 < d.Cout) v.y = __ldg(src + 1);
+                        if (VW == 4 && co + 2 < d.Cout) v.z = __ldg(src + 2);
+                        if (VW == 4 && co + 3 < d.Cout) v.w = __ldg(src + 3);
+                    }
+                }
+            }
+            rw[k] = v;
+        }
+    };
+    auto commit = [&]() {
+#pragma unroll
+        for (int k = 0; k < IN_PER; k++)
+        {
+            int const idx = tid + 256 * k;
+            if (idx < IN_ITEMS)
+            {
+                int const cv = idx % (CI_T / VI), px = idx / (CI_T / VI);
+                int const r = px / IW, c = px % IW;
+                float* dst = &s_in[r][c][cv * VI];
+                dst[0] = rin[k].x;
+                if (VI == 4) { dst[1] = rin[k].y; dst[2] = rin[k].z; dst[3] = rin[k].w; }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < W_PER; k++)
+        {
+            int const idx = tid + 256 * k;
+            if (idx < W_ITEMS)
+            {
+                int const cov = idx % (CO_T / VW), ci = (idx / (CO_T / VW)) % CI_T, kk = idx / ((CO_T / VW) * CI_T);
+                if (VW == 4) *reinterpret_cast<float4*>(&s_w[kk][ci][cov * 4]) = rw[k];
+                else s_w[kk][ci][cov] = rw[k].x;
+            }
+        }
+    };
+
+    fetch(0);
     for (int c0 = 0; c0 < d.Cin; c0 += CI_T)
     {
-        for (int idx = tid; idx < IH * IW * CI_T; idx += 256)
-        {
-            int ci = idx % CI_T, px = idx / CI_T;
-            int r = px / IW, c = px % IW;
-            int y = ty0 + r - d.pad_top, x = tx0 + c - d.pad_left;
-            float v = 0.f;
-            if (y >= 0 && y < d.H && x >= 0 && x < d.W && c0 + ci < d.Cin)
-                v = in[(static_cast<size_t>(y) * d.W + x) * d.Cin + c0 + ci];
-            s_in[r][c][ci] = v;
-        }
-        for (int idx = tid; idx < KS * KS * CI_T * CO_T; idx += 256)
-        {
-            int co = idx % CO_T, ci = (idx / CO_T) % CI_T, k = idx / (CO_T * CI_T);
-            float v = 0.f;
-            if (c0 + ci < d.Cin && cot0 + co < d.Cout)
-                v = w[(static_cast<size_t>(k) * d.Cin + c0 + ci) * d.Cout + cot0 + co];
-            s_w[k][ci][co] = v;
-        }
+        commit();
         __syncthreads();
+        if (c0 + CI_T < d.Cin) fetch(c0 + CI_T);
 
 #pragma unroll
         for (int kh = 0; kh < KS; kh++)
