@@ -542,10 +542,13 @@ __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d,
     {
         while (node >= 0)
         {
-            float4 n0 = __ldg(nodes + 4 * node + 0);
-            float4 n1 = __ldg(nodes + 4 * node + 1);
-            float4 n2 = __ldg(nodes + 4 * node + 2);
-            float4 n3 = __ldg(nodes + 4 * node + 3);
+            // one 64-byte node: a single widening multiply-add for the address
+            float4 const* const np = reinterpret_cast<float4 const*>(
+                reinterpret_cast<char const*>(nodes) + static_cast<size_t>(static_cast<uint32_t>(node)) * 64u);
+            float4 n0 = __ldg(np + 0);
+            float4 n1 = __ldg(np + 1);
+            float4 n2 = __ldg(np + 2);
+            float4 n3 = __ldg(np + 3);
             if (STATS) n_box += 2;
 
             // n = (c0.min, c1.min, c0.max, c1.max) per axis: .lo pair = mins, .hi pair = maxes
