@@ -478,14 +478,15 @@ def run_b200_arm(args):
     scene_bytes = info.device_bytes
     roofline = {"bound": "fp32", "kernel": "render_bvh_spp_kernel<false,1>" if args.spp >= 32 else "render_bvh_kernel", "achieved": achieved, "peak": fp32_peak,
                 "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None,
-                "traffic": 6.55e6 if world == 1 and args.spp == WORKLOAD["spp"] else None,
-                "traffic_source": "ncu --set full, dram__bytes_read+write per launch: 5.69 MB + 0.86 MB "
+                "traffic": 8.68e6 if world == 1 and args.spp == WORKLOAD["spp"] else None,
+                "traffic_source": "ncu --set full, dram__bytes_read+write per launch: 6.64 MB + 2.04 MB "
                                   "(profiles/r01_bvh_spp_kernel_ncu_full_summary.csv; scene and frame stay in the 126 MB L2)",
                 "peak_source": "srtMeasureFp32Peak live FFMA microbenchmark (MEASURED_PEAKS.json has no FP32 figure)",
                 "algorithmic_flops_per_launch": flops_per_step * share,
                 "box_tests": boxes, "tri_tests": tris, "kernel_ms": kern_ms,
                 "algorithmic_bytes_per_launch": rows * W * 12 + scene_bytes,
-                "issue_slots": {"busy_frac": 0.725, "threads_per_instruction": 27.7, "l1_hit": 0.998,
+                "issue_slots": {"busy_frac": 0.725, "threads_per_instruction": 26.6, "l1_hit": 0.991,
+                                "warp_instructions_per_launch": 19.64e9,
                                 "source": "ncu --set full of this kernel on this workload (smsp__issue_active, "
                                           "profiles/r01_bvh_spp_kernel_ncu_full_summary.csv): the kernel is bound by "
                                           "instruction issue, ~40 SASS instructions per two-box node visit"},
