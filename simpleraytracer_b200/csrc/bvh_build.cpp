@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 namespace ML {
 namespace {
@@ -42,7 +43,12 @@ struct Box
     }
 };
 
-constexpr int kBins = 16;
+constexpr int kMaxBins = 64;
+static int const kBins = [] {   // SAH bins per axis (SRT_BVH_BINS=4..64, experiments)
+    char const* e = std::getenv("SRT_BVH_BINS");
+    int v = e ? std::atoi(e) : 16;
+    return v < 4 ? 4 : (v > kMaxBins ? kMaxBins : v);
+}();
 constexpr int kMedianDepth = 40;
 
 inline float IntBitsToFloat(int32_t v)
@@ -176,16 +182,16 @@ private:
             float extent = cmax[a] - cmin[a];
             if (!(extent > 0.f)) continue;
             float scale = static_cast<float>(kBins) / extent;
-            Box bin_box[kBins];
-            int bin_cnt[kBins] = {};
+            Box bin_box[kMaxBins];
+            int bin_cnt[kMaxBins] = {};
             for (int i = first; i < first + count; i++)
             {
                 int b = BinOf(m_prims[i].c[a], cmin[a], scale);
                 bin_cnt[b]++;
                 bin_box[b].Grow(m_prims[i].bmin, m_prims[i].bmax);
             }
-            float right_area[kBins];
-            int right_cnt[kBins];
+            float right_area[kMaxBins];
+            int right_cnt[kMaxBins];
             Box acc;
             int cnt = 0;
             for (int b = kBins - 1; b > 0; b--)
