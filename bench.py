@@ -227,8 +227,11 @@ def inference_leg(ctx, scene, cam, light, params, rank, world, dist, torch, dev,
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         return float(dt.item()) / reps
 
-    for prec, key in ((api.MLX_PRECISION_FP32, "fp32"), (api.MLX_PRECISION_BF16, "bf16")):
+    for prec, key in ((api.MLX_PRECISION_FP32, "fp32"), (api.MLX_PRECISION_BF16X3, "bf16x3"),
+                      (api.MLX_PRECISION_BF16, "bf16")):
         model.set_precision(prec)
+        if key == "bf16x3":
+            res["bf16x3_tc_layers"] = model.tensor_core_layers()
         # e2e: host buffers in, host buffers out (outputs' host pointers were handed out by read())
         for b in outs:
             b.read()
@@ -270,6 +273,7 @@ def inference_leg(ctx, scene, cam, light, params, rank, world, dist, torch, dev,
     peaks, src = measured_peaks()
     ops = res.pop("bf16_ops")
     fp32_ops = res.pop("fp32_ops")
+    x3_ops = res.pop("bf16x3_ops")
     # the dominant kernel: the launch with the most algorithmic work (the 64->64 layers), the slowest of those
     k = max(range(len(ops)), key=lambda j: (ops[j][1], ops[j][0]))
     ms, fl, by = ops[k]
@@ -294,6 +298,11 @@ def inference_leg(ctx, scene, cam, light, params, rank, world, dist, torch, dev,
             "e2e": {"value": res["bf16_e2e_images_per_s"], "unit": "images/s",
                     "h2d_bytes_per_step": NET["batch"] * W * H * 12, "d2h_bytes_per_step": NET["batch"] * W * H * 12},
             "fp32": {"value": res["fp32_images_per_s"], "e2e": res["fp32_e2e_images_per_s"]},
+            # fp32-grade results on the tensor cores: split bf16 operands, three MMAs per product
+            # (MLX_PRECISION_BF16X3; bound 1e-4 of the range against the fp32 oracle, tests/test_model_gpu.py)
+            "fp32_grade_tensor_core": {"value": res["bf16x3_images_per_s"], "e2e": res["bf16x3_e2e_images_per_s"],
+                                       "tensor_core_layers": res["bf16x3_tc_layers"],
+                                       "all_ops_ms": [round(o[0], 4) for o in x3_ops]},
             "tensor_core_layers": res["tc_layers"], "launches_per_image": res["launches_per_image"],
             "render_plus_infer_ms": res["render_plus_infer_ms"], "roofline": roof, "cpu_baseline": cpu}
 

@@ -53,9 +53,15 @@ ML_API_ENTRY void mlxIpcClose(ml_context context, void* device_pointer);
  * cores (tcgen05 + TMEM) for every 3x3 / stride 1 / SAME layer with 16, 32 or 64k input
  * channels; activations between such layers are stored as bf16.  Image I/O stays
  * ML_FLOAT32 / ML_FLOAT16 as declared by the graph.  May be called before or after
- * mlSetModelInputInfo.  mlxModelTensorCoreLayers reports how many layers use that path. */
+ * mlSetModelInputInfo.  mlxModelTensorCoreLayers reports how many layers use that path.
+ * MLX_PRECISION_BF16X3 (or MLB200_PRECISION=bf16x3): the same tensor-core layers with fp32-grade
+ * results -- every fp32 operand x is split into two bf16 halves (x = hi + lo to 16 mantissa bits)
+ * and each product is issued as hi*hi + lo*hi + hi*lo into the fp32 accumulator (the dropped lo*lo
+ * term is 2^-16 relative); tensors between layers stay fp32.  Stated bound: 1e-4 of the output
+ * range against the fp32 oracle (measured ~1e-6), i.e. inside the 1e-3 bar of the fp32 path. */
 #define MLX_PRECISION_FP32 0
 #define MLX_PRECISION_BF16 1
+#define MLX_PRECISION_BF16X3 2
 ML_API_ENTRY ml_status mlxSetModelPrecision(ml_model model, int precision);
 ML_API_ENTRY size_t mlxModelTensorCoreLayers(ml_model model);
 

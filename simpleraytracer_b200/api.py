@@ -15,7 +15,7 @@ import numpy as np
 _LIB_PATH = Path(__file__).resolve().parent / "lib" / "libModelRunner.so"
 
 ML_OK, ML_FAIL = 0, 1
-MLX_PRECISION_FP32, MLX_PRECISION_BF16 = 0, 1
+MLX_PRECISION_FP32, MLX_PRECISION_BF16, MLX_PRECISION_BF16X3 = 0, 1, 2
 ML_FLOAT32, ML_FLOAT16 = 0, 1
 SRT_SHADE_ALBEDO, SRT_SHADE_LAMBERT, SRT_SHADE_SHADOW = 0, 1, 2
 SRT_ACCEL_BRUTE, SRT_ACCEL_BVH = 0, 1
@@ -295,7 +295,8 @@ class Model:
         return int(self.lib.mlxModelLaunchCount(self.handle))
 
     def set_precision(self, precision: int):
-        """mlxSetModelPrecision: MLX_PRECISION_FP32 (0) or MLX_PRECISION_BF16 (1, tcgen05 layers)."""
+        """mlxSetModelPrecision: MLX_PRECISION_FP32 (0), MLX_PRECISION_BF16 (1, tcgen05 layers) or
+        MLX_PRECISION_BF16X3 (2, tcgen05 layers with split operands: fp32-grade results)."""
         if self.lib.mlxSetModelPrecision(self.handle, int(precision)) != ML_OK:
             raise MLError(self.error())
 

@@ -49,6 +49,7 @@ constexpr int kEpiWarps = 8;         // two per TMEM lane quarter, each takes ha
 constexpr int kTcThreads = 64 + 32 * kEpiWarps;   // TMA warp + MMA warp + epilogue warps
 constexpr int kMaxStages = 8;
 constexpr int kMaxAcc = 4;
+constexpr int kMaxChunks = 16;       // K chunks per filter row (tile-per-stage kernel)
 
 struct TcParams
 {
@@ -80,6 +81,15 @@ struct TcParams
     int rows_mode;       // 1: conv3x3_tc_rows_kernel (filter rows stacked along N), 0: conv3x3_tc_kernel
     int debug;           // MLB200_TC_DEBUG bit 0: no TMA loads of A, bit 1: no MMAs, bit 2: no epilogue math,
                          // bit 3: no TMA stores (timing experiments only; results are garbage)
+    // Tile-per-stage kernel: K chunk c of a filter row multiplies the activation box at channel
+    // a_coord[c] with filter chunk b_chunk[c] (of n_bchunks per tap).  Plain bf16: the identity.
+    // Split mode (bf16x3, fp32-grade): activations and filter are stored as [hi | lo] bf16 halves
+    // (x = hi + lo to 16 mantissa bits) and the chunk list runs hi*hi, lo*hi, hi*lo into the same
+    // fp32 accumulator (the lo*lo term, 2^-16 relative, is dropped).
+    int split;
+    int n_bchunks;
+    int a_coord[kMaxChunks];
+    int b_chunk[kMaxChunks];
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -308,7 +318,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~uintptr_t(1023u));
     uint32_t const b_tile_bytes = static_cast<uint32_t>(P.N) * KC * 2u;
     uint32_t const a_stage_bytes = static_cast<uint32_t>(P.stage_bytes);
-    uint32_t const n_b_tiles = 9u * P.n_chunks;
+    uint32_t const n_b_tiles = 9u * static_cast<uint32_t>(P.n_bchunks);
     uint32_t const out_tile_bytes = P.out_bf16 ? static_cast<uint32_t>(kTileM) * P.N * 2u : 0u;
     uint8_t* smem_b = smem;                                       // filter, resident
     uint8_t* smem_a = smem_b + n_b_tiles * b_tile_bytes;           // A ring
@@ -362,8 +372,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
         {
             bar_expect_tx(w_full, n_b_tiles * b_tile_bytes);
             for (uint32_t t = 0; t < 9u; t++)
-                for (int ch = 0; ch < P.n_chunks; ch++)
-                    tma_load_2d(smem_b + (t * P.n_chunks + ch) * b_tile_bytes, &w_map, ch * KC,
+                for (int ch = 0; ch < P.n_bchunks; ch++)
+                    tma_load_2d(smem_b + (t * P.n_bchunks + ch) * b_tile_bytes, &w_map, ch * KC,
                                 static_cast<int>(t) * P.N, w_full);
         }
         __syncwarp();
@@ -397,12 +407,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                                 int const iy = y + kh0 + r - 1;
                                 if (P.halo)
                                 {
-                                    tma_load_3d(dst, &in_map, ch * KC, x0 - 1, iy, &full[s]);
+                                    tma_load_3d(dst, &in_map, P.a_coord[ch], x0 - 1, iy, &full[s]);
                                 }
                                 else
                                 {
                                     for (int kw = 0; kw < 3; kw++)
-                                        tma_load_3d(dst + kw * P.tap_stride, &in_map, ch * KC, x0 + kw - 1, iy,
+                                        tma_load_3d(dst + kw * P.tap_stride, &in_map, P.a_coord[ch], x0 + kw - 1, iy,
                                                     &full[s]);
                                 }
                             }
@@ -441,7 +451,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
         uint32_t const stage_u = a_stage_bytes >> 4, tap_u = static_cast<uint32_t>(P.tap_stride) >> 4;
         uint32_t const b_tile_u = b_tile_bytes >> 4, row_u = static_cast<uint32_t>(P.row_bytes) >> 4;
         uint32_t const rps = static_cast<uint32_t>(P.rps), n_chunks = static_cast<uint32_t>(P.n_chunks);
-        uint32_t const b_tap_u = n_chunks * b_tile_u, b_row_u = 3u * b_tap_u;
+        uint32_t const b_tap_u = static_cast<uint32_t>(P.n_bchunks) * b_tile_u, b_row_u = 3u * b_tap_u;
         uint32_t s = 0, ph = 0, acc = 0, aph = 0;
         TC_PROF_T0();
         for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x)
@@ -464,7 +474,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                         if (!(P.debug & 2))
                         {
                             uint32_t const a_st = a_lo0 + s * stage_u;
-                            uint32_t const b_st = b_lo0 + kh0 * b_row_u + ch * b_tile_u;
+                            uint32_t const b_st = b_lo0 + kh0 * b_row_u + static_cast<uint32_t>(P.b_chunk[ch]) * b_tile_u;
 #pragma unroll
                             for (uint32_t r = 0; r < 3u; r++)
                             {
@@ -608,9 +618,21 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                     else if (x < P.W)
                     {
                         float* o = static_cast<float*>(out) + pixel * P.Cout;
+                        if ((P.Cout & 3) == 0)
+                        {
+                            // 16-byte stores (buffers come from cudaMalloc; pixel * Cout + cb is a multiple of 4)
 #pragma unroll
-                        for (int j = 0; j < 16; j++)
-                            if (cb + j < P.Cout) o[cb + j] = v[j];
+                            for (int j4 = 0; j4 < 4; j4++)
+                                if (cb + 4 * j4 < P.Cout)
+                                    *reinterpret_cast<float4*>(o + cb + 4 * j4) =
+                                        make_float4(v[4 * j4], v[4 * j4 + 1], v[4 * j4 + 2], v[4 * j4 + 3]);
+                        }
+                        else
+                        {
+#pragma unroll
+                            for (int j = 0; j < 16; j++)
+                                if (cb + j < P.Cout) o[cb + j] = v[j];
+                        }
                     }
                 }
             }
@@ -1212,13 +1234,17 @@ struct ConvTc
 
 int ConvTcPaddedCout(int Cout) { return (Cout + 15) / 16 * 16; }
 
-bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding, int Cin, int Cout)
+bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding, int Cin, int Cout, bool split)
 {
     if (KH != 3 || KW != 3 || stride != 1 || dilation != 1 || !same_padding) return false;
     if (!(Cin == 16 || Cin == 32 || (Cin > 0 && Cin % 64 == 0))) return false;
     int const N = ConvTcPaddedCout(Cout);
     if (Cout < 1 || N > 256) return false;
     int const KC = Cin < 64 ? Cin : 64;
+    if ((split ? 3 : 1) * (Cin / KC) > kMaxChunks) return false;
+    // split: the resident filter holds the hi and the lo half, the output is fp32 (no staging tiles);
+    // three ring stages at least, or the MMA pipe waits on every TMA round trip
+    if (split) return SmemBytes(N, 2 * Cin, KC, 3, false) <= 226u * 1024u;
     return SmemBytes(N, Cin, KC, 2, true) <= 226u * 1024u;
 }
 
@@ -1236,16 +1262,48 @@ std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout, in
     return packed;
 }
 
+std::vector<uint16_t> ConvTcPackWeightsSplit(float const* hwio, int Cin, int Cout, int Cin_pad)
+{
+    // [tap][co][hi: Cin_pad | lo: Cin_pad], w = hi + lo up to 2^-17 relative
+    int const N = ConvTcPaddedCout(Cout);
+    std::vector<uint16_t> packed(static_cast<size_t>(9) * N * 2 * Cin_pad, 0);
+    for (int t = 0; t < 9; t++)
+        for (int co = 0; co < Cout; co++)
+            for (int ci = 0; ci < Cin; ci++)
+            {
+                float const w = hwio[(static_cast<size_t>(t) * Cin + ci) * Cout + co];
+                __nv_bfloat16 hi = __float2bfloat16_rn(w);
+                __nv_bfloat16 lo = __float2bfloat16_rn(w - __bfloat162float(hi));
+                size_t const row = (static_cast<size_t>(t) * N + co) * 2 * Cin_pad;
+                packed[row + ci] = *reinterpret_cast<uint16_t*>(&hi);
+                packed[row + Cin_pad + ci] = *reinterpret_cast<uint16_t*>(&lo);
+            }
+    return packed;
+}
+
 ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16, int H, int W, int Cin, int Cout,
-                     bool out_bf16, Act act, float alpha, int sm_count)
+                     bool out_bf16, Act act, float alpha, int sm_count, bool split)
 {
     auto op = std::make_unique<ConvTc>();
     TcParams& p = op->p;
     p.H = H; p.W = W; p.Cin = Cin; p.Cout = Cout;
     p.N = ConvTcPaddedCout(Cout);
     if (out_bf16 && p.N != Cout) throw std::runtime_error("bf16 output needs Cout to be a multiple of 16");
+    if (split && out_bf16) throw std::runtime_error("split (bf16x3) layers write fp32");
     p.KC = Cin < 64 ? Cin : 64;
-    p.n_chunks = Cin / p.KC;
+    int const n_real = Cin / p.KC;
+    int const Ct = split ? 2 * Cin : Cin;      // channels of the activation and filter tensors ([hi | lo] when split)
+    p.split = split ? 1 : 0;
+    p.n_chunks = split ? 3 * n_real : n_real;
+    p.n_bchunks = split ? 2 * n_real : n_real;
+    if (p.n_chunks > kMaxChunks) throw std::runtime_error("too many K chunks");
+    for (int c = 0; c < kMaxChunks; c++) { p.a_coord[c] = 0; p.b_chunk[c] = 0; }
+    for (int c = 0; c < p.n_chunks; c++)
+    {
+        int const term = c / n_real, r = c - term * n_real;   // split terms: hi*hi, lo*hi, hi*lo
+        p.a_coord[c] = (term == 1 ? Cin : 0) + r * p.KC;
+        p.b_chunk[c] = (term == 2 ? n_real : 0) + r;
+    }
     p.layout_type = p.KC == 64 ? 2 : p.KC == 32 ? 4 : 6;
     p.sbo = 8 * p.KC * 2;
     p.tiles_per_row = (W + kTileM - 1) / kTileM;
@@ -1262,14 +1320,14 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     p.halo = HaloMode(p.KC) ? 1 : 0;
     p.row_bytes = static_cast<int>(StageBytes(p.KC));
     int const want_rps = std::getenv("MLB200_TC_RPS") ? std::atoi(std::getenv("MLB200_TC_RPS")) : 3;
-    p.rps = (want_rps == 3 && SmemBytes(p.N, Cin, p.KC, 2, out_bf16, 3) <= 226u * 1024u) ? 3 : 1;
+    p.rps = (want_rps == 3 && SmemBytes(p.N, Ct, p.KC, 2, out_bf16, 3) <= 226u * 1024u) ? 3 : 1;
     p.stage_bytes = p.rps * p.row_bytes;
     p.tap_stride = p.halo ? p.KC * 2 : kTileM * p.KC * 2;
     p.stage_tx = p.rps * (p.halo ? (kTileM + 2) * p.KC * 2 : 3 * kTileM * p.KC * 2);
     p.prof = nullptr;
     if (std::getenv("MLB200_TC_PROF") != nullptr)
         ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&p.prof), 16 * sizeof(unsigned long long)));
-    p.rows_mode = RowsModeFits(p.N, Cin, out_bf16) ? 1 : 0;
+    p.rows_mode = (!split && RowsModeFits(p.N, Cin, out_bf16)) ? 1 : 0;
     p.wait_ns = EnvInt("MLB200_TC_WAIT_NS", 0);
     p.stages = kMaxStages;
     if (p.rows_mode)
@@ -1288,23 +1346,23 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     }
     else
     {
-        while (p.stages > 2 && SmemBytes(p.N, Cin, p.KC, p.stages, out_bf16, p.rps) > 226u * 1024u) p.stages--;
-        op->smem = SmemBytes(p.N, Cin, p.KC, p.stages, out_bf16, p.rps);
+        while (p.stages > 2 && SmemBytes(p.N, Ct, p.KC, p.stages, out_bf16, p.rps) > 226u * 1024u) p.stages--;
+        op->smem = SmemBytes(p.N, Ct, p.KC, p.stages, out_bf16, p.rps);
         op->grid = p.n_tiles < sm_count ? p.n_tiles : sm_count;
     }
     if (op->smem > 226u * 1024u) throw std::runtime_error("filter does not fit in shared memory");
 
     // activation: [H][W][Cin] bf16, box = KC channels x 128 pixels x 1 row
     {
-        cuuint64_t dims[3] = {static_cast<cuuint64_t>(Cin), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H)};
-        cuuint64_t strides[2] = {static_cast<cuuint64_t>(Cin) * 2, static_cast<cuuint64_t>(W) * Cin * 2};
+        cuuint64_t dims[3] = {static_cast<cuuint64_t>(Ct), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H)};
+        cuuint64_t strides[2] = {static_cast<cuuint64_t>(Ct) * 2, static_cast<cuuint64_t>(W) * Ct * 2};
         cuuint32_t box[3] = {static_cast<cuuint32_t>(p.KC), static_cast<cuuint32_t>(p.halo ? kTileM + 2 : kTileM), 1};
         Encode(&op->in_map, d_in, 3, dims, strides, box, SwizzleFor(p.KC));
     }
     // filter: [9 * N][Cin] bf16, box = KC channels x N rows
     {
-        cuuint64_t dims[2] = {static_cast<cuuint64_t>(Cin), static_cast<cuuint64_t>(9) * p.N};
-        cuuint64_t strides[1] = {static_cast<cuuint64_t>(Cin) * 2};
+        cuuint64_t dims[2] = {static_cast<cuuint64_t>(Ct), static_cast<cuuint64_t>(9) * p.N};
+        cuuint64_t strides[1] = {static_cast<cuuint64_t>(Ct) * 2};
         cuuint32_t box[2] = {static_cast<cuuint32_t>(p.KC), static_cast<cuuint32_t>(p.N)};
         Encode(&op->w_map, d_w_packed, 2, dims, strides, box, SwizzleFor(p.KC));
     }

@@ -102,7 +102,10 @@ Model::Model(DeviceStatePtr device, ml_model_params const* params) : m_device(st
     BuildPlan(graph, input_idx, output_idx);
     FusePlan();
     if (char const* e = std::getenv("MLB200_PRECISION"))
-        m_precision = (std::string(e) == "bf16" || std::string(e) == "BF16") ? 1 : 0;
+    {
+        std::string const v(e);
+        m_precision = (v == "bf16" || v == "BF16") ? 1 : (v == "bf16x3" || v == "BF16X3") ? 2 : 0;
+    }
 
     // Upload constants once; they stay resident in HBM for the model's life.
     // (m_device == nullptr: host-only inspection, mlxInspectModel.)
@@ -574,6 +577,17 @@ void Model::AssignPrecision()
         Op& op = m_ops[i];
         op.tc = false;
         op.pad_in = false;
+        op.split = false;
+        if (m_precision == 2 && op.kind == OpKind::Conv)
+        {
+            // fp32-grade on the tensor cores: tensors stay fp32, every supported layer splits its own input
+            int const c = m_tensors[op.in[0]].C;
+            int const cp = c < 16 ? 16 : c;
+            if (c > 0 && nn::ConvTcSupported(op.KH, op.KW, op.stride, op.dilation, op.same_padding, cp,
+                                             m_tensors[op.out].C, true))
+                tc[i] = 1, op.split = true;
+            continue;
+        }
         if (m_precision != 1 || op.kind != OpKind::Conv) continue;
         int const cin = m_tensors[op.in[0]].C;
         // a thin first layer (e.g. RGB) runs on the tensor cores too, on a 16-channel zero-padded bf16 copy
@@ -620,7 +634,7 @@ size_t Model::TensorCoreLayers() const
 ml_status Model::SetPrecision(int precision)
 {
     m_error.clear();
-    if (precision != 0 && precision != 1)
+    if (precision != 0 && precision != 1 && precision != 2)
     {
         m_error = "Unsupported precision: " + std::to_string(precision);
         return ML_FAIL;
@@ -653,6 +667,10 @@ void Model::ReleaseBuffers()
     for (void* p : m_buffers) cudaFree(p);
     m_buffers.clear();
     m_buffer_bytes.clear();
+    cudaFree(m_split_buffer);
+    m_split_buffer = nullptr;
+    cudaFree(m_alias_in);
+    m_alias_in = nullptr;
     cudaFree(m_in_f32);
     cudaFree(m_out_f32);
     m_in_f32 = m_out_f32 = nullptr;
@@ -702,11 +720,35 @@ void Model::AllocateBuffers()
             }
     }
     // Tensor-core layers: repack the filter once, bind the TMA tensor maps to the (now fixed) buffers.
+    size_t split_bytes = 0;
+    for (Op const& op : m_ops)
+        if (op.tc && op.split)
+        {
+            TensorInfo const& a = m_tensors[op.in[0]];
+            split_bytes = std::max(split_bytes, static_cast<size_t>(a.H) * a.W * 2 * (a.C < 16 ? 16 : a.C) * 2);
+        }
+    if (split_bytes > 0) ML_CUDA_CHECK(cudaMalloc(&m_split_buffer, split_bytes));
     for (Op& op : m_ops)
     {
         if (!op.tc) continue;
         TensorInfo const& a = m_tensors[op.in[0]];
         TensorInfo const& o = m_tensors[op.out];
+        if (op.split)
+        {
+            int const cp = a.C < 16 ? 16 : a.C;
+            if (op.packed_split < 0)
+            {
+                std::vector<uint16_t> packed = nn::ConvTcPackWeightsSplit(m_consts[op.weights].host.data(), a.C, o.C, cp);
+                void* d = nullptr;
+                ML_CUDA_CHECK(cudaMalloc(&d, packed.size() * 2));
+                m_packed.push_back(d);
+                op.packed_split = static_cast<int>(m_packed.size()) - 1;
+                ML_CUDA_CHECK(cudaMemcpy(d, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
+            }
+            op.tc_op = nn::ConvTcCreate(m_split_buffer, m_packed[op.packed_split], nullptr, a.H, a.W, cp, o.C, false,
+                                        op.act, op.alpha, m_device->prop.multiProcessorCount, true);
+            continue;
+        }
         int const cin = op.pad_in ? 16 : a.C;
         if (op.pad_in)
             ML_CUDA_CHECK(cudaMalloc(&op.pad_buffer, static_cast<size_t>(a.H) * a.W * 16 * 2));
@@ -756,7 +798,7 @@ std::string Model::Describe() const
                << " padding=" << (op.same_padding ? "SAME" : "VALID") << " wsum=" << sum;
         }
         if (op.residual >= 0) os << " residual=t" << op.residual;
-        if (op.tc) os << " engine=tcgen05_bf16";
+        if (op.tc) os << (op.split ? " engine=tcgen05_bf16x3" : " engine=tcgen05_bf16");
         if (m_tensors[op.out].bf16) os << " out=bf16";
         os << " bias=" << (op.bias >= 0 ? "yes" : "no") << " act=" << acts[static_cast<int>(op.act)];
         if (op.act == nn::Act::LeakyRelu) os << " alpha=" << op.alpha;
@@ -851,6 +893,24 @@ ml_status Model::SetInputInfo(ml_image_info const* info)
 
 void Model::Run(float const* d_in, float* d_out, cudaStream_t stream)
 {
+    // In-place inference (input image == output image): a tensor-core layer adds its folded residual
+    // in a pass AFTER the convolution has written the output, so a residual that is the model input
+    // must not share storage with the output.  (The fp32 kernels add it in their epilogue, where each
+    // element is read before the same thread overwrites it.)
+    if (static_cast<void const*>(d_in) == static_cast<void const*>(d_out))
+    {
+        bool clash = false;
+        for (Op const& op : m_ops)
+            clash |= op.tc && op.residual == m_input_tensor && op.out == m_output_tensor;
+        if (clash)
+        {
+            TensorInfo const& t = m_tensors[m_input_tensor];
+            size_t const bytes = static_cast<size_t>(t.H) * t.W * t.C * sizeof(float);
+            if (m_alias_in == nullptr) ML_CUDA_CHECK(cudaMalloc(&m_alias_in, std::max<size_t>(bytes, 16)));
+            ML_CUDA_CHECK(cudaMemcpyAsync(m_alias_in, d_in, bytes, cudaMemcpyDeviceToDevice, stream));
+            d_in = static_cast<float const*>(m_alias_in);
+        }
+    }
     for (Op const& op : m_ops) RunOp(op, d_in, d_out, stream);
 }
 
@@ -889,7 +949,10 @@ void Model::RunOp(Op const& op, float const* d_in, float* d_out, cudaStream_t st
                 d.residual = op.residual >= 0 ? ptr(op.residual) : nullptr;
                 if (op.tc)
                 {
-                    if (op.pad_in)
+                    if (op.split)
+                        nn::SplitToBf16HiLo(ptr(op.in[0]), m_split_buffer, static_cast<size_t>(a.H) * a.W, a.C,
+                                            a.C < 16 ? 16 : a.C, stream);
+                    else if (op.pad_in)
                         nn::PadToBf16x16(ptr(op.in[0]), op.pad_buffer, static_cast<size_t>(a.H) * a.W, a.C, stream);
                     nn::ConvTcRun(op.tc_op, bias, ptr(op.out), stream);
                     // The folded Add runs as its own in-place pass here: inside the tensor-core epilogue the

@@ -80,6 +80,10 @@ private:
         nn::ConvTc* tc_op = nullptr;
         bool pad_in = false;   // fp32 input with < 16 channels: zero-padded to 16 bf16 channels first
         void* pad_buffer = nullptr;
+        // bf16x3 (precision 2): fp32 tensors either side; the input is split into [hi | lo] bf16 halves
+        // in m_split_buffer right before the layer, the filter is packed as hi/lo halves
+        bool split = false;
+        int packed_split = -1; // index into m_packed
     };
 
     struct DeviceConst
@@ -130,6 +134,8 @@ private:
     std::vector<void*> m_packed;  // device copies of repacked bf16 filters
     std::vector<void*> m_buffers;
     std::vector<size_t> m_buffer_bytes;
+    void* m_split_buffer = nullptr; // bf16 [H][W][hi|lo] input of the current bf16x3 layer (ops run one at a time)
+    void* m_alias_in = nullptr;  // copy of the input for in-place inference through tensor-core layers (see Run)
     float* m_in_f32 = nullptr;   // staging when images are FLOAT16
     float* m_out_f32 = nullptr;
     std::string m_error;

@@ -404,6 +404,48 @@ __global__ void pad_to_bf16x16_kernel(float const* __restrict__ in, uint4* __res
     }
 }
 
+// One thread per (pixel, group of 8 channels): 8 fp32 in, 16 bytes of hi and 16 bytes of lo out.
+__global__ void split_bf16_hilo_kernel(float const* __restrict__ in, uint4* __restrict__ out, size_t pixels, int C,
+                                       int Cp)
+{
+    int const groups = Cp >> 3;
+    size_t const total = pixels * static_cast<size_t>(groups);
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    bool const vec = (C & 3) == 0;
+    for (; i < total; i += stride)
+    {
+        size_t const pix = i / groups;
+        int const c0 = static_cast<int>(i - pix * groups) << 3;
+        float v[8];
+        float const* src = in + pix * C + c0;
+        if (vec && c0 + 8 <= C)
+        {
+            float4 a = *reinterpret_cast<float4 const*>(src), b = *reinterpret_cast<float4 const*>(src + 4);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        }
+        else
+        {
+#pragma unroll
+            for (int c = 0; c < 8; c++) v[c] = c0 + c < C ? src[c] : 0.f;
+        }
+        uint32_t hi[4], lo[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++)
+        {
+            __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * c], v[2 * c + 1]);
+            float2 const hf = __bfloat1622float2(h);
+            __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * c] - hf.x, v[2 * c + 1] - hf.y);
+            hi[c] = *reinterpret_cast<uint32_t*>(&h);
+            lo[c] = *reinterpret_cast<uint32_t*>(&l);
+        }
+        // row of 2*Cp bf16 = 2*groups units of 16 bytes: hi units first, lo units after
+        size_t const row = pix * static_cast<size_t>(2 * groups);
+        out[row + (c0 >> 3)] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        out[row + groups + (c0 >> 3)] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
+}
+
 inline unsigned EltGrid(size_t n)
 {
     size_t blocks = (n + 255) / 256;
@@ -448,6 +490,15 @@ void PadToBf16x16(float const* in, void* out_bf16, size_t pixels, int C, cudaStr
     if (pixels == 0) return;
     if (C < 1 || C > 16) throw std::runtime_error("PadToBf16x16: 1..16 channels");
     pad_to_bf16x16_kernel<<<EltGrid(pixels), 256, 0, stream>>>(in, static_cast<uint4*>(out_bf16), pixels, C);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void SplitToBf16HiLo(float const* in, void* out_bf16, size_t pixels, int C, int Cp, cudaStream_t stream)
+{
+    if (pixels == 0) return;
+    if (C < 1 || Cp < C || (Cp & 7) != 0) throw std::runtime_error("SplitToBf16HiLo: bad channel counts");
+    split_bf16_hilo_kernel<<<EltGrid(pixels * static_cast<size_t>(Cp >> 3)), 256, 0, stream>>>(
+        in, static_cast<uint4*>(out_bf16), pixels, C, Cp);
     ML_CUDA_CHECK(cudaGetLastError());
 }
 

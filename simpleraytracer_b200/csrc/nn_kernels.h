@@ -50,17 +50,25 @@ void Conv2dFp32ToBf16(float const* in, float const* w, float const* bias, void* 
 // ---- bf16 tensor-core path (conv_tc_kernels.cu): 3x3, stride 1, SAME, tcgen05 + TMEM + TMA.
 // Activations bf16 NHWC, filter repacked [tap][Cout padded to 16][Cin] bf16, fp32 accumulation.
 struct ConvTc; // one planned layer: tensor maps bound to fixed device buffers
-bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding, int Cin, int Cout);
+// split = the bf16x3 (fp32-grade) variant: operands stored as [hi | lo] bf16 halves, three products per
+// K chunk (hi*hi + lo*hi + hi*lo) into the fp32 accumulator, fp32 output.
+bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding, int Cin, int Cout,
+                     bool split = false);
 int ConvTcPaddedCout(int Cout);
 // Cin_pad >= Cin: input channels beyond Cin get zero filter taps (3-channel first layer padded to 16).
 std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout, int Cin_pad);
+// Split filter: [tap][Cout padded][hi: Cin_pad | lo: Cin_pad] with w = hi + lo.
+std::vector<uint16_t> ConvTcPackWeightsSplit(float const* hwio, int Cin, int Cout, int Cin_pad);
+// fp32 [pixels][C] -> bf16 [pixels][hi: Cp | lo: Cp], x = hi + lo to 16 mantissa bits, channels >= C zero.
+// Cp is a multiple of 8, Cp >= C.
+void SplitToBf16HiLo(float const* in, void* out_bf16, size_t pixels, int C, int Cp, cudaStream_t stream);
 // fp32 [pixels][C <= 16] -> bf16 [pixels][16], zero padded (input of a padded first layer).
 void PadToBf16x16(float const* in, void* out_bf16, size_t pixels, int C, cudaStream_t stream);
 // out_bf16: bf16 NHWC output (Cout % 16 == 0) for the next tensor-core layer; else fp32 NHWC.
 // d_out_bf16: the (fixed) bf16 output buffer the TMA store is bound to; ignored for fp32 output,
 // whose pointer is given to ConvTcRun.
 ConvTc* ConvTcCreate(void const* d_in_bf16, void const* d_w_packed, void* d_out_bf16, int H, int W, int Cin,
-                     int Cout, bool out_bf16, Act act, float alpha, int sm_count);
+                     int Cout, bool out_bf16, Act act, float alpha, int sm_count, bool split = false);
 void ConvTcRun(ConvTc const* op, float const* bias, void* out, cudaStream_t stream);
 void ConvTcDestroy(ConvTc* op);
 void FloatToHalf(float const* in, void* out, size_t n, cudaStream_t stream);

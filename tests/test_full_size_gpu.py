@@ -97,5 +97,10 @@ def test_config5_conv_net_1080p_vs_oracle(ctx, tmp_path):
     model.infer(inp, out)
     err16 = float(np.abs(out.read() - ref).max()) / scale
     assert err16 <= 3e-2, f"bf16 path: {err16:.3e} of the output range"
+    model.set_precision(api.MLX_PRECISION_BF16X3)           # split operands: fp32-grade on the tensor cores
+    assert model.tensor_core_layers() == 6
+    model.infer(inp, out)
+    err_x3 = float(np.abs(out.read() - ref).max()) / scale
+    assert err_x3 <= 1e-4, f"bf16x3 path: {err_x3:.3e} of the output range"
     for obj in (inp, out, model):
         obj.release()

@@ -446,6 +446,57 @@ def test_bf16_tensor_core_denoiser(ctx, tmp_path, cfg, kernel, monkeypatch):
         obj.release()
 
 
+BF16X3_VS_FP32 = 1e-4   # stated bound of the split-operand tensor-core path, fraction of the output range
+
+
+@pytest.mark.parametrize("cfg", [
+    dict(width=64, depth=4, act="Relu", w=300, h=37, tc=4),        # 64->64: 3 K chunks over [hi|lo], SW128
+    dict(width=32, depth=3, act="LeakyRelu", w=128, h=9, tc=3),    # SW64
+    dict(width=16, depth=3, act="Relu", w=131, h=5, tc=3),         # SW32
+    dict(width=64, depth=5, act="Relu", w=1000, h=150, tc=5),      # many tiles per CTA: ring + TMEM phases wrap
+    dict(width=64, depth=3, act="Tanh", w=257, h=11, tc=3),        # slow-path activation
+    dict(width=64, depth=3, act="Relu", w=140, h=1, tc=3),         # one image row
+    dict(width=128, depth=3, act="Relu", w=70, h=20, tc=2),        # 128->128 does not fit: fp32; 128->3 = 6 K chunks
+    dict(width=48, depth=3, act="Relu", w=129, h=2, tc=1),         # Cin = 48 is not a tensor-core shape: only layer 0
+])
+def test_bf16x3_tensor_core_denoiser_is_fp32_grade(ctx, tmp_path, cfg):
+    """MLX_PRECISION_BF16X3: split-operand tcgen05 layers against the fp32 conv oracle (tolerance 1e-4 of
+    the range, ten times inside the 1e-3 bar north_star sets for fp32 inference)."""
+    path = tmp_path / "d.pb"
+    _, layers = gw.make_denoiser(path, channels=3, width=cfg["width"], depth=cfg["depth"], seed=11, act=cfg["act"])
+    w, h = cfg["w"], cfg["h"]
+    model, i, o = prepared_model(ctx, path, w, h)
+    x = np.random.default_rng(5).random((h, w, 3), dtype=np.float32)
+    inp = ctx.create_image(w, h, 3); out = ctx.create_image(w, h, 3)
+    inp.write(x)
+    model.infer(inp, out)
+    fp32 = out.read().copy()
+    model.set_precision(api.MLX_PRECISION_BF16X3)
+    assert model.tensor_core_layers() == cfg["tc"]
+    model.infer(inp, out)
+    got = out.read().copy()
+    ref = O.run_denoiser(x, layers, alpha=0.1)
+    scale = float(np.abs(ref).max())
+    err = float(np.abs(got - ref).max()) / scale
+    assert err <= BF16X3_VS_FP32, f"{cfg}: {err:.3e} vs the fp32 oracle"
+    # in place (input image == output image), and back to fp32 bit for bit
+    inp2 = ctx.create_image(w, h, 3)
+    inp2.write(x)
+    model.infer(inp2, inp2)
+    assert np.array_equal(inp2.read(), got)
+    model.set_precision(api.MLX_PRECISION_BF16)
+    model.infer(inp, out)
+    bf16 = out.read().copy()
+    inp2.write(x)
+    model.infer(inp2, inp2)                        # in place through the bf16 layers as well
+    assert np.array_equal(inp2.read(), bf16)
+    model.set_precision(api.MLX_PRECISION_FP32)
+    model.infer(inp, out)
+    assert np.array_equal(out.read(), fp32)
+    for obj in (inp, inp2, out, model):
+        obj.release()
+
+
 @pytest.mark.parametrize("shape", [(1, 1), (127, 3), (128, 4), (129, 5), (255, 31), (256, 32), (257, 33), (3, 200),
                                    (385, 7), (640, 360), (37, 1080), (1025, 2)])
 def test_bf16_row_stacked_kernel_tiles_any_frame(ctx, tmp_path, shape):
