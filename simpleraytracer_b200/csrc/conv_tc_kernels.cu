@@ -87,6 +87,7 @@ struct TcParams
     // (x = hi + lo to 16 mantissa bits) and the chunk list runs hi*hi, lo*hi, hi*lo into the same
     // fp32 accumulator (the lo*lo term, 2^-16 relative, is dropped).
     int split;
+    int out_split;       // 1: the fp32-output epilogue writes bf16 [hi: N | lo: N] halves per pixel instead
     int n_bchunks;
     int a_coord[kMaxChunks];
     int b_chunk[kMaxChunks];
@@ -614,6 +615,31 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                         *reinterpret_cast<uint4*>(base + off1) =
                             make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
                                        pack_bf16(v[14], v[15]));
+                    }
+                    else if (P.out_split)
+                    {
+                        // bf16x3: v = hi + lo, hi to channels [cb, cb+16), lo to [N + cb, ...) of the pixel's row of
+                        // 2N bf16: four 16-byte stores, whole 32-byte sectors
+                        if (x < P.W)
+                        {
+                            uint32_t hi[8], lo[8];
+#pragma unroll
+                            for (int j = 0; j < 8; j++)
+                            {
+                                __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                                float2 const hf = __bfloat1622float2(h);
+                                __nv_bfloat162 l = __floats2bfloat162_rn(v[2 * j] - hf.x, v[2 * j + 1] - hf.y);
+                                hi[j] = *reinterpret_cast<uint32_t*>(&h);
+                                lo[j] = *reinterpret_cast<uint32_t*>(&l);
+                            }
+                            uint8_t* const o = static_cast<uint8_t*>(out) + pixel * (static_cast<size_t>(P.N) * 4u)
+                                             + static_cast<size_t>(cb) * 2u;
+                            *reinterpret_cast<uint4*>(o) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                            *reinterpret_cast<uint4*>(o + 16) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+                            uint8_t* const ol = o + static_cast<size_t>(P.N) * 2u;
+                            *reinterpret_cast<uint4*>(ol) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                            *reinterpret_cast<uint4*>(ol + 16) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+                        }
                     }
                     else if (x < P.W)
                     {
@@ -1282,7 +1308,7 @@ std::vector<uint16_t> ConvTcPackWeightsSplit(float const* hwio, int Cin, int Cou
 }
 
 ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16, int H, int W, int Cin, int Cout,
-                     bool out_bf16, Act act, float alpha, int sm_count, bool split)
+                     bool out_bf16, Act act, float alpha, int sm_count, bool split, bool out_split)
 {
     auto op = std::make_unique<ConvTc>();
     TcParams& p = op->p;
@@ -1294,6 +1320,8 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     int const n_real = Cin / p.KC;
     int const Ct = split ? 2 * Cin : Cin;      // channels of the activation and filter tensors ([hi | lo] when split)
     p.split = split ? 1 : 0;
+    p.out_split = out_split ? 1 : 0;
+    if (out_split && (out_bf16 || p.N != Cout)) throw std::runtime_error("split output needs fp32 mode and Cout % 16 == 0");
     p.n_chunks = split ? 3 * n_real : n_real;
     p.n_bchunks = split ? 2 * n_real : n_real;
     if (p.n_chunks > kMaxChunks) throw std::runtime_error("too many K chunks");
@@ -1327,7 +1355,7 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     p.prof = nullptr;
     if (std::getenv("MLB200_TC_PROF") != nullptr)
         ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&p.prof), 16 * sizeof(unsigned long long)));
-    p.rows_mode = (!split && RowsModeFits(p.N, Cin, out_bf16)) ? 1 : 0;
+    p.rows_mode = (!split && !out_split && RowsModeFits(p.N, Cin, out_bf16)) ? 1 : 0;
     p.wait_ns = EnvInt("MLB200_TC_WAIT_NS", 0);
     p.stages = kMaxStages;
     if (p.rows_mode)

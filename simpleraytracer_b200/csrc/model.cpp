@@ -567,7 +567,7 @@ void Model::InferShapes(size_t H, size_t W, size_t C)
 // e.g. 3 channels) stays on CUDA cores and writes bf16 directly.
 void Model::AssignPrecision()
 {
-    for (auto& t : m_tensors) t.bf16 = false;
+    for (auto& t : m_tensors) t.bf16 = t.split = false;
     std::vector<char> tc(m_ops.size(), 0);
     auto plain3x3 = [](Op const& op) {
         return op.KH == 3 && op.KW == 3 && op.stride == 1 && op.dilation == 1;
@@ -622,6 +622,24 @@ void Model::AssignPrecision()
     }
     for (size_t i = 0; i < m_ops.size(); i++) m_ops[i].tc = tc[i] != 0;
     for (size_t t = 0; t < m_tensors.size(); t++) m_tensors[t].bf16 = bf[t] != 0;
+    // bf16x3: a tensor between two split layers is written by the producer's epilogue directly as
+    // [hi | lo] bf16 halves (no fp32 round trip, no split pass) iff every reader is a split layer
+    // taking it as its convolution input.
+    for (Op const& op : m_ops)
+    {
+        if (!(op.tc && op.split) || op.residual >= 0) continue;
+        if (op.out == m_output_tensor || op.out == m_input_tensor) continue;
+        if (m_tensors[op.out].C % 16 != 0) continue;
+        bool any = false, all = true;
+        for (Op const& r : m_ops)
+            for (size_t k = 0; k < r.in.size(); k++)
+                if (r.in[k] == op.out)
+                {
+                    any = true;
+                    if (!(r.tc && r.split && r.kind == OpKind::Conv && k == 0 && r.residual != op.out)) all = false;
+                }
+        m_tensors[op.out].split = any && all;
+    }
 }
 
 size_t Model::TensorCoreLayers() const
@@ -722,7 +740,7 @@ void Model::AllocateBuffers()
     // Tensor-core layers: repack the filter once, bind the TMA tensor maps to the (now fixed) buffers.
     size_t split_bytes = 0;
     for (Op const& op : m_ops)
-        if (op.tc && op.split)
+        if (op.tc && op.split && !m_tensors[op.in[0]].split)
         {
             TensorInfo const& a = m_tensors[op.in[0]];
             split_bytes = std::max(split_bytes, static_cast<size_t>(a.H) * a.W * 2 * (a.C < 16 ? 16 : a.C) * 2);
@@ -745,8 +763,9 @@ void Model::AllocateBuffers()
                 op.packed_split = static_cast<int>(m_packed.size()) - 1;
                 ML_CUDA_CHECK(cudaMemcpy(d, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
             }
-            op.tc_op = nn::ConvTcCreate(m_split_buffer, m_packed[op.packed_split], nullptr, a.H, a.W, cp, o.C, false,
-                                        op.act, op.alpha, m_device->prop.multiProcessorCount, true);
+            op.tc_op = nn::ConvTcCreate(a.split ? m_buffers[a.buffer] : m_split_buffer, m_packed[op.packed_split],
+                                        nullptr, a.H, a.W, cp, o.C, false, op.act, op.alpha,
+                                        m_device->prop.multiProcessorCount, true, o.split);
             continue;
         }
         int const cin = op.pad_in ? 16 : a.C;
@@ -800,6 +819,7 @@ std::string Model::Describe() const
         if (op.residual >= 0) os << " residual=t" << op.residual;
         if (op.tc) os << (op.split ? " engine=tcgen05_bf16x3" : " engine=tcgen05_bf16");
         if (m_tensors[op.out].bf16) os << " out=bf16";
+        if (m_tensors[op.out].split) os << " out=bf16_hi_lo";
         os << " bias=" << (op.bias >= 0 ? "yes" : "no") << " act=" << acts[static_cast<int>(op.act)];
         if (op.act == nn::Act::LeakyRelu) os << " alpha=" << op.alpha;
         os << "\n";
@@ -950,8 +970,11 @@ void Model::RunOp(Op const& op, float const* d_in, float* d_out, cudaStream_t st
                 if (op.tc)
                 {
                     if (op.split)
-                        nn::SplitToBf16HiLo(ptr(op.in[0]), m_split_buffer, static_cast<size_t>(a.H) * a.W, a.C,
-                                            a.C < 16 ? 16 : a.C, stream);
+                    {
+                        if (!a.split)
+                            nn::SplitToBf16HiLo(ptr(op.in[0]), m_split_buffer, static_cast<size_t>(a.H) * a.W, a.C,
+                                                a.C < 16 ? 16 : a.C, stream);
+                    }
                     else if (op.pad_in)
                         nn::PadToBf16x16(ptr(op.in[0]), op.pad_buffer, static_cast<size_t>(a.H) * a.W, a.C, stream);
                     nn::ConvTcRun(op.tc_op, bias, ptr(op.out), stream);

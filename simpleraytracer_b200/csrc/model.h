@@ -57,6 +57,7 @@ private:
         int buffer = -1;       // index into m_buffers; -1 = external (input / output image)
         int last_use = -1;     // index of the last op reading it
         bool bf16 = false;     // stored as bf16 NHWC (between tensor-core layers); else fp32
+        bool split = false;    // stored as bf16 [hi: C | lo: C] per pixel (between bf16x3 layers; 4 bytes per element)
     };
 
     struct Op

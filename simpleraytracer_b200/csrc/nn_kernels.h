@@ -68,7 +68,8 @@ void PadToBf16x16(float const* in, void* out_bf16, size_t pixels, int C, cudaStr
 // d_out_bf16: the (fixed) bf16 output buffer the TMA store is bound to; ignored for fp32 output,
 // whose pointer is given to ConvTcRun.
 ConvTc* ConvTcCreate(void const* d_in_bf16, void const* d_w_packed, void* d_out_bf16, int H, int W, int Cin,
-                     int Cout, bool out_bf16, Act act, float alpha, int sm_count, bool split = false);
+                     int Cout, bool out_bf16, Act act, float alpha, int sm_count, bool split = false,
+                     bool out_split = false);   // out_split: the epilogue writes bf16 [hi | lo] halves (Cout % 16 == 0)
 void ConvTcRun(ConvTc const* op, float const* bias, void* out, cudaStream_t stream);
 void ConvTcDestroy(ConvTc* op);
 void FloatToHalf(float const* in, void* out, size_t n, cudaStream_t stream);
