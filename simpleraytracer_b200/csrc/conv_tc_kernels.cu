@@ -91,6 +91,14 @@ struct TcParams
     int n_bchunks;
     int a_coord[kMaxChunks];
     int b_chunk[kMaxChunks];
+    // Split mode, "wide" form (2N <= 256): the filter tile of a (tap, chunk) stacks the hi rows and the
+    // lo rows along N, so ONE M128 x 2N MMA computes A_hi*B_hi into columns [0,N) and A_hi*B_lo into
+    // [N,2N) while reading A_hi from shared memory once; A_lo*B_hi is an N-wide MMA on the tile's first
+    // N rows.  The epilogue adds the two column halves.  14 KB of operand reads per K step instead of
+    // 18 KB -- the tile-per-stage kernel is bound by exactly that.
+    int wide;
+    int acc_cols;        // TMEM columns per accumulator: 2N (wide) or N
+    int chunk_wide[kMaxChunks];
 };
 
 // ---------------------------------------------------------------- PTX helpers
@@ -317,7 +325,8 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment: the 128-byte swizzle pattern repeats every 1024 bytes
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023u) & ~uintptr_t(1023u));
-    uint32_t const b_tile_bytes = static_cast<uint32_t>(P.N) * KC * 2u;
+    uint32_t const b_rows = static_cast<uint32_t>(P.wide ? 2 * P.N : P.N);   // filter rows per (tap, chunk) tile
+    uint32_t const b_tile_bytes = b_rows * KC * 2u;
     uint32_t const a_stage_bytes = static_cast<uint32_t>(P.stage_bytes);
     uint32_t const n_b_tiles = 9u * static_cast<uint32_t>(P.n_bchunks);
     uint32_t const out_tile_bytes = P.out_bf16 ? static_cast<uint32_t>(kTileM) * P.N * 2u : 0u;
@@ -375,7 +384,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
             for (uint32_t t = 0; t < 9u; t++)
                 for (int ch = 0; ch < P.n_bchunks; ch++)
                     tma_load_2d(smem_b + (t * P.n_bchunks + ch) * b_tile_bytes, &w_map, ch * KC,
-                                static_cast<int>(t) * P.N, w_full);
+                                static_cast<int>(t * b_rows), w_full);
         }
         __syncwarp();
         uint32_t s = 0, ph = 0;
@@ -437,9 +446,12 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     {
         // ---- MMA issuer.  Instruction descriptor (cute::UMMA::InstrDescriptor): D = fp32 [4,6),
         // A = B = bf16 [7,10) [10,13), both K-major, N>>3 at [17,23), M>>4 at [24,29).
-        uint32_t const idesc = (1u << 4) | (1u << 7) | (1u << 10)
-                             | (static_cast<uint32_t>(P.N >> 3) << 17)
-                             | (static_cast<uint32_t>(kTileM >> 4) << 24);
+        uint32_t const idesc_n = (1u << 4) | (1u << 7) | (1u << 10)
+                               | (static_cast<uint32_t>(P.N >> 3) << 17)
+                               | (static_cast<uint32_t>(kTileM >> 4) << 24);
+        uint32_t const idesc_w = (1u << 4) | (1u << 7) | (1u << 10)
+                               | (static_cast<uint32_t>((2 * P.N) >> 3) << 17)
+                               | (static_cast<uint32_t>(kTileM >> 4) << 24);
         bar_wait(w_full, 0);
         tc_fence_after();
         // Everything of the two shared-memory descriptors except the start address is constant;
@@ -461,7 +473,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
             bar_wait(&acc_empty[acc], aph ^ 1u);
             TC_PROF_ADD(0);
             tc_fence_after();
-            uint32_t const d_tmem = tmem_base + acc * static_cast<uint32_t>(P.N);
+            uint32_t const d_tmem = tmem_base + acc * static_cast<uint32_t>(P.acc_cols);
             for (uint32_t kh0 = 0; kh0 < 3u; kh0 += rps)
             {
                 for (uint32_t ch = 0; ch < n_chunks; ch++)
@@ -476,6 +488,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                         {
                             uint32_t const a_st = a_lo0 + s * stage_u;
                             uint32_t const b_st = b_lo0 + kh0 * b_row_u + static_cast<uint32_t>(P.b_chunk[ch]) * b_tile_u;
+                            uint32_t const idesc = P.chunk_wide[ch] ? idesc_w : idesc_n;
 #pragma unroll
                             for (uint32_t r = 0; r < 3u; r++)
                             {
@@ -555,23 +568,29 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
             bar_wait(&acc_full[acc], aph);
             TC_PROF_ADD(0);
             tc_fence_after();
-            uint32_t const taddr = tmem_base + acc * static_cast<uint32_t>(P.N) + ((q * 32u) << 16);
+            uint32_t const taddr = tmem_base + acc * static_cast<uint32_t>(P.acc_cols) + ((q * 32u) << 16);
             uint8_t* const stg = smem_o + buf * out_tile_bytes;
             int const x = x0 + static_cast<int>(row);
             size_t const pixel = static_cast<size_t>(y) * P.W + x;
-            for (int c0 = c_begin; c0 < c_end && !(P.debug & 4); c0 += 32)
+            for (int c0 = c_begin; c0 < c_end && !(P.debug & 4); c0 += (P.wide ? 16 : 32))
             {
                 // two 16-column loads in flight, one wait (N is a multiple of 16: the second
                 // half is warp-uniformly skipped on the last odd chunk)
                 uint32_t r[32];
-                bool const two = c0 + 16 < c_end;
+                // wide (bf16x3): the second load is the same 16 channels' hi*lo half, N columns further on
+                bool const two = P.wide || c0 + 16 < c_end;
                 tc_ld16(taddr + static_cast<uint32_t>(c0), *reinterpret_cast<uint32_t(*)[16]>(&r[0]));
-                if (two) tc_ld16(taddr + static_cast<uint32_t>(c0 + 16), *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
+                if (two) tc_ld16(taddr + static_cast<uint32_t>(P.wide ? P.N + c0 : c0 + 16), *reinterpret_cast<uint32_t(*)[16]>(&r[16]));
                 tc_ld_wait();
+                if (P.wide)
+                {
+#pragma unroll
+                    for (int j = 0; j < 16; j++) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r[16 + j]));
+                }
 #pragma unroll
                 for (int h = 0; h < 2; h++)
                 {
-                    if (h == 1 && !two) break;
+                    if (h == 1 && (!two || P.wide)) break;
                     int const cb = c0 + 16 * h;
                     float v[16];
 #pragma unroll
@@ -1268,6 +1287,7 @@ bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding
     if (Cout < 1 || N > 256) return false;
     int const KC = Cin < 64 ? Cin : 64;
     if ((split ? 3 : 1) * (Cin / KC) > kMaxChunks) return false;
+    if (split && N > 256) return false;
     // split: the resident filter holds the hi and the lo half, the output is fp32 (no staging tiles);
     // three ring stages at least, or the MMA pipe waits on every TMA round trip
     if (split) return SmemBytes(N, 2 * Cin, KC, 3, false) <= 226u * 1024u;
@@ -1288,11 +1308,31 @@ std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout, in
     return packed;
 }
 
+bool ConvTcSplitWide(int Cout)
+{
+    return 2 * ConvTcPaddedCout(Cout) <= 256 && EnvInt("MLB200_X3_WIDE", 1) != 0;
+}
+
 std::vector<uint16_t> ConvTcPackWeightsSplit(float const* hwio, int Cin, int Cout, int Cin_pad)
 {
-    // [tap][co][hi: Cin_pad | lo: Cin_pad], w = hi + lo up to 2^-17 relative
     int const N = ConvTcPaddedCout(Cout);
     std::vector<uint16_t> packed(static_cast<size_t>(9) * N * 2 * Cin_pad, 0);
+    if (ConvTcSplitWide(Cout))
+    {
+        // wide form: [tap][hi rows: N | lo rows: N][Cin_pad]
+        for (int t = 0; t < 9; t++)
+            for (int co = 0; co < Cout; co++)
+                for (int ci = 0; ci < Cin; ci++)
+                {
+                    float const w = hwio[(static_cast<size_t>(t) * Cin + ci) * Cout + co];
+                    __nv_bfloat16 hi = __float2bfloat16_rn(w);
+                    __nv_bfloat16 lo = __float2bfloat16_rn(w - __bfloat162float(hi));
+                    packed[(static_cast<size_t>(t) * 2 * N + co) * Cin_pad + ci] = *reinterpret_cast<uint16_t*>(&hi);
+                    packed[(static_cast<size_t>(t) * 2 * N + N + co) * Cin_pad + ci] = *reinterpret_cast<uint16_t*>(&lo);
+                }
+        return packed;
+    }
+    // [tap][co][hi: Cin_pad | lo: Cin_pad], w = hi + lo up to 2^-17 relative
     for (int t = 0; t < 9; t++)
         for (int co = 0; co < Cout; co++)
             for (int ci = 0; ci < Cin; ci++)
@@ -1322,24 +1362,37 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     p.split = split ? 1 : 0;
     p.out_split = out_split ? 1 : 0;
     if (out_split && (out_bf16 || p.N != Cout)) throw std::runtime_error("split output needs fp32 mode and Cout % 16 == 0");
-    p.n_chunks = split ? 3 * n_real : n_real;
-    p.n_bchunks = split ? 2 * n_real : n_real;
+    p.wide = (split && ConvTcSplitWide(Cout)) ? 1 : 0;
+    p.acc_cols = p.wide ? 2 * p.N : p.N;
+    p.n_chunks = p.wide ? 2 * n_real : split ? 3 * n_real : n_real;
+    p.n_bchunks = (split && !p.wide) ? 2 * n_real : n_real;
     if (p.n_chunks > kMaxChunks) throw std::runtime_error("too many K chunks");
-    for (int c = 0; c < kMaxChunks; c++) { p.a_coord[c] = 0; p.b_chunk[c] = 0; }
+    for (int c = 0; c < kMaxChunks; c++) { p.a_coord[c] = 0; p.b_chunk[c] = 0; p.chunk_wide[c] = 0; }
     for (int c = 0; c < p.n_chunks; c++)
     {
-        int const term = c / n_real, r = c - term * n_real;   // split terms: hi*hi, lo*hi, hi*lo
-        p.a_coord[c] = (term == 1 ? Cin : 0) + r * p.KC;
-        p.b_chunk[c] = (term == 2 ? n_real : 0) + r;
+        if (p.wide)
+        {
+            // per real chunk: A_hi x [B_hi | B_lo] (2N wide, first: it overwrites every column), then A_lo x B_hi
+            int const r = c >> 1, lo = c & 1;
+            p.a_coord[c] = (lo ? Cin : 0) + r * p.KC;
+            p.b_chunk[c] = r;
+            p.chunk_wide[c] = lo ? 0 : 1;
+        }
+        else
+        {
+            int const term = c / n_real, r = c - term * n_real;   // split terms: hi*hi, lo*hi, hi*lo
+            p.a_coord[c] = (term == 1 ? Cin : 0) + r * p.KC;
+            p.b_chunk[c] = (term == 2 ? n_real : 0) + r;
+        }
     }
     p.layout_type = p.KC == 64 ? 2 : p.KC == 32 ? 4 : 6;
     p.sbo = 8 * p.KC * 2;
     p.tiles_per_row = (W + kTileM - 1) / kTileM;
     p.n_tiles = p.tiles_per_row * H;
     int const want_acc = std::getenv("MLB200_TC_ACC") ? std::atoi(std::getenv("MLB200_TC_ACC")) : kMaxAcc;
-    p.n_acc = (want_acc >= 4 && 4 * p.N <= 512) ? 4 : 2;
+    p.n_acc = (want_acc >= 4 && 4 * p.acc_cols <= 512) ? 4 : 2;
     int cols = 32;
-    while (cols < p.n_acc * p.N) cols *= 2;
+    while (cols < p.n_acc * p.acc_cols) cols *= 2;
     p.tmem_cols = cols;
     p.out_bf16 = out_bf16 ? 1 : 0;
     p.act = act;
@@ -1389,9 +1442,11 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     }
     // filter: [9 * N][Cin] bf16, box = KC channels x N rows
     {
-        cuuint64_t dims[2] = {static_cast<cuuint64_t>(Ct), static_cast<cuuint64_t>(9) * p.N};
-        cuuint64_t strides[1] = {static_cast<cuuint64_t>(Ct) * 2};
-        cuuint32_t box[2] = {static_cast<cuuint32_t>(p.KC), static_cast<cuuint32_t>(p.N)};
+        // (wide split: [9 * 2N][Cin], box = KC channels x 2N rows -- the hi rows and the lo rows of a tap)
+        int const Cw = p.wide ? Cin : Ct, rows = p.wide ? 2 * p.N : p.N;
+        cuuint64_t dims[2] = {static_cast<cuuint64_t>(Cw), static_cast<cuuint64_t>(9) * rows};
+        cuuint64_t strides[1] = {static_cast<cuuint64_t>(Cw) * 2};
+        cuuint32_t box[2] = {static_cast<cuuint32_t>(p.KC), static_cast<cuuint32_t>(rows)};
         Encode(&op->w_map, d_w_packed, 2, dims, strides, box, SwizzleFor(p.KC));
     }
     // bf16 output: [H][W][N] bf16, box = min(N, 64) channels x 128 pixels (the TMA store clips at W)

@@ -459,9 +459,12 @@ BF16X3_VS_FP32 = 1e-4   # stated bound of the split-operand tensor-core path, fr
     dict(width=128, depth=3, act="Relu", w=70, h=20, tc=2),        # 128->128 does not fit: fp32; 128->3 = 6 K chunks
     dict(width=48, depth=3, act="Relu", w=129, h=2, tc=1),         # Cin = 48 is not a tensor-core shape: only layer 0
 ])
-def test_bf16x3_tensor_core_denoiser_is_fp32_grade(ctx, tmp_path, cfg):
+@pytest.mark.parametrize("form", ["wide", "narrow"])
+def test_bf16x3_tensor_core_denoiser_is_fp32_grade(ctx, tmp_path, cfg, form, monkeypatch):
     """MLX_PRECISION_BF16X3: split-operand tcgen05 layers against the fp32 conv oracle (tolerance 1e-4 of
-    the range, ten times inside the 1e-3 bar north_star sets for fp32 inference)."""
+    the range, ten times inside the 1e-3 bar north_star sets for fp32 inference).  Both MMA forms: hi and
+    lo filter rows stacked along N (default where 2N <= 256) and three N-wide products per K chunk."""
+    monkeypatch.setenv("MLB200_X3_WIDE", "1" if form == "wide" else "0")
     path = tmp_path / "d.pb"
     _, layers = gw.make_denoiser(path, channels=3, width=cfg["width"], depth=cfg["depth"], seed=11, act=cfg["act"])
     w, h = cfg["w"], cfg["h"]
