@@ -47,18 +47,20 @@ ML_API_ENTRY ml_status mlxIpcExportImage(ml_image image, void* handle_out);
 ML_API_ENTRY void* mlxIpcOpen(ml_context context, void const* handle);
 ML_API_ENTRY void mlxIpcClose(ml_context context, void* device_pointer);
 
-/* Arithmetic of the model's wide 3x3 convolution layers.  MLX_PRECISION_FP32 (default, or
- * MLB200_PRECISION unset): fp32 on the CUDA cores.  MLX_PRECISION_BF16 (or
- * MLB200_PRECISION=bf16 at mlCreateModel): bf16 operands, fp32 accumulation on the tensor
- * cores (tcgen05 + TMEM) for every 3x3 / stride 1 / SAME layer with 16, 32 or 64k input
- * channels; activations between such layers are stored as bf16.  Image I/O stays
- * ML_FLOAT32 / ML_FLOAT16 as declared by the graph.  May be called before or after
- * mlSetModelInputInfo.  mlxModelTensorCoreLayers reports how many layers use that path.
- * MLX_PRECISION_BF16X3 (or MLB200_PRECISION=bf16x3): the same tensor-core layers with fp32-grade
- * results -- every fp32 operand x is split into two bf16 halves (x = hi + lo to 16 mantissa bits)
- * and each product is issued as hi*hi + lo*hi + hi*lo into the fp32 accumulator (the dropped lo*lo
- * term is 2^-16 relative); tensors between layers stay fp32.  Stated bound: 1e-4 of the output
- * range against the fp32 oracle (measured ~1e-6), i.e. inside the 1e-3 bar of the fp32 path. */
+/* Arithmetic of the model's 3x3 / stride 1 / SAME convolution layers with 16, 32 or 64k input
+ * channels (a thinner first layer, e.g. RGB, is zero-padded to 16) whose filter fits in shared
+ * memory; every other layer always runs in fp32 on the CUDA cores.
+ *   MLX_PRECISION_BF16X3 (default; MLB200_PRECISION=bf16x3): tensor cores (tcgen05 + TMEM) with
+ *     fp32-grade results -- every fp32 operand x is split into two bf16 halves (x = hi + lo to 16
+ *     mantissa bits) and each product is issued as hi*hi + hi*lo + lo*hi into the fp32 accumulator
+ *     (the dropped lo*lo term is 2^-16 relative).  Stated bound: 1e-4 of the output range against
+ *     the fp32 oracle (measured ~1e-5), inside the 1e-3 bar of fp32 inference.  Non-finite inputs
+ *     give NaN where fp32 arithmetic would give +-inf.
+ *   MLX_PRECISION_FP32 (MLB200_PRECISION=fp32): plain fp32 FMAs on the CUDA cores (~1e-6).
+ *   MLX_PRECISION_BF16 (MLB200_PRECISION=bf16): bf16 operands, fp32 accumulation on the tensor
+ *     cores; activations between such layers are stored as bf16.  Stated bound 3e-2 of the range.
+ * Image I/O stays ML_FLOAT32 / ML_FLOAT16 as declared by the graph.  May be called before or after
+ * mlSetModelInputInfo.  mlxModelTensorCoreLayers reports how many layers run on the tensor cores. */
 #define MLX_PRECISION_FP32 0
 #define MLX_PRECISION_BF16 1
 #define MLX_PRECISION_BF16X3 2

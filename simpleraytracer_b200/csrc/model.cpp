@@ -104,7 +104,9 @@ Model::Model(DeviceStatePtr device, ml_model_params const* params) : m_device(st
     if (char const* e = std::getenv("MLB200_PRECISION"))
     {
         std::string const v(e);
-        m_precision = (v == "bf16" || v == "BF16") ? 1 : (v == "bf16x3" || v == "BF16X3") ? 2 : 0;
+        if (v == "fp32" || v == "FP32") m_precision = 0;
+        else if (v == "bf16" || v == "BF16") m_precision = 1;
+        else if (v == "bf16x3" || v == "BF16X3") m_precision = 2;
     }
 
     // Upload constants once; they stay resident in HBM for the model's life.
@@ -831,7 +833,9 @@ size_t Model::LaunchesPerInfer() const
 {
     size_t n = 0;
     for (auto const& op : m_ops)
-        n += op.kind == OpKind::Concat ? op.in.size() : (1 + (op.tc && op.pad_in ? 1 : 0) + (op.tc && op.residual >= 0 ? 1 : 0));
+        n += op.kind == OpKind::Concat ? op.in.size()
+                                       : (1 + (op.tc && op.pad_in ? 1 : 0) + (op.tc && op.residual >= 0 ? 1 : 0)
+                                          + (op.tc && op.split && !m_tensors[op.in[0]].split ? 1 : 0));
     if (m_input_info.dtype == ML_FLOAT16) n += 2;
     return n;
 }

@@ -34,9 +34,11 @@ public:
     ml_status Profile(ml_image input, ml_image output, float* op_ms, double* op_flops, double* op_bytes,
                       size_t max_ops, size_t* n_ops);
 
-    // Arithmetic of the wide 3x3 layers: 0 = fp32 on CUDA cores (default), 1 = bf16 on the
-    // tensor cores (tcgen05, fp32 accumulation) wherever conv_tc_kernels.cu supports the layer.
-    // Initial value from MLB200_PRECISION=bf16; mlxSetModelPrecision changes it later.
+    // Arithmetic of the 3x3 / stride 1 / SAME layers conv_tc_kernels.cu supports: 0 = fp32 on the CUDA
+    // cores, 1 = bf16 on the tensor cores (tcgen05, fp32 accumulation), 2 = bf16x3 (default): the
+    // tensor cores with every fp32 operand split into two bf16 halves and three products per term --
+    // fp32-grade results (~1e-5 of the range).  Initial value from MLB200_PRECISION=fp32|bf16|bf16x3;
+    // mlxSetModelPrecision changes it later.
     ml_status SetPrecision(int precision);
     int Precision() const { return m_precision; }
     size_t TensorCoreLayers() const;
@@ -130,7 +132,7 @@ private:
     int m_input_tensor = -1;
     int m_output_tensor = -1;
 
-    int m_precision = 0;
+    int m_precision = 2;
     std::vector<cudaEvent_t> m_events; // pool for InferBatch
     std::vector<void*> m_packed;  // device copies of repacked bf16 filters
     std::vector<void*> m_buffers;

@@ -32,7 +32,8 @@ def test_writer_bytes_parse_with_protobuf_runtime():
     assert g2 == g
 
 
-def test_reader_inspects_writer_graph(tmp_path):
+def test_reader_inspects_writer_graph(tmp_path, monkeypatch):
+    monkeypatch.setenv("MLB200_PRECISION", "fp32")           # the plan of the plain CUDA-core path
     path = tmp_path / "m.pb"
     gw.make_denoiser(path, channels=3, width=16, depth=4, seed=1, act="LeakyRelu")
     ok, text = api.inspect_model(path)
@@ -146,8 +147,9 @@ def test_bf16_plan_is_decided_on_the_host(tmp_path, monkeypatch):
     bf16) is host logic -- visible through mlxInspectModel without a GPU."""
     path = tmp_path / "m.pb"
     gw.make_denoiser(path, channels=3, width=64, depth=4, seed=1)
+    monkeypatch.setenv("MLB200_PRECISION", "fp32")
     ok, text = api.inspect_model(path)
-    assert ok and "tcgen05" not in text                      # default precision: fp32 CUDA-core kernels
+    assert ok and "tcgen05" not in text                      # fp32 CUDA-core kernels only
     monkeypatch.setenv("MLB200_PRECISION", "bf16")
     ok, text = api.inspect_model(path)
     assert ok, text
@@ -164,6 +166,32 @@ def test_bf16_plan_is_decided_on_the_host(tmp_path, monkeypatch):
     convs = [l for l in text.splitlines() if l.startswith("Conv ")]
     assert ["engine=tcgen05_bf16" in l for l in convs] == [True, False, True]
     assert "out=bf16" in convs[1]                            # the fp32 layer feeds a tensor-core layer in bf16
+
+
+def test_bf16x3_plan_is_the_default(tmp_path, monkeypatch):
+    """Default precision: fp32-grade tensor-core layers (split bf16 operands).  Tensors between two such
+    layers are written as [hi | lo] halves by the producer; the first layer's input is split by a pass
+    of its own; the last layer writes fp32 and its residual add is a separate pass."""
+    monkeypatch.delenv("MLB200_PRECISION", raising=False)
+    path = tmp_path / "m.pb"
+    gw.make_denoiser(path, channels=3, width=64, depth=4, seed=1)
+    ok, text = api.inspect_model(path)
+    assert ok, text
+    convs = [l for l in text.splitlines() if l.startswith("Conv ")]
+    assert len(convs) == 4 and all("engine=tcgen05_bf16x3" in l for l in convs)
+    assert all("out=bf16_hi_lo" in l for l in convs[:3]) and "out=bf16_hi_lo" not in convs[3]
+    assert "launches=6" in text                              # 4 convs + the input split + the residual add
+    monkeypatch.setenv("MLB200_PRECISION", "bf16x3")
+    assert api.inspect_model(path)[1] == text
+    # 5x5: no tensor-core layer; 128->128: the hi and lo filters do not fit in shared memory
+    gw.make_denoiser(path, channels=3, width=32, depth=3, seed=1, kernel=5)
+    ok, text = api.inspect_model(path)
+    assert ok and "tcgen05" not in text
+    gw.make_denoiser(path, channels=3, width=128, depth=3, seed=1)
+    ok, text = api.inspect_model(path)
+    convs = [l for l in text.splitlines() if l.startswith("Conv ")]
+    assert ["engine=tcgen05_bf16x3" in l for l in convs] == [True, False, True]
+    assert "out=bf16_hi_lo" not in text                      # fp32 either side of the CUDA-core layer
 
 
 def test_add_is_folded_into_the_conv_only_when_the_order_allows(tmp_path):

@@ -61,8 +61,12 @@ def test_denoiser_matches_oracle(ctx, tmp_path, cfg):
     x = np.random.default_rng(2).random((h, w, 3), dtype=np.float32)
     inp = ctx.create_image(w, h, 3); out = ctx.create_image(o.width, o.height, o.channels)
     inp.write(x)
+    model.infer(inp, out)                             # default precision: bf16x3 tensor-core layers where supported
+    ref = O.run_denoiser(x, layers, alpha=0.1)
+    close(out.read(), ref, str(cfg))
+    model.set_precision(api.MLX_PRECISION_FP32)       # the plain CUDA-core path
     model.infer(inp, out)
-    close(out.read(), O.run_denoiser(x, layers, alpha=0.1), str(cfg))
+    close(out.read(), ref, str(cfg) + " fp32")
     assert model.launch_count() == cfg["depth"]       # conv+bias+act per layer; the residual add rides in the last one
     for obj in (inp, out, model):
         obj.release()
@@ -101,8 +105,11 @@ def test_single_conv_variants(ctx, tmp_path, case):
     assert (o.height, o.width, o.channels) == ref.shape
     inp = ctx.create_image(w, h, cin); out = ctx.create_image(o.width, o.height, o.channels)
     inp.write(x)
-    model.infer(inp, out)
+    model.infer(inp, out)                             # default precision (bf16x3 where the shape is supported)
     close(out.read(), ref, str(case))
+    model.set_precision(api.MLX_PRECISION_FP32)
+    model.infer(inp, out)
+    close(out.read(), ref, str(case) + " fp32")
     assert model.launch_count() == 1
     for obj in (inp, out, model):
         obj.release()
@@ -423,6 +430,7 @@ def test_bf16_tensor_core_denoiser(ctx, tmp_path, cfg, kernel, monkeypatch):
     x = np.random.default_rng(5).random((h, w, 3), dtype=np.float32)
     inp = ctx.create_image(w, h, 3); out = ctx.create_image(w, h, 3)
     inp.write(x)
+    model.set_precision(api.MLX_PRECISION_FP32)
     model.infer(inp, out)
     fp32 = out.read().copy()
     assert model.tensor_core_layers() == 0
@@ -472,6 +480,9 @@ def test_bf16x3_tensor_core_denoiser_is_fp32_grade(ctx, tmp_path, cfg, form, mon
     x = np.random.default_rng(5).random((h, w, 3), dtype=np.float32)
     inp = ctx.create_image(w, h, 3); out = ctx.create_image(w, h, 3)
     inp.write(x)
+    assert model.tensor_core_layers() == cfg["tc"]          # bf16x3 is the default precision
+    model.set_precision(api.MLX_PRECISION_FP32)
+    assert model.tensor_core_layers() == 0
     model.infer(inp, out)
     fp32 = out.read().copy()
     model.set_precision(api.MLX_PRECISION_BF16X3)
