@@ -460,6 +460,158 @@ __global__ void __launch_bounds__(kBruteThreads) render_brute_kernel(const __gri
 }
 
 // ---------------------------------------------------------------------------
+// Primary-ray screen grid (scene.h GridView): count / scan / fill, rebuilt per render call
+// ---------------------------------------------------------------------------
+// Camera-space coefficients of P: P - origin = cx*right + cy*up + cz*forward.  A primary ray through
+// the sample (sx, sy) has direction forward + sx*right + sy*up, so it passes through P exactly when
+// cx/cz = sx and cy/cz = sy (cz > 0).  Every point of a triangle whose three vertices have cz > 0
+// projects inside the bounding box of the projected vertices.  The box is dilated by the projection
+// of a world-space slack (4x the BVH box padding, plus the fp32 error of the projection itself) and
+// by 1/4 pixel, which exceeds by orders of magnitude how far outside a triangle the fp32
+// Moller-Trumbore test can still answer "inside" (the BVH boxes rely on a quarter of that slack).
+__device__ __forceinline__ bool grid_project(GridBuild const& G, uint32_t i, float4& box)
+{
+    float4 const v0 = reinterpret_cast<float4 const*>(G.scene.tri_v0)[i];
+    float4 const e1 = reinterpret_cast<float4 const*>(G.scene.tri_e1)[i];
+    float4 const e2 = reinterpret_cast<float4 const*>(G.scene.tri_e2)[i];
+    float tx0 = pos_inf(), tx1 = -pos_inf(), ty0 = pos_inf(), ty1 = -pos_inf();
+    float zmin = pos_inf(), zmax = -pos_inf(), dist = 0.f, tmax = 0.f;
+    float vx[3] = {v0.x, v0.x + e1.x, v0.x + e2.x};
+    float vy[3] = {v0.y, v0.y + e1.y, v0.y + e2.y};
+    float vz[3] = {v0.z, v0.z + e1.z, v0.z + e2.z};
+    float cxs[3], cys[3], czs[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {
+        float const px = vx[k] - G.origin[0], py = vy[k] - G.origin[1], pz = vz[k] - G.origin[2];
+        cxs[k] = G.minv[0] * px + G.minv[1] * py + G.minv[2] * pz;
+        cys[k] = G.minv[3] * px + G.minv[4] * py + G.minv[5] * pz;
+        czs[k] = G.minv[6] * px + G.minv[7] * py + G.minv[8] * pz;
+        zmin = fminf(zmin, czs[k]);
+        zmax = fmaxf(zmax, czs[k]);
+        dist = fmaxf(dist, fabsf(px) + fabsf(py) + fabsf(pz));
+    }
+    // basis scale: |c| <= mnorm * |P - o|
+    float mnorm = 0.f;
+#pragma unroll
+    for (int k = 0; k < 9; k++) mnorm = fmaxf(mnorm, fabsf(G.minv[k]));
+    float const slack_w = (G.pad + 4e-6f * dist) * 3.0f * mnorm;   // camera-space slack of each coefficient
+    box = make_float4(1.f, 1.f, 0.f, 0.f);                         // x0 > x1: not binned
+    if (zmax < -slack_w) return false;                             // wholly behind the camera: no ray reaches it
+    if (!(zmin > 1e-3f * mnorm * dist + 8.0f * slack_w)) return true;   // near or crossing the camera plane: global
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {
+        float const iz = 1.0f / czs[k];
+        float const tx = cxs[k] * iz, ty = cys[k] * iz;
+        tx0 = fminf(tx0, tx); tx1 = fmaxf(tx1, tx);
+        ty0 = fminf(ty0, ty); ty1 = fmaxf(ty1, ty);
+        tmax = fmaxf(tmax, fmaxf(fabsf(tx), fabsf(ty)));
+    }
+    float const slack_t = 2.0f * slack_w * (1.0f + tmax) / zmin;   // d(c/z) <= dc/z + |c| dz / z^2
+    float const kx = 0.5f * static_cast<float>(G.width) / G.half_w, ky = 0.5f * static_cast<float>(G.height) / G.half_h;
+    float const cxp = 0.5f * static_cast<float>(G.width), cyp = 0.5f * static_cast<float>(G.height);
+    // pixel x = (sx / half_w + 1) * W/2 ; pixel y = (1 - sy / half_h) * H/2
+    float const x0 = cxp + (tx0 - slack_t) * kx - 0.25f, x1 = cxp + (tx1 + slack_t) * kx + 0.25f;
+    float const y0 = cyp - (ty1 + slack_t) * ky - 0.25f, y1 = cyp - (ty0 - slack_t) * ky + 0.25f;
+    if (!(x0 <= x1) || !(y0 <= y1) || !isfinite(x0) || !isfinite(x1) || !isfinite(y0) || !isfinite(y1)) return true;
+    box = make_float4(x0, y0, x1, y1);
+    return false;
+}
+
+// tiles a box touches; false when it lies off the frame
+__device__ __forceinline__ bool grid_tile_range(GridBuild const& G, float4 box, int& tx0, int& tx1, int& ty0, int& ty1)
+{
+    float const inv = 1.0f / static_cast<float>(kGridTile);
+    float const fx0 = floorf((box.x - 1.0f) * inv), fx1 = floorf(box.z * inv);
+    float const fy0 = floorf((box.y - 1.0f) * inv), fy1 = floorf(box.w * inv);
+    if (fx1 < 0.f || fy1 < 0.f || fx0 >= static_cast<float>(G.tiles_w) || fy0 >= static_cast<float>(G.tiles_h)) return false;
+    tx0 = static_cast<int>(fmaxf(fx0, 0.f)); tx1 = static_cast<int>(fminf(fx1, static_cast<float>(G.tiles_w - 1)));
+    ty0 = static_cast<int>(fmaxf(fy0, 0.f)); ty1 = static_cast<int>(fminf(fy1, static_cast<float>(G.tiles_h - 1)));
+    return true;
+}
+
+constexpr int kGridMaxTilesPerTri = 1024;   // larger on screen: global list
+
+__global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__ GridBuild G)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= G.scene.n_tris_padded) return;
+    float4 box = make_float4(1.f, 1.f, 0.f, 0.f);
+    bool global = false;
+    if (i < G.scene.n_tris && __float_as_int(reinterpret_cast<float4 const*>(G.scene.tri_v0)[i].w) >= 0)
+        global = grid_project(G, i, box);
+    int tx0, tx1, ty0, ty1;
+    bool const binned = !global && box.x <= box.z && grid_tile_range(G, box, tx0, tx1, ty0, ty1);
+    if (binned && (tx1 - tx0 + 1) * (ty1 - ty0 + 1) > kGridMaxTilesPerTri) global = true;
+    if (global)
+    {
+        uint32_t const k = atomicAdd(&G.flags->n_global, 1u);
+        if (k < kGridMaxGlobal) G.global[k] = i;
+        box = make_float4(1.f, 1.f, 0.f, 0.f);
+    }
+    else if (binned)
+    {
+        for (int ty = ty0; ty <= ty1; ty++)
+            for (int tx = tx0; tx <= tx1; tx++) atomicAdd(&G.tile_cnt[ty * G.tiles_w + tx], 1u);
+    }
+    else
+    {
+        box = make_float4(1.f, 1.f, 0.f, 0.f);   // off the frame or behind the camera
+    }
+    reinterpret_cast<float4*>(G.bbox)[i] = box;
+}
+
+// one block: exclusive prefix sum of the tile counts, cursors reset, verdict
+__global__ void __launch_bounds__(1024) grid_scan_kernel(const __grid_constant__ GridBuild G)
+{
+    __shared__ uint32_t s_part[1024];
+    uint32_t const tiles = G.tiles_w * G.tiles_h;
+    uint32_t const per = (tiles + 1023u) / 1024u;
+    uint32_t const b = threadIdx.x * per, e = min(tiles, b + per);
+    uint32_t sum = 0;
+    for (uint32_t t = b; t < e; t++) sum += G.tile_cnt[t];
+    s_part[threadIdx.x] = sum;
+    __syncthreads();
+    for (uint32_t off = 1; off < 1024u; off <<= 1)
+    {
+        uint32_t const v = threadIdx.x >= off ? s_part[threadIdx.x - off] : 0u;
+        __syncthreads();
+        s_part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    uint32_t run = s_part[threadIdx.x] - sum;
+    for (uint32_t t = b; t < e; t++)
+    {
+        G.tile_off[t] = run;
+        run += G.tile_cnt[t];
+        G.cursor[t] = 0;
+    }
+    if (threadIdx.x == 1023)
+    {
+        uint32_t const total = s_part[1023];
+        G.tile_off[tiles] = total;
+        G.flags->total = total;
+        G.flags->ok = (total <= G.cap && G.flags->n_global <= kGridMaxGlobal) ? 1u : 0u;
+    }
+}
+
+__global__ void __launch_bounds__(256) grid_fill_kernel(const __grid_constant__ GridBuild G)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= G.scene.n_tris || G.flags->ok == 0) return;
+    float4 const box = reinterpret_cast<float4 const*>(G.bbox)[i];
+    int tx0, tx1, ty0, ty1;
+    if (!(box.x <= box.z) || !grid_tile_range(G, box, tx0, tx1, ty0, ty1)) return;
+    for (int ty = ty0; ty <= ty1; ty++)
+        for (int tx = tx0; tx <= tx1; tx++)
+        {
+            uint32_t const t = ty * G.tiles_w + tx;
+            G.items[G.tile_off[t] + atomicAdd(&G.cursor[t], 1u)] = i;
+        }
+}
+
+// ---------------------------------------------------------------------------
 // BVH traversal
 // ---------------------------------------------------------------------------
 constexpr int kBvhThreads = 256;  // 8 warps; each warp owns an 8x4 pixel tile
@@ -687,6 +839,40 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
     constexpr uint32_t SPL = 32u / PIX; // sample lanes per pixel
     static_assert(SPL >= 3, "one lane per (pixel, channel) does the ordered sum");
     __shared__ float s_val[8][32][3];
+    // Primary-ray grid (PIX == 1 only): the block IS one 8x8 grid tile.  The tile's candidate triangles
+    // (plus the frame's global ones) are staged in shared memory once; every warp filters them against
+    // its current pixel (lanes test different candidates, ballot-compacted), and every sample of that
+    // pixel then tests the few survivors instead of walking the BVH.
+    constexpr uint32_t kCand = PIX == 1 ? kGridMaxList + kGridMaxGlobal : 1;
+    __shared__ float4 s_cv0[kCand], s_ce1[kCand], s_ce2[kCand], s_cbox[kCand];
+    __shared__ uint32_t s_cslot[kCand];
+    __shared__ uint8_t s_pixlist[PIX == 1 ? 8 : 1][kCand];
+    uint32_t n_cand = 0;
+    bool use_grid = false;
+    if (PIX == 1 && L.grid.enabled)
+    {
+        GridFlags const fl = *L.grid.flags;
+        uint32_t const ty = (L.row_origin + blockIdx.y * L.row_block_step) / kGridTile;
+        uint32_t const tile = ty * L.grid.tiles_w + blockIdx.x;
+        uint32_t const off = L.grid.tile_off[tile], cnt = L.grid.tile_off[tile + 1] - off;
+        use_grid = fl.ok != 0 && cnt <= kGridMaxList && blockIdx.x < L.grid.tiles_w && ty < L.grid.tiles_h;
+        if (use_grid)   // block-uniform
+        {
+            n_cand = cnt + fl.n_global;
+            if (threadIdx.x < n_cand)
+            {
+                bool const glob = threadIdx.x >= cnt;
+                uint32_t const slot = glob ? L.grid.global[threadIdx.x - cnt] : L.grid.items[off + threadIdx.x];
+                s_cslot[threadIdx.x] = slot;
+                s_cv0[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_v0) + slot);
+                s_ce1[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e1) + slot);
+                s_ce2[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e2) + slot);
+                s_cbox[threadIdx.x] = glob ? make_float4(-pos_inf(), -pos_inf(), pos_inf(), pos_inf())
+                                           : __ldg(reinterpret_cast<float4 const*>(L.grid.bbox) + slot);
+            }
+            __syncthreads();
+        }
+    }
 
     uint32_t const W = L.params.width;
     uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -709,6 +895,25 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
             bool const in_frame = x < W;
             float sum = 0.f; // running sum of channel `sl` of pixel p (lanes with sl < 3)
             Hit first_hit = no_hit();
+            uint32_t n_pix = 0; // candidates whose screen box touches this pixel (closed intervals)
+            if (PIX == 1 && use_grid)
+            {
+                float const px0 = static_cast<float>(x), py0 = static_cast<float>(y);
+                for (uint32_t base = 0; base < n_cand; base += 32u)
+                {
+                    uint32_t const j = base + lane;
+                    bool pass = false;
+                    if (j < n_cand)
+                    {
+                        float4 const b = s_cbox[j];
+                        pass = b.z >= px0 && b.x <= px0 + 1.0f && b.w >= py0 && b.y <= py0 + 1.0f;
+                    }
+                    uint32_t const m = __ballot_sync(0xffffffffu, pass);
+                    if (pass) s_pixlist[warp][n_pix + __popc(m & ((1u << lane) - 1u))] = static_cast<uint8_t>(j);
+                    n_pix += __popc(m);
+                }
+                __syncwarp();
+            }
             for (uint32_t s0 = 0; s0 < spp; s0 += SPL)
             {
                 uint32_t const s = s0 + sl;
@@ -719,7 +924,20 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                     Hit best = no_hit();
                     bool occ = false;
                     n_primary++;
-                    bvh_trace<false, STATS>(L.scene, o, d, L.params.t_min, best, occ, n_box, n_tri, hint_hit);
+                    if (PIX == 1 && use_grid)
+                    {
+                        if (STATS) n_tri += n_pix;
+                        for (uint32_t k = 0; k < n_pix; k++)
+                        {
+                            uint32_t const j = s_pixlist[warp][k];       // same address in every lane: broadcast
+                            float4 const v0 = s_cv0[j], e1 = s_ce1[j], e2 = s_ce2[j];
+                            float ts, adet;
+                            if (mt_inside(o, d, v0, e1, e2, ts, adet))
+                                closest_update(best, ts, adet, __float_as_int(v0.w), s_cslot[j], L.params.t_min);
+                        }
+                    }
+                    else
+                        bvh_trace<false, STATS>(L.scene, o, d, L.params.t_min, best, occ, n_box, n_tri, hint_hit);
                     if (s == 0) first_hit = best;
                     if (best.id < 0)
                     {
@@ -799,6 +1017,35 @@ __global__ void __launch_bounds__(256) fp32_peak_kernel(float* out, float a, flo
 // ---------------------------------------------------------------------------
 // host launchers
 // ---------------------------------------------------------------------------
+// The grid serves the sample-parallel kernel with one pixel per warp pass (spp >= 32).
+static int SppPixelsPerWarp(srt_render_params const& p)
+{
+    static int const pix_env = [] {
+        char const* e = std::getenv("SRT_BVH_PIX");
+        return e ? std::atoi(e) : -1;
+    }();
+    int pix = pix_env >= 0 ? pix_env : (p.spp >= 32 ? 1 : p.spp >= 16 ? 2 : p.spp >= 8 ? 4 : 0);
+    if (pix != 0 && pix != 1 && pix != 2 && pix != 4 && pix != 8) pix = 0;
+    return pix;
+}
+
+bool RenderUsesGrid(srt_render_params const& p)
+{
+    return p.accel == SRT_ACCEL_BVH && SppPixelsPerWarp(p) == 1;
+}
+
+void BuildScreenGrid(GridBuild const& build, cudaStream_t stream)
+{
+    uint32_t const tiles = build.tiles_w * build.tiles_h;
+    ML_CUDA_CHECK(cudaMemsetAsync(build.tile_cnt, 0, static_cast<size_t>(tiles) * sizeof(uint32_t), stream));
+    ML_CUDA_CHECK(cudaMemsetAsync(build.flags, 0, sizeof(GridFlags), stream));
+    uint32_t const blocks = (build.scene.n_tris_padded + 255u) / 256u;
+    grid_count_kernel<<<blocks, 256, 0, stream>>>(build);
+    grid_scan_kernel<<<1, 1024, 0, stream>>>(build);
+    grid_fill_kernel<<<blocks, 256, 0, stream>>>(build);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
 void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
 {
     srt_render_params const& p = launch.params;
@@ -814,12 +1061,7 @@ void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
         }();
         // Sample-parallel kernel when there are enough samples per pixel to fill the
         // lanes; SRT_BVH_PIX=1|2|4|8 pixels per warp pass (0 = pixel-per-thread kernel).
-        static int const pix_env = [] {
-            char const* e = std::getenv("SRT_BVH_PIX");
-            return e ? std::atoi(e) : -1;
-        }();
-        int pix = pix_env >= 0 ? pix_env : (p.spp >= 32 ? 1 : p.spp >= 16 ? 2 : p.spp >= 8 ? 4 : 0);
-        if (pix != 0 && pix != 1 && pix != 2 && pix != 4 && pix != 8) pix = 0;
+        int const pix = SppPixelsPerWarp(p);
         if (pix != 0)
         {
             dim3 sgrid((p.width + kSppTileW - 1) / kSppTileW, launch.n_row_blocks);

@@ -140,6 +140,96 @@ Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const
         m_info.bounds_min[k] = n ? bmin[k] : 0.f;
         m_info.bounds_max[k] = n ? bmax[k] : 0.f;
     }
+    if (n > 0)
+    {
+        // same slack as the BVH boxes (bvh_build.cpp): 2^-18 of the scene extent
+        float dx = bmax[0] - bmin[0], dy = bmax[1] - bmin[1], dz = bmax[2] - bmin[2];
+        float diag = std::sqrt(dx * dx + dy * dy + dz * dz), mag = 0.f;
+        for (int k = 0; k < 3; k++) mag = std::max(mag, std::max(std::fabs(bmin[k]), std::fabs(bmax[k])));
+        m_pad = std::max(diag, mag) * (1.0f / 262144.0f) + FLT_MIN;
+    }
+}
+
+void Scene::FreeGrid()
+{
+    cudaFree(m_d_grid_tiles); cudaFree(m_d_grid_items); cudaFree(m_d_grid_bbox); cudaFree(m_d_grid_misc);
+    m_d_grid_tiles = m_d_grid_items = m_d_grid_bbox = m_d_grid_misc = nullptr;
+    m_grid_tiles = m_grid_cap = 0;
+    m_grid = GridView{};
+}
+
+// Primary-ray grid for this call's camera and frame, built on `stream` (scene.h, GridView).  Leaves
+// m_grid.enabled = 0 when the render will not use it (kernel choice, SRT_GRID=0, singular camera basis).
+void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* params, cudaStream_t stream)
+{
+    m_grid.enabled = 0;
+    static int const want = std::getenv("SRT_GRID") ? std::atoi(std::getenv("SRT_GRID")) : 1;
+    if (!want || params->accel != SRT_ACCEL_BVH || !RenderUsesGrid(*params) || m_view.n_tris == 0) return;
+    if (params->y0 % kGridTile != 0) return;     // tiles are the render kernels' 8-row blocks
+
+    // inverse of the camera basis [right up forward] in double: P - o = cx*right + cy*up + cz*forward
+    double const a[3][3] = {{camera->right[0], camera->up[0], camera->forward[0]},
+                            {camera->right[1], camera->up[1], camera->forward[1]},
+                            {camera->right[2], camera->up[2], camera->forward[2]}};
+    double const det = a[0][0] * (a[1][1] * a[2][2] - a[1][2] * a[2][1])
+                     - a[0][1] * (a[1][0] * a[2][2] - a[1][2] * a[2][0])
+                     + a[0][2] * (a[1][0] * a[2][1] - a[1][1] * a[2][0]);
+    double scale = 0;
+    for (auto const& r : a) for (double v : r) scale = std::max(scale, std::fabs(v));
+    if (!(std::fabs(det) > 1e-6 * scale * scale * scale) || !(camera->half_w > 0.f) || !(camera->half_h > 0.f)) return;
+    GridBuild b{};
+    double inv[3][3];
+    inv[0][0] = (a[1][1] * a[2][2] - a[1][2] * a[2][1]) / det;
+    inv[0][1] = (a[0][2] * a[2][1] - a[0][1] * a[2][2]) / det;
+    inv[0][2] = (a[0][1] * a[1][2] - a[0][2] * a[1][1]) / det;
+    inv[1][0] = (a[1][2] * a[2][0] - a[1][0] * a[2][2]) / det;
+    inv[1][1] = (a[0][0] * a[2][2] - a[0][2] * a[2][0]) / det;
+    inv[1][2] = (a[0][2] * a[1][0] - a[0][0] * a[1][2]) / det;
+    inv[2][0] = (a[1][0] * a[2][1] - a[1][1] * a[2][0]) / det;
+    inv[2][1] = (a[0][1] * a[2][0] - a[0][0] * a[2][1]) / det;
+    inv[2][2] = (a[0][0] * a[1][1] - a[0][1] * a[1][0]) / det;
+    for (int r = 0; r < 3; r++)
+        for (int c = 0; c < 3; c++)
+        {
+            if (!std::isfinite(inv[r][c])) return;
+            b.minv[3 * r + c] = static_cast<float>(inv[r][c]);
+        }
+
+    uint32_t const tw = (params->width + kGridTile - 1) / kGridTile, th = (params->height + kGridTile - 1) / kGridTile;
+    uint32_t const tiles = tw * th;
+    uint32_t const cap = std::max<uint32_t>(16u * m_view.n_tris, 1u << 20);
+    if (tiles > m_grid_tiles || cap > m_grid_cap || m_d_grid_bbox == nullptr)
+    {
+        ML_CUDA_CHECK(cudaStreamSynchronize(stream));
+        if (m_grid_free) ML_CUDA_CHECK(cudaEventSynchronize(m_grid_free));
+        FreeGrid();
+        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_tiles, (3 * static_cast<size_t>(tiles) + 4) * sizeof(uint32_t)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_bbox, static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));
+        m_grid_tiles = tiles;
+        m_grid_cap = cap;
+    }
+    if (m_grid_free == nullptr) ML_CUDA_CHECK(cudaEventCreateWithFlags(&m_grid_free, cudaEventDisableTiming));
+    // a render that still reads the previous grid (possibly on another stream) must finish first
+    ML_CUDA_CHECK(cudaStreamWaitEvent(stream, m_grid_free, 0));
+
+    uint32_t* t = static_cast<uint32_t*>(m_d_grid_tiles);
+    b.scene = m_view;
+    for (int k = 0; k < 3; k++) b.origin[k] = camera->origin[k];
+    b.half_w = camera->half_w; b.half_h = camera->half_h;
+    b.pad = 4.0f * m_pad;
+    b.width = params->width; b.height = params->height; b.tiles_w = tw; b.tiles_h = th; b.cap = cap;
+    b.tile_cnt = t; b.tile_off = t + tiles; b.cursor = t + 2 * static_cast<size_t>(tiles) + 1;
+    b.items = static_cast<uint32_t*>(m_d_grid_items);
+    b.bbox = static_cast<F4*>(m_d_grid_bbox);
+    b.flags = static_cast<GridFlags*>(m_d_grid_misc);
+    b.global = reinterpret_cast<uint32_t*>(b.flags + 1);
+    BuildScreenGrid(b, stream);
+
+    m_grid.tile_off = b.tile_off; m_grid.items = b.items; m_grid.bbox = b.bbox; m_grid.global = b.global;
+    m_grid.flags = b.flags; m_grid.tiles_w = tw; m_grid.tiles_h = th;
+    m_grid.enabled = 1;
 }
 
 void Scene::FreeStaging()
@@ -155,6 +245,8 @@ Scene::~Scene()
     cudaSetDevice(m_device->device);
     cudaStreamSynchronize(m_device->stream);
     FreeStaging();
+    FreeGrid();
+    if (m_grid_free) cudaEventDestroy(m_grid_free);
     for (cudaEvent_t e : m_chunk_events) cudaEventDestroy(e);
     cudaFree(m_d_tris); cudaFree(m_d_albedo); cudaFree(m_d_nodes); cudaFree(m_d_counters);
 }
@@ -209,7 +301,9 @@ ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
         if (stream == nullptr) stream = m_device->stream;
         ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), stream));
         if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, stream));
+        PrepareGrid(camera, params, stream);       // inside the timed region: it is per-frame work
         EnqueueBand(camera, light, params, d_rgb, d_hit_id, d_hit_t, stream);
+        if (m_grid.enabled) ML_CUDA_CHECK(cudaEventRecord(m_grid_free, stream));
         if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, stream));
         ML_CUDA_CHECK(cudaGetLastError());
         m_timed_pending = timed;
@@ -243,6 +337,8 @@ void Scene::EnqueueBand(srt_camera const* camera, srt_light const* light, srt_re
         RowBlocks(*params, launch.row_origin, launch.row_block_step, launch.n_row_blocks);
         static int const hints = std::getenv("SRT_BVH_HINTS") ? std::atoi(std::getenv("SRT_BVH_HINTS")) : 1;
         launch.hints = static_cast<uint32_t>(hints);
+        launch.grid = m_grid;
+        if (launch.row_origin % kGridTile != 0) launch.grid.enabled = 0;
         if (launch.n_row_blocks > 0)
             LaunchRender(launch, m_device->prop.multiProcessorCount, stream);
     }
@@ -339,6 +435,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         cudaEvent_t const ev_begin = m_chunk_events[2 * n_chunks], ev_s1_done = m_chunk_events[2 * n_chunks + 1];
         ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), s0));
         ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s0));
+        PrepareGrid(camera, params, s0);
         ML_CUDA_CHECK(cudaEventRecord(ev_begin, s0));
         ML_CUDA_CHECK(cudaStreamWaitEvent(s1, ev_begin, 0));
         for (size_t k = 0; k < n_chunks; k++)
@@ -397,6 +494,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         }
         ML_CUDA_CHECK(cudaEventRecord(ev_s1_done, s1));
         ML_CUDA_CHECK(cudaStreamWaitEvent(s0, ev_s1_done, 0));
+        if (m_grid.enabled) ML_CUDA_CHECK(cudaEventRecord(m_grid_free, s0));
         ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, s0));
         ML_CUDA_CHECK(cudaGetLastError());
         m_timed_pending = true;

@@ -57,6 +57,29 @@ struct DeviceSceneView
     uint32_t n_tris_padded; // multiple of kTriTile
 };
 
+// Screen-space candidate grid for primary rays (BUILD-DEFINED, docs/RENDER_SPEC.md section 7): per
+// 8x8-pixel tile the triangles whose conservatively dilated screen bounding box touches the tile.
+// All primary rays leave one point, so a ray through pixel (x, y) can only hit triangles whose
+// projection covers that pixel: the closest hit over the tile's (pixel-filtered) list equals the
+// closest hit over the whole scene, and the lexicographic (t, id) rule makes the test order
+// irrelevant.  Rebuilt on the device for every render call (three small kernels); a frame the grid
+// cannot serve (flags.ok == 0) and tiles with long lists fall back to the BVH.
+constexpr uint32_t kGridTile = 8;        // pixels; equals the render kernels' 8-row blocks
+constexpr uint32_t kGridMaxList = 64;    // longer tile lists: that tile walks the BVH instead
+constexpr uint32_t kGridMaxGlobal = 32;  // triangles that cannot be projected safely (near or crossing the
+                                         // camera plane, or huge on screen): tested by every ray
+struct GridFlags { uint32_t ok; uint32_t n_global; uint32_t total; uint32_t pad; };
+struct GridView
+{
+    uint32_t const* tile_off;   // [tiles + 1] exclusive prefix of the list lengths
+    uint32_t const* items;      // triangle slots, tile after tile
+    F4 const* bbox;             // per slot: dilated screen box (x0, y0, x1, y1) in pixels; x0 > x1: not binned
+    uint32_t const* global;     // [kGridMaxGlobal]
+    GridFlags const* flags;
+    uint32_t tiles_w, tiles_h;
+    uint32_t enabled;           // host decision for this launch
+};
+
 class Scene
 {
 public:
@@ -94,6 +117,9 @@ private:
                      void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream);
     void EnsureStaging(size_t pixels);
     void FreeStaging();
+    // Builds the primary-ray grid for this camera / frame on `stream` (if the render will use it).
+    void PrepareGrid(srt_camera const* camera, srt_render_params const* params, cudaStream_t stream);
+    void FreeGrid();
 
     DeviceStatePtr m_device;
     srt_scene_info m_info{};
@@ -108,6 +134,16 @@ private:
     void* m_d_rgb = nullptr; void* m_d_id = nullptr; void* m_d_t = nullptr;
     void* m_h_rgb = nullptr; void* m_h_id = nullptr; void* m_h_t = nullptr;
     size_t m_stage_pixels = 0;
+    // primary-ray grid (device)
+    GridView m_grid{};
+    void* m_d_grid_tiles = nullptr;   // tile_cnt | tile_off | cursor
+    void* m_d_grid_items = nullptr;
+    void* m_d_grid_bbox = nullptr;
+    void* m_d_grid_misc = nullptr;    // GridFlags | global list
+    uint32_t m_grid_tiles = 0;
+    uint32_t m_grid_cap = 0;
+    float m_pad = 0.f;                // world-space slack of the culling structures (as the BVH boxes)
+    cudaEvent_t m_grid_free = nullptr; // the last render that read the grid has finished
     std::vector<cudaEvent_t> m_chunk_events; // RenderHost pipeline
     cudaStream_t m_timed_stream = nullptr;
     bool m_timed_pending = false;
@@ -139,8 +175,23 @@ struct RenderLaunch
     uint32_t row_block_step;
     uint32_t n_row_blocks;
     uint32_t hints;  // 1: rays first test the triangle the lane's previous ray ended on (SRT_BVH_HINTS=0 disables)
+    GridView grid;
 };
 void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream);
+// True when LaunchRender would pick a kernel that reads the primary-ray grid for these parameters.
+bool RenderUsesGrid(srt_render_params const& params);
+struct GridBuild
+{
+    DeviceSceneView scene;
+    float origin[3];
+    float minv[9];          // rows of the inverse of [right up forward]: c = minv * (P - origin)
+    float half_w, half_h;
+    float pad;              // world-space slack
+    uint32_t width, height, tiles_w, tiles_h, cap;
+    uint32_t* tile_cnt; uint32_t* tile_off; uint32_t* cursor; uint32_t* items;
+    F4* bbox; uint32_t* global; GridFlags* flags;
+};
+void BuildScreenGrid(GridBuild const& build, cudaStream_t stream);
 double MeasureFp32Peak(DeviceState const& device, int repeats);
 
 } // namespace ML

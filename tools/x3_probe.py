@@ -1,11 +1,17 @@
-# quick probe: bf16x3 correctness + timing per op
+"""Per-op times and error of the three inference precisions (fp32 CUDA cores, bf16x3, bf16) on a few
+networks.  `python tools/x3_probe.py big` runs only the 1080p benchmark net (use with MLB200_TC_PROF=1
+for the per-role cycle counters of the tensor-core kernels)."""
 import sys, tempfile, numpy as np
 from pathlib import Path
-sys.path.insert(0, "/root/repo"); sys.path.insert(0, "/root/repo/tests")
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT)); sys.path.insert(0, str(ROOT / "tests"))
 import oracle_lib as O
 from simpleraytracer_b200 import api, graphdef_writer as gw
 ctx = api.Context()
-for (W, H, width, depth) in ((300, 37, 64, 4), (131, 5, 16, 3), (1920, 1080, 64, 6)):
+CASES = ((300, 37, 64, 4), (131, 5, 16, 3), (1920, 1080, 64, 6))
+if len(sys.argv) > 1 and sys.argv[1] == "big":
+    CASES = CASES[2:]
+for (W, H, width, depth) in CASES:
     with tempfile.TemporaryDirectory() as d:
         path = Path(d) / "net.pb"
         _, layers = gw.make_denoiser(path, channels=3, width=width, depth=depth, seed=0)
