@@ -508,7 +508,8 @@ __device__ __forceinline__ bool grid_project(GridBuild const& G, uint32_t i, flo
         ty0 = fminf(ty0, ty); ty1 = fmaxf(ty1, ty);
         tmax = fmaxf(tmax, fmaxf(fabsf(tx), fabsf(ty)));
     }
-    float const slack_t = 2.0f * slack_w * (1.0f + tmax) / zmin;   // d(c/z) <= dc/z + |c| dz / z^2
+    // d(c/z) <= dc/z + |c| dz / z^2, doubled: the query point of the light grid is projected in fp32 too
+    float const slack_t = 4.0f * slack_w * (1.0f + tmax) / zmin;
     float const kx = 0.5f * static_cast<float>(G.width) / G.half_w, ky = 0.5f * static_cast<float>(G.height) / G.half_h;
     float const cxp = 0.5f * static_cast<float>(G.width), cyp = 0.5f * static_cast<float>(G.height);
     // pixel x = (sx / half_w + 1) * W/2 ; pixel y = (1 - sy / half_h) * H/2
@@ -522,9 +523,9 @@ __device__ __forceinline__ bool grid_project(GridBuild const& G, uint32_t i, flo
 // tiles a box touches; false when it lies off the frame
 __device__ __forceinline__ bool grid_tile_range(GridBuild const& G, float4 box, int& tx0, int& tx1, int& ty0, int& ty1)
 {
-    float const inv = 1.0f / static_cast<float>(kGridTile);
-    float const fx0 = floorf((box.x - 1.0f) * inv), fx1 = floorf(box.z * inv);
-    float const fy0 = floorf((box.y - 1.0f) * inv), fy1 = floorf(box.w * inv);
+    float const inv = 1.0f / static_cast<float>(G.tile);
+    float const fx0 = floorf((box.x - G.lo_bias) * inv), fx1 = floorf(box.z * inv);
+    float const fy0 = floorf((box.y - G.lo_bias) * inv), fy1 = floorf(box.w * inv);
     if (fx1 < 0.f || fy1 < 0.f || fx0 >= static_cast<float>(G.tiles_w) || fy0 >= static_cast<float>(G.tiles_h)) return false;
     tx0 = static_cast<int>(fmaxf(fx0, 0.f)); tx1 = static_cast<int>(fminf(fx1, static_cast<float>(G.tiles_w - 1)));
     ty0 = static_cast<int>(fmaxf(fy0, 0.f)); ty1 = static_cast<int>(fminf(fy1, static_cast<float>(G.tiles_h - 1)));
@@ -562,38 +563,100 @@ __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__
     reinterpret_cast<float4*>(G.bbox)[i] = box;
 }
 
-// one block: exclusive prefix sum of the tile counts, cursors reset, verdict
-__global__ void __launch_bounds__(1024) grid_scan_kernel(const __grid_constant__ GridBuild G)
+// Exclusive prefix sum of the tile counts in three small launches (the light grid has ~10^6 cells):
+// per-block sums of 4096 cells, one block scanning those sums (+ the verdict), per-block scans.
+constexpr uint32_t kScanBlock = 1024, kScanPerThread = 4, kScanCells = kScanBlock * kScanPerThread;
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s_warp, uint32_t& block_total)
 {
-    __shared__ uint32_t s_part[1024];
-    uint32_t const tiles = G.tiles_w * G.tiles_h;
-    uint32_t const per = (tiles + 1023u) / 1024u;
-    uint32_t const b = threadIdx.x * per, e = min(tiles, b + per);
-    uint32_t sum = 0;
-    for (uint32_t t = b; t < e; t++) sum += G.tile_cnt[t];
-    s_part[threadIdx.x] = sum;
-    __syncthreads();
-    for (uint32_t off = 1; off < 1024u; off <<= 1)
+    uint32_t const lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    uint32_t inc = v;
+#pragma unroll
+    for (uint32_t off = 1; off < 32u; off <<= 1)
     {
-        uint32_t const v = threadIdx.x >= off ? s_part[threadIdx.x - off] : 0u;
-        __syncthreads();
-        s_part[threadIdx.x] += v;
-        __syncthreads();
+        uint32_t const n = __shfl_up_sync(0xffffffffu, inc, off);
+        if (lane >= off) inc += n;
     }
-    uint32_t run = s_part[threadIdx.x] - sum;
+    if (lane == 31u) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0)
+    {
+        uint32_t w = lane < (blockDim.x >> 5) ? s_warp[lane] : 0u;
+        uint32_t winc = w;
+#pragma unroll
+        for (uint32_t off = 1; off < 32u; off <<= 1)
+        {
+            uint32_t const n = __shfl_up_sync(0xffffffffu, winc, off);
+            if (lane >= off) winc += n;
+        }
+        s_warp[lane] = winc - w;           // exclusive offset of each warp
+        if (lane == 31u) s_warp[32] = winc; // block total
+    }
+    __syncthreads();
+    block_total = s_warp[32];
+    return s_warp[warp] + inc - v;
+}
+
+__global__ void __launch_bounds__(kScanBlock) grid_block_sums_kernel(const __grid_constant__ GridBuild G)
+{
+    __shared__ uint32_t s_warp[33];
+    uint32_t const tiles = G.tiles_w * G.tiles_h;
+    uint32_t const base = blockIdx.x * kScanCells + threadIdx.x * kScanPerThread;
+    uint32_t sum = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < kScanPerThread; k++)
+        if (base + k < tiles) sum += G.tile_cnt[base + k];
+    uint32_t total;
+    block_exclusive_scan(sum, s_warp, total);
+    if (threadIdx.x == 0) G.block_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(kScanBlock) grid_scan_sums_kernel(const __grid_constant__ GridBuild G, uint32_t n_blocks)
+{
+    __shared__ uint32_t s_warp[33];
+    uint32_t const per = (n_blocks + kScanBlock - 1u) / kScanBlock;
+    uint32_t const b = threadIdx.x * per, e = min(n_blocks, b + per);
+    uint32_t sum = 0;
+    for (uint32_t t = b; t < e; t++) sum += G.block_sums[t];
+    uint32_t total;
+    uint32_t run = block_exclusive_scan(sum, s_warp, total);
     for (uint32_t t = b; t < e; t++)
     {
-        G.tile_off[t] = run;
-        run += G.tile_cnt[t];
-        G.cursor[t] = 0;
+        uint32_t const v = G.block_sums[t];
+        G.block_sums[t] = run;
+        run += v;
     }
-    if (threadIdx.x == 1023)
+    if (threadIdx.x == 0)
     {
-        uint32_t const total = s_part[1023];
-        G.tile_off[tiles] = total;
+        G.tile_off[G.tiles_w * G.tiles_h] = total;
         G.flags->total = total;
         G.flags->ok = (total <= G.cap && G.flags->n_global <= kGridMaxGlobal) ? 1u : 0u;
     }
+}
+
+__global__ void __launch_bounds__(kScanBlock) grid_scan_blocks_kernel(const __grid_constant__ GridBuild G)
+{
+    __shared__ uint32_t s_warp[33];
+    uint32_t const tiles = G.tiles_w * G.tiles_h;
+    uint32_t const base = blockIdx.x * kScanCells + threadIdx.x * kScanPerThread;
+    uint32_t c[kScanPerThread];
+    uint32_t sum = 0;
+#pragma unroll
+    for (uint32_t k = 0; k < kScanPerThread; k++)
+    {
+        c[k] = base + k < tiles ? G.tile_cnt[base + k] : 0u;
+        sum += c[k];
+    }
+    uint32_t total;
+    uint32_t run = G.block_sums[blockIdx.x] + block_exclusive_scan(sum, s_warp, total);
+#pragma unroll
+    for (uint32_t k = 0; k < kScanPerThread; k++)
+        if (base + k < tiles)
+        {
+            G.tile_off[base + k] = run;
+            G.cursor[base + k] = 0;
+            run += c[k];
+        }
 }
 
 __global__ void __launch_bounds__(256) grid_fill_kernel(const __grid_constant__ GridBuild G)
@@ -772,6 +835,58 @@ __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d,
     }
 }
 
+// Shadow query through the light grid (scene.h LightGridView).  Returns false when the grid cannot
+// answer (shading point behind the light's projection plane, non-finite projection): the caller walks
+// the BVH.  The occluder set is exact: a point of a binned triangle between S and the light projects
+// to S's own cell (boxes dilated for every rounding involved), triangles that could not be binned are
+// in the global list, triangles wholly behind the plane cannot lie between a point in front and the light.
+template <bool STATS>
+__device__ __forceinline__ bool lgrid_shadow(RenderLaunch const& L, V3 so, V3 sd, bool& occluded, uint32_t& hint,
+                                             uint32_t n_global, unsigned long long& n_tri)
+{
+    LightGridView const& G = L.lgrid;
+    float const px = so.x - L.light.position[0], py = so.y - L.light.position[1], pz = so.z - L.light.position[2];
+    float const cz = G.minv[6] * px + G.minv[7] * py + G.minv[8] * pz;
+    if (!(cz > 0.0f)) return false;
+    float const iz = 1.0f / cz;
+    float const gx = G.cx + (G.minv[0] * px + G.minv[1] * py + G.minv[2] * pz) * iz * G.kx;
+    float const gy = G.cy - (G.minv[3] * px + G.minv[4] * py + G.minv[5] * pz) * iz * G.ky;
+    if (!(fabsf(gx) < 1e9f) || !(fabsf(gy) < 1e9f)) return false;
+    int const ix = min(max(static_cast<int>(floorf(gx)), 0), static_cast<int>(G.grid.tiles_w) - 1);
+    int const iy = min(max(static_cast<int>(floorf(gy)), 0), static_cast<int>(G.grid.tiles_h) - 1);
+    uint32_t const cell = static_cast<uint32_t>(iy) * G.grid.tiles_w + static_cast<uint32_t>(ix);
+    float4 const* __restrict__ tv0 = reinterpret_cast<float4 const*>(L.scene.tri_v0);
+    float4 const* __restrict__ te1 = reinterpret_cast<float4 const*>(L.scene.tri_e1);
+    float4 const* __restrict__ te2 = reinterpret_cast<float4 const*>(L.scene.tri_e2);
+    auto test = [&](uint32_t slot) -> bool {
+        float4 const v0 = __ldg(tv0 + slot), e1 = __ldg(te1 + slot), e2 = __ldg(te2 + slot);
+        float ts, adet;
+        if (mt_inside(so, sd, v0, e1, e2, ts, adet))
+        {
+            float const t = __fdiv_rn(ts, adet);
+            if (t > 0.0f && t < 1.0f) { occluded = true; hint = slot; return true; }
+        }
+        return false;
+    };
+    if (hint != kNoHint)
+    {
+        if (STATS) n_tri++;
+        if (test(hint)) return true;
+    }
+    for (uint32_t k = 0; k < n_global; k++)
+    {
+        if (STATS) n_tri++;
+        if (test(__ldg(G.grid.global + k))) return true;
+    }
+    uint32_t const b = __ldg(G.grid.tile_off + cell), e = __ldg(G.grid.tile_off + cell + 1);
+    for (uint32_t k = b; k < e; k++)
+    {
+        if (STATS) n_tri++;
+        if (test(__ldg(G.grid.items + k))) return true;
+    }
+    return true;
+}
+
 // MINB = minimum resident blocks per SM the register allocation must allow.
 template <bool STATS, int MINB>
 __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __grid_constant__ RenderLaunch L)
@@ -887,6 +1002,14 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
     // neighbouring) pixel almost always ends on it too
     uint32_t hint_hit = kNoHint, hint_occ = kNoHint;
     bool const use_hints = L.hints != 0;
+    bool lgrid_ok = false;
+    uint32_t lgrid_global = 0;
+    if (L.lgrid.grid.enabled)
+    {
+        GridFlags const lf = *L.lgrid.grid.flags;
+        lgrid_ok = lf.ok != 0;
+        lgrid_global = lf.n_global;
+    }
     if (y < L.params.y1) // warp-uniform
     {
         for (uint32_t g = 0; g < kSppTileW / PIX; g++)
@@ -951,7 +1074,9 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                         {
                             n_shadow++;
                             Hit dummy = no_hit();
-                            bvh_trace<true, STATS>(L.scene, sh.so, sh.sd, 0.0f, dummy, occ, n_box, n_tri, hint_occ);
+                            dummy.slot = hint_occ;       // in: the last occluder (tested first), out: this ray's occluder
+                            if (!(lgrid_ok && lgrid_shadow<STATS>(L, sh.so, sh.sd, occ, dummy.slot, lgrid_global, n_tri)))
+                                bvh_trace<true, STATS>(L.scene, sh.so, sh.sd, 0.0f, dummy, occ, n_box, n_tri, hint_occ);
                             if (occ)
                             {
                                 rgb = V3{0.f, 0.f, 0.f};
@@ -1040,8 +1165,11 @@ void BuildScreenGrid(GridBuild const& build, cudaStream_t stream)
     ML_CUDA_CHECK(cudaMemsetAsync(build.tile_cnt, 0, static_cast<size_t>(tiles) * sizeof(uint32_t), stream));
     ML_CUDA_CHECK(cudaMemsetAsync(build.flags, 0, sizeof(GridFlags), stream));
     uint32_t const blocks = (build.scene.n_tris_padded + 255u) / 256u;
+    uint32_t const scan_blocks = (tiles + kScanCells - 1u) / kScanCells;
     grid_count_kernel<<<blocks, 256, 0, stream>>>(build);
-    grid_scan_kernel<<<1, 1024, 0, stream>>>(build);
+    grid_block_sums_kernel<<<scan_blocks, kScanBlock, 0, stream>>>(build);
+    grid_scan_sums_kernel<<<1, kScanBlock, 0, stream>>>(build, scan_blocks);
+    grid_scan_blocks_kernel<<<scan_blocks, kScanBlock, 0, stream>>>(build);
     grid_fill_kernel<<<blocks, 256, 0, stream>>>(build);
     ML_CUDA_CHECK(cudaGetLastError());
 }
@@ -1073,7 +1201,7 @@ void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
     } while (0)
             static int const spp_minb = [] {
                 char const* e = std::getenv("SRT_SPP_MINB");
-                return e ? std::atoi(e) : 5; // 48 registers, 5 blocks per SM: +1.5 % over 4 (measured)
+                return e ? std::atoi(e) : 4; // 64 registers, 4 blocks per SM: with the grid paths 48 registers spill (+2.7 %, measured)
             }();
             if (pix == 1 && !st && spp_minb == 5) render_bvh_spp_kernel<false, 1, 5><<<sgrid, 256, 0, stream>>>(launch);
             else if (pix == 1 && !st && spp_minb == 6) render_bvh_spp_kernel<false, 1, 6><<<sgrid, 256, 0, stream>>>(launch);

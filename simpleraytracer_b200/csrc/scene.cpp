@@ -156,6 +156,107 @@ void Scene::FreeGrid()
     m_d_grid_tiles = m_d_grid_items = m_d_grid_bbox = m_d_grid_misc = nullptr;
     m_grid_tiles = m_grid_cap = 0;
     m_grid = GridView{};
+    cudaFree(m_d_lgrid_tiles); cudaFree(m_d_lgrid_items); cudaFree(m_d_lgrid_bbox); cudaFree(m_d_lgrid_misc);
+    m_d_lgrid_tiles = m_d_lgrid_items = m_d_lgrid_bbox = m_d_lgrid_misc = nullptr;
+    m_lgrid_tiles = m_lgrid_cap = 0;
+    m_lgrid = LightGridView{};
+}
+
+// Shadow-ray grid for this call's light (scene.h, LightGridView), built on `stream`.  Used when the
+// whole scene lies in front of a projection plane through the light (a light above, beside or outside
+// the geometry); otherwise m_lgrid.grid.enabled stays 0 and shadow rays walk the BVH.
+void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* params, cudaStream_t stream)
+{
+    m_lgrid.grid.enabled = 0;
+    static int const want = std::getenv("SRT_LIGHT_GRID") ? std::atoi(std::getenv("SRT_LIGHT_GRID")) : 1;
+    if (!want || params->accel != SRT_ACCEL_BVH || params->shade != SRT_SHADE_SHADOW || !RenderUsesGrid(*params)
+        || m_view.n_tris == 0)
+        return;
+    double const lo[3] = {m_info.bounds_min[0], m_info.bounds_min[1], m_info.bounds_min[2]};
+    double const hi[3] = {m_info.bounds_max[0], m_info.bounds_max[1], m_info.bounds_max[2]};
+    double const lp[3] = {light->position[0], light->position[1], light->position[2]};
+    double f[3] = {0.5 * (lo[0] + hi[0]) - lp[0], 0.5 * (lo[1] + hi[1]) - lp[1], 0.5 * (lo[2] + hi[2]) - lp[2]};
+    double const fl = std::sqrt(f[0] * f[0] + f[1] * f[1] + f[2] * f[2]);
+    double const diag = std::sqrt((hi[0] - lo[0]) * (hi[0] - lo[0]) + (hi[1] - lo[1]) * (hi[1] - lo[1])
+                                  + (hi[2] - lo[2]) * (hi[2] - lo[2]));
+    if (!(fl > 1e-6 * (diag + 1e-30)) || !std::isfinite(fl)) return;
+    for (double& v : f) v /= fl;
+    // any unit vector not parallel to f
+    int const k = std::fabs(f[0]) <= std::fabs(f[1]) && std::fabs(f[0]) <= std::fabs(f[2]) ? 0
+                : std::fabs(f[1]) <= std::fabs(f[2]) ? 1 : 2;
+    double a[3] = {0, 0, 0};
+    a[k] = 1.0;
+    double r[3] = {a[1] * f[2] - a[2] * f[1], a[2] * f[0] - a[0] * f[2], a[0] * f[1] - a[1] * f[0]};
+    double const rl = std::sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2]);
+    for (double& v : r) v /= rl;
+    double const u[3] = {f[1] * r[2] - f[2] * r[1], f[2] * r[0] - f[0] * r[2], f[0] * r[1] - f[1] * r[0]};
+    // the 8 corners of the scene box must all lie well in front of the plane; their projections bound the grid
+    double tmax_x = 0, tmax_y = 0;
+    for (int c = 0; c < 8; c++)
+    {
+        double const p[3] = {((c & 1) ? hi[0] : lo[0]) - lp[0], ((c & 2) ? hi[1] : lo[1]) - lp[1],
+                             ((c & 4) ? hi[2] : lo[2]) - lp[2]};
+        double const cz = p[0] * f[0] + p[1] * f[1] + p[2] * f[2];
+        if (!(cz > 1e-2 * (diag + fl))) return;
+        tmax_x = std::max(tmax_x, std::fabs((p[0] * r[0] + p[1] * r[1] + p[2] * r[2]) / cz));
+        tmax_y = std::max(tmax_y, std::fabs((p[0] * u[0] + p[1] * u[1] + p[2] * u[2]) / cz));
+    }
+    if (!(tmax_x > 0) || !(tmax_y > 0) || tmax_x > 50 || tmax_y > 50) return;
+    double const half_w = tmax_x * 1.001 + 1e-6, half_h = tmax_y * 1.001 + 1e-6;
+    // about 8 cells per triangle, split by the aspect of the projected scene
+    double const g = std::min(2048.0, std::max(256.0, std::sqrt(8.0 * static_cast<double>(m_view.n_tris))));
+    uint32_t const gw = static_cast<uint32_t>(std::min(4096.0, std::max(64.0, g * std::sqrt(half_w / half_h))));
+    uint32_t const gh = static_cast<uint32_t>(std::min(4096.0, std::max(64.0, g * std::sqrt(half_h / half_w))));
+    uint32_t const tiles = gw * gh;
+    uint32_t const cap = std::max<uint32_t>(24u * m_view.n_tris, 1u << 20);
+    if (tiles > m_lgrid_tiles || cap > m_lgrid_cap || m_d_lgrid_bbox == nullptr)
+    {
+        ML_CUDA_CHECK(cudaStreamSynchronize(stream));
+        if (m_grid_free) ML_CUDA_CHECK(cudaEventSynchronize(m_grid_free));
+        cudaFree(m_d_lgrid_tiles); cudaFree(m_d_lgrid_items); cudaFree(m_d_lgrid_bbox); cudaFree(m_d_lgrid_misc);
+        m_d_lgrid_tiles = m_d_lgrid_items = m_d_lgrid_bbox = m_d_lgrid_misc = nullptr;
+        m_lgrid_tiles = m_lgrid_cap = 0;
+        ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_bbox, static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));
+        m_lgrid_tiles = tiles;
+        m_lgrid_cap = cap;
+    }
+    if (m_grid_free == nullptr) ML_CUDA_CHECK(cudaEventCreateWithFlags(&m_grid_free, cudaEventDisableTiming));
+    ML_CUDA_CHECK(cudaStreamWaitEvent(stream, m_grid_free, 0));
+
+    GridBuild b{};
+    uint32_t* t = static_cast<uint32_t*>(m_d_lgrid_tiles);
+    b.scene = m_view;
+    for (int i = 0; i < 3; i++)
+    {
+        b.origin[i] = light->position[i];
+        b.minv[i] = static_cast<float>(r[i]);          // orthonormal basis: the inverse is the transpose
+        b.minv[3 + i] = static_cast<float>(u[i]);
+        b.minv[6 + i] = static_cast<float>(f[i]);
+    }
+    b.half_w = static_cast<float>(half_w); b.half_h = static_cast<float>(half_h);
+    b.pad = 4.0f * m_pad;
+    b.width = gw; b.height = gh; b.tiles_w = gw; b.tiles_h = gh; b.cap = cap;
+    b.tile = 1; b.lo_bias = 0.f;
+    b.tile_cnt = t; b.tile_off = t + tiles; b.cursor = t + 2 * static_cast<size_t>(tiles) + 1;
+    b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;
+    b.items = static_cast<uint32_t*>(m_d_lgrid_items);
+    b.bbox = static_cast<F4*>(m_d_lgrid_bbox);
+    b.flags = static_cast<GridFlags*>(m_d_lgrid_misc);
+    b.global = reinterpret_cast<uint32_t*>(b.flags + 1);
+    BuildScreenGrid(b, stream);
+
+    GridView& gv = m_lgrid.grid;
+    gv.tile_off = b.tile_off; gv.items = b.items; gv.bbox = b.bbox; gv.global = b.global; gv.flags = b.flags;
+    gv.tiles_w = gw; gv.tiles_h = gh;
+    for (int i = 0; i < 9; i++) m_lgrid.minv[i] = b.minv[i];
+    m_lgrid.kx = 0.5f * static_cast<float>(gw) / b.half_w;
+    m_lgrid.ky = 0.5f * static_cast<float>(gh) / b.half_h;
+    m_lgrid.cx = 0.5f * static_cast<float>(gw);
+    m_lgrid.cy = 0.5f * static_cast<float>(gh);
+    gv.enabled = 1;
 }
 
 // Primary-ray grid for this call's camera and frame, built on `stream` (scene.h, GridView).  Leaves
@@ -203,7 +304,7 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
         ML_CUDA_CHECK(cudaStreamSynchronize(stream));
         if (m_grid_free) ML_CUDA_CHECK(cudaEventSynchronize(m_grid_free));
         FreeGrid();
-        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_tiles, (3 * static_cast<size_t>(tiles) + 4) * sizeof(uint32_t)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_bbox, static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));
@@ -220,7 +321,9 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
     b.half_w = camera->half_w; b.half_h = camera->half_h;
     b.pad = 4.0f * m_pad;
     b.width = params->width; b.height = params->height; b.tiles_w = tw; b.tiles_h = th; b.cap = cap;
+    b.tile = kGridTile; b.lo_bias = 1.f;
     b.tile_cnt = t; b.tile_off = t + tiles; b.cursor = t + 2 * static_cast<size_t>(tiles) + 1;
+    b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;
     b.items = static_cast<uint32_t*>(m_d_grid_items);
     b.bbox = static_cast<F4*>(m_d_grid_bbox);
     b.flags = static_cast<GridFlags*>(m_d_grid_misc);
@@ -302,8 +405,9 @@ ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
         ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), stream));
         if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, stream));
         PrepareGrid(camera, params, stream);       // inside the timed region: it is per-frame work
+        PrepareLightGrid(light, params, stream);
         EnqueueBand(camera, light, params, d_rgb, d_hit_id, d_hit_t, stream);
-        if (m_grid.enabled) ML_CUDA_CHECK(cudaEventRecord(m_grid_free, stream));
+        if (m_grid.enabled || m_lgrid.grid.enabled) ML_CUDA_CHECK(cudaEventRecord(m_grid_free, stream));
         if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, stream));
         ML_CUDA_CHECK(cudaGetLastError());
         m_timed_pending = timed;
@@ -339,6 +443,7 @@ void Scene::EnqueueBand(srt_camera const* camera, srt_light const* light, srt_re
         launch.hints = static_cast<uint32_t>(hints);
         launch.grid = m_grid;
         if (launch.row_origin % kGridTile != 0) launch.grid.enabled = 0;
+        launch.lgrid = m_lgrid;
         if (launch.n_row_blocks > 0)
             LaunchRender(launch, m_device->prop.multiProcessorCount, stream);
     }
@@ -436,6 +541,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), s0));
         ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s0));
         PrepareGrid(camera, params, s0);
+        PrepareLightGrid(light, params, s0);
         ML_CUDA_CHECK(cudaEventRecord(ev_begin, s0));
         ML_CUDA_CHECK(cudaStreamWaitEvent(s1, ev_begin, 0));
         for (size_t k = 0; k < n_chunks; k++)
@@ -494,7 +600,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         }
         ML_CUDA_CHECK(cudaEventRecord(ev_s1_done, s1));
         ML_CUDA_CHECK(cudaStreamWaitEvent(s0, ev_s1_done, 0));
-        if (m_grid.enabled) ML_CUDA_CHECK(cudaEventRecord(m_grid_free, s0));
+        if (m_grid.enabled || m_lgrid.grid.enabled) ML_CUDA_CHECK(cudaEventRecord(m_grid_free, s0));
         ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, s0));
         ML_CUDA_CHECK(cudaGetLastError());
         m_timed_pending = true;

@@ -80,6 +80,18 @@ struct GridView
     uint32_t enabled;           // host decision for this launch
 };
 
+// The same structure seen from the point light, for shadow rays: every shadow segment ends at the
+// light, so the segment from a shading point S projects to ONE point of a perspective grid centred
+// on the light, and only triangles whose (dilated) projection covers that cell can occlude it.
+// Cells are single grid units (tile = 1); a query is  c = minv * (S - light),  cell = (cx + kx*c.x/c.z,
+// cy - ky*c.y/c.z).  S behind the light's projection plane (c.z <= 0) walks the BVH instead.
+struct LightGridView
+{
+    GridView grid;
+    float minv[9];
+    float kx, ky, cx, cy;
+};
+
 class Scene
 {
 public:
@@ -119,6 +131,7 @@ private:
     void FreeStaging();
     // Builds the primary-ray grid for this camera / frame on `stream` (if the render will use it).
     void PrepareGrid(srt_camera const* camera, srt_render_params const* params, cudaStream_t stream);
+    void PrepareLightGrid(srt_light const* light, srt_render_params const* params, cudaStream_t stream);
     void FreeGrid();
 
     DeviceStatePtr m_device;
@@ -142,6 +155,14 @@ private:
     void* m_d_grid_misc = nullptr;    // GridFlags | global list
     uint32_t m_grid_tiles = 0;
     uint32_t m_grid_cap = 0;
+    // shadow-ray grid (device)
+    LightGridView m_lgrid{};
+    void* m_d_lgrid_tiles = nullptr;
+    void* m_d_lgrid_items = nullptr;
+    void* m_d_lgrid_bbox = nullptr;
+    void* m_d_lgrid_misc = nullptr;
+    uint32_t m_lgrid_tiles = 0;
+    uint32_t m_lgrid_cap = 0;
     float m_pad = 0.f;                // world-space slack of the culling structures (as the BVH boxes)
     cudaEvent_t m_grid_free = nullptr; // the last render that read the grid has finished
     std::vector<cudaEvent_t> m_chunk_events; // RenderHost pipeline
@@ -176,6 +197,7 @@ struct RenderLaunch
     uint32_t n_row_blocks;
     uint32_t hints;  // 1: rays first test the triangle the lane's previous ray ended on (SRT_BVH_HINTS=0 disables)
     GridView grid;
+    LightGridView lgrid;
 };
 void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream);
 // True when LaunchRender would pick a kernel that reads the primary-ray grid for these parameters.
@@ -188,7 +210,10 @@ struct GridBuild
     float half_w, half_h;
     float pad;              // world-space slack
     uint32_t width, height, tiles_w, tiles_h, cap;
+    uint32_t tile;          // grid units per tile: 8 (pixels, camera grid) or 1 (light grid)
+    float lo_bias;          // 1: queries are closed unit squares [x, x+1] (pixels); 0: points
     uint32_t* tile_cnt; uint32_t* tile_off; uint32_t* cursor; uint32_t* items;
+    uint32_t* block_sums;   // [tiles / 4096 + 1] scratch of the prefix sum
     F4* bbox; uint32_t* global; GridFlags* flags;
 };
 void BuildScreenGrid(GridBuild const& build, cudaStream_t stream);
