@@ -469,8 +469,11 @@ __global__ void __launch_bounds__(kBruteThreads) render_brute_kernel(const __gri
 // of a world-space slack (4x the BVH box padding, plus the fp32 error of the projection itself) and
 // by 1/4 pixel, which exceeds by orders of magnitude how far outside a triangle the fp32
 // Moller-Trumbore test can still answer "inside" (the BVH boxes rely on a quarter of that slack).
-__device__ __forceinline__ bool grid_project(GridBuild const& G, uint32_t i, float4& box)
+// edge[k] = (nx, ny, c, *): nx*q.x + ny*q.y + c >= 0 for every query q (centre of a pixel square, or a point)
+// whose rays can hit the triangle; (0, 0, 1, *) = no statement.  edge[0].w = nearest vertex depth minus slack.
+__device__ __forceinline__ bool grid_project(GridBuild const& G, uint32_t i, float4& box, float4 (&edge)[3])
 {
+    edge[0] = edge[1] = edge[2] = make_float4(0.f, 0.f, 1.f, 0.f);
     float4 const v0 = reinterpret_cast<float4 const*>(G.scene.tri_v0)[i];
     float4 const e1 = reinterpret_cast<float4 const*>(G.scene.tri_e1)[i];
     float4 const e2 = reinterpret_cast<float4 const*>(G.scene.tri_e2)[i];
@@ -517,6 +520,42 @@ __device__ __forceinline__ bool grid_project(GridBuild const& G, uint32_t i, flo
     float const y0 = cyp - (ty1 + slack_t) * ky - 0.25f, y1 = cyp - (ty0 - slack_t) * ky + 0.25f;
     if (!(x0 <= x1) || !(y0 <= y1) || !isfinite(x0) || !isfinite(x1) || !isfinite(y0) || !isfinite(y1)) return true;
     box = make_float4(x0, y0, x1, y1);
+    edge[0].w = zmin - slack_w;
+    // Edge functions of the projected triangle (perspective keeps a triangle in front of the plane a
+    // triangle).  Margin: the dilation of the box (slack + 1/4 unit) plus the half extent of a query,
+    // in the L1 norm of the edge normal -- the largest value the function takes over the dilated
+    // square around a query centre.  Skipped for slivers and for coordinates whose products would
+    // round coarser than the margin.
+    float qx[3], qy[3], big = 0.f;
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+    {
+        float const iz = 1.0f / czs[k];
+        qx[k] = cxp + cxs[k] * iz * kx;
+        qy[k] = cyp - cys[k] * iz * ky;
+        big = fmaxf(big, fmaxf(fabsf(qx[k]), fabsf(qy[k])));
+    }
+    float const area2 = (qx[1] - qx[0]) * (qy[2] - qy[0]) - (qy[1] - qy[0]) * (qx[2] - qx[0]);
+    float const ext = fmaxf(x1 - x0, y1 - y0);
+    // fp32 budget: coordinates carry an absolute error of ~1e-7 * big, so an edge normal is off by that
+    // much and the function by up to that times the distance to the query (<= ext); the orientation
+    // (sign of area2) must be beyond doubt, and each edge is used only if a quarter of a unit of its
+    // margin covers these errors several times over.
+    if (big < 2e5f && fabsf(area2) > 1e-5f * big * ext)
+    {
+        float const sgn = area2 > 0.f ? 1.f : -1.f;
+        float const m = slack_t * fmaxf(kx, ky) + 0.25f + G.half_extent;
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+        {
+            int const a = k, b = (k + 1) % 3;
+            float const nx = -sgn * (qy[b] - qy[a]), ny = sgn * (qx[b] - qx[a]);
+            float const n1 = fabsf(nx) + fabsf(ny);
+            if (!(n1 >= 3.2e-6f * big * ext)) continue;
+            float const c = -(nx * qx[a] + ny * qy[a]) + m * n1;
+            edge[k].x = nx; edge[k].y = ny; edge[k].z = c;
+        }
+    }
     return false;
 }
 
@@ -539,9 +578,10 @@ __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__
     uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= G.scene.n_tris_padded) return;
     float4 box = make_float4(1.f, 1.f, 0.f, 0.f);
+    float4 edge[3] = {make_float4(0.f, 0.f, 1.f, 0.f), make_float4(0.f, 0.f, 1.f, 0.f), make_float4(0.f, 0.f, 1.f, 0.f)};
     bool global = false;
     if (i < G.scene.n_tris && __float_as_int(reinterpret_cast<float4 const*>(G.scene.tri_v0)[i].w) >= 0)
-        global = grid_project(G, i, box);
+        global = grid_project(G, i, box, edge);
     int tx0, tx1, ty0, ty1;
     bool const binned = !global && box.x <= box.z && grid_tile_range(G, box, tx0, tx1, ty0, ty1);
     if (binned && (tx1 - tx0 + 1) * (ty1 - ty0 + 1) > kGridMaxTilesPerTri) global = true;
@@ -561,6 +601,8 @@ __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__
         box = make_float4(1.f, 1.f, 0.f, 0.f);   // off the frame or behind the camera
     }
     reinterpret_cast<float4*>(G.bbox)[i] = box;
+#pragma unroll
+    for (int k = 0; k < 3; k++) reinterpret_cast<float4*>(G.edges)[3 * i + k] = edge[k];
 }
 
 // Exclusive prefix sum of the tile counts in three small launches (the light grid has ~10^6 cells):
@@ -879,10 +921,17 @@ __device__ __forceinline__ bool lgrid_shadow(RenderLaunch const& L, V3 so, V3 sd
         if (test(__ldg(G.grid.global + k))) return true;
     }
     uint32_t const b = __ldg(G.grid.tile_off + cell), e = __ldg(G.grid.tile_off + cell + 1);
+    float4 const* __restrict__ edges = reinterpret_cast<float4 const*>(G.grid.edges);
     for (uint32_t k = b; k < e; k++)
     {
+        uint32_t const slot = __ldg(G.grid.items + k);
+        // the projected triangle must cover the query point, and reach nearer to the light than S
+        float4 const e0 = __ldg(edges + 3 * slot), e1 = __ldg(edges + 3 * slot + 1), e2 = __ldg(edges + 3 * slot + 2);
+        if (!(e0.w <= cz) || !(e0.x * gx + e0.y * gy + e0.z >= 0.0f) || !(e1.x * gx + e1.y * gy + e1.z >= 0.0f)
+            || !(e2.x * gx + e2.y * gy + e2.z >= 0.0f))
+            continue;
         if (STATS) n_tri++;
-        if (test(__ldg(G.grid.items + k))) return true;
+        if (test(slot)) return true;
     }
     return true;
 }
@@ -959,7 +1008,7 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
     // its current pixel (lanes test different candidates, ballot-compacted), and every sample of that
     // pixel then tests the few survivors instead of walking the BVH.
     constexpr uint32_t kCand = PIX == 1 ? kGridMaxList + kGridMaxGlobal : 1;
-    __shared__ float4 s_cv0[kCand], s_ce1[kCand], s_ce2[kCand], s_cbox[kCand];
+    __shared__ float4 s_cv0[kCand], s_ce1[kCand], s_ce2[kCand], s_cbox[kCand], s_cedge[3][kCand];
     __shared__ uint32_t s_cslot[kCand];
     __shared__ uint8_t s_pixlist[PIX == 1 ? 8 : 1][kCand];
     uint32_t n_cand = 0;
@@ -984,6 +1033,10 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                 s_ce2[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e2) + slot);
                 s_cbox[threadIdx.x] = glob ? make_float4(-pos_inf(), -pos_inf(), pos_inf(), pos_inf())
                                            : __ldg(reinterpret_cast<float4 const*>(L.grid.bbox) + slot);
+#pragma unroll
+                for (int k = 0; k < 3; k++)
+                    s_cedge[k][threadIdx.x] = glob ? make_float4(0.f, 0.f, 1.f, 0.f)
+                                                   : __ldg(reinterpret_cast<float4 const*>(L.grid.edges) + 3 * slot + k);
             }
             __syncthreads();
         }
@@ -1030,6 +1083,13 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                     {
                         float4 const b = s_cbox[j];
                         pass = b.z >= px0 && b.x <= px0 + 1.0f && b.w >= py0 && b.y <= py0 + 1.0f;
+                        float const qx = px0 + 0.5f, qy = py0 + 0.5f;   // the margin in c covers the pixel square
+#pragma unroll
+                        for (int k = 0; k < 3; k++)
+                        {
+                            float4 const e = s_cedge[k][j];
+                            pass = pass && (e.x * qx + e.y * qy + e.z >= 0.0f);
+                        }
                     }
                     uint32_t const m = __ballot_sync(0xffffffffu, pass);
                     if (pass) s_pixlist[warp][n_pix + __popc(m & ((1u << lane) - 1u))] = static_cast<uint8_t>(j);

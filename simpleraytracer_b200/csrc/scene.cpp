@@ -218,7 +218,7 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
         m_lgrid_tiles = m_lgrid_cap = 0;
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
-        ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_bbox, static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_bbox, 4 * static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));
         m_lgrid_tiles = tiles;
         m_lgrid_cap = cap;
@@ -244,12 +244,15 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;
     b.items = static_cast<uint32_t*>(m_d_lgrid_items);
     b.bbox = static_cast<F4*>(m_d_lgrid_bbox);
+    b.edges = b.bbox + m_view.n_tris_padded;
+    b.half_extent = 0.f;
     b.flags = static_cast<GridFlags*>(m_d_lgrid_misc);
     b.global = reinterpret_cast<uint32_t*>(b.flags + 1);
     BuildScreenGrid(b, stream);
 
     GridView& gv = m_lgrid.grid;
-    gv.tile_off = b.tile_off; gv.items = b.items; gv.bbox = b.bbox; gv.global = b.global; gv.flags = b.flags;
+    gv.tile_off = b.tile_off; gv.items = b.items; gv.bbox = b.bbox; gv.edges = b.edges; gv.global = b.global;
+    gv.flags = b.flags;
     gv.tiles_w = gw; gv.tiles_h = gh;
     for (int i = 0; i < 9; i++) m_lgrid.minv[i] = b.minv[i];
     m_lgrid.kx = 0.5f * static_cast<float>(gw) / b.half_w;
@@ -306,7 +309,7 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
         FreeGrid();
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
-        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_bbox, static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_bbox, 4 * static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));
         m_grid_tiles = tiles;
         m_grid_cap = cap;
@@ -326,11 +329,14 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
     b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;
     b.items = static_cast<uint32_t*>(m_d_grid_items);
     b.bbox = static_cast<F4*>(m_d_grid_bbox);
+    b.edges = b.bbox + m_view.n_tris_padded;
+    b.half_extent = 0.5f;
     b.flags = static_cast<GridFlags*>(m_d_grid_misc);
     b.global = reinterpret_cast<uint32_t*>(b.flags + 1);
     BuildScreenGrid(b, stream);
 
-    m_grid.tile_off = b.tile_off; m_grid.items = b.items; m_grid.bbox = b.bbox; m_grid.global = b.global;
+    m_grid.tile_off = b.tile_off; m_grid.items = b.items; m_grid.bbox = b.bbox; m_grid.edges = b.edges;
+    m_grid.global = b.global;
     m_grid.flags = b.flags; m_grid.tiles_w = tw; m_grid.tiles_h = th;
     m_grid.enabled = 1;
 }

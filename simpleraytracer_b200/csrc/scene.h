@@ -74,6 +74,9 @@ struct GridView
     uint32_t const* tile_off;   // [tiles + 1] exclusive prefix of the list lengths
     uint32_t const* items;      // triangle slots, tile after tile
     F4 const* bbox;             // per slot: dilated screen box (x0, y0, x1, y1) in pixels; x0 > x1: not binned
+    F4 const* edges;            // per slot 3 x (nx, ny, c, *): the projected triangle's edge functions with the
+                                // conservative margin folded into c -- a query at q can only hit the triangle if
+                                // nx*q.x + ny*q.y + c >= 0 for all three; edges[3*slot].w = nearest depth (light grid)
     uint32_t const* global;     // [kGridMaxGlobal]
     GridFlags const* flags;
     uint32_t tiles_w, tiles_h;
@@ -151,7 +154,7 @@ private:
     GridView m_grid{};
     void* m_d_grid_tiles = nullptr;   // tile_cnt | tile_off | cursor
     void* m_d_grid_items = nullptr;
-    void* m_d_grid_bbox = nullptr;
+    void* m_d_grid_bbox = nullptr;    // bbox | edges
     void* m_d_grid_misc = nullptr;    // GridFlags | global list
     uint32_t m_grid_tiles = 0;
     uint32_t m_grid_cap = 0;
@@ -214,7 +217,8 @@ struct GridBuild
     float lo_bias;          // 1: queries are closed unit squares [x, x+1] (pixels); 0: points
     uint32_t* tile_cnt; uint32_t* tile_off; uint32_t* cursor; uint32_t* items;
     uint32_t* block_sums;   // [tiles / 4096 + 1] scratch of the prefix sum
-    F4* bbox; uint32_t* global; GridFlags* flags;
+    F4* bbox; F4* edges; uint32_t* global; GridFlags* flags;
+    float half_extent;      // half size of a query in grid units: 0.5 (pixel squares) or 0 (points)
 };
 void BuildScreenGrid(GridBuild const& build, cudaStream_t stream);
 double MeasureFp32Peak(DeviceState const& device, int repeats);
