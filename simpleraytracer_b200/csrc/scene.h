@@ -65,7 +65,7 @@ struct DeviceSceneView
 // irrelevant.  Rebuilt on the device for every render call (three small kernels); a frame the grid
 // cannot serve (flags.ok == 0) and tiles with long lists fall back to the BVH.
 constexpr uint32_t kGridTile = 8;        // pixels; equals the render kernels' 8-row blocks
-constexpr uint32_t kGridMaxList = 64;    // longer tile lists: that tile walks the BVH instead
+constexpr uint32_t kGridMaxList = 192;   // longer tile lists: that tile walks the BVH instead
 constexpr uint32_t kGridMaxGlobal = 32;  // triangles that cannot be projected safely (near or crossing the
                                          // camera plane, or huge on screen): tested by every ray
 struct GridFlags { uint32_t ok; uint32_t n_global; uint32_t total; uint32_t pad; };
