@@ -330,3 +330,70 @@ def test_render_device_into_torch_tensor(ctx):
     assert np.array_equal(rgb.cpu().numpy(), host[0]) and np.array_equal(hid.cpu().numpy(), host[1])
     assert st.primary_rays == W * H * 2 and st.kernel_ms > 0
     scene.release()
+
+
+def _soup(rng, n, extent):
+    """Triangle soup: mostly small triangles, some long slivers, a few huge ones that cross any camera plane."""
+    c = rng.uniform(-extent, extent, (n, 1, 3))
+    size = np.where(rng.random((n, 1, 1)) < 0.9, 0.04, 0.6) * extent
+    v = c + rng.normal(0, 1, (n, 3, 3)) * size
+    sl = rng.random(n) < 0.05
+    v[sl, 2] = v[sl, 1] + rng.normal(0, 1e-3 * extent, (int(sl.sum()), 3))        # slivers
+    v[:4] = rng.uniform(-3 * extent, 3 * extent, (4, 3, 3))                         # huge
+    return v.reshape(n, 9).astype(np.float32), rng.random((n, 3)).astype(np.float32)
+
+
+def _camera(rng, origin, look_at, fov_w, fov_h, shear=0.0):
+    cam = api.srt_camera()
+    f = np.asarray(look_at, np.float64) - origin
+    f /= np.linalg.norm(f)
+    r = np.cross(f, [0.0, 1.0, 0.0] if abs(f[1]) < 0.9 else [1.0, 0.0, 0.0]); r /= np.linalg.norm(r)
+    u = np.cross(r, f)
+    if shear:      # a basis that is neither orthogonal nor unit length is still a valid camera
+        r = 1.3 * r + shear * u
+        u = 0.8 * u + 0.5 * shear * f
+    cam.origin[:] = [float(x) for x in origin]; cam.forward[:] = [float(x) for x in f]
+    cam.right[:] = [float(x) for x in r]; cam.up[:] = [float(x) for x in u]
+    cam.half_w, cam.half_h = fov_w, fov_h
+    return cam
+
+
+@pytest.mark.parametrize("case", range(8))
+def test_screen_and_light_grids_equal_exhaustive_search(ctx, case):
+    """spp >= 32 renders primary rays through the per-frame screen grid and shadow rays through the light
+    grid (docs/RENDER_SPEC.md section 7).  Both only select candidates, so the frame must equal the
+    exhaustive kernel's bit for bit -- for cameras inside the geometry, triangles behind / across the camera
+    plane, slivers, huge triangles, sheared camera bases, and lights above, beside and inside the scene."""
+    rng = np.random.default_rng(100 + case)
+    W, H = 72, 40
+    v, a = _soup(rng, 600, 10.0)
+    origin = rng.uniform(-8, 8, 3) if case % 2 else rng.uniform(-1, 1, 3) * 25     # inside / outside the soup
+    cam = _camera(rng, origin, rng.uniform(-5, 5, 3), 0.3 + 0.6 * rng.random(), 0.2 + 0.4 * rng.random(),
+                  shear=0.3 if case in (2, 5) else 0.0)
+    light = api.srt_light()
+    lp = [(0, 60, 5), (45, 30, -38), (2, 1, -3), (-70, -55, 64)][case % 4]          # (2,1,-3): inside -> BVH shadows
+    light.position[:] = [float(x) for x in lp]; light.intensity[:] = [900.0, 800.0, 700.0]
+    scene = ctx.create_scene(v, a)
+    common = dict(spp=32 + case, jitter=1, seed=case, shade=api.SRT_SHADE_SHADOW, background=(0.1, 0.2, 0.3))
+    brute = scene.render(cam, light, api.make_params(W, H, accel=api.SRT_ACCEL_BRUTE, **common))
+    grid = scene.render(cam, light, api.make_params(W, H, accel=api.SRT_ACCEL_BVH, **common))
+    for k, name in enumerate(("rgb", "hit_id", "hit_t")):
+        assert np.array_equal(brute[k], grid[k]), f"case {case}: {name} differs from the exhaustive kernel"
+    assert brute[3].shadow_rays == grid[3].shadow_rays
+    # a band that starts off the 8-row tile grid falls back to the BVH for primary rays: same pixels
+    band = scene.render(cam, light, api.make_params(W, H, accel=api.SRT_ACCEL_BVH, y0=13, y1=37, buf_y0=13, **common))
+    assert np.array_equal(band[0][:24], brute[0][13:37]) and np.array_equal(band[1][:24], brute[1][13:37])
+    scene.release()
+
+
+def test_grids_on_cornell_box(ctx):
+    """A dozen wall-sized triangles around the camera: every triangle is 'global' or covers hundreds of
+    tiles; the grid path must still reproduce the oracle."""
+    W, H = 96, 96
+    v, a, cam, light = api.gen_cornell_box(W, H)
+    scene = ctx.create_scene(v, a)
+    p = api.make_params(W, H, spp=33, jitter=1, seed=4, shade=api.SRT_SHADE_SHADOW, accel=api.SRT_ACCEL_BVH)
+    got = scene.render(cam, light, p)
+    ref = O.render(v, a, cam, light, p)
+    assert_parity(got, ref, "cornell through the grids")
+    scene.release()
