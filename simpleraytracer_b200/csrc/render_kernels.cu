@@ -573,6 +573,21 @@ __device__ __forceinline__ bool grid_tile_range(GridBuild const& G, float4 box, 
 
 constexpr int kGridMaxTilesPerTri = 1024;   // larger on screen: global list
 
+// Can any query inside tile (tx, ty) pass the triangle's edge functions?  The functions already carry the
+// margin of ONE query (half_extent); a tile is a square of `tile` units, so its centre gets the remaining
+// half width in the L1 norm of each normal.  Evaluated identically by the count and the fill kernel.
+__device__ __forceinline__ bool grid_tile_touches(GridBuild const& G, float4 const (&edge)[3], int tx, int ty)
+{
+    float const t = static_cast<float>(G.tile);
+    float const qx = (static_cast<float>(tx) + 0.5f) * t, qy = (static_cast<float>(ty) + 0.5f) * t;
+    float const h = 0.5f * t - G.half_extent;
+    bool ok = true;
+#pragma unroll
+    for (int k = 0; k < 3; k++)
+        ok = ok && (edge[k].x * qx + edge[k].y * qy + edge[k].z + h * (fabsf(edge[k].x) + fabsf(edge[k].y)) >= 0.0f);
+    return ok;
+}
+
 __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__ GridBuild G)
 {
     uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -594,7 +609,8 @@ __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__
     else if (binned)
     {
         for (int ty = ty0; ty <= ty1; ty++)
-            for (int tx = tx0; tx <= tx1; tx++) atomicAdd(&G.tile_cnt[ty * G.tiles_w + tx], 1u);
+            for (int tx = tx0; tx <= tx1; tx++)
+                if (grid_tile_touches(G, edge, tx, ty)) atomicAdd(&G.tile_cnt[ty * G.tiles_w + tx], 1u);
     }
     else
     {
@@ -708,9 +724,13 @@ __global__ void __launch_bounds__(256) grid_fill_kernel(const __grid_constant__ 
     float4 const box = reinterpret_cast<float4 const*>(G.bbox)[i];
     int tx0, tx1, ty0, ty1;
     if (!(box.x <= box.z) || !grid_tile_range(G, box, tx0, tx1, ty0, ty1)) return;
+    float4 edge[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) edge[k] = reinterpret_cast<float4 const*>(G.edges)[3 * i + k];
     for (int ty = ty0; ty <= ty1; ty++)
         for (int tx = tx0; tx <= tx1; tx++)
         {
+            if (!grid_tile_touches(G, edge, tx, ty)) continue;
             uint32_t const t = ty * G.tiles_w + tx;
             G.items[G.tile_off[t] + atomicAdd(&G.cursor[t], 1u)] = i;
         }

@@ -160,6 +160,7 @@ void Scene::FreeGrid()
     m_d_lgrid_tiles = m_d_lgrid_items = m_d_lgrid_bbox = m_d_lgrid_misc = nullptr;
     m_lgrid_tiles = m_lgrid_cap = 0;
     m_lgrid = LightGridView{};
+    m_lgrid_valid = false;
 }
 
 // Shadow-ray grid for this call's light (scene.h, LightGridView), built on `stream`.  Used when the
@@ -172,6 +173,16 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     if (!want || params->accel != SRT_ACCEL_BVH || params->shade != SRT_SHADE_SHADOW || !RenderUsesGrid(*params)
         || m_view.n_tris == 0)
         return;
+    // The light grid depends on the scene and the light position only (not on the camera or the frame):
+    // it is kept while the light stays where it is, like the BVH is kept while the scene does.
+    static int const cache = std::getenv("SRT_LIGHT_GRID_CACHE") ? std::atoi(std::getenv("SRT_LIGHT_GRID_CACHE")) : 1;
+    if (cache && m_lgrid_valid && std::memcmp(m_lgrid_light, light->position, sizeof(m_lgrid_light)) == 0)
+    {
+        ML_CUDA_CHECK(cudaStreamWaitEvent(stream, m_lgrid_built, 0));   // built on another stream, perhaps
+        m_lgrid.grid.enabled = 1;
+        return;
+    }
+    m_lgrid_valid = false;
     double const lo[3] = {m_info.bounds_min[0], m_info.bounds_min[1], m_info.bounds_min[2]};
     double const hi[3] = {m_info.bounds_max[0], m_info.bounds_max[1], m_info.bounds_max[2]};
     double const lp[3] = {light->position[0], light->position[1], light->position[2]};
@@ -203,8 +214,10 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     }
     if (!(tmax_x > 0) || !(tmax_y > 0) || tmax_x > 50 || tmax_y > 50) return;
     double const half_w = tmax_x * 1.001 + 1e-6, half_h = tmax_y * 1.001 + 1e-6;
-    // about 8 cells per triangle, split by the aspect of the projected scene
-    double const g = std::min(2048.0, std::max(256.0, std::sqrt(8.0 * static_cast<double>(m_view.n_tris))));
+    // about 32 cells per triangle, split by the aspect of the projected scene: a cell's list then holds little
+    // more than the triangles that really cover it (measured: the list walk was 20 % of the frame at 8)
+    static double const cells_per_tri = std::getenv("SRT_LIGHT_GRID_CELLS") ? std::atof(std::getenv("SRT_LIGHT_GRID_CELLS")) : 32.0;
+    double const g = std::min(4096.0, std::max(256.0, std::sqrt(cells_per_tri * static_cast<double>(m_view.n_tris))));
     uint32_t const gw = static_cast<uint32_t>(std::min(4096.0, std::max(64.0, g * std::sqrt(half_w / half_h))));
     uint32_t const gh = static_cast<uint32_t>(std::min(4096.0, std::max(64.0, g * std::sqrt(half_h / half_w))));
     uint32_t const tiles = gw * gh;
@@ -260,6 +273,10 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     m_lgrid.cx = 0.5f * static_cast<float>(gw);
     m_lgrid.cy = 0.5f * static_cast<float>(gh);
     gv.enabled = 1;
+    if (m_lgrid_built == nullptr) ML_CUDA_CHECK(cudaEventCreateWithFlags(&m_lgrid_built, cudaEventDisableTiming));
+    ML_CUDA_CHECK(cudaEventRecord(m_lgrid_built, stream));
+    std::memcpy(m_lgrid_light, light->position, sizeof(m_lgrid_light));
+    m_lgrid_valid = true;
 }
 
 // Primary-ray grid for this call's camera and frame, built on `stream` (scene.h, GridView).  Leaves
@@ -356,6 +373,7 @@ Scene::~Scene()
     FreeStaging();
     FreeGrid();
     if (m_grid_free) cudaEventDestroy(m_grid_free);
+    if (m_lgrid_built) cudaEventDestroy(m_lgrid_built);
     for (cudaEvent_t e : m_chunk_events) cudaEventDestroy(e);
     cudaFree(m_d_tris); cudaFree(m_d_albedo); cudaFree(m_d_nodes); cudaFree(m_d_counters);
 }

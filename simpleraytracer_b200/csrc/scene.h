@@ -57,7 +57,7 @@ struct DeviceSceneView
     uint32_t n_tris_padded; // multiple of kTriTile
 };
 
-// Screen-space candidate grid for primary rays (BUILD-DEFINED, docs/RENDER_SPEC.md section 7): per
+// Screen-space candidate grid for primary rays (BUILD-DEFINED, docs/RENDER_SPEC.md section 8): per
 // 8x8-pixel tile the triangles whose conservatively dilated screen bounding box touches the tile.
 // All primary rays leave one point, so a ray through pixel (x, y) can only hit triangles whose
 // projection covers that pixel: the closest hit over the tile's (pixel-filtered) list equals the
@@ -166,8 +166,11 @@ private:
     void* m_d_lgrid_misc = nullptr;
     uint32_t m_lgrid_tiles = 0;
     uint32_t m_lgrid_cap = 0;
+    bool m_lgrid_valid = false;       // the light grid on the device was built for m_lgrid_light
+    float m_lgrid_light[3] = {0.f, 0.f, 0.f};
     float m_pad = 0.f;                // world-space slack of the culling structures (as the BVH boxes)
     cudaEvent_t m_grid_free = nullptr; // the last render that read the grid has finished
+    cudaEvent_t m_lgrid_built = nullptr; // the cached light grid is complete
     std::vector<cudaEvent_t> m_chunk_events; // RenderHost pipeline
     cudaStream_t m_timed_stream = nullptr;
     bool m_timed_pending = false;

@@ -361,7 +361,7 @@ def _camera(rng, origin, look_at, fov_w, fov_h, shear=0.0):
 @pytest.mark.parametrize("case", range(8))
 def test_screen_and_light_grids_equal_exhaustive_search(ctx, case):
     """spp >= 32 renders primary rays through the per-frame screen grid and shadow rays through the light
-    grid (docs/RENDER_SPEC.md section 7).  Both only select candidates, so the frame must equal the
+    grid (docs/RENDER_SPEC.md section 8).  Both only select candidates, so the frame must equal the
     exhaustive kernel's bit for bit -- for cameras inside the geometry, triangles behind / across the camera
     plane, slivers, huge triangles, sheared camera bases, and lights above, beside and inside the scene."""
     rng = np.random.default_rng(100 + case)
