@@ -485,22 +485,27 @@ def run_b200_arm(args):
     share = (st.primary_rays + st.shadow_rays) / rays_per_step if rays_per_step else 1.0
     achieved = flops_per_step * share / (kern_ms * 1e-3) / 1e12
     scene_bytes = info.device_bytes
-    roofline = {"bound": "fp32", "kernel": "render_bvh_spp_kernel<false,1>" if args.spp >= 32 else "render_bvh_kernel", "achieved": achieved, "peak": fp32_peak,
+    grid_path = args.spp >= 32
+    roofline = {"bound": "fp32", "kernel": "render_bvh_spp_kernel<false,1> (screen grid + light grid candidate lists, BVH fallback)" if grid_path else "render_bvh_kernel",
+                "achieved": achieved, "peak": fp32_peak,
                 "unit": "TFLOP/s", "frac": achieved / fp32_peak if fp32_peak else None,
-                "traffic": 8.68e6 if world == 1 and args.spp == WORKLOAD["spp"] else None,
-                "traffic_source": "ncu --set full, dram__bytes_read+write per launch: 6.64 MB + 2.04 MB "
-                                  "(profiles/r01_bvh_spp_kernel_ncu_full_summary.csv; scene and frame stay in the 126 MB L2)",
+                "traffic": 23.35e6 if world == 1 and args.spp == WORKLOAD["spp"] else None,
+                "traffic_source": "ncu --set full, dram__bytes_read+write per launch: 23.2 MB + 0.15 MB "
+                                  "(profiles/r01_bvh_spp_grid_kernel_ncu_full_summary.csv; scene, grids and frame stay in the 126 MB L2)",
                 "peak_source": "srtMeasureFp32Peak live FFMA microbenchmark (MEASURED_PEAKS.json has no FP32 figure)",
                 "algorithmic_flops_per_launch": flops_per_step * share,
                 "box_tests": boxes, "tri_tests": tris, "kernel_ms": kern_ms,
                 "algorithmic_bytes_per_launch": rows * W * 12 + scene_bytes,
-                "issue_slots": {"busy_frac": 0.725, "threads_per_instruction": 26.6, "l1_hit": 0.991,
-                                "warp_instructions_per_launch": 19.64e9,
+                "issue_slots": {"busy_frac": 0.807, "threads_per_instruction": 25.4, "l1_hit": 0.971,
+                                "warp_instructions_per_launch": 4.74e9,
                                 "source": "ncu --set full of this kernel on this workload (smsp__issue_active, "
-                                          "profiles/r01_bvh_spp_kernel_ncu_full_summary.csv): the kernel is bound by "
-                                          "instruction issue, ~40 SASS instructions per two-box node visit"},
-                "note": "BVH traversal is instruction-issue bound, not FP32-pipe bound; flops = box_tests*21 + "
-                        "tri_tests*45 counted by the instrumented kernel variant on the same frame"}
+                                          "profiles/r01_bvh_spp_grid_kernel_ncu_full_summary.csv): the kernel is bound by "
+                                          "instruction issue (80.7 % of the issue slots busy); the candidate grids cut the "
+                                          "work from 19.6e9 to 4.7e9 warp instructions per frame"},
+                "note": "instruction-issue bound, not FP32-pipe bound; flops = box_tests*21 + tri_tests*45 counted by the "
+                        "instrumented kernel variant on the same frame -- the grids REMOVE algorithmic work (84 box + 4.6 triangle "
+                        "tests per ray with the BVH alone, 0.04 + 3.7 with the grids), so TFLOP/s falls while Mrays/s rises 4.5x; "
+                        "kernel_ms includes the per-frame grid build (5 small launches before the render kernel)"}
 
     brute = None
     if not args.no_brute:
@@ -545,7 +550,7 @@ def run_b200_arm(args):
                 + C.sizeof(api.srt_camera) + C.sizeof(api.srt_light), "d2h_bytes_per_step": int(d2h.item()),
                 "host_buffer": "pageable (a reference-style caller's std::vector / numpy array)",
                 "value_page_locked_buffer": e2e_pinned_value},
-        "gpu_launches": args.steps, "clocks": clocks.summary(),
+        "gpu_launches": args.steps * (6 if args.spp >= 32 else 1), "clocks": clocks.summary(),
         "peaks": {"fp32_tflops_measured_live": fp32_peak, "hbm_gbs": measured_peaks()[0].get("hbm_gbs"),
                   "source": measured_peaks()[1]},
     }

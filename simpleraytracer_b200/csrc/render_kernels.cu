@@ -571,7 +571,6 @@ __device__ __forceinline__ bool grid_tile_range(GridBuild const& G, float4 box, 
     return true;
 }
 
-constexpr int kGridMaxTilesPerTri = 1024;   // larger on screen: global list
 
 // Can any query inside tile (tx, ty) pass the triangle's edge functions?  The functions already carry the
 // margin of ONE query (half_extent); a tile is a square of `tile` units, so its centre gets the remaining
@@ -599,7 +598,7 @@ __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__
         global = grid_project(G, i, box, edge);
     int tx0, tx1, ty0, ty1;
     bool const binned = !global && box.x <= box.z && grid_tile_range(G, box, tx0, tx1, ty0, ty1);
-    if (binned && (tx1 - tx0 + 1) * (ty1 - ty0 + 1) > kGridMaxTilesPerTri) global = true;
+    if (binned && static_cast<uint32_t>((tx1 - tx0 + 1) * (ty1 - ty0 + 1)) > G.max_tiles_per_tri) global = true;
     if (global)
     {
         uint32_t const k = atomicAdd(&G.flags->n_global, 1u);
@@ -957,6 +956,8 @@ __device__ __forceinline__ bool lgrid_shadow(RenderLaunch const& L, V3 so, V3 sd
 }
 
 // MINB = minimum resident blocks per SM the register allocation must allow.
+constexpr uint32_t kPixGridMaxList = 160;  // thread-per-pixel kernel: longer tile lists walk the BVH
+
 template <bool STATS, int MINB>
 __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __grid_constant__ RenderLaunch L)
 {
@@ -969,6 +970,27 @@ __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __g
     unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
     if (valid)
     {
+        // Screen grid: the 32 pixels of a warp lie in ONE 8x8 tile, so every lane walks the same candidate
+        // list (uniform addresses: broadcast loads) and filters it against its own pixel.
+        bool use_grid = false;
+        uint32_t g_off = 0, g_cnt = 0, g_glob = 0;
+        if (L.grid.enabled)
+        {
+            GridFlags const fl = *L.grid.flags;
+            uint32_t const tile = (y / kGridTile) * L.grid.tiles_w + x / kGridTile;
+            g_off = __ldg(L.grid.tile_off + tile);
+            g_cnt = __ldg(L.grid.tile_off + tile + 1) - g_off;
+            g_glob = fl.n_global;
+            use_grid = fl.ok != 0 && g_cnt <= kPixGridMaxList;
+        }
+        bool lgrid_ok = false;
+        uint32_t lgrid_global = 0;
+        if (L.lgrid.grid.enabled)
+        {
+            GridFlags const lf = *L.lgrid.grid.flags;
+            lgrid_ok = lf.ok != 0;
+            lgrid_global = lf.n_global;
+        }
         V3 const o = v3(L.camera.origin);
         V3 acc = V3{0.f, 0.f, 0.f};
         Hit first_hit = no_hit();
@@ -978,7 +1000,35 @@ __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __g
             Hit best = no_hit();
             bool occ = false;
             n_primary++;
-            bvh_trace<false, STATS>(L.scene, o, d, L.params.t_min, best, occ, n_box, n_tri);
+            if (use_grid)
+            {
+                float const px0 = static_cast<float>(x), py0 = static_cast<float>(y);
+                float const qx = px0 + 0.5f, qy = py0 + 0.5f;
+                float4 const* __restrict__ edges = reinterpret_cast<float4 const*>(L.grid.edges);
+                for (uint32_t k = 0; k < g_cnt + g_glob; k++)
+                {
+                    bool const glob = k >= g_cnt;
+                    uint32_t const slot = glob ? __ldg(L.grid.global + (k - g_cnt)) : __ldg(L.grid.items + g_off + k);
+                    if (!glob)
+                    {
+                        float4 const b = __ldg(reinterpret_cast<float4 const*>(L.grid.bbox) + slot);
+                        if (!(b.z >= px0 && b.x <= px0 + 1.0f && b.w >= py0 && b.y <= py0 + 1.0f)) continue;
+                        float4 const e0 = __ldg(edges + 3 * slot), e1 = __ldg(edges + 3 * slot + 1), e2 = __ldg(edges + 3 * slot + 2);
+                        if (!(e0.x * qx + e0.y * qy + e0.z >= 0.0f) || !(e1.x * qx + e1.y * qy + e1.z >= 0.0f)
+                            || !(e2.x * qx + e2.y * qy + e2.z >= 0.0f))
+                            continue;
+                    }
+                    if (STATS) n_tri++;
+                    float4 const v0 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_v0) + slot);
+                    float4 const e1 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e1) + slot);
+                    float4 const e2 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e2) + slot);
+                    float ts, adet;
+                    if (mt_inside(o, d, v0, e1, e2, ts, adet))
+                        closest_update(best, ts, adet, __float_as_int(v0.w), slot, L.params.t_min);
+                }
+            }
+            else
+                bvh_trace<false, STATS>(L.scene, o, d, L.params.t_min, best, occ, n_box, n_tri);
             if (s == 0) first_hit = best;
             V3 rgb;
             if (best.id < 0)
@@ -993,7 +1043,9 @@ __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __g
                 {
                     n_shadow++;
                     Hit dummy = no_hit();
-                    bvh_trace<true, STATS>(L.scene, sh.so, sh.sd, 0.0f, dummy, occ, n_box, n_tri);
+                    dummy.slot = kNoHint;
+                    if (!(lgrid_ok && lgrid_shadow<STATS>(L, sh.so, sh.sd, occ, dummy.slot, lgrid_global, n_tri)))
+                        bvh_trace<true, STATS>(L.scene, sh.so, sh.sd, 0.0f, dummy, occ, n_box, n_tri);
                     if (occ) rgb = V3{0.f, 0.f, 0.f};
                 }
             }
@@ -1234,9 +1286,13 @@ static int SppPixelsPerWarp(srt_render_params const& p)
     return pix;
 }
 
-bool RenderUsesGrid(srt_render_params const& p)
+// Bit 0: the launch reads the screen grid (thread-per-pixel kernel and the one-pixel-per-warp sample-parallel
+// kernel); bit 1: it reads the light grid (every BVH kernel, when shadow rays are cast).
+int RenderUsesGrid(srt_render_params const& p)
 {
-    return p.accel == SRT_ACCEL_BVH && SppPixelsPerWarp(p) == 1;
+    if (p.accel != SRT_ACCEL_BVH) return 0;
+    int const pix = SppPixelsPerWarp(p);
+    return ((pix == 0 || pix == 1) ? 1 : 0) | (p.shade == SRT_SHADE_SHADOW ? 2 : 0);
 }
 
 void BuildScreenGrid(GridBuild const& build, cudaStream_t stream)

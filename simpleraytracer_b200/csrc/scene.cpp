@@ -5,6 +5,7 @@
 // object (model.cpp:161-176).
 #include "scene.h"
 
+#include <cstdio>
 #include <cstdlib>
 
 #include "context.h"
@@ -170,9 +171,7 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
 {
     m_lgrid.grid.enabled = 0;
     static int const want = std::getenv("SRT_LIGHT_GRID") ? std::atoi(std::getenv("SRT_LIGHT_GRID")) : 1;
-    if (!want || params->accel != SRT_ACCEL_BVH || params->shade != SRT_SHADE_SHADOW || !RenderUsesGrid(*params)
-        || m_view.n_tris == 0)
-        return;
+    if (!want || params->accel != SRT_ACCEL_BVH || !(RenderUsesGrid(*params) & 2) || m_view.n_tris == 0) return;
     // The light grid depends on the scene and the light position only (not on the camera or the frame):
     // it is kept while the light stays where it is, like the BVH is kept while the scene does.
     static int const cache = std::getenv("SRT_LIGHT_GRID_CACHE") ? std::atoi(std::getenv("SRT_LIGHT_GRID_CACHE")) : 1;
@@ -221,7 +220,7 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     uint32_t const gw = static_cast<uint32_t>(std::min(4096.0, std::max(64.0, g * std::sqrt(half_w / half_h))));
     uint32_t const gh = static_cast<uint32_t>(std::min(4096.0, std::max(64.0, g * std::sqrt(half_h / half_w))));
     uint32_t const tiles = gw * gh;
-    uint32_t const cap = std::max<uint32_t>(24u * m_view.n_tris, 1u << 20);
+    uint32_t const cap = std::max<uint32_t>(static_cast<uint32_t>(std::min<uint64_t>(96ull * m_view.n_tris, 1ull << 28)), 1u << 20);
     if (tiles > m_lgrid_tiles || cap > m_lgrid_cap || m_d_lgrid_bbox == nullptr)
     {
         ML_CUDA_CHECK(cudaStreamSynchronize(stream));
@@ -253,6 +252,7 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     b.pad = 4.0f * m_pad;
     b.width = gw; b.height = gh; b.tiles_w = gw; b.tiles_h = gh; b.cap = cap;
     b.tile = 1; b.lo_bias = 0.f;
+    b.max_tiles_per_tri = 1u << 16;    // built once per light position: a few long loops are affordable
     b.tile_cnt = t; b.tile_off = t + tiles; b.cursor = t + 2 * static_cast<size_t>(tiles) + 1;
     b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;
     b.items = static_cast<uint32_t*>(m_d_lgrid_items);
@@ -277,6 +277,15 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     ML_CUDA_CHECK(cudaEventRecord(m_lgrid_built, stream));
     std::memcpy(m_lgrid_light, light->position, sizeof(m_lgrid_light));
     m_lgrid_valid = true;
+    static int const debug = std::getenv("SRT_GRID_DEBUG") ? std::atoi(std::getenv("SRT_GRID_DEBUG")) : 0;
+    if (debug)
+    {
+        GridFlags fl{};
+        ML_CUDA_CHECK(cudaStreamSynchronize(stream));
+        ML_CUDA_CHECK(cudaMemcpy(&fl, b.flags, sizeof(fl), cudaMemcpyDeviceToHost));
+        std::fprintf(stderr, "[srt grid] light %ux%u cells, entries %u (cap %u), global %u, ok %u\n", gw, gh, fl.total, cap,
+                     fl.n_global, fl.ok);
+    }
 }
 
 // Primary-ray grid for this call's camera and frame, built on `stream` (scene.h, GridView).  Leaves
@@ -285,7 +294,7 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
 {
     m_grid.enabled = 0;
     static int const want = std::getenv("SRT_GRID") ? std::atoi(std::getenv("SRT_GRID")) : 1;
-    if (!want || params->accel != SRT_ACCEL_BVH || !RenderUsesGrid(*params) || m_view.n_tris == 0) return;
+    if (!want || params->accel != SRT_ACCEL_BVH || !(RenderUsesGrid(*params) & 1) || m_view.n_tris == 0) return;
     if (params->y0 % kGridTile != 0) return;     // tiles are the render kernels' 8-row blocks
 
     // inverse of the camera basis [right up forward] in double: P - o = cx*right + cy*up + cz*forward
@@ -342,6 +351,7 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
     b.pad = 4.0f * m_pad;
     b.width = params->width; b.height = params->height; b.tiles_w = tw; b.tiles_h = th; b.cap = cap;
     b.tile = kGridTile; b.lo_bias = 1.f;
+    b.max_tiles_per_tri = 1024;
     b.tile_cnt = t; b.tile_off = t + tiles; b.cursor = t + 2 * static_cast<size_t>(tiles) + 1;
     b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;
     b.items = static_cast<uint32_t*>(m_d_grid_items);
@@ -356,6 +366,15 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
     m_grid.global = b.global;
     m_grid.flags = b.flags; m_grid.tiles_w = tw; m_grid.tiles_h = th;
     m_grid.enabled = 1;
+    static int const debug = std::getenv("SRT_GRID_DEBUG") ? std::atoi(std::getenv("SRT_GRID_DEBUG")) : 0;
+    if (debug)
+    {
+        GridFlags f{};
+        ML_CUDA_CHECK(cudaStreamSynchronize(stream));
+        ML_CUDA_CHECK(cudaMemcpy(&f, b.flags, sizeof(f), cudaMemcpyDeviceToHost));
+        std::fprintf(stderr, "[srt grid] screen %ux%u tiles, entries %u (cap %u), global %u, ok %u\n", tw, th, f.total, cap,
+                     f.n_global, f.ok);
+    }
 }
 
 void Scene::FreeStaging()

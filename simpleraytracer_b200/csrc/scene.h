@@ -206,8 +206,8 @@ struct RenderLaunch
     LightGridView lgrid;
 };
 void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream);
-// True when LaunchRender would pick a kernel that reads the primary-ray grid for these parameters.
-bool RenderUsesGrid(srt_render_params const& params);
+// Which candidate grids the kernel LaunchRender picks for these parameters reads: bit 0 screen grid, bit 1 light grid.
+int RenderUsesGrid(srt_render_params const& params);
 struct GridBuild
 {
     DeviceSceneView scene;
@@ -217,6 +217,7 @@ struct GridBuild
     float pad;              // world-space slack
     uint32_t width, height, tiles_w, tiles_h, cap;
     uint32_t tile;          // grid units per tile: 8 (pixels, camera grid) or 1 (light grid)
+    uint32_t max_tiles_per_tri; // a triangle whose box spans more tiles goes to the global list
     float lo_bias;          // 1: queries are closed unit squares [x, x+1] (pixels); 0: points
     uint32_t* tile_cnt; uint32_t* tile_off; uint32_t* cursor; uint32_t* items;
     uint32_t* block_sums;   // [tiles / 4096 + 1] scratch of the prefix sum

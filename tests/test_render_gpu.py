@@ -374,12 +374,14 @@ def test_screen_and_light_grids_equal_exhaustive_search(ctx, case):
     lp = [(0, 60, 5), (45, 30, -38), (2, 1, -3), (-70, -55, 64)][case % 4]          # (2,1,-3): inside -> BVH shadows
     light.position[:] = [float(x) for x in lp]; light.intensity[:] = [900.0, 800.0, 700.0]
     scene = ctx.create_scene(v, a)
-    common = dict(spp=32 + case, jitter=1, seed=case, shade=api.SRT_SHADE_SHADOW, background=(0.1, 0.2, 0.3))
-    brute = scene.render(cam, light, api.make_params(W, H, accel=api.SRT_ACCEL_BRUTE, **common))
-    grid = scene.render(cam, light, api.make_params(W, H, accel=api.SRT_ACCEL_BVH, **common))
-    for k, name in enumerate(("rgb", "hit_id", "hit_t")):
-        assert np.array_equal(brute[k], grid[k]), f"case {case}: {name} differs from the exhaustive kernel"
-    assert brute[3].shadow_rays == grid[3].shadow_rays
+    # 32+ spp: sample-parallel kernel; 1..3 spp: thread-per-pixel kernel (same grids); 9 spp: light grid only
+    for spp in (32 + case, 1 + case % 3, 9):
+        common = dict(spp=spp, jitter=1, seed=case, shade=api.SRT_SHADE_SHADOW, background=(0.1, 0.2, 0.3))
+        brute = scene.render(cam, light, api.make_params(W, H, accel=api.SRT_ACCEL_BRUTE, **common))
+        grid = scene.render(cam, light, api.make_params(W, H, accel=api.SRT_ACCEL_BVH, **common))
+        for k, name in enumerate(("rgb", "hit_id", "hit_t")):
+            assert np.array_equal(brute[k], grid[k]), f"case {case} spp {spp}: {name} differs from the exhaustive kernel"
+        assert brute[3].shadow_rays == grid[3].shadow_rays
     # a band that starts off the 8-row tile grid falls back to the BVH for primary rays: same pixels
     band = scene.render(cam, light, api.make_params(W, H, accel=api.SRT_ACCEL_BVH, y0=13, y1=37, buf_y0=13, **common))
     assert np.array_equal(band[0][:24], brute[0][13:37]) and np.array_equal(band[1][:24], brute[1][13:37])
