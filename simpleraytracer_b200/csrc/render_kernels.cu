@@ -8,8 +8,14 @@
 //    LDS.128.  This is the FP32-FMA-pipe roofline kernel (45 FLOP per test).
 //  * render_bvh_kernel: one thread per pixel, stack traversal of the 64-byte
 //    two-child-box nodes through the read-only path, near child first.
+//  * render_bvh_spp_kernel<PIX>: a warp spreads the samples of PIX pixels over
+//    its lanes (coherent rays), radiance still summed in sample order.
+//  * grid_*_kernel + the grid paths inside the two BVH kernels: per-frame screen
+//    grid (primary rays) and per-light perspective grid (shadow rays) that hand
+//    every ray a short, exact candidate list instead of a tree walk
+//    (docs/RENDER_SPEC.md section 8); the BVH stays as the fallback.
 //
-// Both produce identical results: the winner of a closest-hit query is the
+// All produce identical results: the winner of a closest-hit query is the
 // lexicographic minimum of (t, id) and the barycentric decision is a pure
 // function of (ray, triangle), so traversal order never shows in the output.
 //
