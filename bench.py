@@ -302,9 +302,29 @@ def inference_leg(ctx, scene, cam, light, params, rank, world, dist, torch, dev,
             # (MLX_PRECISION_BF16X3; bound 1e-4 of the range against the fp32 oracle, tests/test_model_gpu.py)
             "fp32_grade_tensor_core": {"value": res["bf16x3_images_per_s"], "e2e": res["bf16x3_e2e_images_per_s"],
                                        "tensor_core_layers": res["bf16x3_tc_layers"],
-                                       "all_ops_ms": [round(o[0], 4) for o in x3_ops]},
+                                       "all_ops_ms": [round(o[0], 4) for o in x3_ops],
+                                       "roofline": x3_roofline(x3_ops, peaks, src)},
             "tensor_core_layers": res["tc_layers"], "launches_per_image": res["launches_per_image"],
             "render_plus_infer_ms": res["render_plus_infer_ms"], "roofline": roof, "cpu_baseline": cpu}
+
+
+def x3_roofline(ops, peaks, src):
+    """Dominant kernel of the default-precision (bf16x3) path: the slowest of the launches with the most work
+    (a 64->64 layer).  Three bf16 MMAs are issued per fp32-equivalent product, so the tensor-pipe figure counts 3x
+    the layer's algorithmic flops; bytes: activations carried as hi + lo bf16 halves = 4 B per element either side."""
+    k = max(range(len(ops)), key=lambda j: (ops[j][1], ops[j][0]))
+    ms, fl, by = ops[k]
+    peak = peaks.get("bf16_tflops")
+    issued = 3.0 * fl / (ms * 1e-3) / 1e12
+    return {"bound": "tensor", "kernel": f"conv3x3_tc_kernel<64> split mode (op {k}: 3x3 conv 64->64 + bias + relu, hi/lo bf16 in/out)",
+            "achieved": issued, "peak": peak, "unit": "TFLOP/s", "frac": issued / peak if peak else None,
+            "fp32_equivalent_tflops": fl / (ms * 1e-3) / 1e12,
+            "peak_source": f"MEASURED_PEAKS.json bf16_tflops (burst: kernel timed alone), {src}",
+            "kernel_ms": ms, "algorithmic_flops_per_launch": fl, "issued_bf16_flops_per_launch": 3.0 * fl,
+            "algorithmic_bytes_per_launch": by, "hbm_gbs_achieved": by / (ms * 1e-3) / 1e9,
+            "traffic": 1018.3e6,
+            "traffic_source": "ncu --set full, dram__bytes_read+write per launch: 531.4 MB + 486.9 MB "
+                              "(profiles/r01_conv_tc_x3_kernel_ncu_full_summary.csv); tensor pipe active 48.3 %"}
 
 
 # --------------------------------------------------------------------------- GPU arm
