@@ -170,7 +170,7 @@ void Scene::FreeGrid()
 void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* params, cudaStream_t stream)
 {
     m_lgrid.grid.enabled = 0;
-    static int const want = std::getenv("SRT_LIGHT_GRID") ? std::atoi(std::getenv("SRT_LIGHT_GRID")) : 1;
+    int const want = std::getenv("SRT_LIGHT_GRID") ? std::atoi(std::getenv("SRT_LIGHT_GRID")) : 1;   // read per call: tests flip it
     if (!want || params->accel != SRT_ACCEL_BVH || !(RenderUsesGrid(*params) & 2) || m_view.n_tris == 0) return;
     // The light grid depends on the scene and the light position only (not on the camera or the frame):
     // it is kept while the light stays where it is, like the BVH is kept while the scene does.
@@ -293,7 +293,7 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
 void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* params, cudaStream_t stream)
 {
     m_grid.enabled = 0;
-    static int const want = std::getenv("SRT_GRID") ? std::atoi(std::getenv("SRT_GRID")) : 1;
+    int const want = std::getenv("SRT_GRID") ? std::atoi(std::getenv("SRT_GRID")) : 1;   // read per call: tests flip it
     if (!want || params->accel != SRT_ACCEL_BVH || !(RenderUsesGrid(*params) & 1) || m_view.n_tris == 0) return;
     if (params->y0 % kGridTile != 0) return;     // tiles are the render kernels' 8-row blocks
 
