@@ -88,6 +88,7 @@ struct TcParams
     // fp32 accumulator (the lo*lo term, 2^-16 relative, is dropped).
     int split;
     int out_split;       // 1: the fp32-output epilogue writes bf16 [hi: N | lo: N] halves per pixel instead
+    int split_stage;     // out_split through the staging tiles + TMA store (when shared memory has room for them)
     int n_bchunks;
     int a_coord[kMaxChunks];
     int b_chunk[kMaxChunks];
@@ -329,7 +330,10 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
     uint32_t const b_tile_bytes = b_rows * KC * 2u;
     uint32_t const a_stage_bytes = static_cast<uint32_t>(P.stage_bytes);
     uint32_t const n_b_tiles = 9u * static_cast<uint32_t>(P.n_bchunks);
-    uint32_t const out_tile_bytes = P.out_bf16 ? static_cast<uint32_t>(kTileM) * P.N * 2u : 0u;
+    // staged output (TMA store): bf16 layers write N channels per pixel, split layers 2N (hi | lo)
+    bool const staged = P.out_bf16 || P.split_stage;
+    uint32_t const NO = static_cast<uint32_t>(P.split_stage ? 2 * P.N : P.N);
+    uint32_t const out_tile_bytes = staged ? static_cast<uint32_t>(kTileM) * NO * 2u : 0u;
     uint8_t* smem_b = smem;                                       // filter, resident
     uint8_t* smem_a = smem_b + n_b_tiles * b_tile_bytes;           // A ring
     uint8_t* smem_o = smem_a + static_cast<uint32_t>(P.stages) * a_stage_bytes;   // 2 output staging tiles
@@ -553,7 +557,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
         int const units = P.N >> 4, half = static_cast<int>(warp - 2u) >> 2;
         int const c_begin = half == 0 ? 0 : ((units + 1) >> 1) << 4;
         int const c_end = half == 0 ? ((units + 1) >> 1) << 4 : P.N;
-        int const OC = P.N < 64 ? P.N : 64;                  // channels per output box / staging chunk
+        int const OC = NO < 64u ? static_cast<int>(NO) : 64;  // channels per output box / staging chunk
         uint32_t const row_bytes = static_cast<uint32_t>(OC) * 2u;
         uint32_t const swz_mask = row_bytes == 128u ? 7u : (row_bytes == 64u ? 3u : 1u);
         uint32_t const chunk_bytes = static_cast<uint32_t>(kTileM) * row_bytes;
@@ -618,22 +622,43 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
 #pragma unroll
                         for (int j = 0; j < 16; j++) v[j] = tc_act(v[j], P.act, P.alpha);
                     }
-                    if (P.out_bf16)
-                    {
-                        // 16 channels = two 16-byte units of this pixel's row in staging chunk cb / 64
-                        uint32_t const oc = static_cast<uint32_t>(cb) >> 6;
-                        uint32_t const unit = (static_cast<uint32_t>(cb) & 63u) >> 3;
+                    // 16 packed channels starting at channel c = two 16-byte units of this pixel's row in staging
+                    // chunk c / 64, under the swizzle TMA expects (address bits, 1024-aligned base)
+                    auto stage16 = [&](uint32_t c, uint4 lo8, uint4 hi8) {
+                        uint32_t const oc = c >> 6, unit = (c & 63u) >> 3;
                         uint32_t off0 = row * row_bytes + unit * 16u;
                         uint32_t off1 = off0 + 16u;
-                        off0 ^= ((off0 >> 7) & swz_mask) << 4;   // the swizzle TMA expects (address bits, 1024-aligned base)
+                        off0 ^= ((off0 >> 7) & swz_mask) << 4;
                         off1 ^= ((off1 >> 7) & swz_mask) << 4;
                         uint8_t* const base = stg + oc * chunk_bytes;
-                        *reinterpret_cast<uint4*>(base + off0) =
-                            make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
-                                       pack_bf16(v[6], v[7]));
-                        *reinterpret_cast<uint4*>(base + off1) =
-                            make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
-                                       pack_bf16(v[14], v[15]));
+                        *reinterpret_cast<uint4*>(base + off0) = lo8;
+                        *reinterpret_cast<uint4*>(base + off1) = hi8;
+                    };
+                    if (P.out_bf16)
+                    {
+                        stage16(static_cast<uint32_t>(cb),
+                                make_uint4(pack_bf16(v[0], v[1]), pack_bf16(v[2], v[3]), pack_bf16(v[4], v[5]),
+                                           pack_bf16(v[6], v[7])),
+                                make_uint4(pack_bf16(v[8], v[9]), pack_bf16(v[10], v[11]), pack_bf16(v[12], v[13]),
+                                           pack_bf16(v[14], v[15])));
+                    }
+                    else if (P.split_stage)
+                    {
+                        // bf16x3 through the staging tile: hi at channel cb, lo at channel N + cb of the 2N-channel row
+                        uint32_t hi[8], lo[8];
+#pragma unroll
+                        for (int j = 0; j < 8; j++)
+                        {
+                            __nv_bfloat162 hh = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+                            float2 const hf = __bfloat1622float2(hh);
+                            __nv_bfloat162 ll = __floats2bfloat162_rn(v[2 * j] - hf.x, v[2 * j + 1] - hf.y);
+                            hi[j] = *reinterpret_cast<uint32_t*>(&hh);
+                            lo[j] = *reinterpret_cast<uint32_t*>(&ll);
+                        }
+                        stage16(static_cast<uint32_t>(cb), make_uint4(hi[0], hi[1], hi[2], hi[3]),
+                                make_uint4(hi[4], hi[5], hi[6], hi[7]));
+                        stage16(static_cast<uint32_t>(P.N + cb), make_uint4(lo[0], lo[1], lo[2], lo[3]),
+                                make_uint4(lo[4], lo[5], lo[6], lo[7]));
                     }
                     else if (P.out_split)
                     {
@@ -688,7 +713,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
             if (lane == 0) bar_arrive(&acc_empty[acc]);
             if (++acc == static_cast<uint32_t>(P.n_acc)) { acc = 0; aph ^= 1u; }
 
-            if (P.out_bf16)
+            if (staged)
             {
                 // generic-proxy writes -> visible to the async proxy (TMA) ; the issuer first makes sure
                 // the store that last read the OTHER staging tile is done, so that after the barrier
@@ -701,7 +726,7 @@ conv3x3_tc_kernel(const __grid_constant__ CUtensorMap in_map, const __grid_const
                 TC_PROF_ADD(4);
                 if (issuer)
                 {
-                    for (int oc = 0; oc * 64 < P.N; oc++)
+                    for (int oc = 0; oc * 64 < static_cast<int>(NO); oc++)
                         tma_store_3d(&out_map, stg + oc * chunk_bytes, oc * 64, x0, y);
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 }
@@ -1218,11 +1243,12 @@ size_t StageBytes(int KC)
     return HaloMode(KC) ? halo : static_cast<size_t>(3) * kTileM * KC * 2;
 }
 
-size_t SmemBytes(int N, int Cin, int KC, int stages, bool out_bf16, int rps = 1)
+// staged_channels: channels per pixel of the two output staging tiles (0: direct stores, no staging)
+size_t SmemBytes(int N, int Cin, int KC, int stages, int staged_channels, int rps = 1)
 {
     size_t b = static_cast<size_t>(9) * N * Cin * 2;
     size_t a = static_cast<size_t>(stages) * StageBytes(KC) * rps;
-    size_t o = out_bf16 ? static_cast<size_t>(2) * kTileM * N * 2 : 0;   // two staging tiles for the TMA store
+    size_t o = static_cast<size_t>(2) * kTileM * staged_channels * 2;    // two staging tiles for the TMA store
     return 1024 /*alignment slack*/ + b + a + o + (2 * kMaxStages + 1 + 2 * kMaxAcc) * sizeof(uint64_t) + 16;
 }
 
@@ -1290,8 +1316,8 @@ bool ConvTcSupported(int KH, int KW, int stride, int dilation, bool same_padding
     if (split && N > 256) return false;
     // split: the resident filter holds the hi and the lo half, the output is fp32 (no staging tiles);
     // three ring stages at least, or the MMA pipe waits on every TMA round trip
-    if (split) return SmemBytes(N, 2 * Cin, KC, 3, false) <= 226u * 1024u;
-    return SmemBytes(N, Cin, KC, 2, true) <= 226u * 1024u;
+    if (split) return SmemBytes(N, 2 * Cin, KC, 3, 0) <= 226u * 1024u;
+    return SmemBytes(N, Cin, KC, 2, N) <= 226u * 1024u;
 }
 
 std::vector<uint16_t> ConvTcPackWeights(float const* hwio, int Cin, int Cout, int Cin_pad)
@@ -1401,7 +1427,12 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     p.halo = HaloMode(p.KC) ? 1 : 0;
     p.row_bytes = static_cast<int>(StageBytes(p.KC));
     int const want_rps = std::getenv("MLB200_TC_RPS") ? std::atoi(std::getenv("MLB200_TC_RPS")) : 3;
-    p.rps = (want_rps == 3 && SmemBytes(p.N, Ct, p.KC, 2, out_bf16, 3) <= 226u * 1024u) ? 3 : 1;
+    // split output through staging + TMA store when four ring stages still fit next to it (thin layers: the
+    // epilogue's direct 16-byte stores were the bound of the 3->64 layer, 3100 of its 3400 cycles per tile)
+    p.split_stage = (out_split && d_out_bf16 != nullptr && EnvInt("MLB200_X3_STAGE", 1) != 0
+                     && SmemBytes(p.N, Ct, p.KC, 4, 2 * p.N) <= 226u * 1024u) ? 1 : 0;
+    int const staged_channels = out_bf16 ? p.N : (p.split_stage ? 2 * p.N : 0);
+    p.rps = (want_rps == 3 && SmemBytes(p.N, Ct, p.KC, 2, staged_channels, 3) <= 226u * 1024u) ? 3 : 1;
     p.stage_bytes = p.rps * p.row_bytes;
     p.tap_stride = p.halo ? p.KC * 2 : kTileM * p.KC * 2;
     p.stage_tx = p.rps * (p.halo ? (kTileM + 2) * p.KC * 2 : 3 * kTileM * p.KC * 2);
@@ -1427,8 +1458,8 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
     }
     else
     {
-        while (p.stages > 2 && SmemBytes(p.N, Ct, p.KC, p.stages, out_bf16, p.rps) > 226u * 1024u) p.stages--;
-        op->smem = SmemBytes(p.N, Ct, p.KC, p.stages, out_bf16, p.rps);
+        while (p.stages > 2 && SmemBytes(p.N, Ct, p.KC, p.stages, staged_channels, p.rps) > 226u * 1024u) p.stages--;
+        op->smem = SmemBytes(p.N, Ct, p.KC, p.stages, staged_channels, p.rps);
         op->grid = p.n_tiles < sm_count ? p.n_tiles : sm_count;
     }
     if (op->smem > 226u * 1024u) throw std::runtime_error("filter does not fit in shared memory");
@@ -1450,12 +1481,13 @@ ConvTc* ConvTcCreate(void const* d_in, void const* d_w_packed, void* d_out_bf16,
         Encode(&op->w_map, d_w_packed, 2, dims, strides, box, SwizzleFor(p.KC));
     }
     // bf16 output: [H][W][N] bf16, box = min(N, 64) channels x 128 pixels (the TMA store clips at W)
-    if (out_bf16)
+    if (out_bf16 || p.split_stage)
     {
         if (d_out_bf16 == nullptr) throw std::runtime_error("bf16 output buffer missing");
-        int const OC = p.N < 64 ? p.N : 64;
-        cuuint64_t dims[3] = {static_cast<cuuint64_t>(p.N), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H)};
-        cuuint64_t strides[2] = {static_cast<cuuint64_t>(p.N) * 2, static_cast<cuuint64_t>(W) * p.N * 2};
+        int const NO = p.split_stage ? 2 * p.N : p.N;      // split: [hi: N | lo: N] per pixel
+        int const OC = NO < 64 ? NO : 64;
+        cuuint64_t dims[3] = {static_cast<cuuint64_t>(NO), static_cast<cuuint64_t>(W), static_cast<cuuint64_t>(H)};
+        cuuint64_t strides[2] = {static_cast<cuuint64_t>(NO) * 2, static_cast<cuuint64_t>(W) * NO * 2};
         cuuint32_t box[3] = {static_cast<cuuint32_t>(OC), kTileM, 1};
         Encode(&op->out_map, d_out_bf16, 3, dims, strides, box, SwizzleFor(OC));
     }

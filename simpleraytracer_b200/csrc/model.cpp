@@ -766,7 +766,7 @@ void Model::AllocateBuffers()
                 ML_CUDA_CHECK(cudaMemcpy(d, packed.data(), packed.size() * 2, cudaMemcpyHostToDevice));
             }
             op.tc_op = nn::ConvTcCreate(a.split ? m_buffers[a.buffer] : m_split_buffer, m_packed[op.packed_split],
-                                        nullptr, a.H, a.W, cp, o.C, false, op.act, op.alpha,
+                                        o.split ? m_buffers[o.buffer] : nullptr, a.H, a.W, cp, o.C, false, op.act, op.alpha,
                                         m_device->prop.multiProcessorCount, true, o.split);
             continue;
         }
