@@ -571,7 +571,8 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         // chunks are sized by the rows this launch OWNS: each one costs a launch, two events and a copy
         // setup (~20 us), which a rank that owns 135 rows of a 1080p frame cannot hide behind 8 of them
         size_t const owned = rows / stride;
-        size_t n_chunks = owned >= 64 ? std::min<size_t>(8, std::max<size_t>(1, owned / 48)) : 1;
+        static size_t const max_chunks = std::getenv("SRT_HOST_CHUNKS") ? std::max(1, std::atoi(std::getenv("SRT_HOST_CHUNKS"))) : 8;
+        size_t n_chunks = owned >= 64 ? std::min<size_t>(max_chunks, std::max<size_t>(1, owned / 48)) : 1;
         size_t const chunk_rows = ((rows + n_chunks - 1) / n_chunks + group - 1) / group * group;
         n_chunks = (rows + chunk_rows - 1) / chunk_rows;
         while (m_chunk_events.size() < 2 * n_chunks + 2)
