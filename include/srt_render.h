@@ -54,7 +54,10 @@ enum srt_shade_mode
 enum srt_accel_mode
 {
     SRT_ACCEL_BRUTE = 0, /* every ray tests every triangle (FP32-pipe roofline)   */
-    SRT_ACCEL_BVH = 1    /* stack traversal of the scene BVH                      */
+    SRT_ACCEL_BVH = 1    /* accelerated: exact candidate grids built on the device (screen tiles for primary
+                            rays, a perspective grid around the light for shadow rays; docs/RENDER_SPEC.md
+                            section 8) in front of a stack traversal of the scene BVH.  Same image as
+                            SRT_ACCEL_BRUTE, bit for bit.                                                  */
 };
 
 struct srt_render_params
