@@ -581,6 +581,12 @@ __device__ __forceinline__ bool grid_tile_range(GridBuild const& G, float4 box, 
 // Can any query inside tile (tx, ty) pass the triangle's edge functions?  The functions already carry the
 // margin of ONE query (half_extent); a tile is a square of `tile` units, so its centre gets the remaining
 // half width in the L1 norm of each normal.  Evaluated identically by the count and the fill kernel.
+__device__ __forceinline__ bool grid_row_owned(GridBuild const& G, int ty)
+{
+    uint32_t const t = static_cast<uint32_t>(ty);
+    return t >= G.ty_begin && t < G.ty_end && (G.ty_stride <= 1u || t % G.ty_stride == G.ty_phase);
+}
+
 __device__ __forceinline__ bool grid_tile_touches(GridBuild const& G, float4 const (&edge)[3], int tx, int ty)
 {
     float const t = static_cast<float>(G.tile);
@@ -614,8 +620,11 @@ __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__
     else if (binned)
     {
         for (int ty = ty0; ty <= ty1; ty++)
+        {
+            if (!grid_row_owned(G, ty)) continue;
             for (int tx = tx0; tx <= tx1; tx++)
                 if (grid_tile_touches(G, edge, tx, ty)) atomicAdd(&G.tile_cnt[ty * G.tiles_w + tx], 1u);
+        }
     }
     else
     {
@@ -735,7 +744,7 @@ __global__ void __launch_bounds__(256) grid_fill_kernel(const __grid_constant__ 
     for (int ty = ty0; ty <= ty1; ty++)
         for (int tx = tx0; tx <= tx1; tx++)
         {
-            if (!grid_tile_touches(G, edge, tx, ty)) continue;
+            if (!grid_row_owned(G, ty) || !grid_tile_touches(G, edge, tx, ty)) continue;
             uint32_t const t = ty * G.tiles_w + tx;
             G.items[G.tile_off[t] + atomicAdd(&G.cursor[t], 1u)] = i;
         }

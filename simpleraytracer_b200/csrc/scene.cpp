@@ -252,6 +252,7 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     b.pad = 4.0f * m_pad;
     b.width = gw; b.height = gh; b.tiles_w = gw; b.tiles_h = gh; b.cap = cap;
     b.tile = 1; b.lo_bias = 0.f;
+    b.ty_begin = 0; b.ty_end = gh; b.ty_stride = 1; b.ty_phase = 0;
     b.max_tiles_per_tri = 1u << 16;    // built once per light position: a few long loops are affordable
     b.tile_cnt = t; b.tile_off = t + tiles; b.cursor = t + 2 * static_cast<size_t>(tiles) + 1;
     b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;
@@ -351,6 +352,11 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
     b.pad = 4.0f * m_pad;
     b.width = params->width; b.height = params->height; b.tiles_w = tw; b.tiles_h = th; b.cap = cap;
     b.tile = kGridTile; b.lo_bias = 1.f;
+    // only the tile rows this call renders (a rank of an interleaved multi-GPU frame owns every N-th)
+    b.ty_begin = params->y0 / kGridTile;
+    b.ty_end = (params->y1 + kGridTile - 1) / kGridTile;
+    b.ty_stride = params->row_block_stride > 1 ? params->row_block_stride : 1;
+    b.ty_phase = params->row_block_phase;
     b.max_tiles_per_tri = 1024;
     b.tile_cnt = t; b.tile_off = t + tiles; b.cursor = t + 2 * static_cast<size_t>(tiles) + 1;
     b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;

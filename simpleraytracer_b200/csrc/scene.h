@@ -218,6 +218,9 @@ struct GridBuild
     uint32_t width, height, tiles_w, tiles_h, cap;
     uint32_t tile;          // grid units per tile: 8 (pixels, camera grid) or 1 (light grid)
     uint32_t max_tiles_per_tri; // a triangle whose box spans more tiles goes to the global list
+    // tile rows this call renders: [ty_begin, ty_end), and with ty_stride > 1 only rows ty % ty_stride == ty_phase
+    // (interleaved multi-GPU sharding); other rows get no entries.  The light grid covers every row.
+    uint32_t ty_begin, ty_end, ty_stride, ty_phase;
     float lo_bias;          // 1: queries are closed unit squares [x, x+1] (pixels); 0: points
     uint32_t* tile_cnt; uint32_t* tile_off; uint32_t* cursor; uint32_t* items;
     uint32_t* block_sums;   // [tiles / 4096 + 1] scratch of the prefix sum
