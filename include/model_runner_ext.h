@@ -47,6 +47,13 @@ ML_API_ENTRY ml_status mlxIpcExportImage(ml_image image, void* handle_out);
 ML_API_ENTRY void* mlxIpcOpen(ml_context context, void const* handle);
 ML_API_ENTRY void mlxIpcClose(ml_context context, void* device_pointer);
 
+/* Raw device memory on the context's GPU (zero-filled) that can be shared with other processes: the
+ * completion flags of a multi-GPU frame (srt_render.h) live in such a buffer on GPU 0.  mlxIpcExportPointer
+ * writes the 64-byte handle of a buffer obtained from mlxDeviceAlloc; peers map it with mlxIpcOpen. */
+ML_API_ENTRY void* mlxDeviceAlloc(ml_context context, size_t bytes);
+ML_API_ENTRY void mlxDeviceFree(ml_context context, void* device_pointer);
+ML_API_ENTRY ml_status mlxIpcExportPointer(ml_context context, void* device_pointer, void* handle_out);
+
 /* Arithmetic of the model's 3x3 / stride 1 / SAME convolution layers with 16, 32 or 64k input
  * channels (a thinner first layer, e.g. RGB, is zero-padded to 16) whose filter fits in shared
  * memory; every other layer always runs in fp32 on the CUDA cores.
@@ -80,6 +87,11 @@ ML_API_ENTRY ml_status mlxInferBatch(ml_model model, ml_image const* inputs, ml_
  * bytes of the op; *n_ops receives the number of ops.  Measurement aid for roofline reports. */
 ML_API_ENTRY ml_status mlxProfileModel(ml_model model, ml_image input, ml_image output, float* op_ms,
                                        double* op_flops, double* op_bytes, size_t max_ops, size_t* n_ops);
+
+/* Device time of the last successful mlxInferBatch() in ms, CUDA events inside the library: from the first
+ * image's upload being enqueued on the copy-in stream to the last image's read-back (or, when no host copy
+ * is due, its last kernel) completing.  Measurement aid for bench.py. */
+ML_API_ENTRY float mlxModelLastBatchMs(ml_model model);
 
 /* Number of kernel launches one mlInfer() of this model enqueues. */
 ML_API_ENTRY size_t mlxModelLaunchCount(ml_model model);

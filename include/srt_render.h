@@ -88,7 +88,10 @@ struct srt_render_stats
     uint64_t shadow_rays;
     uint64_t box_tests;   /* only with collect_stats                             */
     uint64_t tri_tests;   /* only with collect_stats                             */
-    float kernel_ms;      /* CUDA-event time of the render kernel(s)             */
+    float kernel_ms;      /* CUDA-event time of the call's device work: grid build + render kernel(s) */
+    float grid_build_ms;  /* of which: per-frame candidate-grid build (srtRenderDevice* only, else 0) */
+    float light_grid_build_ms; /* build time of the light grid now in use (built once per light position,
+                                  outside later frames: 0 when no light grid exists)                   */
 };
 
 struct srt_scene_info
@@ -164,6 +167,70 @@ ML_API_ENTRY ml_status srtGetRenderStats(srt_scene scene, srt_render_stats* stat
 ML_API_ENTRY ml_status srtRenderToImage(srt_scene scene, srt_camera const* camera,
                                         srt_light const* light, srt_render_params const* params,
                                         ml_image image, srt_render_stats* stats);
+
+/* ---- multi-GPU frames ---------------------------------------------------
+ * One frame is sharded over N GPUs in interleaved 8-row blocks (params.row_block_stride = N,
+ * row_block_phase = rank; scene replicated).  Every GPU's render kernel stores its pixels straight into
+ * ONE frame buffer (the memory of GPU 0, peer-mapped: cudaDeviceEnablePeerAccess inside one process,
+ * mlxIpcOpen across processes) and its last block publishes a completion flag next to it; GPU 0 waits
+ * for the flags on the device.  No gather pass, no host round trip, no collective.
+ *
+ * Flag array (uint32, zero-initialised, in GPU 0's memory): flags[chunk * n_ranks + rank].  A frame uses a
+ * new `value` (an epoch that only grows); waiting is "flag - value >= 0" in wrap-safe arithmetic. */
+
+/* Rows [y0, y1) cut into at most requested_chunks chunks of whole (8 * stride)-row groups: the layout both
+ * srtRenderDeviceSignal and srtGatherFrameHost use.  Chunk k covers rows [y0 + k*chunk_rows, ...). */
+ML_API_ENTRY ml_status srtChunkLayout(srt_render_params const* params, uint32_t requested_chunks,
+                                      uint32_t* chunk_rows, uint32_t* n_chunks);
+
+/* srtRenderDevice + completion flags: the band is rendered as the chunks of srtChunkLayout(params, n_chunks)
+ * and chunk k's last block stores `value` to ((uint32_t*)d_flags)[k * chunk_stride] with system-scope
+ * release ordering after all of the chunk's pixels (d_flags may be peer memory).  Asynchronous. */
+ML_API_ENTRY ml_status srtRenderDeviceSignal(srt_scene scene, srt_camera const* camera,
+                                             srt_light const* light, srt_render_params const* params,
+                                             void* d_rgb, void* d_hit_id, void* d_hit_t, void* stream,
+                                             void* d_flags, uint32_t chunk_stride, uint32_t n_chunks,
+                                             uint32_t value);
+
+/* Enqueues on `stream` (NULL: the context's stream) a device-side wait until the `count` flags
+ * d_flags[k * stride] have reached `value`; work enqueued behind it sees the signalling kernels' pixels.
+ * The wait gives up after timeout_ms (0: 2000) so a dead peer cannot hang the GPU; timeouts are counted
+ * (srtFlagWaitTimeouts, cumulative per context, valid after the stream has been synchronised). */
+ML_API_ENTRY ml_status srtStreamWaitFlags(ml_context context, void* stream, void const* d_flags,
+                                          uint32_t count, uint32_t stride, uint32_t value, uint32_t timeout_ms);
+/* Enqueues a release store of `value` to *d_flag (e.g. "frame consumed", the reverse direction). */
+ML_API_ENTRY ml_status srtStreamWriteFlag(ml_context context, void* stream, void* d_flag, uint32_t value);
+ML_API_ENTRY uint32_t srtFlagWaitTimeouts(ml_context context);
+
+/* GPU 0's half of a host-buffer frame: for every chunk of srtChunkLayout(params, n_chunks) waits (on the
+ * device) for the n_ranks flags of that chunk and copies the chunk's rows of d_rgb (full frame, W*H*3
+ * floats on the context's GPU) into rgb_host while later chunks are still being rendered.  Page-locked
+ * destinations are written straight from the device, pageable ones through pinned staging.  Synchronous;
+ * ML_FAIL (message on the context) if a wait timed out. */
+ML_API_ENTRY ml_status srtGatherFrameHost(ml_context context, srt_render_params const* params,
+                                          void const* d_rgb, void const* d_flags, uint32_t n_ranks,
+                                          uint32_t n_chunks, uint32_t value, float* rgb_host,
+                                          uint32_t timeout_ms);
+
+/* One process, N GPUs (the host side stays C++; no torch, no NCCL): a scene group holds a context and a
+ * scene replica per device (BVH built once), GPU devices[0] owns the frame and the flags, every other
+ * device gets peer access to it, and one persistent host thread per device issues that device's work.
+ * error/error_size receive the reason when creation fails (NULL return). */
+typedef struct srt_scene_group_t* srt_scene_group;
+ML_API_ENTRY srt_scene_group srtCreateSceneGroup(int const* devices, uint32_t n_devices, size_t n_triangles,
+                                                 float const* vertices, float const* albedo, int build_bvh,
+                                                 char* error, size_t error_size);
+/* Renders the full frame on all devices of the group.  rgb_host != NULL: H*W*3 floats receive the frame
+ * (chunked: the copy of chunk k overlaps the rendering of chunk k+1); NULL: the frame stays in GPU 0's
+ * memory (srtSceneGroupFrame).  params.y0/y1/buf_y0/row_block_* are set by the call (whole frame).
+ * Synchronous.  stats: rays summed over the devices; kernel_ms = GPU 0's timeline from its first launch to
+ * "all flags seen" (the frame time on the device). */
+ML_API_ENTRY ml_status srtRenderGroup(srt_scene_group group, srt_camera const* camera, srt_light const* light,
+                                      srt_render_params const* params, float* rgb_host, srt_render_stats* stats);
+ML_API_ENTRY void* srtSceneGroupFrame(srt_scene_group group);
+ML_API_ENTRY uint32_t srtSceneGroupSize(srt_scene_group group);
+ML_API_ENTRY char* srtGetSceneGroupError(srt_scene_group group, char* buffer, size_t buffer_size);
+ML_API_ENTRY void srtReleaseSceneGroup(srt_scene_group group);
 
 /* Independent-FFMA microbenchmark over all SMs: the FP32 roofline denominator
  * (MEASURED_PEAKS.json carries no FP32 figure).  Returns TFLOP/s (FMA = 2). */

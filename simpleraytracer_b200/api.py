@@ -52,7 +52,8 @@ class srt_render_params(C.Structure):
 
 class srt_render_stats(C.Structure):
     _fields_ = [("primary_rays", C.c_uint64), ("shadow_rays", C.c_uint64), ("box_tests", C.c_uint64),
-                ("tri_tests", C.c_uint64), ("kernel_ms", C.c_float)]
+                ("tri_tests", C.c_uint64), ("kernel_ms", C.c_float), ("grid_build_ms", C.c_float),
+                ("light_grid_build_ms", C.c_float)]
 
 
 class srt_scene_info(C.Structure):
@@ -99,6 +100,7 @@ _PROTOTYPES = {
     "mlxInspectModel": (C.c_int, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]),
     "mlxImageDevicePointer": (C.c_void_p, [C.c_void_p, C.c_int, C.c_void_p]),
     "mlxModelLaunchCount": (C.c_size_t, [C.c_void_p]),
+    "mlxModelLastBatchMs": (C.c_float, [C.c_void_p]),
     "mlxSetModelPrecision": (C.c_int, [C.c_void_p, C.c_int]),
     "mlxProfileModel": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
                                   C.c_void_p]),
@@ -108,6 +110,26 @@ _PROTOTYPES = {
     "mlxIpcExportImage": (C.c_int, [C.c_void_p, C.c_void_p]),
     "mlxIpcOpen": (C.c_void_p, [C.c_void_p, C.c_void_p]),
     "mlxIpcClose": (None, [C.c_void_p, C.c_void_p]),
+    "mlxDeviceAlloc": (C.c_void_p, [C.c_void_p, C.c_size_t]),
+    "mlxDeviceFree": (None, [C.c_void_p, C.c_void_p]),
+    "mlxIpcExportPointer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
+    "srtChunkLayout": (C.c_int, [C.POINTER(srt_render_params), C.c_uint32, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]),
+    "srtRenderDeviceSignal": (C.c_int, [C.c_void_p, C.POINTER(srt_camera), C.POINTER(srt_light),
+                                        C.POINTER(srt_render_params), C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "srtStreamWaitFlags": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]),
+    "srtStreamWriteFlag": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint32]),
+    "srtFlagWaitTimeouts": (C.c_uint32, [C.c_void_p]),
+    "srtGatherFrameHost": (C.c_int, [C.c_void_p, C.POINTER(srt_render_params), C.c_void_p, C.c_void_p, C.c_uint32,
+                                     C.c_uint32, C.c_uint32, C.c_void_p, C.c_uint32]),
+    "srtCreateSceneGroup": (C.c_void_p, [C.c_void_p, C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p, C.c_int,
+                                         C.c_char_p, C.c_size_t]),
+    "srtRenderGroup": (C.c_int, [C.c_void_p, C.POINTER(srt_camera), C.POINTER(srt_light),
+                                 C.POINTER(srt_render_params), C.c_void_p, C.POINTER(srt_render_stats)]),
+    "srtSceneGroupFrame": (C.c_void_p, [C.c_void_p]),
+    "srtSceneGroupSize": (C.c_uint32, [C.c_void_p]),
+    "srtGetSceneGroupError": (C.c_void_p, [C.c_void_p, C.c_char_p, C.c_size_t]),
+    "srtReleaseSceneGroup": (None, [C.c_void_p]),
 }
 
 _lib = None
@@ -203,6 +225,41 @@ class Context:
 
     def ipc_close(self, ptr: int):
         self.lib.mlxIpcClose(self.handle, ptr)
+
+    def device_alloc(self, nbytes: int) -> int:
+        """mlxDeviceAlloc: zero-filled raw device memory (e.g. the flag array of a multi-GPU frame)."""
+        p = self.lib.mlxDeviceAlloc(self.handle, nbytes)
+        if not p:
+            raise MLError(self.error())
+        return int(p)
+
+    def device_free(self, ptr: int):
+        self.lib.mlxDeviceFree(self.handle, ptr)
+
+    def ipc_export_pointer(self, ptr: int) -> bytes:
+        buf = C.create_string_buffer(64)
+        if self.lib.mlxIpcExportPointer(self.handle, ptr, buf) != ML_OK:
+            raise MLError(self.error())
+        return buf.raw
+
+    def stream_wait_flags(self, d_flags: int, count: int, value: int, stride=1, stream=0, timeout_ms=0):
+        """srtStreamWaitFlags: device-side wait (spin kernel) until `count` flags have reached `value`."""
+        if self.lib.srtStreamWaitFlags(self.handle, stream or None, d_flags, count, stride, value, timeout_ms) != ML_OK:
+            raise MLError(self.error())
+
+    def stream_write_flag(self, d_flag: int, value: int, stream=0):
+        if self.lib.srtStreamWriteFlag(self.handle, stream or None, d_flag, value) != ML_OK:
+            raise MLError(self.error())
+
+    def flag_wait_timeouts(self) -> int:
+        return int(self.lib.srtFlagWaitTimeouts(self.handle))
+
+    def gather_frame_host(self, params, d_rgb: int, d_flags: int, n_ranks: int, n_chunks: int, value: int,
+                          rgb_host: np.ndarray, timeout_ms=0):
+        """srtGatherFrameHost: rank 0's half of a host-buffer multi-GPU frame."""
+        if self.lib.srtGatherFrameHost(self.handle, C.byref(params), d_rgb, d_flags, n_ranks, n_chunks, value,
+                                       rgb_host.ctypes.data, timeout_ms) != ML_OK:
+            raise MLError(self.error())
 
     def measure_fp32_peak(self, repeats=5) -> float:
         return float(self.lib.srtMeasureFp32Peak(self.handle, repeats))
@@ -323,6 +380,10 @@ class Model:
         if self.lib.mlxInferBatch(self.handle, ia, oa, n) != ML_OK:
             raise MLError(self.error())
 
+    def last_batch_ms(self) -> float:
+        """mlxModelLastBatchMs: device span of the last infer_batch (CUDA events inside the library)."""
+        return float(self.lib.mlxModelLastBatchMs(self.handle))
+
     def release(self):
         if self.handle:
             self.lib.mlReleaseModel(self.handle)
@@ -393,6 +454,15 @@ class Scene:
         if st != ML_OK:
             raise MLError(self.error())
 
+    def render_device_signal(self, camera, light, params, d_rgb, d_flags, value, chunk_stride=1, n_chunks=1,
+                             stream=0):
+        """srtRenderDeviceSignal: srtRenderDevice whose last block(s) publish completion flags."""
+        st = self.lib.srtRenderDeviceSignal(self.handle, C.byref(camera), C.byref(light), C.byref(params),
+                                            d_rgb or None, None, None, stream or None, d_flags, chunk_stride,
+                                            n_chunks, value)
+        if st != ML_OK:
+            raise MLError(self.error())
+
     def stats(self) -> srt_render_stats:
         s = srt_render_stats()
         if self.lib.srtGetRenderStats(self.handle, C.byref(s)) != ML_OK:
@@ -410,6 +480,56 @@ class Scene:
     def release(self):
         if self.handle:
             self.lib.srtReleaseScene(self.handle)
+            self.handle = None
+
+    __del__ = release
+
+
+def chunk_layout(params, requested_chunks):
+    rows, n = C.c_uint32(0), C.c_uint32(0)
+    if load_library().srtChunkLayout(C.byref(params), requested_chunks, C.byref(rows), C.byref(n)) != ML_OK:
+        raise MLError("srtChunkLayout failed")
+    return rows.value, n.value
+
+
+class SceneGroup:
+    """srtCreateSceneGroup / srtRenderGroup: one process, N GPUs, one frame (peer stores + device flags)."""
+
+    def __init__(self, devices, vertices: np.ndarray, albedo: np.ndarray | None = None, build_bvh=True):
+        self.lib = load_library()
+        v = np.ascontiguousarray(vertices, dtype=np.float32).reshape(-1, 9)
+        a = None if albedo is None else np.ascontiguousarray(albedo, dtype=np.float32).reshape(-1, 3)
+        dev = (C.c_int * len(devices))(*devices)
+        err = C.create_string_buffer(1024)
+        self.handle = self.lib.srtCreateSceneGroup(dev, len(devices), len(v), v.ctypes.data if len(v) else None,
+                                                   a.ctypes.data if a is not None and len(a) else None,
+                                                   int(build_bvh), err, len(err))
+        if not self.handle:
+            raise MLError(err.value.decode(errors="replace"))
+
+    def error(self) -> str:
+        return _err(self.lib.srtGetSceneGroupError, self.handle)
+
+    def size(self) -> int:
+        return int(self.lib.srtSceneGroupSize(self.handle))
+
+    def frame_pointer(self) -> int:
+        return int(self.lib.srtSceneGroupFrame(self.handle) or 0)
+
+    def render(self, camera, light, params, rgb_host: np.ndarray | None = None, want_host=True):
+        """Returns (rgb or None, stats).  want_host=False leaves the frame on GPU 0."""
+        if want_host and rgb_host is None:
+            rgb_host = np.zeros((params.height, params.width, 3), dtype=np.float32)
+        stats = srt_render_stats()
+        st = self.lib.srtRenderGroup(self.handle, C.byref(camera), C.byref(light), C.byref(params),
+                                     rgb_host.ctypes.data if want_host else None, C.byref(stats))
+        if st != ML_OK:
+            raise MLError(self.error())
+        return (rgb_host if want_host else None), stats
+
+    def release(self):
+        if self.handle:
+            self.lib.srtReleaseSceneGroup(self.handle)
             self.handle = None
 
     __del__ = release

@@ -68,6 +68,12 @@ struct DeviceState
     cudaEvent_t ev_start = nullptr;
     cudaEvent_t ev_stop = nullptr;
     cudaDeviceProp prop{};
+    // mapped pinned word: number of device-side flag waits that gave up (mlxStreamWaitFlags timeout)
+    uint32_t* wait_timeouts = nullptr;
+    // pinned staging + events of srtGatherFrameHost (pageable destination frames), grown on demand
+    void* gather_stage = nullptr;
+    size_t gather_stage_bytes = 0;
+    cudaEvent_t gather_events[16] = {};
 
     explicit DeviceState(int requested_device = -1); // -1: MLB200_DEVICE, else current device
     ~DeviceState();

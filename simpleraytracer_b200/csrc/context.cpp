@@ -45,6 +45,8 @@ DeviceState::DeviceState(int requested_device)
     ML_CUDA_CHECK(cudaStreamCreateWithFlags(&copy_out, cudaStreamNonBlocking));
     ML_CUDA_CHECK(cudaEventCreate(&ev_start));
     ML_CUDA_CHECK(cudaEventCreate(&ev_stop));
+    ML_CUDA_CHECK(cudaHostAlloc(reinterpret_cast<void**>(&wait_timeouts), sizeof(uint32_t), cudaHostAllocMapped));
+    *wait_timeouts = 0;
 }
 
 DeviceState::~DeviceState()
@@ -56,6 +58,10 @@ DeviceState::~DeviceState()
     if (copy_in) cudaStreamDestroy(copy_in);
     if (copy_out) cudaStreamDestroy(copy_out);
     if (stream) cudaStreamDestroy(stream);
+    if (wait_timeouts) cudaFreeHost(wait_timeouts);
+    if (gather_stage) cudaFreeHost(gather_stage);
+    for (cudaEvent_t e : gather_events)
+        if (e) cudaEventDestroy(e);
 }
 
 Context::Context(int device) : m_device(std::make_shared<DeviceState>(device)) {}

@@ -166,6 +166,8 @@ Model::~Model()
     ReleaseBuffers();
     for (void* p : m_packed) cudaFree(p);
     for (cudaEvent_t e : m_events) cudaEventDestroy(e);
+    if (m_batch_ev0) cudaEventDestroy(m_batch_ev0);
+    if (m_batch_ev1) cudaEventDestroy(m_batch_ev1);
     for (auto& c : m_consts) cudaFree(c.dev);
 }
 
@@ -1151,6 +1153,14 @@ ml_status Model::InferBatch(ml_image const* inputs, ml_image const* outputs, siz
             ML_CUDA_CHECK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             m_events.push_back(e);
         }
+        if (m_batch_ev0 == nullptr)
+        {
+            ML_CUDA_CHECK(cudaEventCreate(&m_batch_ev0));
+            ML_CUDA_CHECK(cudaEventCreate(&m_batch_ev1));
+        }
+        // device span of the batch (mlxModelLastBatchMs): first upload enqueued -> last read-back done.
+        // s_run / s_out only start behind events of s_in, so the s_in record is the earliest point.
+        ML_CUDA_CHECK(cudaEventRecord(m_batch_ev0, s_in));
         for (size_t i = 0; i < n; i++)
         {
             Image* in = Image::FromHandle(inputs[i]);
@@ -1168,9 +1178,11 @@ ml_status Model::InferBatch(ml_image const* inputs, ml_image const* outputs, siz
             ML_CUDA_CHECK(cudaStreamWaitEvent(s_out, m_events[2 * i + 1], 0));
             out->CommitDeviceWrite(s_out);
         }
+        ML_CUDA_CHECK(cudaEventRecord(m_batch_ev1, s_out));   // s_out waits for the last image's kernels above
         ML_CUDA_CHECK(cudaStreamSynchronize(s_in));
         ML_CUDA_CHECK(cudaStreamSynchronize(s_run));
         ML_CUDA_CHECK(cudaStreamSynchronize(s_out));
+        if (n > 0) ML_CUDA_CHECK(cudaEventElapsedTime(&m_last_batch_ms, m_batch_ev0, m_batch_ev1));
         return ML_OK;
     }
     catch (std::exception const& e)
@@ -1349,6 +1361,12 @@ ML_API_ENTRY size_t mlxModelTensorCoreLayers(ml_model model)
 {
     ML::Model* m = ML::Model::FromHandle(model);
     return m != nullptr ? m->TensorCoreLayers() : 0;
+}
+
+ML_API_ENTRY float mlxModelLastBatchMs(ml_model model)
+{
+    if (ML::Model::FromHandle(model) == nullptr) return 0.f;
+    return ML::Model::FromHandle(model)->LastBatchMs();
 }
 
 ML_API_ENTRY size_t mlxModelLaunchCount(ml_model model)

@@ -45,6 +45,7 @@ public:
 
     // Number of kernel launches one Infer() enqueues (bench bookkeeping).
     size_t LaunchesPerInfer() const;
+    float LastBatchMs() const { return m_last_batch_ms; }
     // Text dump of the detected nodes, shapes and fused plan (mlxInspectModel).
     std::string Describe() const;
 
@@ -134,6 +135,8 @@ private:
 
     int m_precision = 2;
     std::vector<cudaEvent_t> m_events; // pool for InferBatch
+    cudaEvent_t m_batch_ev0 = nullptr, m_batch_ev1 = nullptr; // device span of the last InferBatch (timing enabled)
+    float m_last_batch_ms = 0.f;
     std::vector<void*> m_packed;  // device copies of repacked bf16 filters
     std::vector<void*> m_buffers;
     std::vector<size_t> m_buffer_bytes;

@@ -199,22 +199,54 @@ __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v)
     return v;
 }
 
+// End of a render block: ray counters and the completion signal.
+//  * Counters: warp sums -> shared-memory atomics -> ONE global atomic per counter per block (and only for
+//    counters that are non-zero); box / triangle test counts exist only in the collect_stats variants.
+//  * Signal (RenderLaunch::d_signal, multi-GPU frames): thread 0 of every block fences its block's stores at
+//    system scope (they may be peer stores into another GPU's frame) and takes a ticket; the block that draws
+//    the last ticket resets it and publishes signal_value with a system-scope release store.  A consumer that
+//    observes the value with an acquire load (wait_flags_kernel) therefore sees every pixel of the launch.
+// Called by every thread of the block, outside divergent control flow.
 __device__ __forceinline__ void flush_counters(RenderLaunch const& L, unsigned long long primary,
                                                unsigned long long shadow, unsigned long long boxes,
                                                unsigned long long tris)
 {
+    __shared__ unsigned long long s_cnt[4];
+    if (threadIdx.x < 4) s_cnt[threadIdx.x] = 0ull;
+    __syncthreads();
     primary = warp_sum(primary);
     shadow = warp_sum(shadow);
-    boxes = warp_sum(boxes);
-    tris = warp_sum(tris);
+    if (L.params.collect_stats)
+    {
+        boxes = warp_sum(boxes);
+        tris = warp_sum(tris);
+    }
     if ((threadIdx.x & 31) == 0)
     {
-        atomicAdd(L.d_counters + 0, primary);
-        atomicAdd(L.d_counters + 1, shadow);
+        if (primary) atomicAdd(&s_cnt[0], primary);
+        if (shadow) atomicAdd(&s_cnt[1], shadow);
         if (L.params.collect_stats)
         {
-            atomicAdd(L.d_counters + 2, boxes);
-            atomicAdd(L.d_counters + 3, tris);
+            atomicAdd(&s_cnt[2], boxes);
+            atomicAdd(&s_cnt[3], tris);
+        }
+    }
+    __syncthreads();   // also orders every thread's pixel stores before thread 0's fence below
+    if (threadIdx.x == 0)
+    {
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            if (s_cnt[k]) atomicAdd(L.d_counters + k, s_cnt[k]);
+        if (L.d_signal)
+        {
+            __threadfence_system();
+            uint32_t const blocks = gridDim.x * gridDim.y * gridDim.z;
+            if (atomicAdd(L.d_ticket, 1u) == blocks - 1u)
+            {
+                *L.d_ticket = 0u;   // next launch on this stream starts from zero
+                __threadfence_system();
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(L.d_signal), "r"(L.signal_value) : "memory");
+            }
         }
     }
 }
@@ -727,6 +759,7 @@ __global__ void __launch_bounds__(kScanBlock) grid_scan_blocks_kernel(const __gr
         {
             G.tile_off[base + k] = run;
             G.cursor[base + k] = 0;
+            G.tile_cnt[base + k] = 0;   // invariant: all counts are zero between builds (no per-frame memset)
             run += c[k];
         }
 }
@@ -1313,8 +1346,8 @@ int RenderUsesGrid(srt_render_params const& p)
 void BuildScreenGrid(GridBuild const& build, cudaStream_t stream)
 {
     uint32_t const tiles = build.tiles_w * build.tiles_h;
-    ML_CUDA_CHECK(cudaMemsetAsync(build.tile_cnt, 0, static_cast<size_t>(tiles) * sizeof(uint32_t), stream));
-    ML_CUDA_CHECK(cudaMemsetAsync(build.flags, 0, sizeof(GridFlags), stream));
+    // tile_cnt is all zero here: zero-filled at allocation, re-zeroed by grid_scan_blocks_kernel of the last build.
+    if (!build.flags_prezeroed) ML_CUDA_CHECK(cudaMemsetAsync(build.flags, 0, sizeof(GridFlags), stream));
     uint32_t const blocks = (build.scene.n_tris_padded + 255u) / 256u;
     uint32_t const scan_blocks = (tiles + kScanCells - 1u) / kScanCells;
     grid_count_kernel<<<blocks, 256, 0, stream>>>(build);
@@ -1322,6 +1355,67 @@ void BuildScreenGrid(GridBuild const& build, cudaStream_t stream)
     grid_scan_sums_kernel<<<1, kScanBlock, 0, stream>>>(build, scan_blocks);
     grid_scan_blocks_kernel<<<scan_blocks, kScanBlock, 0, stream>>>(build);
     grid_fill_kernel<<<blocks, 256, 0, stream>>>(build);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------------------
+// Device-side flags: the consumer half of RenderLaunch::d_signal
+// ---------------------------------------------------------------------------
+namespace {
+__device__ __forceinline__ unsigned long long global_timer_ns()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// Thread k spins (acquire loads at system scope) until flags[k * stride] has reached `value` (wrap-safe
+// signed difference); gives up after timeout_ns and counts the timeout in *timeouts (mapped host memory),
+// so a dead peer can never hang the GPU.  Work enqueued behind this kernel sees everything the signalling
+// kernels wrote before their release stores.
+__global__ void wait_flags_kernel(uint32_t const* flags, uint32_t count, uint32_t stride, uint32_t value,
+                                  unsigned long long timeout_ns, uint32_t* timeouts)
+{
+    uint32_t const k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= count) return;
+    uint32_t const* const f = flags + static_cast<size_t>(k) * stride;
+    unsigned long long const t0 = global_timer_ns();
+    uint32_t spins = 0;
+    while (true)
+    {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+        if (static_cast<int32_t>(v - value) >= 0) break;
+        if ((++spins & 63u) == 0u && global_timer_ns() - t0 > timeout_ns)
+        {
+            atomicAdd_system(timeouts, 1u);
+            break;
+        }
+        __nanosleep(100);
+    }
+    __threadfence_system();
+}
+
+__global__ void write_flag_kernel(uint32_t* flag, uint32_t value)
+{
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+} // namespace
+
+void LaunchWaitFlags(uint32_t const* d_flags, uint32_t count, uint32_t stride, uint32_t value,
+                     uint32_t timeout_ms, uint32_t* timeouts_mapped, cudaStream_t stream)
+{
+    if (count == 0) return;
+    uint32_t const threads = count < 256u ? count : 256u;
+    wait_flags_kernel<<<(count + threads - 1u) / threads, threads, 0, stream>>>(
+        d_flags, count, stride, value, static_cast<unsigned long long>(timeout_ms) * 1000000ull, timeouts_mapped);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void LaunchWriteFlag(uint32_t* d_flag, uint32_t value, cudaStream_t stream)
+{
+    write_flag_kernel<<<1, 1, 0, stream>>>(d_flag, value);
     ML_CUDA_CHECK(cudaGetLastError());
 }
 

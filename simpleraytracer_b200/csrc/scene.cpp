@@ -46,10 +46,28 @@ void RowBlocks(srt_render_params const& p, uint32_t& origin, uint32_t& step, uin
     step = 8u * stride;
     count = first < b0 + blocks ? (b0 + blocks - first + stride - 1) / stride : 0;
 }
+
+// Per-frame device scratch (one 64-byte memset per render call): 4 x u64 ray/test counters | 2 x u32 block
+// tickets of the completion signal (one per launch stream) | pad | GridFlags of the screen grid.
+constexpr size_t kScratchBytes = 64;
+constexpr size_t kScratchTicketWord = 8;    // in uint32 units
+constexpr size_t kScratchGridFlagsWord = 12;
 } // namespace
 
+// Rows [y0, y1) cut into at most `requested` chunks of whole (8 * stride)-row groups, so that every chunk
+// holds the same number of row blocks of every rank of an interleaved frame.
+void ChunkLayout(srt_render_params const& p, uint32_t requested, uint32_t& chunk_rows, uint32_t& n_chunks)
+{
+    uint32_t const rows = p.y1 - p.y0;
+    uint32_t const group = 8u * (p.row_block_stride > 1 ? p.row_block_stride : 1u);
+    uint32_t const want = requested > 0 ? requested : 1u;
+    chunk_rows = ((rows + want - 1u) / want + group - 1u) / group * group;
+    if (chunk_rows == 0) chunk_rows = group;
+    n_chunks = rows ? (rows + chunk_rows - 1u) / chunk_rows : 0u;
+}
+
 Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const* albedo,
-             bool build_bvh)
+             bool build_bvh, BvhBuildResult const* prebuilt)
     : m_device(std::move(device))
 {
     if (n > 0 && vertices == nullptr) throw std::runtime_error("Bad vertices argument");
@@ -65,7 +83,8 @@ Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const
     auto t0 = std::chrono::steady_clock::now();
     if (build_bvh)
     {
-        BvhBuildResult bvh = BuildBvh(n, vertices);
+        // a scene group builds the BVH once and hands it to the replica of every device
+        BvhBuildResult bvh = prebuilt ? *prebuilt : BuildBvh(n, vertices);
         m_nodes_host = std::move(bvh.nodes);
         order = bvh.order;
     }
@@ -107,14 +126,14 @@ Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const
         ML_CUDA_CHECK(cudaMalloc(&m_d_tris, tri_bytes));
         ML_CUDA_CHECK(cudaMalloc(&m_d_albedo, alb_bytes));
         if (node_bytes) ML_CUDA_CHECK(cudaMalloc(&m_d_nodes, node_bytes));
-        ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&m_d_counters), 4 * sizeof(unsigned long long)));
+        ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&m_d_counters), kScratchBytes));
         cudaStream_t s = m_device->stream;
         ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s));
         ML_CUDA_CHECK(cudaMemcpyAsync(m_d_tris, soa.data(), tri_bytes, cudaMemcpyHostToDevice, s));
         ML_CUDA_CHECK(cudaMemcpyAsync(m_d_albedo, alb.data(), alb_bytes, cudaMemcpyHostToDevice, s));
         if (node_bytes)
             ML_CUDA_CHECK(cudaMemcpyAsync(m_d_nodes, m_nodes_host.data(), node_bytes, cudaMemcpyHostToDevice, s));
-        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), s));
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, kScratchBytes, s));
         ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, s));
         ML_CUDA_CHECK(cudaStreamSynchronize(s));
         ML_CUDA_CHECK(cudaEventElapsedTime(&m_info.upload_ms, m_device->ev_start, m_device->ev_stop));
@@ -229,6 +248,8 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
         m_d_lgrid_tiles = m_d_lgrid_items = m_d_lgrid_bbox = m_d_lgrid_misc = nullptr;
         m_lgrid_tiles = m_lgrid_cap = 0;
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t)));
+        // tile counts are zero between builds (grid_scan_blocks_kernel re-zeroes them): no per-build memset
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_lgrid_tiles, 0, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t), stream));
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_bbox, 4 * static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));
@@ -254,14 +275,23 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     b.tile = 1; b.lo_bias = 0.f;
     b.ty_begin = 0; b.ty_end = gh; b.ty_stride = 1; b.ty_phase = 0;
     b.max_tiles_per_tri = 1u << 16;    // built once per light position: a few long loops are affordable
-    b.tile_cnt = t; b.tile_off = t + tiles; b.cursor = t + 2 * static_cast<size_t>(tiles) + 1;
-    b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;
+    // laid out by the CAPACITY of the allocation, so the count array never overlaps another array of an
+    // earlier, differently sized build (its all-zero invariant replaces the per-build memset)
+    size_t const cap_tiles = m_lgrid_tiles;
+    b.tile_cnt = t; b.tile_off = t + cap_tiles; b.cursor = t + 2 * cap_tiles + 1;
+    b.block_sums = t + 3 * cap_tiles + 4;
     b.items = static_cast<uint32_t*>(m_d_lgrid_items);
     b.bbox = static_cast<F4*>(m_d_lgrid_bbox);
     b.edges = b.bbox + m_view.n_tris_padded;
     b.half_extent = 0.f;
     b.flags = static_cast<GridFlags*>(m_d_lgrid_misc);
     b.global = reinterpret_cast<uint32_t*>(b.flags + 1);
+    if (m_lgrid_built == nullptr)
+    {
+        ML_CUDA_CHECK(cudaEventCreate(&m_lgrid_ev0));     // timing enabled: srt_render_stats::light_grid_build_ms
+        ML_CUDA_CHECK(cudaEventCreate(&m_lgrid_built));
+    }
+    ML_CUDA_CHECK(cudaEventRecord(m_lgrid_ev0, stream));
     BuildScreenGrid(b, stream);
 
     GridView& gv = m_lgrid.grid;
@@ -274,7 +304,6 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     m_lgrid.cx = 0.5f * static_cast<float>(gw);
     m_lgrid.cy = 0.5f * static_cast<float>(gh);
     gv.enabled = 1;
-    if (m_lgrid_built == nullptr) ML_CUDA_CHECK(cudaEventCreateWithFlags(&m_lgrid_built, cudaEventDisableTiming));
     ML_CUDA_CHECK(cudaEventRecord(m_lgrid_built, stream));
     std::memcpy(m_lgrid_light, light->position, sizeof(m_lgrid_light));
     m_lgrid_valid = true;
@@ -335,6 +364,7 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
         if (m_grid_free) ML_CUDA_CHECK(cudaEventSynchronize(m_grid_free));
         FreeGrid();
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t)));
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_grid_tiles, 0, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t), stream));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_bbox, 4 * static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));
@@ -358,14 +388,18 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
     b.ty_stride = params->row_block_stride > 1 ? params->row_block_stride : 1;
     b.ty_phase = params->row_block_phase;
     b.max_tiles_per_tri = 1024;
-    b.tile_cnt = t; b.tile_off = t + tiles; b.cursor = t + 2 * static_cast<size_t>(tiles) + 1;
-    b.block_sums = t + 3 * static_cast<size_t>(tiles) + 4;
+    // laid out by the CAPACITY of the allocation, so the count array never overlaps another array of an
+    // earlier, differently sized build (its all-zero invariant replaces the per-build memset)
+    size_t const cap_tiles = m_grid_tiles;
+    b.tile_cnt = t; b.tile_off = t + cap_tiles; b.cursor = t + 2 * cap_tiles + 1;
+    b.block_sums = t + 3 * cap_tiles + 4;
     b.items = static_cast<uint32_t*>(m_d_grid_items);
     b.bbox = static_cast<F4*>(m_d_grid_bbox);
     b.edges = b.bbox + m_view.n_tris_padded;
     b.half_extent = 0.5f;
-    b.flags = static_cast<GridFlags*>(m_d_grid_misc);
-    b.global = reinterpret_cast<uint32_t*>(b.flags + 1);
+    b.flags = reinterpret_cast<GridFlags*>(reinterpret_cast<uint32_t*>(m_d_counters) + kScratchGridFlagsWord);
+    b.flags_prezeroed = 1;     // cleared by the render call's scratch memset
+    b.global = reinterpret_cast<uint32_t*>(static_cast<GridFlags*>(m_d_grid_misc) + 1);
     BuildScreenGrid(b, stream);
 
     m_grid.tile_off = b.tile_off; m_grid.items = b.items; m_grid.bbox = b.bbox; m_grid.edges = b.edges;
@@ -399,6 +433,10 @@ Scene::~Scene()
     FreeGrid();
     if (m_grid_free) cudaEventDestroy(m_grid_free);
     if (m_lgrid_built) cudaEventDestroy(m_lgrid_built);
+    if (m_lgrid_ev0) cudaEventDestroy(m_lgrid_ev0);
+    if (m_ev_grid_done) cudaEventDestroy(m_ev_grid_done);
+    if (m_ev_fork) cudaEventDestroy(m_ev_fork);
+    if (m_ev_join) cudaEventDestroy(m_ev_join);
     for (cudaEvent_t e : m_chunk_events) cudaEventDestroy(e);
     cudaFree(m_d_tris); cudaFree(m_d_albedo); cudaFree(m_d_nodes); cudaFree(m_d_counters);
 }
@@ -444,22 +482,54 @@ bool Scene::Validate(srt_camera const* camera, srt_light const* light, srt_rende
 
 ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
                               srt_render_params const* params, void* d_rgb, void* d_hit_id,
-                              void* d_hit_t, cudaStream_t stream, bool timed)
+                              void* d_hit_t, cudaStream_t stream, bool timed, SignalSpec const* signal)
 {
     if (!Validate(camera, light, params)) return ML_FAIL;
     try
     {
         m_device->MakeCurrent();
         if (stream == nullptr) stream = m_device->stream;
-        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), stream));
+        if (m_ev_grid_done == nullptr)
+        {
+            ML_CUDA_CHECK(cudaEventCreate(&m_ev_grid_done));
+            ML_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_fork, cudaEventDisableTiming));
+            ML_CUDA_CHECK(cudaEventCreateWithFlags(&m_ev_join, cudaEventDisableTiming));
+        }
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, kScratchBytes, stream));   // counters, tickets, screen-grid flags
         if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, stream));
         PrepareGrid(camera, params, stream);       // inside the timed region: it is per-frame work
         PrepareLightGrid(light, params, stream);
-        EnqueueBand(camera, light, params, d_rgb, d_hit_id, d_hit_t, stream);
+        if (timed) ML_CUDA_CHECK(cudaEventRecord(m_ev_grid_done, stream));
+        uint32_t chunk_rows = params->y1 - params->y0, n_chunks = 1;
+        if (signal && signal->n_chunks > 1) ChunkLayout(*params, signal->n_chunks, chunk_rows, n_chunks);
+        if (n_chunks <= 1)
+        {
+            EnqueueBand(camera, light, params, d_rgb, d_hit_id, d_hit_t, stream,
+                        signal ? signal->d_flags : nullptr, signal ? signal->value : 0u, 0);
+        }
+        else
+        {
+            // Chunk launches alternate between the caller's stream and a helper stream, so chunk k+1's blocks
+            // fill the SMs that chunk k's last wave leaves idle; flag k is published by chunk k's last block.
+            cudaStream_t const s1 = m_device->copy_in;
+            ML_CUDA_CHECK(cudaEventRecord(m_ev_fork, stream));
+            ML_CUDA_CHECK(cudaStreamWaitEvent(s1, m_ev_fork, 0));
+            for (uint32_t k = 0; k < n_chunks; k++)
+            {
+                srt_render_params c = *params;
+                c.y0 = params->y0 + k * chunk_rows;
+                c.y1 = std::min(params->y1, c.y0 + chunk_rows);
+                EnqueueBand(camera, light, &c, d_rgb, d_hit_id, d_hit_t, (k & 1u) ? s1 : stream,
+                            signal->d_flags + static_cast<size_t>(k) * signal->chunk_stride, signal->value, k & 1u);
+            }
+            ML_CUDA_CHECK(cudaEventRecord(m_ev_join, s1));
+            ML_CUDA_CHECK(cudaStreamWaitEvent(stream, m_ev_join, 0));
+        }
         if (m_grid.enabled || m_lgrid.grid.enabled) ML_CUDA_CHECK(cudaEventRecord(m_grid_free, stream));
         if (timed) ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, stream));
         ML_CUDA_CHECK(cudaGetLastError());
         m_timed_pending = timed;
+        m_timed_grid = timed;
         m_timed_stream = stream;
         return ML_OK;
     }
@@ -470,32 +540,38 @@ ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
     }
 }
 
-// One kernel launch for the rows params->[y0, y1) (already validated); counters accumulate.
+// One kernel launch for the rows params->[y0, y1) (already validated); counters accumulate.  With d_signal
+// the launch's last block publishes `value` there (RenderLaunch::d_signal); a band in which this call owns
+// no row block still publishes it, from a one-thread kernel.
 void Scene::EnqueueBand(srt_camera const* camera, srt_light const* light, srt_render_params const* params,
-                        void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream)
+                        void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream,
+                        uint32_t* d_signal, uint32_t signal_value, uint32_t ticket)
 {
-    {
-        RenderLaunch launch{};
-        launch.scene = m_view;
-        launch.camera = *camera;
-        launch.light = *light;
-        launch.params = *params;
-        launch.inv2w = 2.0f / static_cast<float>(params->width);
-        launch.inv2h = 2.0f / static_cast<float>(params->height);
-        launch.inv_spp = 1.0f / static_cast<float>(params->spp);
-        launch.d_rgb = static_cast<float*>(d_rgb);
-        launch.d_hit_id = static_cast<int32_t*>(d_hit_id);
-        launch.d_hit_t = static_cast<float*>(d_hit_t);
-        launch.d_counters = m_d_counters;
-        RowBlocks(*params, launch.row_origin, launch.row_block_step, launch.n_row_blocks);
-        static int const hints = std::getenv("SRT_BVH_HINTS") ? std::atoi(std::getenv("SRT_BVH_HINTS")) : 1;
-        launch.hints = static_cast<uint32_t>(hints);
-        launch.grid = m_grid;
-        if (launch.row_origin % kGridTile != 0) launch.grid.enabled = 0;
-        launch.lgrid = m_lgrid;
-        if (launch.n_row_blocks > 0)
-            LaunchRender(launch, m_device->prop.multiProcessorCount, stream);
-    }
+    RenderLaunch launch{};
+    launch.scene = m_view;
+    launch.camera = *camera;
+    launch.light = *light;
+    launch.params = *params;
+    launch.inv2w = 2.0f / static_cast<float>(params->width);
+    launch.inv2h = 2.0f / static_cast<float>(params->height);
+    launch.inv_spp = 1.0f / static_cast<float>(params->spp);
+    launch.d_rgb = static_cast<float*>(d_rgb);
+    launch.d_hit_id = static_cast<int32_t*>(d_hit_id);
+    launch.d_hit_t = static_cast<float*>(d_hit_t);
+    launch.d_counters = m_d_counters;
+    launch.d_signal = d_signal;
+    launch.signal_value = signal_value;
+    launch.d_ticket = reinterpret_cast<uint32_t*>(m_d_counters) + kScratchTicketWord + (ticket & 1u);
+    RowBlocks(*params, launch.row_origin, launch.row_block_step, launch.n_row_blocks);
+    static int const hints = std::getenv("SRT_BVH_HINTS") ? std::atoi(std::getenv("SRT_BVH_HINTS")) : 1;
+    launch.hints = static_cast<uint32_t>(hints);
+    launch.grid = m_grid;
+    if (launch.row_origin % kGridTile != 0) launch.grid.enabled = 0;
+    launch.lgrid = m_lgrid;
+    if (launch.n_row_blocks > 0)
+        LaunchRender(launch, m_device->prop.multiProcessorCount, stream);
+    else if (d_signal)
+        LaunchWriteFlag(d_signal, signal_value, stream);
 }
 
 ml_status Scene::GetStats(srt_render_stats* stats)
@@ -513,8 +589,14 @@ ml_status Scene::GetStats(srt_render_stats* stats)
         stats->box_tests = c[2];
         stats->tri_tests = c[3];
         stats->kernel_ms = 0.f;
+        stats->grid_build_ms = 0.f;
+        stats->light_grid_build_ms = 0.f;
         if (m_timed_pending)
             ML_CUDA_CHECK(cudaEventElapsedTime(&stats->kernel_ms, m_device->ev_start, m_device->ev_stop));
+        if (m_timed_pending && m_timed_grid)
+            ML_CUDA_CHECK(cudaEventElapsedTime(&stats->grid_build_ms, m_device->ev_start, m_ev_grid_done));
+        if (m_lgrid_valid && m_lgrid_ev0 != nullptr && cudaEventQuery(m_lgrid_built) == cudaSuccess)
+            ML_CUDA_CHECK(cudaEventElapsedTime(&stats->light_grid_build_ms, m_lgrid_ev0, m_lgrid_built));
         return ML_OK;
     }
     catch (std::exception const& e)
@@ -588,7 +670,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
             m_chunk_events.push_back(e);
         }
         cudaEvent_t const ev_begin = m_chunk_events[2 * n_chunks], ev_s1_done = m_chunk_events[2 * n_chunks + 1];
-        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, 4 * sizeof(unsigned long long), s0));
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_counters, 0, kScratchBytes, s0));
         ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s0));
         PrepareGrid(camera, params, s0);
         PrepareLightGrid(light, params, s0);
@@ -601,7 +683,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
             srt_render_params c = band;
             c.y0 = params->y0 + static_cast<uint32_t>(r0);
             c.y1 = params->y0 + static_cast<uint32_t>(r1);
-            EnqueueBand(camera, light, &c, m_d_rgb, m_d_id, m_d_t, s);
+            EnqueueBand(camera, light, &c, m_d_rgb, m_d_id, m_d_t, s, nullptr, 0u, 0u);
             ML_CUDA_CHECK(cudaEventRecord(m_chunk_events[2 * k], s));
             ML_CUDA_CHECK(cudaStreamWaitEvent(sc, m_chunk_events[2 * k], 0));
             if (stride == 1)
@@ -654,6 +736,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
         ML_CUDA_CHECK(cudaEventRecord(m_device->ev_stop, s0));
         ML_CUDA_CHECK(cudaGetLastError());
         m_timed_pending = true;
+        m_timed_grid = false;
         m_timed_stream = s0;
 
         // host side: as each chunk lands in the pinned staging, move its (owned) rows into the caller's

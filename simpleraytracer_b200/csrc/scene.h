@@ -102,7 +102,7 @@ public:
     static Scene* FromHandle(srt_scene s) { return reinterpret_cast<Scene*>(s); }
 
     Scene(DeviceStatePtr device, size_t n_triangles, float const* vertices,
-          float const* albedo, bool build_bvh);
+          float const* albedo, bool build_bvh, BvhBuildResult const* prebuilt = nullptr);
     ~Scene();
     Scene(Scene const&) = delete;
     Scene& operator=(Scene const&) = delete;
@@ -112,9 +112,12 @@ public:
 
     // Enqueues the render on `stream`; with `timed` the kernel is bracketed by
     // the context's events (read back by GetStats).
+    // `signal`: device-side completion flags for multi-GPU frames.  The band is rendered as n_chunks launches
+    // (ChunkLayout); chunk k's last block stores `value` to d_flags[k * chunk_stride] (RenderLaunch::d_signal).
+    struct SignalSpec { uint32_t* d_flags; uint32_t chunk_stride; uint32_t n_chunks; uint32_t value; };
     ml_status RenderDevice(srt_camera const* camera, srt_light const* light,
                            srt_render_params const* params, void* d_rgb, void* d_hit_id,
-                           void* d_hit_t, cudaStream_t stream, bool timed);
+                           void* d_hit_t, cudaStream_t stream, bool timed, SignalSpec const* signal = nullptr);
     ml_status RenderHost(srt_camera const* camera, srt_light const* light,
                          srt_render_params const* params, float* rgb, int32_t* hit_id,
                          float* hit_t, srt_render_stats* stats);
@@ -129,7 +132,8 @@ private:
     bool Validate(srt_camera const* camera, srt_light const* light,
                   srt_render_params const* params);
     void EnqueueBand(srt_camera const* camera, srt_light const* light, srt_render_params const* params,
-                     void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream);
+                     void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream,
+                     uint32_t* d_signal, uint32_t signal_value, uint32_t ticket);
     void EnsureStaging(size_t pixels);
     void FreeStaging();
     // Builds the primary-ray grid for this camera / frame on `stream` (if the render will use it).
@@ -143,7 +147,7 @@ private:
     void* m_d_tris = nullptr;     // one allocation: v0 | e1 | e2
     void* m_d_albedo = nullptr;
     void* m_d_nodes = nullptr;
-    unsigned long long* m_d_counters = nullptr; // primary, shadow, box, tri
+    unsigned long long* m_d_counters = nullptr; // per-frame scratch: primary, shadow, box, tri | tickets | grid flags
     std::vector<BvhNode> m_nodes_host;
     std::vector<int32_t> m_order_host;
     // staging for RenderHost (device band buffers + pinned host twins)
@@ -171,6 +175,10 @@ private:
     float m_pad = 0.f;                // world-space slack of the culling structures (as the BVH boxes)
     cudaEvent_t m_grid_free = nullptr; // the last render that read the grid has finished
     cudaEvent_t m_lgrid_built = nullptr; // the cached light grid is complete
+    cudaEvent_t m_lgrid_ev0 = nullptr;   // start of the light grid build (timing)
+    cudaEvent_t m_ev_grid_done = nullptr; // grids built, render kernel next (srt_render_stats::grid_build_ms)
+    cudaEvent_t m_ev_fork = nullptr, m_ev_join = nullptr; // chunked signalled render: helper stream fork / join
+    bool m_timed_grid = false;
     std::vector<cudaEvent_t> m_chunk_events; // RenderHost pipeline
     cudaStream_t m_timed_stream = nullptr;
     bool m_timed_pending = false;
@@ -202,12 +210,20 @@ struct RenderLaunch
     uint32_t row_block_step;
     uint32_t n_row_blocks;
     uint32_t hints;  // 1: rays first test the triangle the lane's previous ray ended on (SRT_BVH_HINTS=0 disables)
+    // Completion signal fused into the render kernel (multi-GPU frames): when d_signal != NULL the LAST block
+    // of the launch to finish (atomic ticket in d_ticket, reset for the next launch) stores signal_value to
+    // *d_signal with system-scope release ordering, after every block's pixels (possibly peer stores over
+    // NVLink into another GPU's frame) have been fenced.  d_signal may itself be peer memory.
+    uint32_t* d_signal;
+    uint32_t* d_ticket;
+    uint32_t signal_value;
     GridView grid;
     LightGridView lgrid;
 };
 void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream);
 // Which candidate grids the kernel LaunchRender picks for these parameters reads: bit 0 screen grid, bit 1 light grid.
 int RenderUsesGrid(srt_render_params const& params);
+void ChunkLayout(srt_render_params const& params, uint32_t requested, uint32_t& chunk_rows, uint32_t& n_chunks);
 struct GridBuild
 {
     DeviceSceneView scene;
@@ -226,8 +242,13 @@ struct GridBuild
     uint32_t* block_sums;   // [tiles / 4096 + 1] scratch of the prefix sum
     F4* bbox; F4* edges; uint32_t* global; GridFlags* flags;
     float half_extent;      // half size of a query in grid units: 0.5 (pixel squares) or 0 (points)
+    uint32_t flags_prezeroed; // 1: the caller's per-frame scratch memset already cleared *flags
 };
 void BuildScreenGrid(GridBuild const& build, cudaStream_t stream);
+// Consumer / producer halves of the device-side completion flags (render_kernels.cu).
+void LaunchWaitFlags(uint32_t const* d_flags, uint32_t count, uint32_t stride, uint32_t value,
+                     uint32_t timeout_ms, uint32_t* timeouts_mapped, cudaStream_t stream);
+void LaunchWriteFlag(uint32_t* d_flag, uint32_t value, cudaStream_t stream);
 double MeasureFp32Peak(DeviceState const& device, int repeats);
 
 } // namespace ML

@@ -4,8 +4,12 @@
 // little-endian fp32, width*height*3 values, on stdout or into a file.
 //
 //   srt_render -s cornell|mesh [-n triangles] [-seed N] -w W -h H [-spp N]
-//              [-shade albedo|lambert|shadow] [-accel bvh|brute] [-o file]
+//              [-shade albedo|lambert|shadow] [-accel bvh|brute] [-o file] [-gpus N | -devices a,b,...]
 //   srt_render -s mesh -n 100000 -w 800 -h 600 -spp 16 | test_app -m denoiser.pb -w 800 -h 600 > out.bin
+//
+// -gpus N (or an explicit -devices list) renders the one frame on N GPUs of this process through
+// srtCreateSceneGroup / srtRenderGroup (interleaved row blocks, peer stores into GPU 0's frame, device-side
+// completion flags); the output is bit-identical to the single-GPU frame.
 //
 // Uses only the C ABI (model_runner.h + srt_render.h), like test_app does; the
 // frame is rendered into an ml_image and read through mlMapImage.  Exit status
@@ -27,6 +31,7 @@ namespace {
     std::fprintf(stderr,
                  "usage: srt_render -s cornell|mesh [-n triangles] [-seed N] -w width -h height [-spp N]\n"
                  "                  [-shade albedo|lambert|shadow] [-accel bvh|brute] [-o output_file]\n"
+                 "                  [-gpus N | -devices a,b,...]\n"
                  "writes width*height*3 fp32 values (HWC, no header) to output_file or stdout\n");
     std::exit(255);
 }
@@ -44,6 +49,7 @@ int main(int argc, char** argv)
     std::string scene_name = "cornell", out_path, shade = "shadow", accel = "bvh";
     size_t n_tris = 100000;
     uint32_t seed = 1, width = 0, height = 0, spp = 1;
+    std::vector<int> devices;
     for (int i = 1; i < argc; i++)
     {
         std::string a = argv[i];
@@ -60,18 +66,47 @@ int main(int argc, char** argv)
         else if (a == "-shade") shade = next();
         else if (a == "-accel") accel = next();
         else if (a == "-o") out_path = next();
+        else if (a == "-gpus")
+        {
+            int const n = std::atoi(next());
+            if (n < 1) Usage();
+            devices.clear();
+            for (int d = 0; d < n; d++) devices.push_back(d);
+        }
+        else if (a == "-devices")
+        {
+            devices.clear();
+            for (char const* c = next(); *c;)
+            {
+                devices.push_back(std::atoi(c));
+                while (*c && *c != ',') c++;
+                if (*c == ',') c++;
+            }
+            if (devices.empty()) Usage();
+        }
         else Usage();
     }
     if (width == 0 || height == 0 || spp == 0) Usage();
 
     ml_context ctx = nullptr;
     srt_scene scene = nullptr;
+    srt_scene_group group = nullptr;
     ml_image image = nullptr;
     int status = 0;
     try
     {
-        ctx = mlCreateContext();
-        if (ctx == nullptr) throw std::runtime_error("mlCreateContext failed (no CUDA device?)");
+        bool const multi = devices.size() > 1;
+        if (!multi)
+        {
+            ctx = devices.empty() ? mlCreateContext() : nullptr;
+            if (!devices.empty())
+            {
+                // one explicit device: the reference API has no device argument, MLB200_DEVICE selects it
+                setenv("MLB200_DEVICE", std::to_string(devices[0]).c_str(), 1);
+                ctx = mlCreateContext();
+            }
+            if (ctx == nullptr) throw std::runtime_error("mlCreateContext failed (no CUDA device?)");
+        }
 
         std::vector<float> vertices, albedo;
         srt_camera cam{};
@@ -92,13 +127,6 @@ int main(int argc, char** argv)
         }
         else Usage();
 
-        scene = srtCreateScene(ctx, n_tris, vertices.data(), albedo.data(), accel == "bvh" ? 1 : 0);
-        if (scene == nullptr) throw std::runtime_error("srtCreateScene: " + ContextError(ctx));
-
-        ml_image_info info{ML_FLOAT32, width, height, 3};
-        image = mlCreateImage(ctx, &info);
-        if (image == nullptr) throw std::runtime_error("mlCreateImage: " + ContextError(ctx));
-
         srt_render_params p{};
         p.width = width; p.height = height; p.y0 = 0; p.y1 = height; p.buf_y0 = 0;
         p.spp = spp; p.jitter = spp > 1 ? 1u : 0u; p.seed = seed;
@@ -107,22 +135,44 @@ int main(int argc, char** argv)
         p.t_min = 1e-4f; p.shadow_eps = 1e-3f;
         p.background[0] = 0.5f; p.background[1] = 0.7f; p.background[2] = 0.9f;
         srt_render_stats st{};
-        if (srtRenderToImage(scene, &cam, &light, &p, image, &st) != ML_OK)
-        {
-            char buf[1024];
-            throw std::runtime_error(std::string("srtRenderToImage: ") + srtGetSceneError(scene, buf, sizeof(buf)));
-        }
+        std::vector<float> host_frame;
         size_t bytes = 0;
-        void* data = mlMapImage(image, &bytes);
-        if (data == nullptr) throw std::runtime_error("mlMapImage failed");
+        void* data = nullptr;
+        if (multi)
+        {
+            char err[1024];
+            group = srtCreateSceneGroup(devices.data(), static_cast<uint32_t>(devices.size()), n_tris, vertices.data(),
+                                        albedo.data(), accel == "bvh" ? 1 : 0, err, sizeof(err));
+            if (group == nullptr) throw std::runtime_error(std::string("srtCreateSceneGroup: ") + err);
+            host_frame.resize(static_cast<size_t>(width) * height * 3);
+            if (srtRenderGroup(group, &cam, &light, &p, host_frame.data(), &st) != ML_OK)
+                throw std::runtime_error(std::string("srtRenderGroup: ") + srtGetSceneGroupError(group, err, sizeof(err)));
+            data = host_frame.data();
+            bytes = host_frame.size() * sizeof(float);
+        }
+        else
+        {
+            scene = srtCreateScene(ctx, n_tris, vertices.data(), albedo.data(), accel == "bvh" ? 1 : 0);
+            if (scene == nullptr) throw std::runtime_error("srtCreateScene: " + ContextError(ctx));
+            ml_image_info info{ML_FLOAT32, width, height, 3};
+            image = mlCreateImage(ctx, &info);
+            if (image == nullptr) throw std::runtime_error("mlCreateImage: " + ContextError(ctx));
+            if (srtRenderToImage(scene, &cam, &light, &p, image, &st) != ML_OK)
+            {
+                char buf[1024];
+                throw std::runtime_error(std::string("srtRenderToImage: ") + srtGetSceneError(scene, buf, sizeof(buf)));
+            }
+            data = mlMapImage(image, &bytes);
+            if (data == nullptr) throw std::runtime_error("mlMapImage failed");
+        }
         FILE* f = out_path.empty() ? stdout : std::fopen(out_path.c_str(), "wb");
         if (f == nullptr) throw std::runtime_error("cannot open " + out_path);
         size_t const written = std::fwrite(data, 1, bytes, f);
         if (f != stdout) std::fclose(f); else std::fflush(stdout);
-        mlUnmapImage(image, data);
+        if (!multi) mlUnmapImage(image, data);
         if (written != bytes) throw std::runtime_error("short write");
-        std::fprintf(stderr, "srt_render: %ux%u, %zu triangles, %llu primary + %llu shadow rays, kernel %.3f ms (%.1f Mrays/s)\n",
-                     width, height, n_tris, static_cast<unsigned long long>(st.primary_rays),
+        std::fprintf(stderr, "srt_render: %zu GPU(s), %ux%u, %zu triangles, %llu primary + %llu shadow rays, kernel %.3f ms (%.1f Mrays/s)\n",
+                     multi ? devices.size() : size_t(1), width, height, n_tris, static_cast<unsigned long long>(st.primary_rays),
                      static_cast<unsigned long long>(st.shadow_rays), st.kernel_ms,
                      st.kernel_ms > 0 ? (st.primary_rays + st.shadow_rays) / (st.kernel_ms * 1e3) : 0.0);
     }
@@ -133,6 +183,7 @@ int main(int argc, char** argv)
     }
     mlReleaseImage(image);
     if (scene != nullptr) srtReleaseScene(scene);
+    if (group != nullptr) srtReleaseSceneGroup(group);
     mlReleaseContext(ctx);
     return status;
 }

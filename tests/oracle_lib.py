@@ -27,6 +27,48 @@ class orc_params(C.Structure):
 
 
 _lib = None
+_scenes = None
+
+
+def scenes_lib():
+    """oracle/libsrtscenes.so: the seeded scene generators compiled alone (no CUDA, no product library)."""
+    global _scenes
+    if _scenes is None:
+        so = ROOT / "oracle" / "libsrtscenes.so"
+        if not so.exists():
+            subprocess.check_call(["make", "-C", str(ROOT / "oracle"), "libsrtscenes.so"])
+        _scenes = C.CDLL(str(so))
+        _scenes.orc_gen_mesh.restype = C.c_int
+        _scenes.orc_gen_mesh.argtypes = [C.c_uint32, C.c_size_t, C.c_void_p, C.c_void_p, C.POINTER(orc_camera),
+                                         C.POINTER(orc_light), C.c_uint32, C.c_uint32]
+        _scenes.orc_gen_cornell_box.restype = C.c_size_t
+        _scenes.orc_gen_cornell_box.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(orc_camera), C.POINTER(orc_light),
+                                                C.c_uint32, C.c_uint32]
+    return _scenes
+
+
+def gen_mesh(seed, n_triangles, width, height):
+    v = np.zeros((n_triangles, 9), np.float32)
+    a = np.zeros((n_triangles, 3), np.float32)
+    cam, light = orc_camera(), orc_light()
+    if scenes_lib().orc_gen_mesh(seed, n_triangles, v.ctypes.data, a.ctypes.data, C.byref(cam), C.byref(light),
+                                 width, height) != 0:
+        raise RuntimeError("orc_gen_mesh failed")
+    return v, a, cam, light
+
+
+def gen_cornell_box(width, height):
+    n = scenes_lib().orc_gen_cornell_box(None, None, None, None, width, height)
+    v = np.zeros((n, 9), np.float32)
+    a = np.zeros((n, 3), np.float32)
+    cam, light = orc_camera(), orc_light()
+    scenes_lib().orc_gen_cornell_box(v.ctypes.data, a.ctypes.data, C.byref(cam), C.byref(light), width, height)
+    return v, a, cam, light
+
+
+def last_setup_ms() -> float:
+    """Host time the last render() spent building the oracle's BVH."""
+    return float(lib().orc_last_setup_ms())
 
 
 def lib():
@@ -39,6 +81,8 @@ def lib():
         _lib.orc_render.argtypes = [C.c_uint64, C.c_void_p, C.c_void_p, C.POINTER(orc_camera),
                                     C.POINTER(orc_light), C.POINTER(orc_params), C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_void_p, C.c_int, C.c_int]
+        _lib.orc_last_setup_ms.restype = C.c_double
+        _lib.orc_last_setup_ms.argtypes = []
         _lib.orc_intersect.restype = C.c_int
         _lib.orc_intersect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_float)]
         _lib.orc_conv2d.restype = C.c_int

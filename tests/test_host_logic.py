@@ -112,3 +112,17 @@ def test_gather_bands_world_size_2_gloo(tmp_path, height):
 def test_product_refuses_to_run_without_gpu():
     with pytest.raises(api.MLError):
         api.Context()
+
+
+def test_oracle_side_generator_equals_the_product_generator():
+    """oracle/libsrtscenes.so (scenes.cpp compiled alone by the host compiler) feeds the CPU arm of bench.py;
+    it must emit exactly the arrays srtGenMesh / srtGenCornellBox emit."""
+    import oracle_lib as O
+    for seed, n, w, h in ((1, 100_000, 1920, 1080), (9, 12345, 64, 36), (3, 0, 8, 8)):
+        v1, a1, c1, l1 = api.gen_mesh(seed, n, w, h)
+        v2, a2, c2, l2 = O.gen_mesh(seed, n, w, h)
+        assert np.array_equal(v1, v2) and np.array_equal(a1, a2)
+        assert bytes(c1) == bytes(c2) and bytes(l1) == bytes(l2)
+    v1, a1, c1, l1 = api.gen_cornell_box(512, 512)
+    v2, a2, c2, l2 = O.gen_cornell_box(512, 512)
+    assert np.array_equal(v1, v2) and np.array_equal(a1, a2) and bytes(c1) == bytes(c2) and bytes(l1) == bytes(l2)
