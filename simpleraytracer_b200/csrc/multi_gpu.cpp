@@ -430,7 +430,7 @@ ml_status SceneGroup::Render(srt_camera const* camera, srt_light const* light, s
         whole.row_block_stride = n > 1 ? n : 0;
         whole.row_block_phase = 0;
         // chunks only pay when there is a host copy to overlap with the rendering of the next chunk
-        static int const env_chunks = std::getenv("SRT_GROUP_CHUNKS") ? std::atoi(std::getenv("SRT_GROUP_CHUNKS")) : 0;
+        int const env_chunks = std::getenv("SRT_GROUP_CHUNKS") ? std::atoi(std::getenv("SRT_GROUP_CHUNKS")) : 0;   // per call: tests flip it
         uint32_t want = rgb_host ? (static_cast<uint64_t>(params->width) * params->height >= (1u << 20) ? 4u : 1u) : 1u;
         if (env_chunks > 0) want = static_cast<uint32_t>(std::min(env_chunks, 16));
         uint32_t chunk_rows = 0, n_chunks = 0;
@@ -443,7 +443,13 @@ ml_status SceneGroup::Render(srt_camera const* camera, srt_light const* light, s
             m_job_id++;
         }
         m_cv_job.notify_all();
-        // GPU 0's consumer side, enqueued while the workers issue the renders
+        // GPU 0's consumer side is enqueued AFTER every worker has issued its launches: a spinning wait kernel
+        // must never sit in a hardware work queue ahead of a kernel it is waiting for (streams can share a
+        // queue -- CUDA_DEVICE_MAX_CONNECTIONS -- and replicas may share one GPU).
+        {
+            std::unique_lock<std::mutex> lock(m_mutex);
+            m_cv_done.wait(lock, [&] { return m_pending == 0; });
+        }
         dev0.MakeCurrent();
         uint32_t const before = *dev0.wait_timeouts;
         std::string gather_error;
@@ -458,11 +464,7 @@ ml_status SceneGroup::Render(srt_camera const* camera, srt_light const* light, s
         }
         catch (std::exception const& e)
         {
-            gather_error = e.what();     // the workers must still be collected before the call returns
-        }
-        {
-            std::unique_lock<std::mutex> lock(m_mutex);
-            m_cv_done.wait(lock, [&] { return m_pending == 0; });
+            gather_error = e.what();     // a worker's own error (below) explains a missing flag better
         }
         for (uint32_t r = 0; r < n; r++)
             if (m_members[r].status != ML_OK)

@@ -154,22 +154,18 @@ __device__ __forceinline__ void closest_update(Hit& best, float ts, float adet, 
 // ray is needed, its origin/direction.
 struct ShadeOut { V3 rgb; V3 so, sd; bool need_shadow; };
 
-__device__ __forceinline__ ShadeOut shade_hit(RenderLaunch const& L, V3 o, V3 d, Hit h)
+// `n` is the triangle's geometric unit normal normalize(e1 x e2) -- a pure function of the triangle, evaluated
+// once per triangle by tri_normals_kernel with the operation sequence of the spec (cross3, dot3, __fsqrt_rn,
+// __fdiv_rn(1, len), three mul) instead of once per sample -- and `alb` its albedo.
+__device__ __forceinline__ ShadeOut shade_hit(RenderLaunch const& L, V3 o, V3 d, float t, V3 n, V3 alb)
 {
     ShadeOut out;
     out.need_shadow = false;
     out.so = V3{0.f, 0.f, 0.f};
     out.sd = V3{0.f, 0.f, 0.f};
-    V3 alb = v3(__ldg(reinterpret_cast<float4 const*>(L.scene.albedo) + h.id));
     if (L.params.shade == SRT_SHADE_ALBEDO) { out.rgb = alb; return out; }
 
-    float4 e1 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e1) + h.slot);
-    float4 e2 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e2) + h.slot);
-    V3 P = V3{fma_(h.t, d.x, o.x), fma_(h.t, d.y, o.y), fma_(h.t, d.z, o.z)};
-    V3 nr = cross3(v3(e1), v3(e2));
-    float nl = __fsqrt_rn(dot3(nr, nr));
-    float inl = __fdiv_rn(1.0f, nl);
-    V3 n = V3{mul(nr.x, inl), mul(nr.y, inl), mul(nr.z, inl)};
+    V3 P = V3{fma_(t, d.x, o.x), fma_(t, d.y, o.y), fma_(t, d.z, o.z)};
     if (dot3(n, d) > 0.0f) n = V3{-n.x, -n.y, -n.z};
     V3 Lv = V3{sub(L.light.position[0], P.x), sub(L.light.position[1], P.y), sub(L.light.position[2], P.z)};
     float dist2 = dot3(Lv, Lv);
@@ -191,6 +187,15 @@ __device__ __forceinline__ ShadeOut shade_hit(RenderLaunch const& L, V3 o, V3 d,
                     sub(L.light.position[2], out.so.z)};
     }
     return out;
+}
+
+// Shading inputs of a hit from the scene arrays in HBM / L2 (paths that do not hold them in shared memory).
+__device__ __forceinline__ ShadeOut shade_hit(RenderLaunch const& L, V3 o, V3 d, Hit h)
+{
+    V3 const alb = v3(__ldg(reinterpret_cast<float4 const*>(L.scene.albedo) + h.id));
+    V3 n = V3{0.f, 0.f, 0.f};
+    if (L.params.shade != SRT_SHADE_ALBEDO) n = v3(__ldg(reinterpret_cast<float4 const*>(L.scene.tri_n) + h.slot));
+    return shade_hit(L, o, d, h.t, n, alb);
 }
 
 __device__ __forceinline__ unsigned long long warp_sum(unsigned long long v)
@@ -249,6 +254,24 @@ __device__ __forceinline__ void flush_counters(RenderLaunch const& L, unsigned l
             }
         }
     }
+}
+
+// Block timeline probe (SRT_BLOCK_TRACE=1): see RenderLaunch::d_trace.
+__device__ __forceinline__ unsigned long long trace_now()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void trace_block(RenderLaunch const& L, unsigned long long t_start)
+{
+    if (L.d_trace == nullptr || threadIdx.x != 0) return;
+    unsigned long long const t_end = trace_now();
+    atomicMax(L.d_trace + 0, ~t_start);          // ~min(start)
+    atomicMax(L.d_trace + 1, t_start);
+    atomicMax(L.d_trace + 2, t_end);
+    atomicAdd(L.d_trace + 3, t_end - t_start);
+    atomicMax(L.d_trace + 4, t_end - t_start);
 }
 
 // Writes one finished pixel (section 5).  `pix` is the full-frame pixel index.
@@ -783,6 +806,44 @@ __global__ void __launch_bounds__(256) grid_fill_kernel(const __grid_constant__ 
         }
 }
 
+// Light grid only: every cell's list ordered by the triangles' nearest depth edges[3*slot].w, ascending (ties by
+// slot, so the build is deterministic), one thread per cell, insertion sort (lists average about one entry).
+__global__ void __launch_bounds__(256) sort_cells_by_depth_kernel(const __grid_constant__ GridBuild G)
+{
+    uint32_t const cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell >= G.tiles_w * G.tiles_h || G.flags->ok == 0) return;
+    uint32_t const b = G.tile_off[cell], e = G.tile_off[cell + 1];
+    float4 const* edges = reinterpret_cast<float4 const*>(G.edges);
+    for (uint32_t i = b + 1; i < e; i++)
+    {
+        uint32_t const s = G.items[i];
+        float const d = edges[3 * s].w;
+        uint32_t j = i;
+        while (j > b)
+        {
+            uint32_t const p = G.items[j - 1];
+            float const dp = edges[3 * p].w;
+            if (dp < d || (dp == d && p < s)) break;
+            G.items[j] = p;
+            j--;
+        }
+        G.items[j] = s;
+    }
+}
+
+// tri_n[i] = normalize(e1[i] x e2[i]) with the spec's operation sequence (docs/RENDER_SPEC.md section 4): the
+// bits every shaded sample used to recompute.  Degenerate triangles give the same NaN/inf as before.
+__global__ void __launch_bounds__(256) tri_normals_kernel(float4 const* __restrict__ e1, float4 const* __restrict__ e2,
+                                                          float4* __restrict__ n, uint32_t count)
+{
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    V3 const nr = cross3(v3(e1[i]), v3(e2[i]));
+    float const nl = __fsqrt_rn(dot3(nr, nr));
+    float const inl = __fdiv_rn(1.0f, nl);
+    n[i] = make_float4(mul(nr.x, inl), mul(nr.y, inl), mul(nr.z, inl), 0.f);
+}
+
 // ---------------------------------------------------------------------------
 // BVH traversal
 // ---------------------------------------------------------------------------
@@ -949,17 +1010,32 @@ __device__ __forceinline__ void bvh_trace(DeviceSceneView const& sc, V3 o, V3 d,
 // the BVH.  The occluder set is exact: a point of a binned triangle between S and the light projects
 // to S's own cell (boxes dilated for every rounding involved), triangles that could not be binned are
 // in the global list, triangles wholly behind the plane cannot lie between a point in front and the light.
+// Culling arithmetic below (projection, edge functions) never enters the image: it uses explicit FMAs and an
+// approximate reciprocal; the grid's dilation budgets ~34 ulps of relative error for this projection.
+__device__ __forceinline__ float rcp_approx(float x)
+{
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ bool edge_pass(float4 e, float qx, float qy)
+{
+    return __fmaf_rn(e.x, qx, __fmaf_rn(e.y, qy, e.z)) >= 0.0f;
+}
+
 template <bool STATS>
 __device__ __forceinline__ bool lgrid_shadow(RenderLaunch const& L, V3 so, V3 sd, bool& occluded, uint32_t& hint,
                                              uint32_t n_global, unsigned long long& n_tri)
 {
     LightGridView const& G = L.lgrid;
     float const px = so.x - L.light.position[0], py = so.y - L.light.position[1], pz = so.z - L.light.position[2];
-    float const cz = G.minv[6] * px + G.minv[7] * py + G.minv[8] * pz;
+    float const cz = __fmaf_rn(G.minv[6], px, __fmaf_rn(G.minv[7], py, G.minv[8] * pz));
     if (!(cz > 0.0f)) return false;
-    float const iz = 1.0f / cz;
-    float const gx = G.cx + (G.minv[0] * px + G.minv[1] * py + G.minv[2] * pz) * iz * G.kx;
-    float const gy = G.cy - (G.minv[3] * px + G.minv[4] * py + G.minv[5] * pz) * iz * G.ky;
+    float const iz = rcp_approx(cz);
+    float const cx = __fmaf_rn(G.minv[0], px, __fmaf_rn(G.minv[1], py, G.minv[2] * pz));
+    float const cy = __fmaf_rn(G.minv[3], px, __fmaf_rn(G.minv[4], py, G.minv[5] * pz));
+    float const gx = __fmaf_rn(cx * iz, G.kx, G.cx);
+    float const gy = __fmaf_rn(-(cy * iz), G.ky, G.cy);
     if (!(fabsf(gx) < 1e9f) || !(fabsf(gy) < 1e9f)) return false;
     int const ix = min(max(static_cast<int>(floorf(gx)), 0), static_cast<int>(G.grid.tiles_w) - 1);
     int const iy = min(max(static_cast<int>(floorf(gy)), 0), static_cast<int>(G.grid.tiles_h) - 1);
@@ -989,14 +1065,17 @@ __device__ __forceinline__ bool lgrid_shadow(RenderLaunch const& L, V3 so, V3 sd
     }
     uint32_t const b = __ldg(G.grid.tile_off + cell), e = __ldg(G.grid.tile_off + cell + 1);
     float4 const* __restrict__ edges = reinterpret_cast<float4 const*>(G.grid.edges);
+    // The cell's list is sorted by the triangles' nearest depth (sort_cells_by_depth_kernel): a triangle can only
+    // lie between the shading point and the light if it reaches nearer to the light than the point, so the walk
+    // ends at the first entry beyond it.
     for (uint32_t k = b; k < e; k++)
     {
         uint32_t const slot = __ldg(G.grid.items + k);
-        // the projected triangle must cover the query point, and reach nearer to the light than S
-        float4 const e0 = __ldg(edges + 3 * slot), e1 = __ldg(edges + 3 * slot + 1), e2 = __ldg(edges + 3 * slot + 2);
-        if (!(e0.w <= cz) || !(e0.x * gx + e0.y * gy + e0.z >= 0.0f) || !(e1.x * gx + e1.y * gy + e1.z >= 0.0f)
-            || !(e2.x * gx + e2.y * gy + e2.z >= 0.0f))
-            continue;
+        float4 const e0 = __ldg(edges + 3 * slot);
+        if (!(e0.w <= cz)) break;
+        // the projected triangle must cover the query point
+        if (!edge_pass(e0, gx, gy)) continue;
+        if (!edge_pass(__ldg(edges + 3 * slot + 1), gx, gy) || !edge_pass(__ldg(edges + 3 * slot + 2), gx, gy)) continue;
         if (STATS) n_tri++;
         if (test(slot)) return true;
     }
@@ -1402,6 +1481,22 @@ __global__ void write_flag_kernel(uint32_t* flag, uint32_t value)
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
 }
 } // namespace
+
+void LaunchTriNormals(F4 const* e1, F4 const* e2, F4* n, uint32_t count, cudaStream_t stream)
+{
+    if (count == 0) return;
+    tri_normals_kernel<<<(count + 255u) / 256u, 256, 0, stream>>>(reinterpret_cast<float4 const*>(e1),
+                                                                 reinterpret_cast<float4 const*>(e2),
+                                                                 reinterpret_cast<float4*>(n), count);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void LaunchSortCellsByDepth(GridBuild const& build, cudaStream_t stream)
+{
+    uint32_t const cells = build.tiles_w * build.tiles_h;
+    sort_cells_by_depth_kernel<<<(cells + 255u) / 256u, 256, 0, stream>>>(build);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
 
 void LaunchWaitFlags(uint32_t const* d_flags, uint32_t count, uint32_t stride, uint32_t value,
                      uint32_t timeout_ms, uint32_t* timeouts_mapped, cudaStream_t stream)

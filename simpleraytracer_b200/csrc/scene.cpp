@@ -119,17 +119,22 @@ Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const
 
     // ---- upload ----------------------------------------------------------------
     size_t const tri_bytes = soa.size() * sizeof(F4);
+    size_t const nrm_bytes = padded * sizeof(F4);      // tri_n, behind the three uploaded arrays
     size_t const alb_bytes = alb.size() * sizeof(F4);
     size_t const node_bytes = m_nodes_host.size() * sizeof(BvhNode);
     try
     {
-        ML_CUDA_CHECK(cudaMalloc(&m_d_tris, tri_bytes));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_tris, tri_bytes + nrm_bytes));
         ML_CUDA_CHECK(cudaMalloc(&m_d_albedo, alb_bytes));
         if (node_bytes) ML_CUDA_CHECK(cudaMalloc(&m_d_nodes, node_bytes));
         ML_CUDA_CHECK(cudaMalloc(reinterpret_cast<void**>(&m_d_counters), kScratchBytes));
         cudaStream_t s = m_device->stream;
         ML_CUDA_CHECK(cudaEventRecord(m_device->ev_start, s));
         ML_CUDA_CHECK(cudaMemcpyAsync(m_d_tris, soa.data(), tri_bytes, cudaMemcpyHostToDevice, s));
+        {
+            F4* const base = static_cast<F4*>(m_d_tris);
+            LaunchTriNormals(base + padded, base + 2 * padded, base + 3 * padded, static_cast<uint32_t>(padded), s);
+        }
         ML_CUDA_CHECK(cudaMemcpyAsync(m_d_albedo, alb.data(), alb_bytes, cudaMemcpyHostToDevice, s));
         if (node_bytes)
             ML_CUDA_CHECK(cudaMemcpyAsync(m_d_nodes, m_nodes_host.data(), node_bytes, cudaMemcpyHostToDevice, s));
@@ -147,6 +152,7 @@ Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const
     m_view.tri_v0 = static_cast<F4 const*>(m_d_tris);
     m_view.tri_e1 = m_view.tri_v0 + padded;
     m_view.tri_e2 = m_view.tri_e1 + padded;
+    m_view.tri_n = m_view.tri_e2 + padded;
     m_view.albedo = static_cast<F4 const*>(m_d_albedo);
     m_view.nodes = static_cast<F4 const*>(m_d_nodes);
     m_view.n_tris = static_cast<uint32_t>(n);
@@ -154,7 +160,7 @@ Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const
 
     m_info.n_triangles = n;
     m_info.n_bvh_nodes = m_nodes_host.size();
-    m_info.device_bytes = tri_bytes + alb_bytes + node_bytes;
+    m_info.device_bytes = tri_bytes + nrm_bytes + alb_bytes + node_bytes;
     for (int k = 0; k < 3; k++)
     {
         m_info.bounds_min[k] = n ? bmin[k] : 0.f;
@@ -293,6 +299,7 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     }
     ML_CUDA_CHECK(cudaEventRecord(m_lgrid_ev0, stream));
     BuildScreenGrid(b, stream);
+    LaunchSortCellsByDepth(b, stream);     // shadow rays stop at the first entry beyond the shading point
 
     GridView& gv = m_lgrid.grid;
     gv.tile_off = b.tile_off; gv.items = b.items; gv.bbox = b.bbox; gv.edges = b.edges; gv.global = b.global;

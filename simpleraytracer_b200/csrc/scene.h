@@ -6,6 +6,7 @@
 // memory):
 //   tri_v0[i] = (v0.x, v0.y, v0.z, bits(original triangle id))
 //   tri_e1[i] = (v1 - v0, 0)        tri_e2[i] = (v2 - v0, 0)
+//   tri_n[i]  = (normalize(e1 x e2), 0)             same slot order, filled by a device kernel at upload
 //   albedo[id] = (r, g, b, 0)                       indexed by ORIGINAL id
 //   nodes[4*k .. 4*k+3]: one 64-byte inner BVH node (two child boxes + refs)
 // Triangles are stored in BVH leaf order (identity when no BVH is built) and
@@ -51,6 +52,8 @@ struct DeviceSceneView
     F4 const* tri_v0;
     F4 const* tri_e1;
     F4 const* tri_e2;
+    F4 const* tri_n;        // per slot: geometric unit normal normalize(e1 x e2), computed ONCE on the device at
+                            // upload with the exact operation sequence of docs/RENDER_SPEC.md section 4
     F4 const* albedo;
     F4 const* nodes;
     uint32_t n_tris;        // real triangles
@@ -214,6 +217,9 @@ struct RenderLaunch
     // of the launch to finish (atomic ticket in d_ticket, reset for the next launch) stores signal_value to
     // *d_signal with system-scope release ordering, after every block's pixels (possibly peer stores over
     // NVLink into another GPU's frame) have been fenced.  d_signal may itself be peer memory.
+    // SRT_BLOCK_TRACE=1 (diagnostic): 5 x u64 {min block start, max block start, max block end, sum of block
+    // durations, max block duration} in ns of %globaltimer; NULL otherwise
+    unsigned long long* d_trace;
     uint32_t* d_signal;
     uint32_t* d_ticket;
     uint32_t signal_value;
@@ -249,6 +255,10 @@ void BuildScreenGrid(GridBuild const& build, cudaStream_t stream);
 void LaunchWaitFlags(uint32_t const* d_flags, uint32_t count, uint32_t stride, uint32_t value,
                      uint32_t timeout_ms, uint32_t* timeouts_mapped, cudaStream_t stream);
 void LaunchWriteFlag(uint32_t* d_flag, uint32_t value, cudaStream_t stream);
+// tri_n[i] = normalize(tri_e1[i] x tri_e2[i]) for all padded slots (scene upload).
+void LaunchTriNormals(F4 const* e1, F4 const* e2, F4* n, uint32_t count, cudaStream_t stream);
+// Sorts every cell's list of a (light) grid by the triangles' nearest depth (edges[3*slot].w), ascending.
+void LaunchSortCellsByDepth(GridBuild const& build, cudaStream_t stream);
 double MeasureFp32Peak(DeviceState const& device, int repeats);
 
 } // namespace ML

@@ -23,6 +23,17 @@ def gpu_count():
     return torch.cuda.device_count()
 
 
+def device_to_host(ptr, arr):
+    """cudaMemcpy through the CUDA runtime torch has loaded (same primary context as the library's)."""
+    import ctypes as C
+    import torch
+    torch.cuda.init()
+    rt = C.CDLL("libcudart.so.12")
+    rt.cudaMemcpy.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int]
+    rt.cudaMemcpy.restype = C.c_int
+    assert rt.cudaMemcpy(arr.ctypes.data, ptr, arr.nbytes, 2) == 0       # cudaMemcpyDeviceToHost
+
+
 COMMON = dict(jitter=1, seed=3, shade=api.SRT_SHADE_SHADOW, accel=api.SRT_ACCEL_BVH, background=(0.5, 0.7, 0.9))
 
 
@@ -40,22 +51,20 @@ def test_scene_group_replicas_on_one_gpu_equal_single_render(ctx, shape):
     group = api.SceneGroup([0] * n, v, a)
     assert group.size() == n
     for chunks in ("1", "3"):
-        os.environ["SRT_GROUP_CHUNKS"] = chunks     # read once per process: only the first value sticks; both are valid
+        os.environ["SRT_GROUP_CHUNKS"] = chunks     # read at every call
         got, st = group.render(cam, light, p)
         assert np.array_equal(got, want)
         assert st.primary_rays == st1.primary_rays and st.shadow_rays == st1.shadow_rays
         assert st.kernel_ms > 0
-    # frame left on GPU 0 (no host copy), read back through torch
-    import torch
+    # frame left on GPU 0 (no host copy): read it back with a plain cudaMemcpy
     _, st = group.render(cam, light, p, want_host=False)
     ptr = group.frame_pointer()
     assert ptr
     dev = np.empty((H, W, 3), np.float32)
-    from ctypes import c_void_p
-    rt = torch.cuda.cudart()
-    assert int(rt.cudaMemcpy(dev.ctypes.data, ptr, dev.nbytes, 2)) == 0     # cudaMemcpyDeviceToHost
+    device_to_host(ptr, dev)
     assert np.array_equal(dev, want)
     # page-locked destination: chunks copied straight from the device
+    import torch
     pinned = torch.zeros((H, W, 3), dtype=torch.float32).pin_memory()
     got, _ = group.render(cam, light, p, rgb_host=pinned.numpy())
     assert np.array_equal(pinned.numpy(), want)
