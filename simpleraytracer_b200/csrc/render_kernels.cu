@@ -654,40 +654,83 @@ __device__ __forceinline__ bool grid_tile_touches(GridBuild const& G, float4 con
     return ok;
 }
 
+// Tiles of one triangle's box, visited by the calling thread alone (COOP = false) or by the 32 lanes of its
+// warp together (COOP = true: lane t takes tiles t, t + 32, ...).  A thread per triangle serialises the few
+// triangles that cover hundreds of tiles -- up to max_tiles_per_tri dependent atomics in one thread, which was
+// most of the build time of frames with large triangles; the warp walks those boxes 32 tiles at a time.
+constexpr uint32_t kGridCoopTiles = 16;   // boxes with more tiles are walked by the whole warp
+
+template <bool COOP, class Visit>
+__device__ __forceinline__ void grid_visit_tiles(GridBuild const& G, float4 const (&edge)[3], int tx0, int tx1, int ty0,
+                                                 int ty1, Visit&& visit)
+{
+    uint32_t const w = static_cast<uint32_t>(tx1 - tx0 + 1), n = w * static_cast<uint32_t>(ty1 - ty0 + 1);
+    uint32_t const first = COOP ? (threadIdx.x & 31u) : 0u, step = COOP ? 32u : 1u;
+    for (uint32_t t = first; t < n; t += step)
+    {
+        uint32_t const r = t / w;
+        int const ty = ty0 + static_cast<int>(r), tx = tx0 + static_cast<int>(t - r * w);
+        if (grid_row_owned(G, ty) && grid_tile_touches(G, edge, tx, ty)) visit(static_cast<uint32_t>(ty) * G.tiles_w + tx);
+    }
+}
+
+// Walks the boxes of a warp's triangles: small ones per thread, then every large one by the whole warp (its box,
+// edge functions and slot broadcast from the owning lane).  Called by all 32 lanes.
+template <class Visit>
+__device__ __forceinline__ void grid_walk_warp(GridBuild const& G, bool binned, uint32_t slot, float4 const (&edge)[3],
+                                               int tx0, int tx1, int ty0, int ty1, Visit&& visit)
+{
+    uint32_t const n = binned ? static_cast<uint32_t>((tx1 - tx0 + 1) * (ty1 - ty0 + 1)) : 0u;
+    bool const big = n > kGridCoopTiles;
+    if (binned && !big)
+        grid_visit_tiles<false>(G, edge, tx0, tx1, ty0, ty1, [&](uint32_t tile) { visit(tile, slot); });
+    uint32_t todo = __ballot_sync(0xffffffffu, big);
+    while (todo)
+    {
+        int const src = __ffs(todo) - 1;
+        todo &= todo - 1u;
+        float4 e[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++)
+        {
+            e[k].x = __shfl_sync(0xffffffffu, edge[k].x, src);
+            e[k].y = __shfl_sync(0xffffffffu, edge[k].y, src);
+            e[k].z = __shfl_sync(0xffffffffu, edge[k].z, src);
+            e[k].w = 0.f;
+        }
+        int const bx0 = __shfl_sync(0xffffffffu, tx0, src), bx1 = __shfl_sync(0xffffffffu, tx1, src);
+        int const by0 = __shfl_sync(0xffffffffu, ty0, src), by1 = __shfl_sync(0xffffffffu, ty1, src);
+        uint32_t const bslot = __shfl_sync(0xffffffffu, slot, src);
+        grid_visit_tiles<true>(G, e, bx0, bx1, by0, by1, [&](uint32_t tile) { visit(tile, bslot); });
+    }
+}
+
 __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__ GridBuild G)
 {
-    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= G.scene.n_tris_padded) return;
+    uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;     // n_tris_padded is a multiple of the block size
     float4 box = make_float4(1.f, 1.f, 0.f, 0.f);
     float4 edge[3] = {make_float4(0.f, 0.f, 1.f, 0.f), make_float4(0.f, 0.f, 1.f, 0.f), make_float4(0.f, 0.f, 1.f, 0.f)};
     bool global = false;
-    if (i < G.scene.n_tris && __float_as_int(reinterpret_cast<float4 const*>(G.scene.tri_v0)[i].w) >= 0)
-        global = grid_project(G, i, box, edge);
-    int tx0, tx1, ty0, ty1;
-    bool const binned = !global && box.x <= box.z && grid_tile_range(G, box, tx0, tx1, ty0, ty1);
+    bool const real = i < G.scene.n_tris && __float_as_int(reinterpret_cast<float4 const*>(G.scene.tri_v0)[i].w) >= 0;
+    if (real) global = grid_project(G, i, box, edge);
+    int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+    bool binned = !global && box.x <= box.z && grid_tile_range(G, box, tx0, tx1, ty0, ty1);
     if (binned && static_cast<uint32_t>((tx1 - tx0 + 1) * (ty1 - ty0 + 1)) > G.max_tiles_per_tri) global = true;
     if (global)
     {
         uint32_t const k = atomicAdd(&G.flags->n_global, 1u);
         if (k < kGridMaxGlobal) G.global[k] = i;
-        box = make_float4(1.f, 1.f, 0.f, 0.f);
+        binned = false;
     }
-    else if (binned)
+    if (!binned) box = make_float4(1.f, 1.f, 0.f, 0.f);   // global, off the frame or behind the camera
+    grid_walk_warp(G, binned, i, edge, tx0, tx1, ty0, ty1,
+                   [&](uint32_t tile, uint32_t) { atomicAdd(&G.tile_cnt[tile], 1u); });
+    if (i < G.scene.n_tris_padded)
     {
-        for (int ty = ty0; ty <= ty1; ty++)
-        {
-            if (!grid_row_owned(G, ty)) continue;
-            for (int tx = tx0; tx <= tx1; tx++)
-                if (grid_tile_touches(G, edge, tx, ty)) atomicAdd(&G.tile_cnt[ty * G.tiles_w + tx], 1u);
-        }
-    }
-    else
-    {
-        box = make_float4(1.f, 1.f, 0.f, 0.f);   // off the frame or behind the camera
-    }
-    reinterpret_cast<float4*>(G.bbox)[i] = box;
+        reinterpret_cast<float4*>(G.bbox)[i] = box;
 #pragma unroll
-    for (int k = 0; k < 3; k++) reinterpret_cast<float4*>(G.edges)[3 * i + k] = edge[k];
+        for (int k = 0; k < 3; k++) reinterpret_cast<float4*>(G.edges)[3 * i + k] = edge[k];
+    }
 }
 
 // Exclusive prefix sum of the tile counts in three small launches (the light grid has ~10^6 cells):
@@ -790,20 +833,21 @@ __global__ void __launch_bounds__(kScanBlock) grid_scan_blocks_kernel(const __gr
 __global__ void __launch_bounds__(256) grid_fill_kernel(const __grid_constant__ GridBuild G)
 {
     uint32_t const i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= G.scene.n_tris || G.flags->ok == 0) return;
-    float4 const box = reinterpret_cast<float4 const*>(G.bbox)[i];
-    int tx0, tx1, ty0, ty1;
-    if (!(box.x <= box.z) || !grid_tile_range(G, box, tx0, tx1, ty0, ty1)) return;
-    float4 edge[3];
+    if (G.flags->ok == 0) return;      // grid-uniform
+    float4 box = make_float4(1.f, 1.f, 0.f, 0.f);
+    float4 edge[3] = {make_float4(0.f, 0.f, 1.f, 0.f), make_float4(0.f, 0.f, 1.f, 0.f), make_float4(0.f, 0.f, 1.f, 0.f)};
+    if (i < G.scene.n_tris)
+    {
+        box = reinterpret_cast<float4 const*>(G.bbox)[i];
 #pragma unroll
-    for (int k = 0; k < 3; k++) edge[k] = reinterpret_cast<float4 const*>(G.edges)[3 * i + k];
-    for (int ty = ty0; ty <= ty1; ty++)
-        for (int tx = tx0; tx <= tx1; tx++)
-        {
-            if (!grid_row_owned(G, ty) || !grid_tile_touches(G, edge, tx, ty)) continue;
-            uint32_t const t = ty * G.tiles_w + tx;
-            G.items[G.tile_off[t] + atomicAdd(&G.cursor[t], 1u)] = i;
-        }
+        for (int k = 0; k < 3; k++) edge[k] = reinterpret_cast<float4 const*>(G.edges)[3 * i + k];
+    }
+    int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+    bool const binned = box.x <= box.z && grid_tile_range(G, box, tx0, tx1, ty0, ty1);
+    // the same walk as grid_count_kernel (same boxes, same edge functions, same decisions)
+    grid_walk_warp(G, binned, i, edge, tx0, tx1, ty0, ty1, [&](uint32_t tile, uint32_t slot) {
+        G.items[G.tile_off[tile] + atomicAdd(&G.cursor[tile], 1u)] = slot;
+    });
 }
 
 // Light grid only: every cell's list ordered by the triangles' nearest depth edges[3*slot].w, ascending (ties by
@@ -1093,6 +1137,10 @@ __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __g
     uint32_t const x = blockIdx.x * kBvhBlockW + (warp & 3u) * 8u + (lane & 7u);
     uint32_t const y = L.row_origin + blockIdx.y * L.row_block_step + (warp >> 2) * 4u + (lane >> 3);
     bool const valid = x < W && y < L.params.y1;
+    unsigned long long const t_block = L.d_trace ? trace_now() : 0ull;
+    // a warp's 8x4 pixels are four 96-byte row segments of the frame: staged here, written as 128-bit stores
+    __shared__ __align__(16) float s_out[kBvhThreads / 32][4][24];
+    V3 out_rgb = V3{0.f, 0.f, 0.f};
 
     unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
     if (valid)
@@ -1180,8 +1228,38 @@ __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __g
             acc.y = add(acc.y, rgb.y);
             acc.z = add(acc.z, rgb.z);
         }
-        store_pixel(L, y * W + x, acc, first_hit);
+        out_rgb = V3{mul(acc.x, L.inv_spp), mul(acc.y, L.inv_spp), mul(acc.z, L.inv_spp)};
+        size_t const out = static_cast<size_t>(y * W + x) - static_cast<size_t>(L.params.buf_y0) * W;
+        if (L.d_hit_id) L.d_hit_id[out] = first_hit.id;
+        if (L.d_hit_t) L.d_hit_t[out] = first_hit.t;
     }
+    if (L.d_rgb)
+    {
+        // whole, 16-byte aligned segments (every tile of a frame whose width is a multiple of 4, edges aside):
+        // 24 lanes store one float4 each; otherwise every valid lane stores its own three floats
+        uint32_t const lx = lane & 7u, ly = lane >> 3;
+        uint32_t const x0 = x - lx, y0 = y - ly;
+        float* const seg = L.d_rgb + (static_cast<size_t>(y0 * W + x0) - static_cast<size_t>(L.params.buf_y0) * W) * 3;
+        bool const vec = __all_sync(0xffffffffu, valid) && (W & 3u) == 0u && (reinterpret_cast<uintptr_t>(seg) & 15u) == 0;
+        if (vec)
+        {
+            float* const mine = &s_out[warp][ly][lx * 3u];
+            mine[0] = out_rgb.x; mine[1] = out_rgb.y; mine[2] = out_rgb.z;
+            __syncwarp();
+            if (lane < 24u)
+            {
+                uint32_t const r = lane / 6u, v = lane - r * 6u;
+                reinterpret_cast<float4*>(seg + static_cast<size_t>(r) * W * 3u)[v] =
+                    reinterpret_cast<float4 const*>(s_out[warp][r])[v];
+            }
+        }
+        else if (valid)
+        {
+            float* const px = seg + (static_cast<size_t>(ly) * W + lx) * 3u;
+            px[0] = out_rgb.x; px[1] = out_rgb.y; px[2] = out_rgb.z;
+        }
+    }
+    trace_block(L, t_block);
     flush_counters(L, n_primary, n_shadow, n_box, n_tri);
 }
 
@@ -1196,22 +1274,49 @@ __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __g
 // pixel-per-thread kernel and the oracle (docs/RENDER_SPEC.md section 5).
 constexpr int kSppTileW = 8; // block = 8 warps; warp w owns row w of an 8x8 pixel tile
 
+// Moller-Trumbore against a staged candidate whose ray-ORIGIN-dependent terms are precomputed: all primary
+// rays leave the camera origin o, so tv = o - v0, q = tv x e1 and tsr = e2 . q are per-triangle constants of
+// the frame.  They are produced by the same operations on the same operands as in mt_inside, hence the
+// same bits; what is left per ray is p = d x e2, det = e1 . p, us = tv . p, vs = d . q: 15 instead of 33
+// FP32 instructions.
+__device__ __forceinline__ bool mt_inside_pre(V3 d, float4 e1_tsr, float4 e2_id, float4 tv4, float4 q4,
+                                              float& ts, float& adet)
+{
+    V3 const E1 = v3(e1_tsr), E2 = v3(e2_id), tv = v3(tv4), q = v3(q4);
+    V3 const p = cross3(d, E2);
+    float const det = dot3(E1, p);
+    float us = dot3(tv, p);
+    float vs = dot3(d, q);
+    uint32_t const sgn = __float_as_uint(det) & 0x80000000u;
+    us = __uint_as_float(__float_as_uint(us) ^ sgn);
+    vs = __uint_as_float(__float_as_uint(vs) ^ sgn);
+    ts = __uint_as_float(__float_as_uint(e1_tsr.w) ^ sgn);
+    adet = fabsf(det);
+    return (us >= 0.0f) & (vs >= 0.0f) & (add(us, vs) <= adet);
+}
+
 template <bool STATS, int PIX, int MINB = 4>
 __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_constant__ RenderLaunch L)
 {
     constexpr uint32_t SPL = 32u / PIX; // sample lanes per pixel
-    static_assert(SPL >= 3, "one lane per (pixel, channel) does the ordered sum");
-    __shared__ float s_val[8][32][3];
+    static_assert(SPL >= 4, "one lane per (pixel, channel) does the ordered sum; 128-bit reads of the sample values");
+    unsigned long long const t_block = L.d_trace ? trace_now() : 0ull;
+    // sample values of the current pass, channel-major so that the summing lane reads them as float4
+    __shared__ __align__(16) float s_val[8][3][32];
+    // finished pixels of the warp's row (8 pixels x RGB): written to the frame as 128-bit stores
+    __shared__ __align__(16) float s_out[8][24];
     // Primary-ray grid (PIX == 1 only): the block IS one 8x8 grid tile.  The tile's candidate triangles
-    // (plus the frame's global ones) are staged in shared memory once; every warp filters them against
-    // its current pixel (lanes test different candidates, ballot-compacted), and every sample of that
-    // pixel then tests the few survivors instead of walking the BVH.
+    // (plus the frame's global ones) are staged in shared memory once -- edges, the origin-dependent
+    // Moller-Trumbore terms, unit normal and albedo, so that neither the test nor the shading of a sample
+    // touches global memory; every warp filters them against its current pixel (lanes test different
+    // candidates, ballot-compacted), and every sample of that pixel then tests the few survivors.
     constexpr uint32_t kCand = PIX == 1 ? kGridMaxList + kGridMaxGlobal : 1;
-    __shared__ float4 s_cv0[kCand], s_ce1[kCand], s_ce2[kCand], s_cbox[kCand], s_cedge[3][kCand];
-    __shared__ uint32_t s_cslot[kCand];
+    __shared__ float4 s_ce1[kCand], s_ce2[kCand], s_ctv[kCand], s_cq[kCand], s_cn[kCand], s_calb[kCand];
+    __shared__ float4 s_cbox[kCand], s_cedge[3][kCand];
     __shared__ uint8_t s_pixlist[PIX == 1 ? 8 : 1][kCand];
     uint32_t n_cand = 0;
     bool use_grid = false;
+    V3 const o = v3(L.camera.origin);
     if (PIX == 1 && L.grid.enabled)
     {
         GridFlags const fl = *L.grid.flags;
@@ -1226,10 +1331,17 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
             {
                 bool const glob = threadIdx.x >= cnt;
                 uint32_t const slot = glob ? L.grid.global[threadIdx.x - cnt] : L.grid.items[off + threadIdx.x];
-                s_cslot[threadIdx.x] = slot;
-                s_cv0[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_v0) + slot);
-                s_ce1[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e1) + slot);
-                s_ce2[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e2) + slot);
+                float4 const v0 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_v0) + slot);
+                float4 const e1 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e1) + slot);
+                float4 const e2 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e2) + slot);
+                V3 const tv = V3{sub(o.x, v0.x), sub(o.y, v0.y), sub(o.z, v0.z)};
+                V3 const q = cross3(tv, v3(e1));
+                s_ce1[threadIdx.x] = make_float4(e1.x, e1.y, e1.z, dot3(v3(e2), q));
+                s_ce2[threadIdx.x] = make_float4(e2.x, e2.y, e2.z, v0.w);          // .w = bits(triangle id)
+                s_ctv[threadIdx.x] = make_float4(tv.x, tv.y, tv.z, 0.f);
+                s_cq[threadIdx.x] = make_float4(q.x, q.y, q.z, 0.f);
+                s_cn[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_n) + slot);
+                s_calb[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.albedo) + __float_as_int(v0.w));
                 s_cbox[threadIdx.x] = glob ? make_float4(-pos_inf(), -pos_inf(), pos_inf(), pos_inf())
                                            : __ldg(reinterpret_cast<float4 const*>(L.grid.bbox) + slot);
 #pragma unroll
@@ -1246,7 +1358,6 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
     uint32_t const p = lane / SPL, sl = lane % SPL;
     uint32_t const y = L.row_origin + blockIdx.y * L.row_block_step + warp;
     uint32_t const spp = L.params.spp;
-    V3 const o = v3(L.camera.origin);
     V3 const bg = v3(L.params.background);
 
     unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
@@ -1274,6 +1385,7 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
             if (PIX == 1 && use_grid)
             {
                 float const px0 = static_cast<float>(x), py0 = static_cast<float>(y);
+                float const qx = px0 + 0.5f, qy = py0 + 0.5f;   // the margin in c covers the pixel square
                 for (uint32_t base = 0; base < n_cand; base += 32u)
                 {
                     uint32_t const j = base + lane;
@@ -1282,13 +1394,8 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                     {
                         float4 const b = s_cbox[j];
                         pass = b.z >= px0 && b.x <= px0 + 1.0f && b.w >= py0 && b.y <= py0 + 1.0f;
-                        float const qx = px0 + 0.5f, qy = py0 + 0.5f;   // the margin in c covers the pixel square
 #pragma unroll
-                        for (int k = 0; k < 3; k++)
-                        {
-                            float4 const e = s_cedge[k][j];
-                            pass = pass && (e.x * qx + e.y * qy + e.z >= 0.0f);
-                        }
+                        for (int k = 0; k < 3; k++) pass = pass && edge_pass(s_cedge[k][j], qx, qy);
                     }
                     uint32_t const m = __ballot_sync(0xffffffffu, pass);
                     if (pass) s_pixlist[warp][n_pix + __popc(m & ((1u << lane) - 1u))] = static_cast<uint8_t>(j);
@@ -1306,20 +1413,30 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                     Hit best = no_hit();
                     bool occ = false;
                     n_primary++;
+                    ShadeOut sh;
+                    sh.need_shadow = false;
                     if (PIX == 1 && use_grid)
                     {
                         if (STATS) n_tri += n_pix;
                         for (uint32_t k = 0; k < n_pix; k++)
                         {
                             uint32_t const j = s_pixlist[warp][k];       // same address in every lane: broadcast
-                            float4 const v0 = s_cv0[j], e1 = s_ce1[j], e2 = s_ce2[j];
+                            float4 const e1 = s_ce1[j], e2 = s_ce2[j];
                             float ts, adet;
-                            if (mt_inside(o, d, v0, e1, e2, ts, adet))
-                                closest_update(best, ts, adet, __float_as_int(v0.w), s_cslot[j], L.params.t_min);
+                            if (mt_inside_pre(d, e1, e2, s_ctv[j], s_cq[j], ts, adet))
+                                closest_update(best, ts, adet, __float_as_int(e2.w), j, L.params.t_min);   // slot = list index
                         }
+                        if (best.id >= 0) sh = shade_hit(L, o, d, best.t, v3(s_cn[best.slot]), v3(s_calb[best.slot]));
                     }
                     else
+                    {
                         bvh_trace<false, STATS>(L.scene, o, d, L.params.t_min, best, occ, n_box, n_tri, hint_hit);
+                        if (best.id >= 0)
+                        {
+                            sh = shade_hit(L, o, d, best);
+                            if (use_hints) hint_hit = best.slot;
+                        }
+                    }
                     if (s == 0) first_hit = best;
                     if (best.id < 0)
                     {
@@ -1327,7 +1444,6 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                     }
                     else
                     {
-                        ShadeOut sh = shade_hit(L, o, d, best);
                         rgb = sh.rgb;
                         if (sh.need_shadow)
                         {
@@ -1342,32 +1458,55 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                                 if (use_hints) hint_occ = dummy.slot;
                             }
                         }
-                        if (use_hints) hint_hit = best.slot;
                     }
                 }
-                s_val[warp][lane][0] = rgb.x;
-                s_val[warp][lane][1] = rgb.y;
-                s_val[warp][lane][2] = rgb.z;
+                s_val[warp][0][lane] = rgb.x;
+                s_val[warp][1][lane] = rgb.y;
+                s_val[warp][2][lane] = rgb.z;
                 __syncwarp();
                 if (sl < 3)
                 {
+                    // ordered sum (docs/RENDER_SPEC.md section 5): sample values strictly in index order
+                    float const* const v = &s_val[warp][sl][p * SPL];
                     uint32_t const n = min(SPL, spp - s0);
-                    for (uint32_t j = 0; j < n; j++) sum = add(sum, s_val[warp][p * SPL + j][sl]);
+                    if (n == SPL)
+                    {
+#pragma unroll
+                        for (uint32_t j = 0; j < SPL; j += 4)
+                        {
+                            float4 const q4 = *reinterpret_cast<float4 const*>(v + j);
+                            sum = add(add(add(add(sum, q4.x), q4.y), q4.z), q4.w);
+                        }
+                    }
+                    else
+                        for (uint32_t j = 0; j < n; j++) sum = add(sum, v[j]);
                 }
                 __syncwarp();
             }
-            if (in_frame)
+            if (sl < 3) s_out[warp][(g * PIX + p) * 3 + sl] = mul(sum, L.inv_spp);
+            if (in_frame && sl == 0) // this lane traced sample 0
             {
                 size_t const out = static_cast<size_t>(y * W + x) - static_cast<size_t>(L.params.buf_y0) * W;
-                if (sl < 3 && L.d_rgb) L.d_rgb[out * 3 + sl] = mul(sum, L.inv_spp);
-                if (sl == 0) // this lane traced sample 0
-                {
-                    if (L.d_hit_id) L.d_hit_id[out] = first_hit.id;
-                    if (L.d_hit_t) L.d_hit_t[out] = first_hit.t;
-                }
+                if (L.d_hit_id) L.d_hit_id[out] = first_hit.id;
+                if (L.d_hit_t) L.d_hit_t[out] = first_hit.t;
             }
         }
+        // the warp's 8 pixels x RGB = 96 contiguous bytes of the frame: six 128-bit stores in one instruction
+        // when the row segment is whole and 16-byte aligned (W % 4 == 0), coalesced scalar stores otherwise
+        __syncwarp();
+        if (L.d_rgb)
+        {
+            uint32_t const x0 = blockIdx.x * kSppTileW;
+            float* const dst = L.d_rgb + (static_cast<size_t>(y * W + x0) - static_cast<size_t>(L.params.buf_y0) * W) * 3;
+            if (x0 + kSppTileW <= W && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0)
+            {
+                if (lane < 6) reinterpret_cast<float4*>(dst)[lane] = reinterpret_cast<float4 const*>(s_out[warp])[lane];
+            }
+            else if (lane < 24 && x0 + lane / 3 < W)
+                dst[lane] = s_out[warp][lane];
+        }
     }
+    trace_block(L, t_block);
     flush_counters(L, n_primary, n_shadow, n_box, n_tri);
 }
 

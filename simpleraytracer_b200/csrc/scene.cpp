@@ -47,11 +47,12 @@ void RowBlocks(srt_render_params const& p, uint32_t& origin, uint32_t& step, uin
     count = first < b0 + blocks ? (b0 + blocks - first + stride - 1) / stride : 0;
 }
 
-// Per-frame device scratch (one 64-byte memset per render call): 4 x u64 ray/test counters | 2 x u32 block
-// tickets of the completion signal (one per launch stream) | pad | GridFlags of the screen grid.
-constexpr size_t kScratchBytes = 64;
+// Per-frame device scratch (one 128-byte memset per render call): 4 x u64 ray/test counters | 2 x u32 block
+// tickets of the completion signal (one per launch stream) | pad | GridFlags of the screen grid | block trace.
+constexpr size_t kScratchBytes = 128;
 constexpr size_t kScratchTicketWord = 8;    // in uint32 units
 constexpr size_t kScratchGridFlagsWord = 12;
+constexpr size_t kScratchTraceU64 = 8;      // 5 x u64 block timeline probe (SRT_BLOCK_TRACE=1)
 } // namespace
 
 // Rows [y0, y1) cut into at most `requested` chunks of whole (8 * stride)-row groups, so that every chunk
@@ -280,7 +281,9 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     b.width = gw; b.height = gh; b.tiles_w = gw; b.tiles_h = gh; b.cap = cap;
     b.tile = 1; b.lo_bias = 0.f;
     b.ty_begin = 0; b.ty_end = gh; b.ty_stride = 1; b.ty_phase = 0;
-    b.max_tiles_per_tri = 1u << 16;    // built once per light position: a few long loops are affordable
+    // built once per light position: long walks are affordable.  A scene of at most kGridMaxGlobal triangles needs
+    // no lists at all: every triangle goes to the global list and each shadow ray tests them all.
+    b.max_tiles_per_tri = m_view.n_tris <= kGridMaxGlobal ? 0u : 1u << 16;
     // laid out by the CAPACITY of the allocation, so the count array never overlaps another array of an
     // earlier, differently sized build (its all-zero invariant replaces the per-build memset)
     size_t const cap_tiles = m_lgrid_tiles;
@@ -394,7 +397,7 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
     b.ty_end = (params->y1 + kGridTile - 1) / kGridTile;
     b.ty_stride = params->row_block_stride > 1 ? params->row_block_stride : 1;
     b.ty_phase = params->row_block_phase;
-    b.max_tiles_per_tri = 1024;
+    b.max_tiles_per_tri = m_view.n_tris <= kGridMaxGlobal ? 0u : 1024u;   // tiny scenes: all global, no binning
     // laid out by the CAPACITY of the allocation, so the count array never overlaps another array of an
     // earlier, differently sized build (its all-zero invariant replaces the per-build memset)
     size_t const cap_tiles = m_grid_tiles;
@@ -569,6 +572,8 @@ void Scene::EnqueueBand(srt_camera const* camera, srt_light const* light, srt_re
     launch.d_signal = d_signal;
     launch.signal_value = signal_value;
     launch.d_ticket = reinterpret_cast<uint32_t*>(m_d_counters) + kScratchTicketWord + (ticket & 1u);
+    static int const trace = std::getenv("SRT_BLOCK_TRACE") ? std::atoi(std::getenv("SRT_BLOCK_TRACE")) : 0;
+    launch.d_trace = trace ? m_d_counters + kScratchTraceU64 : nullptr;
     RowBlocks(*params, launch.row_origin, launch.row_block_step, launch.n_row_blocks);
     static int const hints = std::getenv("SRT_BVH_HINTS") ? std::atoi(std::getenv("SRT_BVH_HINTS")) : 1;
     launch.hints = static_cast<uint32_t>(hints);
@@ -595,6 +600,17 @@ ml_status Scene::GetStats(srt_render_stats* stats)
         stats->shadow_rays = c[1];
         stats->box_tests = c[2];
         stats->tri_tests = c[3];
+        if (std::getenv("SRT_BLOCK_TRACE") && std::atoi(std::getenv("SRT_BLOCK_TRACE")))
+        {
+            // diagnostic: when did the launch run out of fresh blocks, and how long did it drain
+            unsigned long long t[5] = {};
+            ML_CUDA_CHECK(cudaMemcpy(t, m_d_counters + kScratchTraceU64, sizeof(t), cudaMemcpyDeviceToHost));
+            unsigned long long const first = ~t[0];
+            if (t[2] > first)
+                std::fprintf(stderr, "[srt trace] span %.1f us, last block start at %.1f us (drain %.1f us), "
+                                     "sum of block durations %.1f us, longest block %.1f us\n",
+                             (t[2] - first) * 1e-3, (t[1] - first) * 1e-3, (t[2] - t[1]) * 1e-3, t[3] * 1e-3, t[4] * 1e-3);
+        }
         stats->kernel_ms = 0.f;
         stats->grid_build_ms = 0.f;
         stats->light_grid_build_ms = 0.f;
