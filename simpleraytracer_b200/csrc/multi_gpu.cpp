@@ -269,6 +269,7 @@ private:
         std::unique_ptr<Scene> scene;
         std::thread thread;
         ml_status status = ML_OK;
+        cudaEvent_t done = nullptr;   // same-GPU replicas only: their launches have completed
     };
     struct Job
     {
@@ -357,6 +358,7 @@ SceneGroup::~SceneGroup()
     {
         cudaSetDevice(m.device->device);
         cudaStreamSynchronize(m.device->stream);
+        if (m.done) cudaEventDestroy(m.done);
         m.scene.reset();
     }
     cudaSetDevice(m_members[0].device->device);
@@ -449,6 +451,20 @@ ml_status SceneGroup::Render(srt_camera const* camera, srt_light const* light, s
         {
             std::unique_lock<std::mutex> lock(m_mutex);
             m_cv_done.wait(lock, [&] { return m_pending == 0; });
+        }
+        // Replicas that share the owner's GPU (tests on a one-GPU box) are ordered by a stream dependency instead:
+        // kernels that spin on one another must never be separate launches on ONE GPU (nothing guarantees that
+        // they run at the same time), so the wait kernel there only ever finds flags that are already set.
+        bool shared_gpu = false;
+        for (uint32_t r = 1; r < n; r++) shared_gpu = shared_gpu || m_members[r].device->device == dev0.device;
+        for (uint32_t r = 0; r < n && shared_gpu; r++)
+        {
+            Member& m = m_members[r];
+            if (m.device->device != dev0.device || m.status != ML_OK) continue;
+            m.device->MakeCurrent();
+            if (m.done == nullptr) ML_CUDA_CHECK(cudaEventCreateWithFlags(&m.done, cudaEventDisableTiming));
+            ML_CUDA_CHECK(cudaEventRecord(m.done, m.device->stream));
+            ML_CUDA_CHECK(cudaStreamWaitEvent(dev0.copy_out, m.done, 0));
         }
         dev0.MakeCurrent();
         uint32_t const before = *dev0.wait_timeouts;

@@ -89,16 +89,22 @@ def test_signal_flags_and_gather_between_two_contexts(ctx):
         rows, n_chunks = api.chunk_layout(whole, chunks)
         assert rows % (8 * N) == 0 and rows * n_chunks >= H
         host = np.full((H, W, 3), -1.0, np.float32)
-        for r in reversed(range(N)):            # rank 0 last: the consumer must really wait for the others
+        for r in reversed(range(N)):
             p = api.make_params(W, H, spp=4, row_block_stride=N, row_block_phase=r, **COMMON)
             scenes[r].render_device_signal(cam, light, p, d_frame, d_flags + 4 * r, epoch, chunk_stride=N,
                                            n_chunks=n_chunks)
+        # Both 'ranks' share ONE GPU here: the producers are drained before the consumer's spin kernel is
+        # launched (kernels that wait on one another must not be separate launches on one GPU); the genuinely
+        # concurrent wait is exercised on real peers (test_scene_group_on_real_peers, the bench test).
+        for sc in scenes:
+            sc.stats()
         ranks[0].gather_frame_host(whole, d_frame, d_flags, N, n_chunks, epoch, host)
         assert np.array_equal(host, want), f"epoch {epoch}"
     # device-side wait only (the device-timed bench step): frame complete once the wait kernel has run
     for r in range(N):
         p = api.make_params(W, H, spp=4, row_block_stride=N, row_block_phase=r, **COMMON)
         scenes[r].render_device_signal(cam, light, p, d_frame, d_flags + 4 * r, 9, chunk_stride=N)
+    scenes[1].stats()                            # drained first: one GPU (see above)
     ranks[0].stream_wait_flags(d_flags, N, 9)
     scenes[0].stats()                            # synchronises rank 0's stream
     assert ranks[0].flag_wait_timeouts() == 0
