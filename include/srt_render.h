@@ -232,6 +232,28 @@ ML_API_ENTRY uint32_t srtSceneGroupSize(srt_scene_group group);
 ML_API_ENTRY char* srtGetSceneGroupError(srt_scene_group group, char* buffer, size_t buffer_size);
 ML_API_ENTRY void srtReleaseSceneGroup(srt_scene_group group);
 
+/* ---- render without allocation -------------------------------------------
+ * srtRenderDeviceNoAlloc has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  It is srtRenderDevice -- same arguments, same pixels, bit for bit -- with all of
+ * the call's scratch memory (ray counters, the screen grid's tile lists and per-triangle records) in ONE static
+ * device array of the library (about 4.3 MB that every GPU loading the library holds until exit) instead of
+ * buffers the scene allocates on demand.  It calls no cudaMalloc / cudaFree / allocating routine and creates
+ * no events; inputs (the resident scene) and outputs (d_rgb / d_hit_id / d_hit_t, device pointers, any may be
+ * NULL) are the caller's.  Limits: the scene holds at most SRT_NOALLOC_MAX_TRIANGLES triangles and the frame at
+ * most SRT_NOALLOC_MAX_TILES 8x8-pixel tiles (e.g. 1024 x 1024); beyond either the call fails with ML_FAIL and a
+ * message on the scene.  Shadow rays walk the BVH (no light grid: its scratch scales with the scene).
+ * Asynchronous on `stream` (NULL: the context's stream); no ray statistics (srtGetRenderStats does not see this
+ * call).  Every call on a GPU shares the one array, which keeps the previous call's contents (what must start at
+ * zero is cleared by the call itself): calls that OVERLAP on the GPU -- other streams, other scenes, other
+ * threads -- race and give undefined pixels; serialise them.  The first call on a device resolves the array's
+ * address (cudaGetSymbolAddress): make one call before starting a graph capture. */
+#define SRT_NOALLOC_MAX_TRIANGLES 32768
+#define SRT_NOALLOC_MAX_TILES 16384
+ML_API_ENTRY ml_status srtRenderDeviceNoAlloc(srt_scene scene, srt_camera const* camera,
+                                              srt_light const* light, srt_render_params const* params,
+                                              void* d_rgb, void* d_hit_id, void* d_hit_t, void* stream);
+
 /* Independent-FFMA microbenchmark over all SMs: the FP32 roofline denominator
  * (MEASURED_PEAKS.json carries no FP32 figure).  Returns TFLOP/s (FMA = 2). */
 ML_API_ENTRY double srtMeasureFp32Peak(ml_context context, int repeats);

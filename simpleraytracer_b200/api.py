@@ -19,6 +19,7 @@ MLX_PRECISION_FP32, MLX_PRECISION_BF16, MLX_PRECISION_BF16X3 = 0, 1, 2
 ML_FLOAT32, ML_FLOAT16 = 0, 1
 SRT_SHADE_ALBEDO, SRT_SHADE_LAMBERT, SRT_SHADE_SHADOW = 0, 1, 2
 SRT_ACCEL_BRUTE, SRT_ACCEL_BVH = 0, 1
+SRT_NOALLOC_MAX_TRIANGLES, SRT_NOALLOC_MAX_TILES = 32768, 16384
 
 
 class MLError(RuntimeError):
@@ -93,6 +94,9 @@ _PROTOTYPES = {
     "srtRenderDevice": (C.c_int, [C.c_void_p, C.POINTER(srt_camera), C.POINTER(srt_light),
                                   C.POINTER(srt_render_params), C.c_void_p, C.c_void_p, C.c_void_p,
                                   C.c_void_p]),
+    "srtRenderDeviceNoAlloc": (C.c_int, [C.c_void_p, C.POINTER(srt_camera), C.POINTER(srt_light),
+                                         C.POINTER(srt_render_params), C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_void_p]),
     "srtGetRenderStats": (C.c_int, [C.c_void_p, C.POINTER(srt_render_stats)]),
     "srtRenderToImage": (C.c_int, [C.c_void_p, C.POINTER(srt_camera), C.POINTER(srt_light),
                                    C.POINTER(srt_render_params), C.c_void_p, C.POINTER(srt_render_stats)]),
@@ -460,6 +464,13 @@ class Scene:
         st = self.lib.srtRenderDeviceSignal(self.handle, C.byref(camera), C.byref(light), C.byref(params),
                                             d_rgb or None, None, None, stream or None, d_flags, chunk_stride,
                                             n_chunks, value)
+        if st != ML_OK:
+            raise MLError(self.error())
+
+    def render_device_no_alloc(self, camera, light, params, d_rgb=0, d_hit_id=0, d_hit_t=0, stream=0):
+        """srtRenderDeviceNoAlloc: srtRenderDevice with its scratch in the library's static device array."""
+        st = self.lib.srtRenderDeviceNoAlloc(self.handle, C.byref(camera), C.byref(light), C.byref(params),
+                                             d_rgb or None, d_hit_id or None, d_hit_t or None, stream or None)
         if st != ML_OK:
             raise MLError(self.error())
 

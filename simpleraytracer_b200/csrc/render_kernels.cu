@@ -24,6 +24,8 @@
 
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 namespace ML {
 namespace {
 
@@ -1723,6 +1725,87 @@ void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
         }
     }
     ML_CUDA_CHECK(cudaGetLastError());
+}
+
+// ---------------------------------------------------------------------------
+// srtRenderDeviceNoAlloc: the render with its per-frame scratch in STATIC device memory
+// ---------------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops).  The scratch every render call needs -- ray counters and
+// block tickets, and the screen grid's tile counts / offsets / cursors / lists / per-triangle boxes and edge
+// functions -- lives in one file-scope array that every GPU loading the library holds until exit.
+// Layout (regions 256-byte aligned); sizes follow SRT_NOALLOC_MAX_TRIANGLES / SRT_NOALLOC_MAX_TILES:
+constexpr size_t kNaTris = SRT_NOALLOC_MAX_TRIANGLES, kNaTiles = SRT_NOALLOC_MAX_TILES;
+constexpr size_t kNaAlign = 256;
+constexpr size_t NaRound(size_t n) { return (n + kNaAlign - 1) / kNaAlign * kNaAlign; }
+constexpr size_t kNaFrameBytes = 256;                                        // counters | tickets | GridFlags (as Scene's scratch)
+constexpr size_t kNaGlobalOff = kNaFrameBytes;                               // kGridMaxGlobal u32
+constexpr size_t kNaTilesOff = NaRound(kNaGlobalOff + kGridMaxGlobal * 4);   // tile_cnt | tile_off | cursor | block_sums
+constexpr size_t kNaTileWords = 3 * kNaTiles + 16 + kNaTiles / 4096 + 8;
+constexpr size_t kNaItemsOff = NaRound(kNaTilesOff + kNaTileWords * 4);
+constexpr size_t kNaItems = 16 * kNaTris;                                    // list entries; more: flags.ok = 0, BVH walk
+constexpr size_t kNaBoxOff = NaRound(kNaItemsOff + kNaItems * 4);            // bbox | edges: 4 float4 per triangle slot
+constexpr size_t kNaBytes = NaRound(kNaBoxOff + 4 * kNaTris * sizeof(float4));
+static_assert(kNaTris % kTriTile == 0, "padded triangle count must fit");
+static_assert(kNaBytes <= (size_t(8) << 20), "keep the static scratch modest");
+
+// In host code this name is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaBytes];
+
+// Device address of the scratch on `device` (current): resolved once per device, return code checked.
+static unsigned char* NoAllocScratchAddress(int device)
+{
+    static std::mutex mutex;
+    static unsigned char* address[64] = {};
+    if (device < 0 || device >= 64) throw std::runtime_error("srtRenderDeviceNoAlloc: device ordinal out of range");
+    std::lock_guard<std::mutex> lock(mutex);
+    if (address[device] == nullptr)
+    {
+        void* ptr = nullptr;
+        ML_CUDA_CHECK(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+        if (ptr == nullptr) throw std::runtime_error("srtRenderDeviceNoAlloc: cudaGetSymbolAddress returned NULL");
+        address[device] = static_cast<unsigned char*>(ptr);
+    }
+    return address[device];
+}
+
+// `launch` / `build` arrive complete except for every pointer into scratch memory, which is set here.  Calls
+// nothing that allocates: cudaGetSymbolAddress (first call per device), cudaMemsetAsync, kernel launches.
+// The array keeps the previous call's contents: what must start at zero is cleared on `stream` first.  Calls
+// that overlap on the GPU (other streams, other scenes, other threads) share the array and race.
+void RenderNoAllocScratch(int device, RenderLaunch launch, GridBuild build, bool use_grid, int sm_count,
+                          cudaStream_t stream)
+{
+    unsigned char* const base = NoAllocScratchAddress(device);
+    unsigned long long* const frame = reinterpret_cast<unsigned long long*>(base);
+    ML_CUDA_CHECK(cudaMemsetAsync(base, 0, kNaFrameBytes, stream));
+    launch.d_counters = frame;                                         // 4 x u64
+    launch.d_ticket = reinterpret_cast<uint32_t*>(frame) + 8;          // 2 x u32
+    launch.d_signal = nullptr;
+    launch.d_trace = nullptr;
+    launch.grid = GridView{};
+    launch.lgrid = LightGridView{};                                    // shadow rays walk the BVH: no light-grid scratch
+    if (use_grid)
+    {
+        uint32_t* const t = reinterpret_cast<uint32_t*>(base + kNaTilesOff);
+        uint32_t const tiles = build.tiles_w * build.tiles_h;
+        ML_CUDA_CHECK(cudaMemsetAsync(t, 0, static_cast<size_t>(tiles) * sizeof(uint32_t), stream));   // tile counts
+        build.cap = static_cast<uint32_t>(kNaItems);
+        build.tile_cnt = t; build.tile_off = t + kNaTiles; build.cursor = t + 2 * kNaTiles + 1;
+        build.block_sums = t + 3 * kNaTiles + 4;
+        build.items = reinterpret_cast<uint32_t*>(base + kNaItemsOff);
+        build.bbox = reinterpret_cast<F4*>(base + kNaBoxOff);
+        build.edges = build.bbox + build.scene.n_tris_padded;
+        build.flags = reinterpret_cast<GridFlags*>(reinterpret_cast<uint32_t*>(frame) + 12);
+        build.flags_prezeroed = 1;
+        build.global = reinterpret_cast<uint32_t*>(base + kNaGlobalOff);
+        BuildScreenGrid(build, stream);
+        launch.grid.tile_off = build.tile_off; launch.grid.items = build.items; launch.grid.bbox = build.bbox;
+        launch.grid.edges = build.edges; launch.grid.global = build.global; launch.grid.flags = build.flags;
+        launch.grid.tiles_w = build.tiles_w; launch.grid.tiles_h = build.tiles_h;
+        launch.grid.enabled = 1;
+    }
+    if (launch.n_row_blocks > 0) LaunchRender(launch, sm_count, stream);
 }
 
 double MeasureFp32Peak(DeviceState const& device, int repeats)

@@ -586,6 +586,94 @@ void Scene::EnqueueBand(srt_camera const* camera, srt_light const* light, srt_re
         LaunchWriteFlag(d_signal, signal_value, stream);
 }
 
+// srtRenderDeviceNoAlloc.  A separate path on purpose (RenderDevice is untouched): nothing here allocates, creates
+// events or touches the scene's own grid buffers; the per-frame scratch is the static array of render_kernels.cu.
+ml_status Scene::RenderDeviceNoAlloc(srt_camera const* camera, srt_light const* light, srt_render_params const* params,
+                                     void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream)
+{
+    if (!Validate(camera, light, params)) return ML_FAIL;
+    try
+    {
+        uint32_t const tw = (params->width + kGridTile - 1) / kGridTile, th = (params->height + kGridTile - 1) / kGridTile;
+        if (m_view.n_tris > SRT_NOALLOC_MAX_TRIANGLES || m_view.n_tris_padded > SRT_NOALLOC_MAX_TRIANGLES)
+            throw std::runtime_error("srtRenderDeviceNoAlloc: the scene has " + std::to_string(m_view.n_tris)
+                                     + " triangles; the static scratch holds at most "
+                                     + std::to_string(SRT_NOALLOC_MAX_TRIANGLES) + " (use srtRenderDevice)");
+        if (static_cast<uint64_t>(tw) * th > SRT_NOALLOC_MAX_TILES)
+            throw std::runtime_error("srtRenderDeviceNoAlloc: a " + std::to_string(params->width) + " x "
+                                     + std::to_string(params->height) + " frame has " + std::to_string(uint64_t(tw) * th)
+                                     + " 8x8 tiles; the static scratch holds at most "
+                                     + std::to_string(SRT_NOALLOC_MAX_TILES) + " (use srtRenderDevice)");
+        m_device->MakeCurrent();
+        if (stream == nullptr) stream = m_device->stream;
+
+        RenderLaunch launch{};
+        launch.scene = m_view;
+        launch.camera = *camera;
+        launch.light = *light;
+        launch.params = *params;
+        launch.params.collect_stats = 0;
+        launch.inv2w = 2.0f / static_cast<float>(params->width);
+        launch.inv2h = 2.0f / static_cast<float>(params->height);
+        launch.inv_spp = 1.0f / static_cast<float>(params->spp);
+        launch.d_rgb = static_cast<float*>(d_rgb);
+        launch.d_hit_id = static_cast<int32_t*>(d_hit_id);
+        launch.d_hit_t = static_cast<float*>(d_hit_t);
+        RowBlocks(*params, launch.row_origin, launch.row_block_step, launch.n_row_blocks);
+        launch.hints = 1;
+
+        // screen grid for this camera, as PrepareGrid decides and parameterises it (pointers: RenderNoAllocScratch)
+        GridBuild b{};
+        bool use_grid = params->accel == SRT_ACCEL_BVH && (RenderUsesGrid(*params) & 1) && m_view.n_tris > 0
+                        && params->y0 % kGridTile == 0 && launch.row_origin % kGridTile == 0;
+        if (use_grid)
+        {
+            double const a[3][3] = {{camera->right[0], camera->up[0], camera->forward[0]},
+                                    {camera->right[1], camera->up[1], camera->forward[1]},
+                                    {camera->right[2], camera->up[2], camera->forward[2]}};
+            double const c00 = a[1][1] * a[2][2] - a[1][2] * a[2][1], c01 = a[1][0] * a[2][2] - a[1][2] * a[2][0],
+                         c02 = a[1][0] * a[2][1] - a[1][1] * a[2][0];
+            double const det = a[0][0] * c00 - a[0][1] * c01 + a[0][2] * c02;
+            double scale = 0;
+            for (auto const& r : a) for (double v : r) scale = std::max(scale, std::fabs(v));
+            use_grid = std::fabs(det) > 1e-6 * scale * scale * scale && camera->half_w > 0.f && camera->half_h > 0.f;
+            double const inv[9] = {c00 / det, (a[0][2] * a[2][1] - a[0][1] * a[2][2]) / det,
+                                   (a[0][1] * a[1][2] - a[0][2] * a[1][1]) / det,
+                                   -c01 / det, (a[0][0] * a[2][2] - a[0][2] * a[2][0]) / det,
+                                   (a[0][2] * a[1][0] - a[0][0] * a[1][2]) / det,
+                                   c02 / det, (a[0][1] * a[2][0] - a[0][0] * a[2][1]) / det,
+                                   (a[0][0] * a[1][1] - a[0][1] * a[1][0]) / det};
+            for (int k = 0; k < 9 && use_grid; k++)
+            {
+                use_grid = std::isfinite(inv[k]);
+                b.minv[k] = static_cast<float>(inv[k]);
+            }
+        }
+        if (use_grid)
+        {
+            b.scene = m_view;
+            for (int k = 0; k < 3; k++) b.origin[k] = camera->origin[k];
+            b.half_w = camera->half_w; b.half_h = camera->half_h;
+            b.pad = 4.0f * m_pad;
+            b.width = params->width; b.height = params->height; b.tiles_w = tw; b.tiles_h = th;
+            b.tile = kGridTile; b.lo_bias = 1.f;
+            b.ty_begin = params->y0 / kGridTile;
+            b.ty_end = (params->y1 + kGridTile - 1) / kGridTile;
+            b.ty_stride = params->row_block_stride > 1 ? params->row_block_stride : 1;
+            b.ty_phase = params->row_block_phase;
+            b.max_tiles_per_tri = m_view.n_tris <= kGridMaxGlobal ? 0u : 1024u;
+            b.half_extent = 0.5f;
+        }
+        RenderNoAllocScratch(m_device->device, launch, b, use_grid, m_device->prop.multiProcessorCount, stream);
+        return ML_OK;
+    }
+    catch (std::exception const& e)
+    {
+        m_error = e.what();
+        return ML_FAIL;
+    }
+}
+
 ml_status Scene::GetStats(srt_render_stats* stats)
 {
     if (stats == nullptr) return ML_FAIL;
@@ -885,6 +973,15 @@ ML_API_ENTRY ml_status srtRenderDevice(srt_scene scene, srt_camera const* camera
     if (ML::Scene::FromHandle(scene) == nullptr) return ML_FAIL;
     return ML::Scene::FromHandle(scene)->RenderDevice(camera, light, params, d_rgb, d_hit_id, d_hit_t,
                                                       static_cast<cudaStream_t>(stream), true);
+}
+
+ML_API_ENTRY ml_status srtRenderDeviceNoAlloc(srt_scene scene, srt_camera const* camera,
+                                              srt_light const* light, srt_render_params const* params,
+                                              void* d_rgb, void* d_hit_id, void* d_hit_t, void* stream)
+{
+    if (ML::Scene::FromHandle(scene) == nullptr) return ML_FAIL;
+    return ML::Scene::FromHandle(scene)->RenderDeviceNoAlloc(camera, light, params, d_rgb, d_hit_id, d_hit_t,
+                                                             static_cast<cudaStream_t>(stream));
 }
 
 ML_API_ENTRY ml_status srtGetRenderStats(srt_scene scene, srt_render_stats* stats)

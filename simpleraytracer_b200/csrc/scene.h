@@ -121,6 +121,9 @@ public:
     ml_status RenderDevice(srt_camera const* camera, srt_light const* light,
                            srt_render_params const* params, void* d_rgb, void* d_hit_id,
                            void* d_hit_t, cudaStream_t stream, bool timed, SignalSpec const* signal = nullptr);
+    // srtRenderDeviceNoAlloc: RenderDevice without any allocation (static scratch, no events, no light grid).
+    ml_status RenderDeviceNoAlloc(srt_camera const* camera, srt_light const* light, srt_render_params const* params,
+                                  void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream);
     ml_status RenderHost(srt_camera const* camera, srt_light const* light,
                          srt_render_params const* params, float* rgb, int32_t* hit_id,
                          float* hit_t, srt_render_stats* stats);
@@ -259,6 +262,9 @@ void LaunchWriteFlag(uint32_t* d_flag, uint32_t value, cudaStream_t stream);
 void LaunchTriNormals(F4 const* e1, F4 const* e2, F4* n, uint32_t count, cudaStream_t stream);
 // Sorts every cell's list of a (light) grid by the triangles' nearest depth (edges[3*slot].w), ascending.
 void LaunchSortCellsByDepth(GridBuild const& build, cudaStream_t stream);
+// srtRenderDeviceNoAlloc (render_kernels.cu): grid build + render with every scratch pointer in static device memory.
+void RenderNoAllocScratch(int device, RenderLaunch launch, GridBuild build, bool use_grid, int sm_count,
+                          cudaStream_t stream);
 double MeasureFp32Peak(DeviceState const& device, int repeats);
 
 } // namespace ML
