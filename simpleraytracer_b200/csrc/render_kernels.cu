@@ -24,6 +24,8 @@
 
 #include <cuda_runtime.h>
 
+#include <algorithm>
+
 #include <mutex>
 
 namespace ML {
@@ -265,10 +267,21 @@ __device__ __forceinline__ unsigned long long trace_now()
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
-__device__ __forceinline__ void trace_block(RenderLaunch const& L, unsigned long long t_start)
+__device__ __forceinline__ void trace_block(RenderLaunch const& L, unsigned long long t_start, uint32_t tile = 0,
+                                            uint32_t cnt = 0, unsigned long long d_box = 0, unsigned long long d_tri = 0,
+                                            uint32_t d_shadow = 0)
 {
     if (L.d_trace == nullptr || threadIdx.x != 0) return;
     unsigned long long const t_end = trace_now();
+    // longest item with its identity: duration ns << 34 | min(list length, 1023) << 24 | tile index; and (racy,
+    // diagnostic only) what thread 0 did in it: box tests, triangle tests, shadow rays (collect_stats variant)
+    unsigned long long const key = ((t_end - t_start) << 34) | (static_cast<unsigned long long>(min(cnt, 1023u)) << 24)
+                                   | (tile & 0xffffffu);
+    if (key > atomicMax(L.d_trace + 5, key))
+    {
+        L.d_trace[6] = d_box;
+        L.d_trace[7] = d_tri | (static_cast<unsigned long long>(d_shadow) << 40);
+    }
     atomicMax(L.d_trace + 0, ~t_start);          // ~min(start)
     atomicMax(L.d_trace + 1, t_start);
     atomicMax(L.d_trace + 2, t_end);
@@ -679,13 +692,13 @@ __device__ __forceinline__ void grid_visit_tiles(GridBuild const& G, float4 cons
 // Walks the boxes of a warp's triangles: small ones per thread, then every large one by the whole warp (its box,
 // edge functions and slot broadcast from the owning lane).  Called by all 32 lanes.
 template <class Visit>
-__device__ __forceinline__ void grid_walk_warp(GridBuild const& G, bool binned, uint32_t slot, float4 const (&edge)[3],
-                                               int tx0, int tx1, int ty0, int ty1, Visit&& visit)
+__device__ __forceinline__ void grid_walk_warp(GridBuild const& G, bool binned, uint32_t slot, float4 box,
+                                               float4 const (&edge)[3], int tx0, int tx1, int ty0, int ty1, Visit&& visit)
 {
     uint32_t const n = binned ? static_cast<uint32_t>((tx1 - tx0 + 1) * (ty1 - ty0 + 1)) : 0u;
     bool const big = n > kGridCoopTiles;
     if (binned && !big)
-        grid_visit_tiles<false>(G, edge, tx0, tx1, ty0, ty1, [&](uint32_t tile) { visit(tile, slot); });
+        grid_visit_tiles<false>(G, edge, tx0, tx1, ty0, ty1, [&](uint32_t tile) { visit(tile, slot, box); });
     uint32_t todo = __ballot_sync(0xffffffffu, big);
     while (todo)
     {
@@ -703,7 +716,9 @@ __device__ __forceinline__ void grid_walk_warp(GridBuild const& G, bool binned, 
         int const bx0 = __shfl_sync(0xffffffffu, tx0, src), bx1 = __shfl_sync(0xffffffffu, tx1, src);
         int const by0 = __shfl_sync(0xffffffffu, ty0, src), by1 = __shfl_sync(0xffffffffu, ty1, src);
         uint32_t const bslot = __shfl_sync(0xffffffffu, slot, src);
-        grid_visit_tiles<true>(G, e, bx0, bx1, by0, by1, [&](uint32_t tile) { visit(tile, bslot); });
+        float4 const bbox = make_float4(__shfl_sync(0xffffffffu, box.x, src), __shfl_sync(0xffffffffu, box.y, src),
+                                        __shfl_sync(0xffffffffu, box.z, src), __shfl_sync(0xffffffffu, box.w, src));
+        grid_visit_tiles<true>(G, e, bx0, bx1, by0, by1, [&](uint32_t tile) { visit(tile, bslot, bbox); });
     }
 }
 
@@ -725,8 +740,8 @@ __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__
         binned = false;
     }
     if (!binned) box = make_float4(1.f, 1.f, 0.f, 0.f);   // global, off the frame or behind the camera
-    grid_walk_warp(G, binned, i, edge, tx0, tx1, ty0, ty1,
-                   [&](uint32_t tile, uint32_t) { atomicAdd(&G.tile_cnt[tile], 1u); });
+    grid_walk_warp(G, binned, i, box, edge, tx0, tx1, ty0, ty1,
+                   [&](uint32_t tile, uint32_t, float4) { atomicAdd(&G.tile_cnt[tile], 1u); });
     if (i < G.scene.n_tris_padded)
     {
         reinterpret_cast<float4*>(G.bbox)[i] = box;
@@ -829,6 +844,37 @@ __global__ void __launch_bounds__(kScanBlock) grid_scan_blocks_kernel(const __gr
             G.cursor[base + k] = 0;
             G.tile_cnt[base + k] = 0;   // invariant: all counts are zero between builds (no per-frame memset)
             run += c[k];
+            // Heaviest-first work list of the render launch.  A tile's cost is what it took in the PREVIOUS frame
+            // (tile_time: ns, written by the render kernel, read and cleared here) -- list length is a poor
+            // predictor: the slowest tiles of the benchmark frame have 8-entry lists and expensive shadow rays.
+            // Tiles are cut into 2 / 4 / 8 items of whole pixel columns so that no item runs much longer than
+            // ~80 us, and sorted into four classes.  Without history (first frame, other kernels) the list length
+            // decides.  Only the schedule depends on this, never a pixel.
+            // entry = tile | first column << 24 | columns << 28 (0 columns = whole tile)
+            if (G.order != nullptr)
+            {
+                uint32_t const ns = G.tile_time[base + k];
+                G.tile_time[base + k] = 0;
+                if (grid_row_owned(G, static_cast<int>((base + k) / G.tiles_w)))
+                {
+                    bool const bvh = c[k] > kGridMaxList;      // list too long to stage: every sample walks the BVH (~1 ms)
+                    uint32_t parts, cls;
+                    if (ns != 0u)
+                    {
+                        parts = ns >= 480000u ? 8u : ns >= 240000u ? 4u : ns >= 120000u ? 2u : 1u;
+                        cls = ns >= 240000u ? 0u : ns >= 90000u ? 1u : ns >= 12000u ? 2u : 3u;
+                    }
+                    else
+                    {
+                        parts = bvh ? 8u : 1u;
+                        cls = bvh ? 0u : c[k] > 48u ? 1u : c[k] > 0u ? 2u : 3u;
+                    }
+                    uint32_t const at = cls * G.order_stride + atomicAdd(&G.bucket_cnt[cls], parts);
+                    uint32_t const cols = 8u / parts;
+                    for (uint32_t part = 0; part < parts; part++)
+                        G.order[at + part] = (base + k) | (parts > 1u ? ((part * cols) << 24) | (cols << 28) : 0u);
+                }
+            }
         }
 }
 
@@ -847,7 +893,7 @@ __global__ void __launch_bounds__(256) grid_fill_kernel(const __grid_constant__ 
     int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
     bool const binned = box.x <= box.z && grid_tile_range(G, box, tx0, tx1, ty0, ty1);
     // the same walk as grid_count_kernel (same boxes, same edge functions, same decisions)
-    grid_walk_warp(G, binned, i, edge, tx0, tx1, ty0, ty1, [&](uint32_t tile, uint32_t slot) {
+    grid_walk_warp(G, binned, i, box, edge, tx0, tx1, ty0, ty1, [&](uint32_t tile, uint32_t slot, float4) {
         G.items[G.tile_off[tile] + atomicAdd(&G.cursor[tile], 1u)] = slot;
     });
 }
@@ -1114,11 +1160,15 @@ __device__ __forceinline__ bool lgrid_shadow(RenderLaunch const& L, V3 so, V3 sd
     // The cell's list is sorted by the triangles' nearest depth (sort_cells_by_depth_kernel): a triangle can only
     // lie between the shading point and the light if it reaches nearer to the light than the point, so the walk
     // ends at the first entry beyond it.
+    // A cell seen at a grazing angle from the light can list hundreds of triangles (measured: tiles whose shadow
+    // rays spent 13K instructions each in this loop); after max_walk entries the BVH decides the rest (exact).
+    uint32_t const e_walk = min(e, b + G.max_walk);
     for (uint32_t k = b; k < e; k++)
     {
         uint32_t const slot = __ldg(G.grid.items + k);
         float4 const e0 = __ldg(edges + 3 * slot);
         if (!(e0.w <= cz)) break;
+        if (k >= e_walk) return false;
         // the projected triangle must cover the query point
         if (!edge_pass(e0, gx, gy)) continue;
         if (!edge_pass(__ldg(edges + 3 * slot + 1), gx, gy) || !edge_pass(__ldg(edges + 3 * slot + 2), gx, gy)) continue;
@@ -1297,12 +1347,12 @@ __device__ __forceinline__ bool mt_inside_pre(V3 d, float4 e1_tsr, float4 e2_id,
     return (us >= 0.0f) & (vs >= 0.0f) & (add(us, vs) <= adet);
 }
 
-template <bool STATS, int PIX, int MINB = 4>
+template <bool STATS, int PIX, int MINB = 4, bool PERSIST = false>
 __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_constant__ RenderLaunch L)
 {
     constexpr uint32_t SPL = 32u / PIX; // sample lanes per pixel
+    if (L.d_trace != nullptr && threadIdx.x == 0) atomicMax(L.d_trace + 12, ~trace_now());   // earliest block entry
     static_assert(SPL >= 4, "one lane per (pixel, channel) does the ordered sum; 128-bit reads of the sample values");
-    unsigned long long const t_block = L.d_trace ? trace_now() : 0ull;
     // sample values of the current pass, channel-major so that the summing lane reads them as float4
     __shared__ __align__(16) float s_val[8][3][32];
     // finished pixels of the warp's row (8 pixels x RGB): written to the frame as 128-bit stores
@@ -1316,16 +1366,79 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
     __shared__ float4 s_ce1[kCand], s_ce2[kCand], s_ctv[kCand], s_cq[kCand], s_cn[kCand], s_calb[kCand];
     __shared__ float4 s_cbox[kCand], s_cedge[3][kCand];
     __shared__ uint8_t s_pixlist[PIX == 1 ? 8 : 1][kCand];
-    uint32_t n_cand = 0;
-    bool use_grid = false;
     V3 const o = v3(L.camera.origin);
+    uint32_t const W = L.params.width;
+    uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t const p = lane / SPL, sl = lane % SPL;
+    uint32_t const spp = L.params.spp;
+    V3 const bg = v3(L.params.background);
+
+    unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
+    // triangle this lane's previous primary / shadow ray ended on: the next ray of the same (or the
+    // neighbouring) pixel almost always ends on it too
+    uint32_t hint_hit = kNoHint, hint_occ = kNoHint;
+    bool const use_hints = L.hints != 0;
+    bool lgrid_ok = false;
+    uint32_t lgrid_global = 0;
+    if (L.lgrid.grid.enabled)
+    {
+        GridFlags const lf = *L.lgrid.grid.flags;
+        lgrid_ok = lf.ok != 0;
+        lgrid_global = lf.n_global;
+    }
+
+    // Work items.  Plain launch: the block renders the 8x8 pixel tile (blockIdx.x, owned row block blockIdx.y)
+    // and is done.  Ordered launch (RenderLaunch::ordered, PIX == 1): the blocks are PERSISTENT (one per
+    // resident slot) and pull items from the list the grid build left in GridView::order -- heaviest class
+    // first, costly tiles cut into 2 / 4 / 8 items of whole pixel columns -- through an atomic cursor, so the
+    // launch neither pays a block start per tile nor drains on a millisecond-long tile (the longest tile of the
+    // benchmark frame takes 1.1 ms: more than a whole frame should take on a rank of eight).
+    constexpr bool persistent = PIX == 1 && PERSIST;      // compile-time: the plain kernel carries none of this
+    uint32_t n_items = 0;
+    if (persistent)
+        for (uint32_t c = 0; c < kGridBuckets; c++) n_items += L.grid.bucket_cnt[c];
+    __shared__ uint32_t s_item;
+    // thread 0 draws the NEXT item's index while the current item is being rendered (the atomic's round trip to
+    // L2 hides behind the work) and publishes it at the barrier that ends the item
+    uint32_t next_item = 0;
+    if (persistent && threadIdx.x == 0) s_item = atomicAdd(L.d_work, 1u);
+    for (;;)
+    {
+    uint32_t bx = blockIdx.x, row0 = L.row_origin + blockIdx.y * L.row_block_step;
+    uint32_t g_begin = 0, g_end = kSppTileW / PIX;      // pixel columns (groups) of the tile this item covers
+    if (persistent)
+    {
+        __syncthreads();                 // s_item published; every warp has left the previous item's shared arrays
+        uint32_t i = s_item, cls = 0;
+        if (i >= n_items) break;         // block-uniform
+        if (threadIdx.x == 0) next_item = atomicAdd(L.d_work, 1u);
+        for (; cls < kGridBuckets - 1u; cls++)
+        {
+            uint32_t const n = L.grid.bucket_cnt[cls];
+            if (i < n) break;
+            i -= n;
+        }
+        uint32_t const entry = L.grid.order[cls * L.grid.order_stride + i];
+        uint32_t const t = entry & 0xffffffu, cols = entry >> 28;     // cols 0: whole tile; else `cols` columns from bits 24..27
+        uint32_t const tyo = t / L.grid.tiles_w;
+        bx = t - tyo * L.grid.tiles_w;
+        row0 = tyo * kGridTile;
+        if (cols) { g_begin = (entry >> 24) & 15u; g_end = g_begin + cols; }
+    }
+    bool const timed_item = persistent && L.grid.enabled && L.grid.tile_time != nullptr;
+    unsigned long long const t_block = (L.d_trace || timed_item) ? trace_now() : 0ull;
+    unsigned long long const box0 = n_box, tri0 = n_tri;
+    uint32_t const shadow0 = n_shadow;
+    uint32_t n_cand = 0, trace_tile = 0, trace_cnt = 0;
+    bool use_grid = false;
     if (PIX == 1 && L.grid.enabled)
     {
         GridFlags const fl = *L.grid.flags;
-        uint32_t const ty = (L.row_origin + blockIdx.y * L.row_block_step) / kGridTile;
-        uint32_t const tile = ty * L.grid.tiles_w + blockIdx.x;
+        uint32_t const ty = row0 / kGridTile;
+        uint32_t const tile = ty * L.grid.tiles_w + bx;
         uint32_t const off = L.grid.tile_off[tile], cnt = L.grid.tile_off[tile + 1] - off;
-        use_grid = fl.ok != 0 && cnt <= kGridMaxList && blockIdx.x < L.grid.tiles_w && ty < L.grid.tiles_h;
+        trace_tile = tile; trace_cnt = cnt;
+        use_grid = fl.ok != 0 && cnt <= kGridMaxList && bx < L.grid.tiles_w && ty < L.grid.tiles_h;
         if (use_grid)   // block-uniform
         {
             n_cand = cnt + fl.n_global;
@@ -1355,31 +1468,12 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
         }
     }
 
-    uint32_t const W = L.params.width;
-    uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint32_t const p = lane / SPL, sl = lane % SPL;
-    uint32_t const y = L.row_origin + blockIdx.y * L.row_block_step + warp;
-    uint32_t const spp = L.params.spp;
-    V3 const bg = v3(L.params.background);
-
-    unsigned long long n_primary = 0, n_shadow = 0, n_box = 0, n_tri = 0;
-    // triangle this lane's previous primary / shadow ray ended on: the next ray of the same (or the
-    // neighbouring) pixel almost always ends on it too
-    uint32_t hint_hit = kNoHint, hint_occ = kNoHint;
-    bool const use_hints = L.hints != 0;
-    bool lgrid_ok = false;
-    uint32_t lgrid_global = 0;
-    if (L.lgrid.grid.enabled)
-    {
-        GridFlags const lf = *L.lgrid.grid.flags;
-        lgrid_ok = lf.ok != 0;
-        lgrid_global = lf.n_global;
-    }
+    uint32_t const y = row0 + warp;
     if (y < L.params.y1) // warp-uniform
     {
-        for (uint32_t g = 0; g < kSppTileW / PIX; g++)
+        for (uint32_t g = g_begin; g < g_end; g++)
         {
-            uint32_t const x = blockIdx.x * kSppTileW + g * PIX + p;
+            uint32_t const x = bx * kSppTileW + g * PIX + p;
             bool const in_frame = x < W;
             float sum = 0.f; // running sum of channel `sl` of pixel p (lanes with sl < 3)
             Hit first_hit = no_hit();
@@ -1498,18 +1592,38 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
         __syncwarp();
         if (L.d_rgb)
         {
-            uint32_t const x0 = blockIdx.x * kSppTileW;
+            uint32_t const x0 = bx * kSppTileW;
             float* const dst = L.d_rgb + (static_cast<size_t>(y * W + x0) - static_cast<size_t>(L.params.buf_y0) * W) * 3;
-            if (x0 + kSppTileW <= W && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0)
+            bool const whole = g_begin == 0 && g_end == kSppTileW / PIX;
+            if (whole && x0 + kSppTileW <= W && (reinterpret_cast<uintptr_t>(dst) & 15u) == 0)
             {
                 if (lane < 6) reinterpret_cast<float4*>(dst)[lane] = reinterpret_cast<float4 const*>(s_out[warp])[lane];
             }
-            else if (lane < 24 && x0 + lane / 3 < W)
-                dst[lane] = s_out[warp][lane];
+            else
+            {
+                uint32_t const f = g_begin * PIX * 3u + lane;      // float index within the row segment
+                if (f < g_end * PIX * 3u && x0 + f / 3u < W) dst[f] = s_out[warp][f];
+            }
         }
     }
-    trace_block(L, t_block);
+    // The item ends when its SLOWEST warp does (rows of a tile differ a lot: timing warp 0 alone missed up to
+    // 180 us per item).  What it took goes to the next frame's work list; parts of a tile add up.
+    if (persistent || timed_item || L.d_trace != nullptr) __syncthreads();
+    if (persistent && threadIdx.x == 0) s_item = next_item;
+    if (timed_item && threadIdx.x == 0 && bx < L.grid.tiles_w)
+        atomicAdd(L.grid.tile_time + trace_tile, static_cast<uint32_t>(min(trace_now() - t_block, 0xffffffffull)));
+    if (L.d_trace != nullptr && warp == 0)    // warp 0's busiest lane and lane sum (diagnostic)
+    {
+        uint32_t const db = static_cast<uint32_t>(n_box - box0), dt = static_cast<uint32_t>(n_tri - tri0);
+        uint32_t const mb = __reduce_max_sync(0xffffffffu, db), mt = __reduce_max_sync(0xffffffffu, dt);
+        uint32_t const sb = __reduce_add_sync(0xffffffffu, db), st = __reduce_add_sync(0xffffffffu, dt);
+        trace_block(L, t_block, trace_tile, trace_cnt, (static_cast<unsigned long long>(mb) << 32) | sb,
+                    (static_cast<unsigned long long>(mt) << 20) | st, n_shadow - shadow0);
+    }
+    if (!persistent) break;
+    }
     flush_counters(L, n_primary, n_shadow, n_box, n_tri);
+    if (L.d_trace != nullptr && threadIdx.x == 0) atomicMax(L.d_trace + 13, trace_now());    // latest block exit
 }
 
 // ---------------------------------------------------------------------------
@@ -1674,6 +1788,9 @@ void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
         if (pix != 0)
         {
             dim3 sgrid((p.width + kSppTileW - 1) / kSppTileW, launch.n_row_blocks);
+            // ordered launch: persistent blocks, one per resident slot (4 per SM), pulling work items
+            if (pix == 1 && launch.ordered)
+                sgrid = dim3(std::min<uint32_t>(sgrid.x * sgrid.y, static_cast<uint32_t>(sm_count) * 4u), 1);
             bool const st = p.collect_stats != 0;
 #define SRT_SPP_LAUNCH(PIX)                                                                   \
     do {                                                                                      \
@@ -1684,7 +1801,12 @@ void LaunchRender(RenderLaunch const& launch, int sm_count, cudaStream_t stream)
                 char const* e = std::getenv("SRT_SPP_MINB");
                 return e ? std::atoi(e) : 4; // 64 registers, 4 blocks per SM: with the grid paths 48 registers spill (+2.7 %, measured)
             }();
-            if (pix == 1 && !st && spp_minb == 5) render_bvh_spp_kernel<false, 1, 5><<<sgrid, 256, 0, stream>>>(launch);
+            if (pix == 1 && launch.ordered)
+            {
+                if (st) render_bvh_spp_kernel<true, 1, 4, true><<<sgrid, 256, 0, stream>>>(launch);
+                else render_bvh_spp_kernel<false, 1, 4, true><<<sgrid, 256, 0, stream>>>(launch);
+            }
+            else if (pix == 1 && !st && spp_minb == 5) render_bvh_spp_kernel<false, 1, 5><<<sgrid, 256, 0, stream>>>(launch);
             else if (pix == 1 && !st && spp_minb == 6) render_bvh_spp_kernel<false, 1, 6><<<sgrid, 256, 0, stream>>>(launch);
             else if (pix == 1 && !st && spp_minb == 3) render_bvh_spp_kernel<false, 1, 3><<<sgrid, 256, 0, stream>>>(launch);
             else if (pix == 1) SRT_SPP_LAUNCH(1);

@@ -47,12 +47,14 @@ void RowBlocks(srt_render_params const& p, uint32_t& origin, uint32_t& step, uin
     count = first < b0 + blocks ? (b0 + blocks - first + stride - 1) / stride : 0;
 }
 
-// Per-frame device scratch (one 128-byte memset per render call): 4 x u64 ray/test counters | 2 x u32 block
+// Per-frame device scratch (one 256-byte memset per render call): 4 x u64 ray/test counters | 2 x u32 block
 // tickets of the completion signal (one per launch stream) | pad | GridFlags of the screen grid | block trace.
-constexpr size_t kScratchBytes = 128;
+constexpr size_t kScratchBytes = 256;
 constexpr size_t kScratchTicketWord = 8;    // in uint32 units
 constexpr size_t kScratchGridFlagsWord = 12;
-constexpr size_t kScratchTraceU64 = 8;      // 5 x u64 block timeline probe (SRT_BLOCK_TRACE=1)
+constexpr size_t kScratchBucketWord = 32;    // kGridBuckets x u32 item counters of the work list
+constexpr size_t kScratchWorkWord = 36;      // u32 cursor of the persistent render blocks
+constexpr size_t kScratchTraceU64 = 8;      // 8 x u64 block timeline probe (SRT_BLOCK_TRACE=1): words 16..31
 } // namespace
 
 // Rows [y0, y1) cut into at most `requested` chunks of whole (8 * stride)-row groups, so that every chunk
@@ -180,7 +182,8 @@ Scene::Scene(DeviceStatePtr device, size_t n, float const* vertices, float const
 void Scene::FreeGrid()
 {
     cudaFree(m_d_grid_tiles); cudaFree(m_d_grid_items); cudaFree(m_d_grid_bbox); cudaFree(m_d_grid_misc);
-    m_d_grid_tiles = m_d_grid_items = m_d_grid_bbox = m_d_grid_misc = nullptr;
+    cudaFree(m_d_grid_order);
+    m_d_grid_tiles = m_d_grid_items = m_d_grid_bbox = m_d_grid_misc = m_d_grid_order = nullptr;
     m_grid_tiles = m_grid_cap = 0;
     m_grid = GridView{};
     cudaFree(m_d_lgrid_tiles); cudaFree(m_d_lgrid_items); cudaFree(m_d_lgrid_bbox); cudaFree(m_d_lgrid_misc);
@@ -313,6 +316,8 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     m_lgrid.ky = 0.5f * static_cast<float>(gh) / b.half_h;
     m_lgrid.cx = 0.5f * static_cast<float>(gw);
     m_lgrid.cy = 0.5f * static_cast<float>(gh);
+    static int const max_walk = std::getenv("SRT_LIGHT_WALK") ? std::atoi(std::getenv("SRT_LIGHT_WALK")) : 48;
+    m_lgrid.max_walk = static_cast<uint32_t>(std::max(max_walk, 1));
     gv.enabled = 1;
     ML_CUDA_CHECK(cudaEventRecord(m_lgrid_built, stream));
     std::memcpy(m_lgrid_light, light->position, sizeof(m_lgrid_light));
@@ -378,6 +383,9 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_bbox, 4 * static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));
+        // per-tile times of the previous frame (zero = no history) | up to 8 items per tile and class
+        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_order, (static_cast<size_t>(kGridBuckets) * 8u + 1u) * tiles * sizeof(uint32_t)));
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_grid_order, 0, static_cast<size_t>(tiles) * sizeof(uint32_t), stream));
         m_grid_tiles = tiles;
         m_grid_cap = cap;
     }
@@ -410,11 +418,17 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
     b.flags = reinterpret_cast<GridFlags*>(reinterpret_cast<uint32_t*>(m_d_counters) + kScratchGridFlagsWord);
     b.flags_prezeroed = 1;     // cleared by the render call's scratch memset
     b.global = reinterpret_cast<uint32_t*>(static_cast<GridFlags*>(m_d_grid_misc) + 1);
+    b.tile_time = static_cast<uint32_t*>(m_d_grid_order);
+    b.order = b.tile_time + m_grid_tiles;
+    b.bucket_cnt = reinterpret_cast<uint32_t*>(m_d_counters) + kScratchBucketWord;
+    b.order_stride = 8u * m_grid_tiles;
     BuildScreenGrid(b, stream);
 
     m_grid.tile_off = b.tile_off; m_grid.items = b.items; m_grid.bbox = b.bbox; m_grid.edges = b.edges;
     m_grid.global = b.global;
     m_grid.flags = b.flags; m_grid.tiles_w = tw; m_grid.tiles_h = th;
+    m_grid.order = b.order; m_grid.bucket_cnt = b.bucket_cnt; m_grid.order_stride = b.order_stride;
+    m_grid.tile_time = b.tile_time;
     m_grid.enabled = 1;
     static int const debug = std::getenv("SRT_GRID_DEBUG") ? std::atoi(std::getenv("SRT_GRID_DEBUG")) : 0;
     if (debug)
@@ -515,7 +529,7 @@ ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
         if (n_chunks <= 1)
         {
             EnqueueBand(camera, light, params, d_rgb, d_hit_id, d_hit_t, stream,
-                        signal ? signal->d_flags : nullptr, signal ? signal->value : 0u, 0);
+                        signal ? signal->d_flags : nullptr, signal ? signal->value : 0u, 0, true);
         }
         else
         {
@@ -530,7 +544,7 @@ ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
                 c.y0 = params->y0 + k * chunk_rows;
                 c.y1 = std::min(params->y1, c.y0 + chunk_rows);
                 EnqueueBand(camera, light, &c, d_rgb, d_hit_id, d_hit_t, (k & 1u) ? s1 : stream,
-                            signal->d_flags + static_cast<size_t>(k) * signal->chunk_stride, signal->value, k & 1u);
+                            signal->d_flags + static_cast<size_t>(k) * signal->chunk_stride, signal->value, k & 1u, false);
             }
             ML_CUDA_CHECK(cudaEventRecord(m_ev_join, s1));
             ML_CUDA_CHECK(cudaStreamWaitEvent(stream, m_ev_join, 0));
@@ -555,7 +569,7 @@ ml_status Scene::RenderDevice(srt_camera const* camera, srt_light const* light,
 // no row block still publishes it, from a one-thread kernel.
 void Scene::EnqueueBand(srt_camera const* camera, srt_light const* light, srt_render_params const* params,
                         void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream,
-                        uint32_t* d_signal, uint32_t signal_value, uint32_t ticket)
+                        uint32_t* d_signal, uint32_t signal_value, uint32_t ticket, bool whole_band)
 {
     RenderLaunch launch{};
     launch.scene = m_view;
@@ -580,6 +594,15 @@ void Scene::EnqueueBand(srt_camera const* camera, srt_light const* light, srt_re
     launch.grid = m_grid;
     if (launch.row_origin % kGridTile != 0) launch.grid.enabled = 0;
     launch.lgrid = m_lgrid;
+    // heaviest-first work list: only a launch over exactly the band the grid (and its list) was built for
+    // Measured (config 3): the work list costs ~3 % of a single GPU's frame (4.91 vs 4.75 ms: item fetch, two
+    // barriers per item) and wins as soon as the frame is sharded (N = 2: 2.57 vs 2.63 ms; N = 8: long tiles no
+    // longer bound the rank).  SRT_BLOCK_ORDER: 0 never, 1 sharded frames (default), 2 always.
+    static int const want_order = std::getenv("SRT_BLOCK_ORDER") ? std::atoi(std::getenv("SRT_BLOCK_ORDER")) : 1;
+    bool const sharded = params->row_block_stride > 1;
+    launch.ordered = (whole_band && (want_order == 2 || (want_order == 1 && sharded)) && launch.grid.enabled
+                      && launch.grid.order != nullptr) ? 1u : 0u;
+    launch.d_work = reinterpret_cast<uint32_t*>(m_d_counters) + kScratchWorkWord;
     if (launch.n_row_blocks > 0)
         LaunchRender(launch, m_device->prop.multiProcessorCount, stream);
     else if (d_signal)
@@ -688,17 +711,6 @@ ml_status Scene::GetStats(srt_render_stats* stats)
         stats->shadow_rays = c[1];
         stats->box_tests = c[2];
         stats->tri_tests = c[3];
-        if (std::getenv("SRT_BLOCK_TRACE") && std::atoi(std::getenv("SRT_BLOCK_TRACE")))
-        {
-            // diagnostic: when did the launch run out of fresh blocks, and how long did it drain
-            unsigned long long t[5] = {};
-            ML_CUDA_CHECK(cudaMemcpy(t, m_d_counters + kScratchTraceU64, sizeof(t), cudaMemcpyDeviceToHost));
-            unsigned long long const first = ~t[0];
-            if (t[2] > first)
-                std::fprintf(stderr, "[srt trace] span %.1f us, last block start at %.1f us (drain %.1f us), "
-                                     "sum of block durations %.1f us, longest block %.1f us\n",
-                             (t[2] - first) * 1e-3, (t[1] - first) * 1e-3, (t[2] - t[1]) * 1e-3, t[3] * 1e-3, t[4] * 1e-3);
-        }
         stats->kernel_ms = 0.f;
         stats->grid_build_ms = 0.f;
         stats->light_grid_build_ms = 0.f;
@@ -708,6 +720,42 @@ ml_status Scene::GetStats(srt_render_stats* stats)
             ML_CUDA_CHECK(cudaEventElapsedTime(&stats->grid_build_ms, m_device->ev_start, m_ev_grid_done));
         if (m_lgrid_valid && m_lgrid_ev0 != nullptr && cudaEventQuery(m_lgrid_built) == cudaSuccess)
             ML_CUDA_CHECK(cudaEventElapsedTime(&stats->light_grid_build_ms, m_lgrid_ev0, m_lgrid_built));
+        if (std::getenv("SRT_BLOCK_TRACE") && std::atoi(std::getenv("SRT_BLOCK_TRACE")))
+        {
+            // diagnostic: when did the launch run out of fresh blocks, and how long did it drain
+            unsigned long long t[8] = {};
+            ML_CUDA_CHECK(cudaMemcpy(t, m_d_counters + kScratchTraceU64, sizeof(t), cudaMemcpyDeviceToHost));
+            unsigned long long const first = ~t[0];
+            if (t[2] > first)
+                std::fprintf(stderr, "[srt trace] dev %d events: call %.1f us, grid build %.1f us | items: span %.1f us, last start at %.1f us (drain %.1f us), "
+                                     "sum of block durations %.1f us, longest block %.1f us\n",
+                             m_device->device, stats->kernel_ms * 1e3, stats->grid_build_ms * 1e3,
+                             (t[2] - first) * 1e-3, (t[1] - first) * 1e-3, (t[2] - t[1]) * 1e-3, t[3] * 1e-3, t[4] * 1e-3);
+            {
+                unsigned long long e[2] = {};
+                ML_CUDA_CHECK(cudaMemcpy(e, m_d_counters + kScratchTraceU64 + 12, sizeof(e), cudaMemcpyDeviceToHost));
+                if (e[0] && e[1])
+                    std::fprintf(stderr, "[srt trace] dev %d kernel: first block entry -> first item %.1f us, last item end -> "
+                                         "last block exit %.1f us\n", m_device->device, (static_cast<double>(first) - static_cast<double>(~e[0])) * 1e-3,
+                                 (static_cast<double>(e[1]) - static_cast<double>(t[2])) * 1e-3);
+            }
+            if (t[5] && m_grid.tiles_w)
+            {
+                uint32_t buckets[8] = {};
+                ML_CUDA_CHECK(cudaMemcpy(buckets, reinterpret_cast<uint32_t*>(m_d_counters) + kScratchBucketWord,
+                                         5 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+                unsigned const tile = static_cast<unsigned>(t[5] & 0xffffffu);
+                std::fprintf(stderr, "[srt trace] longest item: %.1f us, tile (%u, %u), list length %u; items per class "
+                                     "%u / %u / %u / %u, cursor %u\n", (t[5] >> 34) * 1e-3, tile % m_grid.tiles_w,
+                             tile / m_grid.tiles_w, static_cast<unsigned>((t[5] >> 24) & 1023u), buckets[0], buckets[1],
+                             buckets[2], buckets[3], buckets[4]);
+                if (t[6] || t[7])
+                    std::fprintf(stderr, "[srt trace]   its warp 0: box tests max lane %llu, all lanes %llu; triangle tests max "
+                                         "lane %llu, all lanes %llu; lane 0 cast %llu shadow rays\n", t[6] >> 32,
+                                 t[6] & 0xffffffffull, (t[7] >> 20) & 0xfffffull, t[7] & 0xfffffull, t[7] >> 40);
+            }
+        }
+
         return ML_OK;
     }
     catch (std::exception const& e)
@@ -794,7 +842,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
             srt_render_params c = band;
             c.y0 = params->y0 + static_cast<uint32_t>(r0);
             c.y1 = params->y0 + static_cast<uint32_t>(r1);
-            EnqueueBand(camera, light, &c, m_d_rgb, m_d_id, m_d_t, s, nullptr, 0u, 0u);
+            EnqueueBand(camera, light, &c, m_d_rgb, m_d_id, m_d_t, s, nullptr, 0u, 0u, n_chunks == 1);
             ML_CUDA_CHECK(cudaEventRecord(m_chunk_events[2 * k], s));
             ML_CUDA_CHECK(cudaStreamWaitEvent(sc, m_chunk_events[2 * k], 0));
             if (stride == 1)

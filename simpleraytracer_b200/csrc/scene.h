@@ -84,7 +84,17 @@ struct GridView
     GridFlags const* flags;
     uint32_t tiles_w, tiles_h;
     uint32_t enabled;           // host decision for this launch
+    // Heaviest-first work list (screen grid): the owned tiles sorted into kGridBuckets classes of estimated cost,
+    // order[b * order_stride + i] = i-th item of class b (bits 0..23 tile; bits 28..31 = columns, 0 = the whole
+    // tile, else that many of its eight pixel columns starting at bits 24..27), bucket_cnt[b] = items in class b.
+    // A launch that covers exactly the band the grid was built for runs persistent blocks over this list, so the
+    // long items start first and the launch drains on short ones.
+    uint32_t const* order;
+    uint32_t const* bucket_cnt;
+    uint32_t order_stride;
+    uint32_t* tile_time;        // [tiles] ns per tile of this frame, for the next frame's list (NULL: not recorded)
 };
+constexpr uint32_t kGridBuckets = 4;
 
 // The same structure seen from the point light, for shadow rays: every shadow segment ends at the
 // light, so the segment from a shading point S projects to ONE point of a perspective grid centred
@@ -96,6 +106,7 @@ struct LightGridView
     GridView grid;
     float minv[9];
     float kx, ky, cx, cy;
+    uint32_t max_walk;      // list entries a shadow ray tests before it hands the query to the BVH (SRT_LIGHT_WALK)
 };
 
 class Scene
@@ -139,7 +150,7 @@ private:
                   srt_render_params const* params);
     void EnqueueBand(srt_camera const* camera, srt_light const* light, srt_render_params const* params,
                      void* d_rgb, void* d_hit_id, void* d_hit_t, cudaStream_t stream,
-                     uint32_t* d_signal, uint32_t signal_value, uint32_t ticket);
+                     uint32_t* d_signal, uint32_t signal_value, uint32_t ticket, bool whole_band);
     void EnsureStaging(size_t pixels);
     void FreeStaging();
     // Builds the primary-ray grid for this camera / frame on `stream` (if the render will use it).
@@ -166,6 +177,7 @@ private:
     void* m_d_grid_items = nullptr;
     void* m_d_grid_bbox = nullptr;    // bbox | edges
     void* m_d_grid_misc = nullptr;    // GridFlags | global list
+    void* m_d_grid_order = nullptr;   // m_grid_tiles tile times | kGridBuckets x 8 x m_grid_tiles work items
     uint32_t m_grid_tiles = 0;
     uint32_t m_grid_cap = 0;
     // shadow-ray grid (device)
@@ -215,6 +227,9 @@ struct RenderLaunch
     uint32_t row_origin;
     uint32_t row_block_step;
     uint32_t n_row_blocks;
+    uint32_t ordered; // 1 (sample-parallel kernel, one pixel per warp pass): persistent blocks pull work items from
+                      // grid.order (heaviest class first, heavy tiles split in four) through the cursor *d_work
+    uint32_t* d_work; // zeroed by the per-frame scratch memset
     uint32_t hints;  // 1: rays first test the triangle the lane's previous ray ended on (SRT_BVH_HINTS=0 disables)
     // Completion signal fused into the render kernel (multi-GPU frames): when d_signal != NULL the LAST block
     // of the launch to finish (atomic ticket in d_ticket, reset for the next launch) stores signal_value to
@@ -249,6 +264,10 @@ struct GridBuild
     float lo_bias;          // 1: queries are closed unit squares [x, x+1] (pixels); 0: points
     uint32_t* tile_cnt; uint32_t* tile_off; uint32_t* cursor; uint32_t* items;
     uint32_t* block_sums;   // [tiles / 4096 + 1] scratch of the prefix sum
+    uint32_t* tile_time;    // [tiles] or NULL: ns each tile took in the previous frame (render kernel adds, build clears)
+    uint32_t* order;        // [kGridBuckets * order_stride] or NULL (light grid, no-alloc path): see GridView::order
+    uint32_t* bucket_cnt;   // [kGridBuckets], zeroed by the caller's per-frame scratch memset
+    uint32_t order_stride;
     F4* bbox; F4* edges; uint32_t* global; GridFlags* flags;
     float half_extent;      // half size of a query in grid units: 0.5 (pixel squares) or 0 (points)
     uint32_t flags_prezeroed; // 1: the caller's per-frame scratch memset already cleared *flags
