@@ -857,7 +857,7 @@ __device__ __forceinline__ void grid_phase_scan_blocks(GridBuild const& G, uint3
             // (tile_time: ns, written by the render kernel, read and cleared here) -- list length is a poor
             // predictor: the slowest tiles of the benchmark frame have 8-entry lists and expensive shadow rays.
             // Tiles are cut into 2 / 4 / 8 items of whole pixel columns so that no item runs much longer than
-            // ~80 us, and sorted into four classes.  Without history (first frame, other kernels) the list length
+            // ~80 us, and sorted into eight classes.  Without history (first frame, other kernels) the list length
             // decides.  Only the schedule depends on this, never a pixel.
             // entry = tile | first column << 24 | columns << 28 (0 columns = whole tile)
             if (G.order != nullptr)
@@ -871,12 +871,15 @@ __device__ __forceinline__ void grid_phase_scan_blocks(GridBuild const& G, uint3
                     if (ns != 0u)
                     {
                         parts = ns >= 480000u ? 8u : ns >= 240000u ? 4u : ns >= 120000u ? 2u : 1u;
-                        cls = ns >= 240000u ? 0u : ns >= 90000u ? 1u : ns >= 12000u ? 2u : 3u;
+                        // eight classes, started in this order: the finer the classes, the shorter the items that are
+                        // still running when the list runs dry
+                        cls = ns >= 240000u ? 0u : ns >= 170000u ? 1u : ns >= 120000u ? 2u : ns >= 85000u ? 3u
+                            : ns >= 60000u ? 4u : ns >= 40000u ? 5u : ns >= 12000u ? 6u : 7u;
                     }
                     else
                     {
                         parts = bvh ? 8u : 1u;
-                        cls = bvh ? 0u : c[k] > 48u ? 1u : c[k] > 0u ? 2u : 3u;
+                        cls = bvh ? 0u : c[k] > 48u ? 3u : c[k] > 0u ? 5u : 7u;
                     }
                     // slot within this block's share of the class list (shared-memory atomic; the block then takes
                     // its share with ONE global atomic per class: 32 400 global atomics on four counters cost 40 us)

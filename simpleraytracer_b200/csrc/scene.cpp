@@ -53,8 +53,8 @@ constexpr size_t kScratchBytes = 256;
 constexpr size_t kScratchTicketWord = 8;    // in uint32 units
 constexpr size_t kScratchGridFlagsWord = 12;
 constexpr size_t kScratchBucketWord = 32;    // kGridBuckets x u32 item counters of the work list
-constexpr size_t kScratchWorkWord = 36;      // u32 cursor of the persistent render blocks
-constexpr size_t kScratchTraceU64 = 8;      // 8 x u64 block timeline probe (SRT_BLOCK_TRACE=1): words 16..31
+constexpr size_t kScratchWorkWord = 44;      // u32 cursor of the persistent render blocks
+constexpr size_t kScratchTraceU64 = 8;      // 8 x u64 block timeline probe (SRT_BLOCK_TRACE=1): words 16..31, + entry / exit stamps in words 40..43
 } // namespace
 
 // Rows [y0, y1) cut into at most `requested` chunks of whole (8 * stride)-row groups, so that every chunk
@@ -741,14 +741,17 @@ ml_status Scene::GetStats(srt_render_stats* stats)
             }
             if (t[5] && m_grid.tiles_w)
             {
-                uint32_t buckets[8] = {};
+                uint32_t buckets[9] = {};
                 ML_CUDA_CHECK(cudaMemcpy(buckets, reinterpret_cast<uint32_t*>(m_d_counters) + kScratchBucketWord,
-                                         5 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+                                         8 * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+                ML_CUDA_CHECK(cudaMemcpy(buckets + 8, reinterpret_cast<uint32_t*>(m_d_counters) + kScratchWorkWord,
+                                         sizeof(uint32_t), cudaMemcpyDeviceToHost));
                 unsigned const tile = static_cast<unsigned>(t[5] & 0xffffffu);
                 std::fprintf(stderr, "[srt trace] longest item: %.1f us, tile (%u, %u), list length %u; items per class "
-                                     "%u / %u / %u / %u, cursor %u\n", (t[5] >> 34) * 1e-3, tile % m_grid.tiles_w,
-                             tile / m_grid.tiles_w, static_cast<unsigned>((t[5] >> 24) & 1023u), buckets[0], buckets[1],
-                             buckets[2], buckets[3], buckets[4]);
+                                     "%u / %u / %u / %u / %u / %u / %u / %u, cursor %u\n", (t[5] >> 34) * 1e-3,
+                             tile % m_grid.tiles_w, tile / m_grid.tiles_w, static_cast<unsigned>((t[5] >> 24) & 1023u),
+                             buckets[0], buckets[1], buckets[2], buckets[3], buckets[4], buckets[5], buckets[6], buckets[7],
+                             buckets[8]);
                 if (t[6] || t[7])
                     std::fprintf(stderr, "[srt trace]   its warp 0: box tests max lane %llu, all lanes %llu; triangle tests max "
                                          "lane %llu, all lanes %llu; lane 0 cast %llu shadow rays\n", t[6] >> 32,

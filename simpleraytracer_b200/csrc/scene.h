@@ -94,7 +94,7 @@ struct GridView
     uint32_t order_stride;
     uint32_t* tile_time;        // [tiles] ns per tile of this frame, for the next frame's list (NULL: not recorded)
 };
-constexpr uint32_t kGridBuckets = 4;
+constexpr uint32_t kGridBuckets = 8;
 
 // The same structure seen from the point light, for shadow rays: every shadow segment ends at the
 // light, so the segment from a shading point S projects to ONE point of a perspective grid centred
