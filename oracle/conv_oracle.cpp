@@ -9,7 +9,11 @@
 // (SURVEY.md section 8c).  What is restated here is the published definition of the
 // TensorFlow ops a frozen image-to-image graph uses:
 //   Conv2D (NHWC input, HWIO filter, SAME/VALID padding, stride, dilation),
-//   BiasAdd, Relu / LeakyRelu / Relu6 / Sigmoid / Tanh, Add, ConcatV2(axis=3).
+//   BiasAdd, Relu / LeakyRelu / Relu6 / Sigmoid / Tanh, Add, ConcatV2(axis=3),
+//   MaxPool / AvgPool, ResizeNearestNeighbor / ResizeBilinear (align_corners, half_pixel_centers),
+//   DepthToSpace, Pad / MirrorPad, FusedBatchNorm (inference), Mul / Sub / RealDiv -- the ops around the
+//   convolutions of an encoder / decoder denoiser (tensorflow/core/kernels/{pooling_ops_common,
+//   image/resize_*_op, depthtospace_op, pad_op, mirror_pad_op}: published semantics, restated scalar).
 // Fixed accumulation order (kh, kw, cin), fp32 with fmaf.  Independent
 // cross-check in tests: torch.nn.functional.conv2d on the CPU.
 #include <algorithm>
@@ -119,6 +123,108 @@ void orc_add_bias_act(float const* a, float const* b, float const* bias, uint64_
         if (bias) v = v + bias[i % static_cast<uint64_t>(C)];
         out[i] = Activate(v, act, alpha);
     }
+}
+
+// MaxPool (is_max) / AvgPool over K x K windows, stride, TensorFlow SAME / VALID; AvgPool divides by the number of
+// in-bounds taps.  out: OH x OW x C with OH/OW from orc_conv_geometry(in, K, stride, 1, same).
+void orc_pool2d(float const* in, int H, int W, int C, int K, int stride, int same, int is_max, float* out)
+{
+    int OH, OW, pt, pl;
+    orc_conv_geometry(H, K, stride, 1, same, &OH, &pt);
+    orc_conv_geometry(W, K, stride, 1, same, &OW, &pl);
+    for (int oy = 0; oy < OH; oy++)
+        for (int ox = 0; ox < OW; ox++)
+            for (int c = 0; c < C; c++)
+            {
+                float acc = is_max ? -INFINITY : 0.f;
+                int taps = 0;
+                for (int ky = 0; ky < K; ky++)
+                    for (int kx = 0; kx < K; kx++)
+                    {
+                        int const y = oy * stride - pt + ky, x = ox * stride - pl + kx;
+                        if (y < 0 || y >= H || x < 0 || x >= W) continue;
+                        float const v = in[(static_cast<size_t>(y) * W + x) * C + c];
+                        acc = is_max ? std::max(acc, v) : acc + v;
+                        taps++;
+                    }
+                out[(static_cast<size_t>(oy) * OW + ox) * C + c] = is_max ? acc : acc / static_cast<float>(taps ? taps : 1);
+            }
+}
+
+// ResizeNearestNeighbor (bilinear = 0) / ResizeBilinear (1): tensorflow/core/kernels/image/resize_*_op.cc and
+// image_resizer_state.h (CalculateResizeScale, LegacyScaler / HalfPixelScaler, compute_interpolation_weights).
+void orc_resize(float const* in, int H, int W, int C, int OH, int OW, int bilinear, int align_corners, int half_pixel,
+                float* out)
+{
+    auto scale = [&](int i, int o) {
+        return (align_corners && o > 1) ? static_cast<float>(i - 1) / static_cast<float>(o - 1)
+                                        : static_cast<float>(i) / static_cast<float>(o);
+    };
+    float const sy = scale(H, OH), sx = scale(W, OW);
+    for (int oy = 0; oy < OH; oy++)
+        for (int ox = 0; ox < OW; ox++)
+            for (int c = 0; c < C; c++)
+            {
+                float r;
+                if (!bilinear)
+                {
+                    float const fy = half_pixel ? (static_cast<float>(oy) + 0.5f) * sy : static_cast<float>(oy) * sy;
+                    float const fx = half_pixel ? (static_cast<float>(ox) + 0.5f) * sx : static_cast<float>(ox) * sx;
+                    int y = std::min(static_cast<int>(align_corners ? std::round(fy) : std::floor(fy)), H - 1);
+                    int x = std::min(static_cast<int>(align_corners ? std::round(fx) : std::floor(fx)), W - 1);
+                    y = std::max(y, 0); x = std::max(x, 0);
+                    r = in[(static_cast<size_t>(y) * W + x) * C + c];
+                }
+                else
+                {
+                    float const fy = half_pixel ? (static_cast<float>(oy) + 0.5f) * sy - 0.5f : static_cast<float>(oy) * sy;
+                    float const fx = half_pixel ? (static_cast<float>(ox) + 0.5f) * sx - 0.5f : static_cast<float>(ox) * sx;
+                    float const fy0 = std::floor(fy), fx0 = std::floor(fx);
+                    int const y0 = std::max(static_cast<int>(fy0), 0), y1 = std::min(static_cast<int>(std::ceil(fy)), H - 1);
+                    int const x0 = std::max(static_cast<int>(fx0), 0), x1 = std::min(static_cast<int>(std::ceil(fx)), W - 1);
+                    float const ly = fy - fy0, lx = fx - fx0;
+                    auto at = [&](int y, int x) { return in[(static_cast<size_t>(y) * W + x) * C + c]; };
+                    float const top = at(y0, x0) + (at(y0, x1) - at(y0, x0)) * lx;
+                    float const bottom = at(y1, x0) + (at(y1, x1) - at(y1, x0)) * lx;
+                    r = top + (bottom - top) * ly;
+                }
+                out[(static_cast<size_t>(oy) * OW + ox) * C + c] = r;
+            }
+}
+
+// DepthToSpace, NHWC: out[h*bs + i][w*bs + j][c] = in[h][w][(i*bs + j)*Co + c], Co = C / bs^2.
+void orc_depth_to_space(float const* in, int H, int W, int C, int bs, float* out)
+{
+    int const Co = C / (bs * bs), OW = W * bs;
+    for (int h = 0; h < H; h++)
+        for (int w = 0; w < W; w++)
+            for (int i = 0; i < bs; i++)
+                for (int j = 0; j < bs; j++)
+                    for (int c = 0; c < Co; c++)
+                        out[((static_cast<size_t>(h) * bs + i) * OW + (w * bs + j)) * Co + c] =
+                            in[(static_cast<size_t>(h) * W + w) * C + (i * bs + j) * Co + c];
+}
+
+// Pad (mode 0: zeros) / MirrorPad (1: REFLECT, 2: SYMMETRIC) on the H and W axes.
+void orc_pad2d(float const* in, int H, int W, int C, int top, int bottom, int left, int right, int mode, float* out)
+{
+    int const OH = H + top + bottom, OW = W + left + right;
+    auto mirror = [&](int v, int n) {
+        int const off = mode == 1 ? 0 : 1;
+        if (v < 0) return -v - off;
+        if (v >= n) return 2 * n - v - 2 + off;
+        return v;
+    };
+    for (int oy = 0; oy < OH; oy++)
+        for (int ox = 0; ox < OW; ox++)
+        {
+            int y = oy - top, x = ox - left;
+            bool const outside = y < 0 || y >= H || x < 0 || x >= W;
+            if (mode != 0) { y = mirror(y, H); x = mirror(x, W); }
+            for (int c = 0; c < C; c++)
+                out[(static_cast<size_t>(oy) * OW + ox) * C + c] =
+                    (mode == 0 && outside) ? 0.f : in[(static_cast<size_t>(y) * W + x) * C + c];
+        }
 }
 
 } // extern "C"

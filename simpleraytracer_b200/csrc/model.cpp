@@ -14,6 +14,8 @@
 // the input is read from and the result written to the images' device buffers.
 #include "model.h"
 
+#include <cmath>
+
 #include "dtype.h"
 #include "image.h"
 #include "model_runner_ext.h"
@@ -397,6 +399,264 @@ Model::Value Model::Evaluate(pb::Graph const& graph, int idx, std::vector<Value>
         m_ops.push_back(op);
         result.tensor = op.out;
     }
+    else if (node.op == "MaxPool" || node.op == "AvgPool")
+    {
+        if (pb::Attr const* df = node.Find("data_format"))
+            if (df->has_s && df->s != "NHWC") Unimplemented(node, "data_format " + df->s);
+        pb::Attr const* ks = node.Find("ksize");
+        pb::Attr const* st = node.Find("strides");
+        pb::Attr const* pad = node.Find("padding");
+        if (ks == nullptr || ks->list_i.size() != 4 || ks->list_i[0] != 1 || ks->list_i[3] != 1
+            || ks->list_i[1] != ks->list_i[2] || ks->list_i[1] < 1 || ks->list_i[1] > 16)
+            Unimplemented(node, "ksize (square windows over H and W only)");
+        if (st == nullptr || st->list_i.size() != 4 || st->list_i[0] != 1 || st->list_i[3] != 1
+            || st->list_i[1] != st->list_i[2] || st->list_i[1] < 1)
+            Unimplemented(node, "strides");
+        if (pad == nullptr || !pad->has_s || (pad->s != "SAME" && pad->s != "VALID")) Unimplemented(node, "padding");
+        Op op;
+        op.kind = OpKind::Pool;
+        op.name = node.name;
+        op.in = {activation(0)};
+        op.KH = op.KW = static_cast<int>(ks->list_i[1]);
+        op.stride = static_cast<int>(st->list_i[1]);
+        op.same_padding = pad->s == "SAME";
+        op.pool_max = node.op == "MaxPool";
+        op.out = NewTensor(m_tensors[op.in[0]].C);
+        m_ops.push_back(op);
+        result.tensor = op.out;
+    }
+    else if (node.op == "ResizeNearestNeighbor" || node.op == "ResizeBilinear")
+    {
+        Op op;
+        op.kind = OpKind::Resize;
+        op.name = node.name;
+        op.in = {activation(0)};
+        op.bilinear = node.op == "ResizeBilinear";
+        if (pb::Attr const* a = node.Find("align_corners")) op.align_corners = a->has_b && a->b;
+        if (pb::Attr const* a = node.Find("half_pixel_centers")) op.half_pixel = a->has_b && a->b;
+        if (op.align_corners && op.half_pixel) Unimplemented(node, "align_corners together with half_pixel_centers");
+        Value size = input_value(1);
+        if (size.is_const)
+        {
+            if (size.constant->ints.size() != 2 || size.constant->ints[0] < 1 || size.constant->ints[1] < 1)
+                Unimplemented(node, "size must hold two positive integers");
+            op.size_h = static_cast<int>(size.constant->ints[0]);
+            op.size_w = static_cast<int>(size.constant->ints[1]);
+        }
+        else if (size.shape_ref >= 0 && size.shape_hw)
+        {
+            op.size_ref = size.shape_ref;
+            op.mul_h = size.shape_mul_h;
+            op.mul_w = size.shape_mul_w;
+        }
+        else Unimplemented(node, "size must be a constant or Shape(x)[1:3] * constant");
+        op.out = NewTensor(m_tensors[op.in[0]].C);
+        m_ops.push_back(op);
+        result.tensor = op.out;
+    }
+    else if (node.op == "Shape")
+    {
+        result.shape_ref = activation(0);
+    }
+    else if (node.op == "StridedSlice" || node.op == "Mul" || node.op == "Sub" || node.op == "RealDiv")
+    {
+        Value a = input_value(0);
+        if (node.op == "StridedSlice")
+        {
+            // only Shape(x)[1:3]: the (H, W) of a tensor
+            if (a.shape_ref < 0 || a.shape_hw) Unimplemented(node, "StridedSlice of anything but a Shape");
+            Value b = input_value(1), e = input_value(2);
+            bool ok = b.is_const && e.is_const && b.constant->ints.size() == 1 && e.constant->ints.size() == 1
+                      && b.constant->ints[0] == 1 && e.constant->ints[0] == 3;
+            if (data_input_count() > 3)
+            {
+                Value st = input_value(3);
+                ok = ok && st.is_const && st.constant->ints.size() == 1 && st.constant->ints[0] == 1;
+            }
+            for (char const* mask : {"begin_mask", "end_mask", "ellipsis_mask", "new_axis_mask", "shrink_axis_mask"})
+                if (pb::Attr const* m = node.Find(mask)) ok = ok && (!m->has_i || m->i == 0);
+            if (!ok) Unimplemented(node, "StridedSlice other than Shape(x)[1:3]");
+            result = a;
+            result.shape_hw = true;
+        }
+        else
+        {
+            Value b = input_value(1);
+            if (node.op == "Mul" && ((a.shape_ref >= 0) != (b.shape_ref >= 0)))
+            {
+                // Shape(x)[1:3] * [sy, sx]
+                Value const& sh = a.shape_ref >= 0 ? a : b;
+                Value const& k = a.shape_ref >= 0 ? b : a;
+                if (!sh.shape_hw || !k.is_const || (k.constant->ints.size() != 2 && k.constant->ints.size() != 1)
+                    || k.constant->ints[0] < 1 || k.constant->ints.back() < 1)
+                    Unimplemented(node, "shape arithmetic other than Shape(x)[1:3] * positive constants");
+                result = sh;
+                result.shape_mul_h = sh.shape_mul_h * static_cast<int>(k.constant->ints[0]);
+                result.shape_mul_w = sh.shape_mul_w * static_cast<int>(k.constant->ints.back());
+            }
+            else if (a.shape_ref >= 0 || b.shape_ref >= 0) Unimplemented(node, "shape arithmetic");
+            else if (a.is_const && b.is_const) Unimplemented(node, "constant folding");
+            else if (a.is_const || b.is_const)
+            {
+                // tensor (op) per-channel or scalar constant: out = in * scale + bias
+                bool const const_first = a.is_const;
+                Value const& x = const_first ? b : a;
+                Value const& k = const_first ? a : b;
+                size_t const n = k.constant->values.size();
+                int const C = m_tensors[x.tensor].C;
+                if (n == 0 || (n != 1 && C != 0 && static_cast<int>(n) != C))
+                    Unimplemented(node, "constant of " + std::to_string(n) + " values on " + std::to_string(C) + " channels");
+                size_t const len = (n == 1 && C > 1) ? static_cast<size_t>(C) : n;
+                std::vector<float> scale(len, 1.0f), bias(len, 0.0f);
+                bool use_scale = false, use_bias = false;
+                for (size_t c = 0; c < len; c++)
+                {
+                    float const v = k.constant->values[n == 1 ? 0 : c];
+                    if (node.op == "Mul") { scale[c] = v; use_scale = true; }
+                    else if (node.op == "Sub")
+                    {
+                        if (const_first) { scale[c] = -1.0f; bias[c] = v; use_scale = true; }   // k - x
+                        else bias[c] = -v;                                                      // x - k
+                        use_bias = true;
+                    }
+                    else  // RealDiv
+                    {
+                        if (const_first) Unimplemented(node, "constant / tensor");
+                        scale[c] = 1.0f / v;      // x / k as x * (1 / k): within 1 ulp of the division
+                        use_scale = true;
+                    }
+                }
+                Op op;
+                op.kind = OpKind::BiasAct;
+                op.name = node.name;
+                op.in = {x.tensor};
+                if (use_scale) op.scale = AddConst(std::move(scale));
+                if (use_bias) op.bias = AddConst(std::move(bias));
+                op.out = NewTensor(C != 0 ? C : static_cast<int>(len));
+                m_ops.push_back(op);
+                result.tensor = op.out;
+            }
+            else
+            {
+                if (node.op == "RealDiv") Unimplemented(node, "tensor / tensor");
+                Op op;
+                op.kind = OpKind::Binary;
+                op.name = node.name;
+                op.binary = node.op == "Sub" ? 1 : 2;
+                op.in = {a.tensor, b.tensor};
+                op.out = NewTensor(m_tensors[a.tensor].C);
+                m_ops.push_back(op);
+                result.tensor = op.out;
+            }
+        }
+    }
+    else if (node.op == "DepthToSpace")
+    {
+        if (pb::Attr const* df = node.Find("data_format"))
+            if (df->has_s && df->s != "NHWC") Unimplemented(node, "data_format " + df->s);
+        pb::Attr const* bs = node.Find("block_size");
+        if (bs == nullptr || !bs->has_i || bs->i < 2 || bs->i > 8) Unimplemented(node, "block_size");
+        Op op;
+        op.kind = OpKind::DepthToSpace;
+        op.name = node.name;
+        op.in = {activation(0)};
+        op.block = static_cast<int>(bs->i);
+        int const C = m_tensors[op.in[0]].C;
+        if (C == 0 || C % (op.block * op.block) != 0)
+            Unimplemented(node, std::to_string(C) + " channels with block_size " + std::to_string(op.block));
+        op.out = NewTensor(C / (op.block * op.block));
+        m_ops.push_back(op);
+        result.tensor = op.out;
+    }
+    else if (node.op == "Pad" || node.op == "PadV2" || node.op == "MirrorPad")
+    {
+        Op op;
+        op.kind = OpKind::Pad;
+        op.name = node.name;
+        op.in = {activation(0)};
+        Value pads = input_value(1);
+        if (!pads.is_const || pads.constant->ints.size() != 8) Unimplemented(node, "paddings must be a constant [4, 2]");
+        auto const& pv = pads.constant->ints;
+        if (pv[0] != 0 || pv[1] != 0 || pv[6] != 0 || pv[7] != 0) Unimplemented(node, "padding of the batch or channel axis");
+        for (int k = 2; k < 6; k++)
+            if (pv[k] < 0 || pv[k] > 4096) Unimplemented(node, "padding amount");
+        op.pad_t = static_cast<int>(pv[2]); op.pad_b = static_cast<int>(pv[3]);
+        op.pad_l = static_cast<int>(pv[4]); op.pad_r = static_cast<int>(pv[5]);
+        if (node.op == "MirrorPad")
+        {
+            pb::Attr const* m = node.Find("mode");
+            if (m == nullptr || !m->has_s || (m->s != "REFLECT" && m->s != "SYMMETRIC")) Unimplemented(node, "mode");
+            op.pad_mode = m->s == "REFLECT" ? 1 : 2;
+        }
+        else if (node.op == "PadV2")
+        {
+            Value cv = input_value(2);
+            if (!cv.is_const || cv.constant->values.size() != 1 || cv.constant->values[0] != 0.0f)
+                Unimplemented(node, "PadV2 with a non-zero constant");
+        }
+        op.out = NewTensor(m_tensors[op.in[0]].C);
+        m_ops.push_back(op);
+        result.tensor = op.out;
+    }
+    else if (node.op == "FusedBatchNorm" || node.op == "FusedBatchNormV2" || node.op == "FusedBatchNormV3")
+    {
+        // inference form: y = (x - mean) * scale / sqrt(variance + epsilon) + offset, as one per-channel multiply-add
+        if (pb::Attr const* df = node.Find("data_format"))
+            if (df->has_s && df->s != "NHWC") Unimplemented(node, "data_format " + df->s);
+        if (pb::Attr const* tr = node.Find("is_training"))
+            if (tr->has_b && tr->b) Unimplemented(node, "is_training = true");
+        int const x = activation(0);
+        Value sc = input_value(1), of = input_value(2), mean = input_value(3), var = input_value(4);
+        if (!sc.is_const || !of.is_const || !mean.is_const || !var.is_const) Unimplemented(node, "non-constant statistics");
+        size_t const n = sc.constant->values.size();
+        if (n == 0 || of.constant->values.size() != n || mean.constant->values.size() != n || var.constant->values.size() != n
+            || (m_tensors[x].C != 0 && static_cast<size_t>(m_tensors[x].C) != n))
+            Unimplemented(node, "statistics do not match the channel count");
+        float eps = 1e-3f;
+        if (pb::Attr const* e = node.Find("epsilon")) if (e->has_f) eps = e->f;
+        std::vector<float> scale(n), bias(n);
+        for (size_t c = 0; c < n; c++)
+        {
+            double const inv = static_cast<double>(sc.constant->values[c])
+                               / std::sqrt(static_cast<double>(var.constant->values[c]) + static_cast<double>(eps));
+            scale[c] = static_cast<float>(inv);
+            bias[c] = static_cast<float>(static_cast<double>(of.constant->values[c]) - static_cast<double>(mean.constant->values[c]) * inv);
+        }
+        Op op;
+        op.kind = OpKind::BiasAct;
+        op.name = node.name;
+        op.in = {x};
+        op.scale = AddConst(std::move(scale));
+        op.bias = AddConst(std::move(bias));
+        op.out = NewTensor(static_cast<int>(n));
+        m_ops.push_back(op);
+        result.tensor = op.out;
+    }
+    else if (node.op == "Squeeze" || node.op == "ExpandDims" || node.op == "Reshape")
+    {
+        // N = 1 and dense NHWC: dropping / adding the batch axis or restating [1, H, W, C] moves no data.
+        if (node.op == "Reshape")
+        {
+            Value shp = input_value(1);
+            int const C = m_tensors[activation(0)].C;
+            bool ok = shp.is_const && (shp.constant->ints.size() == 4 || shp.constant->ints.size() == 3);
+            if (ok)
+            {
+                auto const& d = shp.constant->ints;
+                if (d.size() == 4 && d[0] != 1 && d[0] != -1) ok = false;
+                if (d.back() != -1 && C != 0 && d.back() != C) ok = false;    // the channel count must stay
+            }
+            if (!ok) Unimplemented(node, "Reshape other than to [1, H, W, C] / [H, W, C] with unchanged channels");
+        }
+        else if (node.op == "Squeeze")
+        {
+            if (pb::Attr const* sd = node.Find("squeeze_dims"))
+                for (int64_t d : sd->list_i)
+                    if (d != 0 && d != -4) Unimplemented(node, "squeeze of an axis other than the batch");
+        }
+        result = input_value(0);
+        if (result.is_const) Unimplemented(node, "constant folding");
+    }
     else
     {
         Unimplemented(node, "unsupported op");
@@ -434,6 +694,32 @@ void Model::FusePlan()
             if (prod.act != nn::Act::None) continue; // activation already applied: order matters
             if (prod.residual >= 0) continue;        // the residual is added after the activation
             bool const has_bias = op.bias >= 0;
+            if (op.scale >= 0)
+            {
+                // out = prod(...) * s + b: a convolution takes s into its filter (per output channel) and bias, a
+                // multiply-add composes; anything else keeps the op (FusedBatchNorm after Conv2D costs nothing)
+                auto const& sc = m_consts[op.scale].host;
+                if (prod.kind == OpKind::Conv)
+                {
+                    auto& w = m_consts[prod.weights].host;
+                    size_t const cout = sc.size();
+                    if (cout == 0 || w.size() % cout != 0 || static_cast<int>(cout) != m_tensors[prod.out].C) continue;
+                    for (size_t k = 0; k < w.size(); k++) w[k] *= sc[k % cout];       // HWIO: output channel fastest
+                    if (prod.bias >= 0)
+                        for (size_t k = 0; k < cout; k++) m_consts[prod.bias].host[k] *= sc[k];
+                }
+                else if (prod.kind == OpKind::BiasAct)
+                {
+                    if (prod.bias >= 0 && m_consts[prod.bias].host.size() != sc.size()) continue;
+                    if (prod.scale >= 0 && m_consts[prod.scale].host.size() != sc.size()) continue;
+                    if (prod.bias >= 0)
+                        for (size_t k = 0; k < sc.size(); k++) m_consts[prod.bias].host[k] *= sc[k];
+                    if (prod.scale >= 0)
+                        for (size_t k = 0; k < sc.size(); k++) m_consts[prod.scale].host[k] *= sc[k];
+                    else prod.scale = op.scale;
+                }
+                else continue;
+            }
             if (prod.kind == OpKind::Conv || prod.kind == OpKind::BiasAct)
             {
                 if (has_bias && prod.bias >= 0)
@@ -558,6 +844,54 @@ void Model::InferShapes(size_t H, size_t W, size_t C)
                         throw std::runtime_error("'" + op.name + "' operands differ in spatial size");
                 o.H = a.H; o.W = a.W;
                 break;
+            case OpKind::Pool:
+            {
+                auto out_dim = [&](int n) {
+                    if (n == 0) return 0;
+                    if (op.same_padding) return (n + op.stride - 1) / op.stride;
+                    return n >= op.KH ? (n - op.KH) / op.stride + 1 : 0;
+                };
+                if (o.C == 0) o.C = a.C;
+                o.H = out_dim(a.H); o.W = out_dim(a.W);
+                if ((a.H && !o.H) || (a.W && !o.W))
+                    throw std::runtime_error("'" + op.name + "' output is empty for a " + std::to_string(a.W) + " x "
+                                             + std::to_string(a.H) + " input");
+                break;
+            }
+            case OpKind::Resize:
+                if (o.C == 0) o.C = a.C;
+                if (op.size_ref >= 0)
+                {
+                    o.H = m_tensors[op.size_ref].H * op.mul_h;
+                    o.W = m_tensors[op.size_ref].W * op.mul_w;
+                }
+                else if (a.H != 0 && a.W != 0) { o.H = op.size_h; o.W = op.size_w; }
+                break;
+            case OpKind::DepthToSpace:
+                o.H = a.H * op.block; o.W = a.W * op.block;
+                break;
+            case OpKind::Pad:
+                if (o.C == 0) o.C = a.C;
+                if (a.H != 0 && a.W != 0)
+                {
+                    if (op.pad_mode != 0)
+                    {
+                        int const lim_h = op.pad_mode == 1 ? a.H - 1 : a.H, lim_w = op.pad_mode == 1 ? a.W - 1 : a.W;
+                        if (op.pad_t > lim_h || op.pad_b > lim_h || op.pad_l > lim_w || op.pad_r > lim_w)
+                            throw std::runtime_error("'" + op.name + "' mirrors more rows or columns than the input has");
+                    }
+                    o.H = a.H + op.pad_t + op.pad_b; o.W = a.W + op.pad_l + op.pad_r;
+                }
+                break;
+            case OpKind::Binary:
+            {
+                TensorInfo const& b = m_tensors[op.in[1]];
+                if (a.C != b.C || a.H != b.H || a.W != b.W)
+                    throw std::runtime_error("'" + op.name + "' operands differ in shape");
+                if (o.C == 0) o.C = a.C;
+                o.H = a.H; o.W = a.W;
+                break;
+            }
         }
     }
     AssignPrecision();
@@ -799,7 +1133,8 @@ void Model::AllocateBuffers()
 
 std::string Model::Describe() const
 {
-    static char const* const kinds[] = {"Conv", "BiasAct", "Add", "Concat", "Copy"};
+    static char const* const kinds[] = {"Conv", "BiasAct", "Add", "Concat", "Copy", "Pool", "Resize", "DepthToSpace", "Pad",
+                                        "Binary"};
     static char const* const acts[] = {"none", "relu", "leaky_relu", "relu6", "sigmoid", "tanh"};
     std::ostringstream os;
     os << "input_node=" << m_input_node << " output_node=" << m_output_node << "\n";
@@ -820,6 +1155,22 @@ std::string Model::Describe() const
             os << " k=" << op.KH << "x" << op.KW << " stride=" << op.stride << " dilation=" << op.dilation
                << " padding=" << (op.same_padding ? "SAME" : "VALID") << " wsum=" << sum;
         }
+        if (op.kind == OpKind::Pool)
+            os << (op.pool_max ? " max" : " avg") << " k=" << op.KH << " stride=" << op.stride << " padding="
+               << (op.same_padding ? "SAME" : "VALID");
+        if (op.kind == OpKind::Resize)
+        {
+            os << (op.bilinear ? " bilinear" : " nearest") << " align_corners=" << op.align_corners
+               << " half_pixel_centers=" << op.half_pixel;
+            if (op.size_ref >= 0) os << " size=t" << op.size_ref << ".hw*(" << op.mul_h << "," << op.mul_w << ")";
+            else os << " size=" << op.size_h << "x" << op.size_w;
+        }
+        if (op.kind == OpKind::DepthToSpace) os << " block=" << op.block;
+        if (op.kind == OpKind::Pad)
+            os << " pads=" << op.pad_t << "," << op.pad_b << "," << op.pad_l << "," << op.pad_r << " mode="
+               << (op.pad_mode == 0 ? "CONSTANT" : op.pad_mode == 1 ? "REFLECT" : "SYMMETRIC");
+        if (op.kind == OpKind::Binary) os << (op.binary == 1 ? " sub" : " mul");
+        if (op.scale >= 0) os << " scale=yes";
         if (op.residual >= 0) os << " residual=t" << op.residual;
         if (op.tc) os << (op.split ? " engine=tcgen05_bf16x3" : " engine=tcgen05_bf16");
         if (m_tensors[op.out].bf16) os << " out=bf16";
@@ -925,9 +1276,21 @@ void Model::Run(float const* d_in, float* d_out, cudaStream_t stream)
     // element is read before the same thread overwrites it.)
     if (static_cast<void const*>(d_in) == static_cast<void const*>(d_out))
     {
+        // Likewise any op that writes the output while reading the input NON-elementwise (a convolution's main
+        // input, a concat, pool, resize, depth-to-space or pad: neighbouring pixels or another layout): the
+        // reference is safe here because TensorFlow copies the input into its own tensor (model.cpp:336).
         bool clash = false;
         for (Op const& op : m_ops)
-            clash |= op.tc && op.residual == m_input_tensor && op.out == m_output_tensor;
+        {
+            if (op.out != m_output_tensor) continue;
+            clash |= op.tc && op.residual == m_input_tensor;
+            bool const elementwise = op.kind == OpKind::BiasAct || op.kind == OpKind::Add || op.kind == OpKind::Binary
+                                     || op.kind == OpKind::Copy;
+            for (size_t k = 0; k < op.in.size(); k++)
+                if (op.in[k] == m_input_tensor && !elementwise
+                    && !(op.kind == OpKind::Conv && static_cast<int>(op.in[k]) == op.residual && k > 0))
+                    clash = true;
+        }
         if (clash)
         {
             TensorInfo const& t = m_tensors[m_input_tensor];
@@ -997,8 +1360,47 @@ void Model::RunOp(Op const& op, float const* d_in, float* d_out, cudaStream_t st
                 break;
             }
             case OpKind::BiasAct:
-                nn::BiasAct(ptr(op.in[0]), op.bias >= 0 ? m_consts[op.bias].dev : nullptr, ptr(op.out),
-                            n_out, o.C, op.act, op.alpha, stream);
+                if (op.scale >= 0)
+                    nn::ScaleBiasAct(ptr(op.in[0]), m_consts[op.scale].dev, op.bias >= 0 ? m_consts[op.bias].dev : nullptr,
+                                     ptr(op.out), n_out, o.C, op.act, op.alpha, stream);
+                else
+                    nn::BiasAct(ptr(op.in[0]), op.bias >= 0 ? m_consts[op.bias].dev : nullptr, ptr(op.out),
+                                n_out, o.C, op.act, op.alpha, stream);
+                break;
+            case OpKind::Binary:
+                nn::BinaryAct(ptr(op.in[0]), ptr(op.in[1]), ptr(op.out), n_out, op.binary, op.act, op.alpha, stream);
+                break;
+            case OpKind::Pool:
+            {
+                nn::PoolDesc d{};
+                d.H = a.H; d.W = a.W; d.C = a.C; d.OH = o.H; d.OW = o.W; d.K = op.KH; d.stride = op.stride;
+                d.is_max = op.pool_max ? 1 : 0;
+                if (op.same_padding)      // TensorFlow SAME: total = max((out-1)*stride + k - in, 0), low half first
+                {
+                    d.pad_top = std::max((o.H - 1) * op.stride + op.KH - a.H, 0) / 2;
+                    d.pad_left = std::max((o.W - 1) * op.stride + op.KH - a.W, 0) / 2;
+                }
+                nn::Pool2d(ptr(op.in[0]), ptr(op.out), d, stream);
+                break;
+            }
+            case OpKind::Resize:
+            {
+                nn::ResizeDesc d{};
+                d.H = a.H; d.W = a.W; d.C = a.C; d.OH = o.H; d.OW = o.W;
+                d.bilinear = op.bilinear; d.align_corners = op.align_corners; d.half_pixel = op.half_pixel;
+                auto scale = [&](int in, int out) {
+                    return (op.align_corners && out > 1) ? static_cast<float>(in - 1) / static_cast<float>(out - 1)
+                                                         : static_cast<float>(in) / static_cast<float>(out);
+                };
+                d.scale_y = scale(a.H, o.H); d.scale_x = scale(a.W, o.W);
+                nn::Resize(ptr(op.in[0]), ptr(op.out), d, stream);
+                break;
+            }
+            case OpKind::DepthToSpace:
+                nn::DepthToSpace(ptr(op.in[0]), ptr(op.out), a.H, a.W, a.C, op.block, stream);
+                break;
+            case OpKind::Pad:
+                nn::Pad2d(ptr(op.in[0]), ptr(op.out), a.H, a.W, a.C, op.pad_t, op.pad_l, o.H, o.W, op.pad_mode, stream);
                 break;
             case OpKind::Add:
                 nn::AddAct(ptr(op.in[0]), ptr(op.in[1]), ptr(op.out), n_out, op.act, op.alpha, stream);

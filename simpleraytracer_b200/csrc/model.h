@@ -51,7 +51,8 @@ public:
 
 private:
     // ---- execution plan ---------------------------------------------------
-    enum class OpKind { Conv, BiasAct, Add, Concat, Copy };
+    // Pool .. Binary: the ops around the convolutions of an encoder / decoder graph (U-Net style denoisers)
+    enum class OpKind { Conv, BiasAct, Add, Concat, Copy, Pool, Resize, DepthToSpace, Pad, Binary };
 
     struct TensorInfo
     {
@@ -75,6 +76,16 @@ private:
         int bias = -1;         // index into m_consts or -1
         nn::Act act = nn::Act::None;
         float alpha = 0.2f;
+        int scale = -1;        // BiasAct: per-channel multiplier applied BEFORE the bias (Mul by a constant, FusedBatchNorm)
+        // Pool: KH = KW = window, stride, same_padding; pool_max.  Resize: bilinear / align_corners / half_pixel and the
+        // output size, either absolute (size_h, size_w) or size_ref's (H, W) times (mul_h, mul_w) -- the
+        // Shape -> StridedSlice -> Mul pattern Keras UpSampling2D exports.  DepthToSpace: block.  Pad: pads + mode.
+        bool pool_max = false;
+        bool bilinear = false, align_corners = false, half_pixel = false;
+        int size_h = 0, size_w = 0, size_ref = -1, mul_h = 1, mul_w = 1;
+        int block = 1;
+        int pad_t = 0, pad_b = 0, pad_l = 0, pad_r = 0, pad_mode = 0;   // 0 CONSTANT, 1 REFLECT, 2 SYMMETRIC
+        int binary = 0;        // Binary: 1 = a - b, 2 = a * b (a + b is OpKind::Add)
         int residual = -1;     // Conv: tensor added after the activation (a following Add folded in); also in `in`
         std::string add_name;  // name of the folded Add node, for its error message
         std::string name;      // for error messages
@@ -101,6 +112,11 @@ private:
         bool is_const = false;
         int tensor = -1;                     // activation tensor id
         std::shared_ptr<pb::Tensor> constant;
+        // an integer vector that depends on the input size: shape_ref's [N, H, W, C] (Shape), its [H, W] slice
+        // (StridedSlice [1:3]) and that slice times constants (Mul) -- only what a resize's `size` input needs
+        int shape_ref = -1;
+        bool shape_hw = false;
+        int shape_mul_h = 1, shape_mul_w = 1;
     };
 
     void BuildPlan(pb::Graph const& graph, int input_idx, int output_idx);

@@ -446,6 +446,149 @@ __global__ void split_bf16_hilo_kernel(float const* __restrict__ in, uint4* __re
     }
 }
 
+// ---------------------------------------------------------------------------
+// The ops around the convolutions of an encoder / decoder graph (TensorFlow op definitions, NHWC, N = 1).
+// One thread per output element, channel index fastest: neighbouring threads touch neighbouring addresses.
+// ---------------------------------------------------------------------------
+// out = act(in * scale[c] + bias[c]); scale / bias may be nullptr (1 / 0).  `out` may alias `in`.
+__global__ void scale_bias_act_kernel(float const* in, float const* __restrict__ scale, float const* __restrict__ bias,
+                                      float* out, size_t n, int C, Act act, float alpha)
+{
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride)
+    {
+        int const c = static_cast<int>(i % C);
+        float v = in[i];
+        if (scale) v = v * scale[c];            // separate multiply and add, like Mul followed by BiasAdd
+        if (bias) v = v + bias[c];
+        out[i] = apply_act(v, act, alpha);
+    }
+}
+
+// mode 0: a + b, 1: a - b, 2: a * b.  `out` may alias an operand.
+__global__ void binary_act_kernel(float const* a, float const* b, float* out, size_t n, int mode, Act act, float alpha)
+{
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride)
+    {
+        float const x = a[i], y = b[i];
+        out[i] = apply_act(mode == 0 ? x + y : mode == 1 ? x - y : x * y, act, alpha);
+    }
+}
+
+// MaxPool / AvgPool, TensorFlow SAME / VALID.  AvgPool divides by the number of IN-BOUNDS taps (padding excluded).
+__global__ void pool2d_kernel(float const* __restrict__ in, float* __restrict__ out, PoolDesc d)
+{
+    size_t const n = static_cast<size_t>(d.OH) * d.OW * d.C;
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride)
+    {
+        int const c = static_cast<int>(i % d.C);
+        size_t const p = i / d.C;
+        int const ox = static_cast<int>(p % d.OW), oy = static_cast<int>(p / d.OW);
+        int const y0 = oy * d.stride - d.pad_top, x0 = ox * d.stride - d.pad_left;
+        float acc = d.is_max ? -__int_as_float(0x7f800000) : 0.0f;
+        int taps = 0;
+        for (int ky = 0; ky < d.K; ky++)
+        {
+            int const y = y0 + ky;
+            if (y < 0 || y >= d.H) continue;
+            for (int kx = 0; kx < d.K; kx++)
+            {
+                int const x = x0 + kx;
+                if (x < 0 || x >= d.W) continue;
+                float const v = in[(static_cast<size_t>(y) * d.W + x) * d.C + c];
+                acc = d.is_max ? fmaxf(acc, v) : acc + v;
+                taps++;
+            }
+        }
+        out[i] = d.is_max ? acc : __fdiv_rn(acc, static_cast<float>(taps > 0 ? taps : 1));
+    }
+}
+
+// ResizeNearestNeighbor / ResizeBilinear (tensorflow/core/kernels/image/resize_*.cc semantics):
+//   scale = align_corners && out > 1 ? (in - 1) / (out - 1) : in / out
+//   nearest : src = min(align_corners ? roundf(s(dst)) : floorf(s(dst)), in - 1)
+//   bilinear: in = s(dst); lower = max(floor(in), 0); upper = min(ceil(in), in - 1); lerp = in - floor(in)
+//   s(dst) = half_pixel_centers ? (dst + 0.5) * scale (nearest) / (dst + 0.5) * scale - 0.5 (bilinear) : dst * scale
+__global__ void resize_kernel(float const* __restrict__ in, float* __restrict__ out, ResizeDesc d)
+{
+    size_t const n = static_cast<size_t>(d.OH) * d.OW * d.C;
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride)
+    {
+        int const c = static_cast<int>(i % d.C);
+        size_t const p = i / d.C;
+        int const ox = static_cast<int>(p % d.OW), oy = static_cast<int>(p / d.OW);
+        if (!d.bilinear)
+        {
+            float const fy = d.half_pixel ? (static_cast<float>(oy) + 0.5f) * d.scale_y : static_cast<float>(oy) * d.scale_y;
+            float const fx = d.half_pixel ? (static_cast<float>(ox) + 0.5f) * d.scale_x : static_cast<float>(ox) * d.scale_x;
+            int const y = min(static_cast<int>(d.align_corners ? roundf(fy) : floorf(fy)), d.H - 1);
+            int const x = min(static_cast<int>(d.align_corners ? roundf(fx) : floorf(fx)), d.W - 1);
+            out[i] = in[(static_cast<size_t>(max(y, 0)) * d.W + max(x, 0)) * d.C + c];
+        }
+        else
+        {
+            float const fy = d.half_pixel ? (static_cast<float>(oy) + 0.5f) * d.scale_y - 0.5f : static_cast<float>(oy) * d.scale_y;
+            float const fx = d.half_pixel ? (static_cast<float>(ox) + 0.5f) * d.scale_x - 0.5f : static_cast<float>(ox) * d.scale_x;
+            float const fy0 = floorf(fy), fx0 = floorf(fx);
+            int const y_lo = max(static_cast<int>(fy0), 0), y_hi = min(static_cast<int>(ceilf(fy)), d.H - 1);
+            int const x_lo = max(static_cast<int>(fx0), 0), x_hi = min(static_cast<int>(ceilf(fx)), d.W - 1);
+            float const ly = fy - fy0, lx = fx - fx0;
+            auto at = [&](int y, int x) { return in[(static_cast<size_t>(y) * d.W + x) * d.C + c]; };
+            float const tl = at(y_lo, x_lo), tr = at(y_lo, x_hi), bl = at(y_hi, x_lo), br = at(y_hi, x_hi);
+            float const top = tl + (tr - tl) * lx, bottom = bl + (br - bl) * lx;
+            out[i] = top + (bottom - top) * ly;
+        }
+    }
+}
+
+// DepthToSpace (NHWC, DCR): out[h*bs + i][w*bs + j][c] = in[h][w][(i*bs + j)*Cout + c]
+__global__ void depth_to_space_kernel(float const* __restrict__ in, float* __restrict__ out, int H, int W, int C, int bs)
+{
+    int const Co = C / (bs * bs), OW = W * bs;
+    size_t const n = static_cast<size_t>(H) * W * C;
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride)
+    {
+        int const c = static_cast<int>(i % Co);
+        size_t const p = i / Co;
+        int const ox = static_cast<int>(p % OW), oy = static_cast<int>(p / OW);
+        int const h = oy / bs, bi = oy - h * bs, w = ox / bs, bj = ox - w * bs;
+        out[i] = in[(static_cast<size_t>(h) * W + w) * C + (bi * bs + bj) * Co + c];
+    }
+}
+
+// Pad (CONSTANT, zeros) / MirrorPad (REFLECT: edge not repeated, SYMMETRIC: edge repeated) on H and W.
+__global__ void pad2d_kernel(float const* __restrict__ in, float* __restrict__ out, int H, int W, int C, int top,
+                             int left, int OH, int OW, int mode)
+{
+    size_t const n = static_cast<size_t>(OH) * OW * C;
+    size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    size_t const stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (; i < n; i += stride)
+    {
+        int const c = static_cast<int>(i % C);
+        size_t const p = i / C;
+        int x = static_cast<int>(p % OW) - left, y = static_cast<int>(p / OW) - top;
+        if (mode == 0)
+        {
+            out[i] = (x < 0 || x >= W || y < 0 || y >= H) ? 0.0f : in[(static_cast<size_t>(y) * W + x) * C + c];
+            continue;
+        }
+        int const off = mode == 1 ? 0 : 1;         // REFLECT: -1 -> 1 ; SYMMETRIC: -1 -> 0
+        if (x < 0) x = -x - off; else if (x >= W) x = 2 * W - x - 2 + off;
+        if (y < 0) y = -y - off; else if (y >= H) y = 2 * H - y - 2 + off;
+        out[i] = in[(static_cast<size_t>(y) * W + x) * C + c];
+    }
+}
+
 inline unsigned EltGrid(size_t n)
 {
     size_t blocks = (n + 255) / 256;
@@ -523,6 +666,54 @@ void ConcatChannels(float const* in, float* out, size_t pixels, int C, int Ctota
 {
     if (pixels == 0) return;
     concat_kernel<<<EltGrid(pixels * C), 256, 0, stream>>>(in, out, pixels, C, Ctotal, c0);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void ScaleBiasAct(float const* in, float const* scale, float const* bias, float* out, size_t n, int C, Act act,
+                  float alpha, cudaStream_t stream)
+{
+    if (n == 0) return;
+    scale_bias_act_kernel<<<EltGrid(n), 256, 0, stream>>>(in, scale, bias, out, n, C, act, alpha);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void BinaryAct(float const* a, float const* b, float* out, size_t n, int mode, Act act, float alpha, cudaStream_t stream)
+{
+    if (n == 0) return;
+    binary_act_kernel<<<EltGrid(n), 256, 0, stream>>>(a, b, out, n, mode, act, alpha);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void Pool2d(float const* in, float* out, PoolDesc const& d, cudaStream_t stream)
+{
+    size_t const n = static_cast<size_t>(d.OH) * d.OW * d.C;
+    if (n == 0) return;
+    pool2d_kernel<<<EltGrid(n), 256, 0, stream>>>(in, out, d);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void Resize(float const* in, float* out, ResizeDesc const& d, cudaStream_t stream)
+{
+    size_t const n = static_cast<size_t>(d.OH) * d.OW * d.C;
+    if (n == 0) return;
+    resize_kernel<<<EltGrid(n), 256, 0, stream>>>(in, out, d);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void DepthToSpace(float const* in, float* out, int H, int W, int C, int block, cudaStream_t stream)
+{
+    size_t const n = static_cast<size_t>(H) * W * C;
+    if (n == 0) return;
+    depth_to_space_kernel<<<EltGrid(n), 256, 0, stream>>>(in, out, H, W, C, block);
+    ML_CUDA_CHECK(cudaGetLastError());
+}
+
+void Pad2d(float const* in, float* out, int H, int W, int C, int top, int left, int OH, int OW, int mode,
+           cudaStream_t stream)
+{
+    size_t const n = static_cast<size_t>(OH) * OW * C;
+    if (n == 0) return;
+    pad2d_kernel<<<EltGrid(n), 256, 0, stream>>>(in, out, H, W, C, top, left, OH, OW, mode);
     ML_CUDA_CHECK(cudaGetLastError());
 }
 

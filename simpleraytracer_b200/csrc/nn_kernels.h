@@ -42,6 +42,20 @@ void AddAct(float const* a, float const* b, float* out, size_t n, Act act, float
 // Copies a [pixels, C] tensor into channels [c0, c0+C) of a [pixels, Ctotal] tensor.
 void ConcatChannels(float const* in, float* out, size_t pixels, int C, int Ctotal, int c0,
                     cudaStream_t stream);
+// ---- the ops around the convolutions of an encoder / decoder graph (TensorFlow op definitions, NHWC, N = 1)
+// out = act(in * scale[c] + bias[c]); scale / bias may be nullptr.  In place allowed.
+void ScaleBiasAct(float const* in, float const* scale, float const* bias, float* out, size_t n, int C, Act act,
+                  float alpha, cudaStream_t stream);
+// mode 0: a + b, 1: a - b, 2: a * b, then the activation.  In place allowed.
+void BinaryAct(float const* a, float const* b, float* out, size_t n, int mode, Act act, float alpha, cudaStream_t stream);
+struct PoolDesc { int H, W, C, OH, OW, K, stride, pad_top, pad_left, is_max; };
+void Pool2d(float const* in, float* out, PoolDesc const& d, cudaStream_t stream);
+struct ResizeDesc { int H, W, C, OH, OW, bilinear, align_corners, half_pixel; float scale_y, scale_x; };
+void Resize(float const* in, float* out, ResizeDesc const& d, cudaStream_t stream);
+void DepthToSpace(float const* in, float* out, int H, int W, int C, int block, cudaStream_t stream);
+// mode 0: CONSTANT (zeros), 1: REFLECT, 2: SYMMETRIC
+void Pad2d(float const* in, float* out, int H, int W, int C, int top, int left, int OH, int OW, int mode,
+           cudaStream_t stream);
 void HalfToFloat(void const* in, float* out, size_t n, cudaStream_t stream);
 // fp32 direct convolution writing bf16 NHWC (feeds the tensor-core layers).
 void Conv2dFp32ToBf16(float const* in, float const* w, float const* bias, void* out_bf16,

@@ -91,6 +91,14 @@ def lib():
                                     C.c_void_p, C.c_int]
         _lib.orc_conv_geometry.restype = None
         _lib.orc_conv_geometry.argtypes = [C.c_int] * 5 + [C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        _lib.orc_pool2d.restype = None
+        _lib.orc_pool2d.argtypes = [C.c_void_p] + [C.c_int] * 7 + [C.c_void_p]
+        _lib.orc_resize.restype = None
+        _lib.orc_resize.argtypes = [C.c_void_p] + [C.c_int] * 8 + [C.c_void_p]
+        _lib.orc_depth_to_space.restype = None
+        _lib.orc_depth_to_space.argtypes = [C.c_void_p] + [C.c_int] * 4 + [C.c_void_p]
+        _lib.orc_pad2d.restype = None
+        _lib.orc_pad2d.argtypes = [C.c_void_p] + [C.c_int] * 8 + [C.c_void_p]
         _lib.orc_add_bias_act.restype = None
         _lib.orc_add_bias_act.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int, C.c_int,
                                           C.c_float, C.c_void_p]
@@ -167,3 +175,101 @@ def run_denoiser(x, layers, residual=True, alpha=0.1, threads=0):
     if residual:
         cur = (np.asarray(x, np.float32) + cur).astype(np.float32)
     return cur
+
+
+def _geometry(n, k, stride, same):
+    o, p = C.c_int(), C.c_int()
+    lib().orc_conv_geometry(n, k, stride, 1, int(same), C.byref(o), C.byref(p))
+    return o.value
+
+
+def pool2d(x, k, stride, padding="SAME", kind="max"):
+    x = np.ascontiguousarray(x, np.float32)
+    H, W, Ch = x.shape
+    same = padding == "SAME"
+    out = np.zeros((_geometry(H, k, stride, same), _geometry(W, k, stride, same), Ch), np.float32)
+    lib().orc_pool2d(x.ctypes.data, H, W, Ch, k, stride, int(same), int(kind == "max"), out.ctypes.data)
+    return out
+
+
+def resize(x, out_h, out_w, bilinear=False, align_corners=False, half_pixel_centers=False):
+    x = np.ascontiguousarray(x, np.float32)
+    H, W, Ch = x.shape
+    out = np.zeros((out_h, out_w, Ch), np.float32)
+    lib().orc_resize(x.ctypes.data, H, W, Ch, out_h, out_w, int(bilinear), int(align_corners), int(half_pixel_centers),
+                     out.ctypes.data)
+    return out
+
+
+def depth_to_space(x, block):
+    x = np.ascontiguousarray(x, np.float32)
+    H, W, Ch = x.shape
+    out = np.zeros((H * block, W * block, Ch // (block * block)), np.float32)
+    lib().orc_depth_to_space(x.ctypes.data, H, W, Ch, block, out.ctypes.data)
+    return out
+
+
+def pad2d(x, top, bottom, left, right, mode="CONSTANT"):
+    x = np.ascontiguousarray(x, np.float32)
+    H, W, Ch = x.shape
+    out = np.zeros((H + top + bottom, W + left + right, Ch), np.float32)
+    lib().orc_pad2d(x.ctypes.data, H, W, Ch, top, bottom, left, right, {"CONSTANT": 0, "REFLECT": 1, "SYMMETRIC": 2}[mode],
+                    out.ctypes.data)
+    return out
+
+
+def batch_norm(x, scale, offset, mean, variance, epsilon):
+    """FusedBatchNorm, inference form, in fp32 like TensorFlow's CPU kernel: (x - mean) * rsqrt(var + eps) * scale + offset."""
+    x = np.asarray(x, np.float32)
+    inv = (np.float32(1.0) / np.sqrt(np.asarray(variance, np.float32) + np.float32(epsilon))).astype(np.float32)
+    return ((x - np.asarray(mean, np.float32)) * (inv * np.asarray(scale, np.float32)) + np.asarray(offset, np.float32)).astype(np.float32)
+
+
+def run_program(x, program):
+    """Oracle interpreter of the op lists graphdef_writer.make_unet() returns: [(op, out, inputs, params)]."""
+    env = {"input": np.ascontiguousarray(x, np.float32)}
+    out = None
+    for op, name, ins, kw in program:
+        a = [env[i] for i in ins]
+        if op == "conv":
+            r = conv2d(a[0], kw["w"], kw.get("b"), stride=kw.get("stride", 1), padding=kw.get("padding", "SAME"),
+                       act=kw.get("act"), alpha=kw.get("alpha", 0.2))
+        elif op == "bn":
+            r = batch_norm(a[0], kw["scale"], kw["offset"], kw["mean"], kw["variance"], kw["epsilon"])
+        elif op == "act":
+            r = lib_act(a[0], kw["act"], kw.get("alpha", 0.2))
+        elif op == "pool":
+            r = pool2d(a[0], kw["k"], kw["stride"], kw.get("padding", "SAME"), kw["kind"])
+        elif op == "resize":
+            h, w = (a[0].shape[0] * kw["factor"], a[0].shape[1] * kw["factor"]) if "factor" in kw else kw["size"]
+            r = resize(a[0], h, w, kw.get("bilinear", False), kw.get("align_corners", False), kw.get("half_pixel_centers", False))
+        elif op == "d2s":
+            r = depth_to_space(a[0], kw["block"])
+        elif op == "pad":
+            r = pad2d(a[0], *kw["pads"], mode=kw.get("mode", "CONSTANT"))
+        elif op == "concat":
+            r = np.concatenate(a, axis=2)
+        elif op == "add":
+            r = (a[0] + a[1]).astype(np.float32)
+        elif op == "sub":
+            r = (a[0] - a[1]).astype(np.float32)
+        elif op == "mul":
+            r = (a[0] * a[1]).astype(np.float32)
+        elif op == "mulc":
+            r = (a[0] * np.asarray(kw["c"], np.float32)).astype(np.float32)
+        elif op == "subc":
+            r = (a[0] - np.asarray(kw["c"], np.float32)).astype(np.float32)
+        elif op == "divc":
+            r = (a[0] / np.asarray(kw["c"], np.float32)).astype(np.float32)
+        else:
+            raise ValueError(op)
+        env[name] = r
+        out = r
+    return out
+
+
+def lib_act(x, act, alpha=0.2):
+    x = np.ascontiguousarray(x, np.float32)
+    out = np.zeros_like(x)
+    lib().orc_add_bias_act(x.ctypes.data, None, None, x.size, 1, ACTS[act], alpha, out.ctypes.data)
+    return out

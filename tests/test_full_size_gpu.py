@@ -114,3 +114,30 @@ def test_config5_conv_net_1080p_vs_oracle(ctx, tmp_path):
     assert elem_rel(got_x3) <= 1e-3, f"bf16x3 path (the default precision): element-relative {elem_rel(got_x3):.3e}"
     for obj in (inp, out, model):
         obj.release()
+
+
+def test_unet_1080p_vs_oracle(ctx, tmp_path):
+    """A two-level U-Net (MaxPool down, Keras-style nearest upsampling, skip concats, FusedBatchNorm, global
+    residual) on one full 1080p image, default precision (bf16x3 tensor-core convolutions) and fp32, vs the oracle."""
+    W, H = 1920, 1080
+    path = tmp_path / "unet.pb"
+    _, prog = gw.make_unet(path, channels=3, width=16, levels=2, seed=2, up="nearest", down="maxpool")
+    model = ctx.create_model(path)
+    i, _ = model.info()
+    i.width, i.height = W, H
+    model.set_input_info(i)
+    x = np.random.default_rng(5).random((H, W, 3), dtype=np.float32)
+    inp = ctx.create_image(W, H, 3); out = ctx.create_image(W, H, 3)
+    inp.write(x)
+    ref = O.run_program(x, prog)
+    scale = float(np.abs(ref).max())
+    assert model.tensor_core_layers() >= 3      # encoder + bottleneck convs; 48- / 96-channel decoder convs stay on the CUDA cores
+    model.infer(inp, out)
+    err = float(np.abs(out.read() - ref).max()) / scale
+    assert err <= 1e-4, f"U-Net, default precision: {err:.3e} of the output range"
+    model.set_precision(api.MLX_PRECISION_FP32)
+    model.infer(inp, out)
+    err = float(np.abs(out.read() - ref).max()) / scale
+    assert err <= 1e-3, f"U-Net, fp32: {err:.3e} of the output range"
+    for obj in (inp, out, model):
+        obj.release()
