@@ -192,10 +192,15 @@ std::shared_ptr<Tensor> ParseTensor(Reader r)
         else r.Skip(w);
     }
 
+    // The dims come from an untrusted file: multiply with an overflow check and cap the element count, so a crafted
+    // shape whose product wraps cannot pass the size checks below with a tiny values vector.
+    constexpr size_t kMaxConstElements = size_t(1) << 31;
     size_t count = 1;
     for (int64_t d : t->shape.dims)
     {
         if (d < 0) throw std::runtime_error("constant tensor with unknown dimension");
+        if (d != 0 && count > kMaxConstElements / static_cast<size_t>(d))
+            throw std::runtime_error("constant tensor too large");
         count *= static_cast<size_t>(d);
     }
 

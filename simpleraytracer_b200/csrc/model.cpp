@@ -155,6 +155,13 @@ Model::Model(DeviceStatePtr device, ml_model_params const* params) : m_device(st
     }
     catch (std::exception const& e)
     {
+        // AllocateBuffers may have got part of the way: give everything back before the object disappears
+        if (m_device)
+        {
+            ReleaseBuffers();
+            for (void* p : m_packed) cudaFree(p);
+            m_packed.clear();
+        }
         for (auto& c : m_consts) cudaFree(c.dev);
         throw std::runtime_error(std::string("Error creating graph: Invalid argument: ") + e.what());
     }
@@ -297,6 +304,12 @@ Model::Value Model::Evaluate(pb::Graph const& graph, int idx, std::vector<Value>
         op.kind = OpKind::Conv;
         op.name = node.name;
         op.in = {in};
+        // every dim must fit an int and the values must be exactly KH*KW*Cin*Cout (untrusted file)
+        for (int64_t d : f.constant->shape.dims)
+            if (d < 1 || d > (int64_t(1) << 20)) Unimplemented(node, "Conv2D filter dimension " + std::to_string(d));
+        if (f.constant->values.size() != f.constant->ElementCount())
+            Unimplemented(node, "Conv2D filter holds " + std::to_string(f.constant->values.size()) + " values for "
+                                    + std::to_string(f.constant->ElementCount()) + " elements");
         op.KH = static_cast<int>(f.constant->shape.dims[0]);
         op.KW = static_cast<int>(f.constant->shape.dims[1]);
         int cin = static_cast<int>(f.constant->shape.dims[2]);
@@ -1537,9 +1550,15 @@ ml_status Model::InferBatch(ml_image const* inputs, ml_image const* outputs, siz
             m_error = "Image " + std::to_string(i) + ": " + m_error;
             return ML_FAIL;
         }
-    if (m_input_info.dtype == ML_FLOAT16)
+    // An image that is one item's output and ANOTHER item's input (or output) cannot be pipelined: the upload of the
+    // later item and the read-back of the earlier one would touch the same buffers concurrently.  Run in order.
+    bool aliased = false;
+    for (size_t i = 0; i < n && !aliased; i++)
+        for (size_t j = 0; j < n && !aliased; j++)
+            aliased = i != j && (outputs[i] == inputs[j] || outputs[i] == outputs[j]);
+    if (m_input_info.dtype == ML_FLOAT16 || aliased)
     {
-        // the fp16 <-> fp32 staging buffers are single: run one after the other
+        // (also: the fp16 <-> fp32 staging buffers are single) run one after the other
         for (size_t i = 0; i < n; i++)
             if (Infer(inputs[i], outputs[i]) != ML_OK) return ML_FAIL;
         return ML_OK;

@@ -619,3 +619,23 @@ def test_unsupported_op_fails_model_creation_loudly(ctx, tmp_path):
     params = api.ml_model_params(str(path).encode(), None, None)
     assert not ctx.lib.mlCreateModel(ctx.handle, C.byref(params))
     assert "Unimplemented" in ctx.error() and "sm" in ctx.error()
+
+
+def test_infer_batch_with_chained_images_runs_in_order(ctx, tmp_path):
+    """An image that is item 0's output and item 1's input: the batch must behave like the two mlInfer calls in
+    order (the pipelined path would upload it while it is still being produced)."""
+    path = tmp_path / "d.pb"
+    gw.make_denoiser(path, channels=3, width=16, depth=2, seed=4)
+    w, h = 96, 40
+    model, i, o = prepared_model(ctx, path, w, h)
+    x = np.random.default_rng(2).random((h, w, 3), dtype=np.float32)
+    a, b, c = (ctx.create_image(w, h, 3) for _ in range(3))
+    a.write(x)
+    model.infer(a, b); model.infer(b, c)
+    want = c.read()
+    b2, c2 = ctx.create_image(w, h, 3), ctx.create_image(w, h, 3)
+    b2.read(); c2.read()                      # host pointers handed out: read-back inside the call
+    model.infer_batch([a, b2], [b2, c2])
+    assert np.array_equal(c2.read(), want)
+    for obj in (a, b, c, b2, c2, model):
+        obj.release()
