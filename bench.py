@@ -49,7 +49,16 @@ CPU_SAMPLE_SPP = 64           # CPU sample: all 64 spp of every pixel (~10 s on 
 FLOP_PER_TRI_TEST = 45        # SURVEY.md section 8d conventions
 FLOP_PER_BOX_TEST = 21
 BACKGROUND = (0.5, 0.7, 0.9)
-E2E_CHUNKS = 4                # chunks of a multi-GPU host frame: copy of chunk k overlaps the render of chunk k+1
+# Flag chunks of a multi-GPU host frame.  1: one work-list render (fastest render, rows finish in no order), the copy
+# pipelined in pieces behind its single flag; > 1: the render itself in that many chunks (natural order), each copied
+# as soon as its flag arrives.  Measured at N = 8 (profiles/r02_e2e_chunks.txt).
+# Which wins depends on what bounds the frame (N = 2: config 3, render-bound, 63.1 Grays/s with 4 chunks against 41.9 with
+# 1; config 4, copy-bound, 2.67 against 1.25): 4 when the frame has >= 8 spp, else 1.  BENCH_E2E_CHUNKS overrides.
+E2E_CHUNKS_ENV = int(os.environ.get("BENCH_E2E_CHUNKS", "0"))
+
+
+def e2e_chunks(spp):
+    return E2E_CHUNKS_ENV if E2E_CHUNKS_ENV > 0 else (4 if spp >= 8 else 1)
 
 
 def parse_args():
@@ -424,9 +433,9 @@ class FrameRig:
             self.ctx.stream_wait_flags(self.d_consumed, 1, self.epoch - 1, stream=s)
             self.scene.render_device_signal(self.cam, self.light, self.params, self.target_ptr,
                                             self.d_flags + 4 * env.rank, self.epoch, chunk_stride=env.world,
-                                            n_chunks=E2E_CHUNKS, stream=s)
+                                            n_chunks=e2e_chunks(self.spp), stream=s)
             if env.rank == 0:
-                self.ctx.gather_frame_host(whole, self.target_ptr, self.d_flags, env.world, E2E_CHUNKS, self.epoch,
+                self.ctx.gather_frame_host(whole, self.target_ptr, self.d_flags, env.world, e2e_chunks(self.spp), self.epoch,
                                            host_rgb)
                 self.ctx.stream_write_flag(self.d_consumed, self.epoch, stream=s)
             env.stream.synchronize()
@@ -839,7 +848,7 @@ def measure_frame_workload(env, ctx, wl, spp, args, steps, warmup, with_nccl_gat
             "e2e": {"value": rays * steps / e2e_s / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_s / steps * 1e3,
                     "h2d_bytes_per_step": 152, "d2h_bytes_per_step": W * H * 12,
                     "host_buffer": "pageable (a reference-style caller's std::vector / numpy array) on rank 0, "
-                                   "the WHOLE frame" + ("" if world == 1 else f", gathered in {E2E_CHUNKS} chunks behind the device flags"),
+                                   "the WHOLE frame" + ("" if world == 1 else f", gathered in {e2e_chunks(rig.spp)} flag chunk(s) behind the device flags"),
                     "value_page_locked_buffer": rays * steps / e2e_pin_s / 1e6,
                     "frame_equal_single_gpu": e2e_equal},
         }

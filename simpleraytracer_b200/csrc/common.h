@@ -86,4 +86,9 @@ struct DeviceState
 
 using DeviceStatePtr = std::shared_ptr<DeviceState>;
 
+// memcpy of a large piece (pinned staging -> the caller's pageable frame) split over a small PERSISTENT pool of host
+// threads (created on first use, alive until exit: starting threads per call cost more than it saved, r01).  Pieces
+// below 2 MiB are copied by the calling thread.  A 99.5 MB 4K frame is host-copy bound on one thread (~9 GB/s).
+void ParallelMemcpy(void* dst, void const* src, size_t bytes);
+
 } // namespace ML

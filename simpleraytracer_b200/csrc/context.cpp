@@ -10,6 +10,12 @@
 #include "model.h"
 #include "model_runner_ext.h"
 
+#include <algorithm>
+#include <condition_variable>
+#include <mutex>
+#include <thread>
+#include <vector>
+
 namespace ML {
 
 DeviceState::DeviceState(int requested_device)
@@ -62,6 +68,85 @@ DeviceState::~DeviceState()
     if (gather_stage) cudaFreeHost(gather_stage);
     for (cudaEvent_t e : gather_events)
         if (e) cudaEventDestroy(e);
+}
+
+namespace {
+// Fixed set of workers; one job at a time (callers are serialised by a mutex: frames are copied one after another).
+class CopyPool
+{
+public:
+    static CopyPool& Instance()
+    {
+        static CopyPool* pool = new CopyPool;     // leaked on purpose: workers may outlive static destruction order
+        return *pool;
+    }
+    void Copy(char* dst, char const* src, size_t bytes)
+    {
+        size_t const n = m_threads.size() + 1;    // the caller copies a slice too
+        std::lock_guard<std::mutex> serial(m_serial);
+        size_t const slice = ((bytes + n - 1) / n + 4095) / 4096 * 4096;
+        {
+            std::lock_guard<std::mutex> lock(m_mutex);
+            m_dst = dst; m_src = src; m_bytes = bytes; m_slice = slice;
+            m_pending = m_threads.size();
+            m_job++;
+        }
+        m_wake.notify_all();
+        CopySlice(0);
+        std::unique_lock<std::mutex> lock(m_mutex);
+        m_done.wait(lock, [&] { return m_pending == 0; });
+    }
+
+private:
+    CopyPool()
+    {
+        unsigned want = std::thread::hardware_concurrency() / 2;
+        if (char const* e = std::getenv("SRT_HOST_COPY_THREADS")) want = static_cast<unsigned>(std::atoi(e));
+        want = std::max(1u, std::min(want, 8u));
+        for (unsigned t = 1; t < want; t++) m_threads.emplace_back([this, t] { Worker(t); });
+        for (auto& th : m_threads) th.detach();
+    }
+    void CopySlice(size_t index)
+    {
+        size_t const begin = index * m_slice;
+        if (begin < m_bytes) std::memcpy(m_dst + begin, m_src + begin, std::min(m_slice, m_bytes - begin));
+    }
+    void Worker(size_t index)
+    {
+        uint64_t seen = 0;
+        for (;;)
+        {
+            {
+                std::unique_lock<std::mutex> lock(m_mutex);
+                m_wake.wait(lock, [&] { return m_job != seen; });
+                seen = m_job;
+            }
+            CopySlice(index);
+            {
+                std::lock_guard<std::mutex> lock(m_mutex);
+                m_pending--;
+            }
+            m_done.notify_one();
+        }
+    }
+    std::vector<std::thread> m_threads;
+    std::mutex m_mutex, m_serial;
+    std::condition_variable m_wake, m_done;
+    char* m_dst = nullptr;
+    char const* m_src = nullptr;
+    size_t m_bytes = 0, m_slice = 0, m_pending = 0;
+    uint64_t m_job = 0;
+};
+} // namespace
+
+void ParallelMemcpy(void* dst, void const* src, size_t bytes)
+{
+    if (bytes < (size_t(2) << 20))
+    {
+        std::memcpy(dst, src, bytes);
+        return;
+    }
+    CopyPool::Instance().Copy(static_cast<char*>(dst), static_cast<char const*>(src), bytes);
 }
 
 Context::Context(int device) : m_device(std::make_shared<DeviceState>(device)) {}

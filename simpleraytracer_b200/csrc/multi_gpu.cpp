@@ -55,27 +55,40 @@ void GatherFrameHost(DeviceState& dev, srt_render_params const& p, void const* d
     uint32_t const before = *dev.wait_timeouts;
     char const* const src = static_cast<char const*>(d_rgb) + static_cast<size_t>(p.y0 - p.buf_y0) * row_bytes;
     char* const dst = reinterpret_cast<char*>(rgb_host) + static_cast<size_t>(p.y0 - p.buf_y0) * row_bytes;
+    // Every flag chunk is copied as up to `pieces` transfers, so that with a pageable destination the host copy of
+    // piece k runs while piece k + 1 crosses PCIe -- also when the frame is ONE flag chunk (a work-list render
+    // finishes rows in no particular order and signals once).  At most 16 pieces in all.
+    uint32_t const pieces = direct ? 1u : std::max(1u, std::min(4u, 16u / n_chunks));
+    struct Piece { size_t r0, r1; };
+    Piece piece[16];
+    uint32_t n_pieces = 0;
     for (uint32_t k = 0; k < n_chunks; k++)
     {
-        size_t const r0 = static_cast<size_t>(k) * chunk_rows, r1 = std::min<size_t>(p.y1 - p.y0, r0 + chunk_rows);
+        size_t const c0 = static_cast<size_t>(k) * chunk_rows, c1 = std::min<size_t>(p.y1 - p.y0, c0 + chunk_rows);
         LaunchWaitFlags(d_flags + static_cast<size_t>(k) * n_ranks, n_ranks, 1u, value,
                         timeout_ms ? timeout_ms : 2000u, dev.wait_timeouts, sc);
-        char* const h = direct ? dst : static_cast<char*>(dev.gather_stage);
-        ML_CUDA_CHECK(cudaMemcpyAsync(h + r0 * row_bytes, src + r0 * row_bytes, (r1 - r0) * row_bytes,
-                                      cudaMemcpyDeviceToHost, sc));
-        if (!direct)
+        size_t const step = (c1 - c0 + pieces - 1) / pieces;
+        for (size_t r0 = c0; r0 < c1; r0 += step)
         {
-            if (dev.gather_events[k] == nullptr)
-                ML_CUDA_CHECK(cudaEventCreateWithFlags(&dev.gather_events[k], cudaEventDisableTiming));
-            ML_CUDA_CHECK(cudaEventRecord(dev.gather_events[k], sc));
+            size_t const r1 = std::min(c1, r0 + step);
+            char* const h = direct ? dst : static_cast<char*>(dev.gather_stage);
+            ML_CUDA_CHECK(cudaMemcpyAsync(h + r0 * row_bytes, src + r0 * row_bytes, (r1 - r0) * row_bytes,
+                                          cudaMemcpyDeviceToHost, sc));
+            if (!direct)
+            {
+                if (dev.gather_events[n_pieces] == nullptr)
+                    ML_CUDA_CHECK(cudaEventCreateWithFlags(&dev.gather_events[n_pieces], cudaEventDisableTiming));
+                ML_CUDA_CHECK(cudaEventRecord(dev.gather_events[n_pieces], sc));
+            }
+            piece[n_pieces++] = Piece{r0, r1};
         }
     }
-    // pageable destination: move each chunk out of the staging buffer as it lands, while later chunks render
-    for (uint32_t k = 0; k < n_chunks && !direct; k++)
+    // pageable destination: move each piece out of the staging buffer as it lands, while later ones are in flight
+    for (uint32_t k = 0; k < n_pieces && !direct; k++)
     {
-        size_t const r0 = static_cast<size_t>(k) * chunk_rows, r1 = std::min<size_t>(p.y1 - p.y0, r0 + chunk_rows);
         ML_CUDA_CHECK(cudaEventSynchronize(dev.gather_events[k]));
-        std::memcpy(dst + r0 * row_bytes, static_cast<char*>(dev.gather_stage) + r0 * row_bytes, (r1 - r0) * row_bytes);
+        ParallelMemcpy(dst + piece[k].r0 * row_bytes, static_cast<char*>(dev.gather_stage) + piece[k].r0 * row_bytes,
+                       (piece[k].r1 - piece[k].r0) * row_bytes);
     }
     ML_CUDA_CHECK(cudaStreamSynchronize(sc));
     if (*dev.wait_timeouts != before)
@@ -431,9 +444,9 @@ ml_status SceneGroup::Render(srt_camera const* camera, srt_light const* light, s
         whole.y0 = 0; whole.y1 = whole.height; whole.buf_y0 = 0;
         whole.row_block_stride = n > 1 ? n : 0;
         whole.row_block_phase = 0;
-        // chunks only pay when there is a host copy to overlap with the rendering of the next chunk
         int const env_chunks = std::getenv("SRT_GROUP_CHUNKS") ? std::atoi(std::getenv("SRT_GROUP_CHUNKS")) : 0;   // per call: tests flip it
-        uint32_t want = rgb_host ? (static_cast<uint64_t>(params->width) * params->height >= (1u << 20) ? 4u : 1u) : 1u;
+        // one flag chunk: the work-list render is the fastest and the gather pipelines the copy in pieces behind it
+        uint32_t want = 1u;
         if (env_chunks > 0) want = static_cast<uint32_t>(std::min(env_chunks, 16));
         uint32_t chunk_rows = 0, n_chunks = 0;
         ChunkLayout(whole, want, chunk_rows, n_chunks);

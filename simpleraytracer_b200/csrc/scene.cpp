@@ -919,7 +919,7 @@ ml_status Scene::RenderHost(srt_camera const* camera, srt_light const* light,
                 }
                 size_t const src = r * W;
                 size_t const dst = static_cast<size_t>(y - params->buf_y0) * W;
-                if (rgb) std::memcpy(rgb + dst * 3, static_cast<float*>(m_h_rgb) + src * 3, run * W * 12);
+                if (rgb) ParallelMemcpy(rgb + dst * 3, static_cast<float*>(m_h_rgb) + src * 3, run * W * 12);
                 if (hit_id) std::memcpy(hit_id + dst, static_cast<int32_t*>(m_h_id) + src, run * W * 4);
                 if (hit_t) std::memcpy(hit_t + dst, static_cast<float*>(m_h_t) + src, run * W * 4);
                 r += run;
