@@ -277,6 +277,9 @@ class Env:
         torch.cuda.set_device(self.local_rank)
         self.dev = torch.device("cuda", self.local_rank)
         if self.world > 1:
+            # NCCL's "NCCL version ..." banner goes to stdout at VERSION level: keep stdout to the one JSON line
+            if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+                os.environ["NCCL_DEBUG"] = "WARN"
             dist.init_process_group("nccl", device_id=self.dev)
         # A dedicated torch stream is made current for everything below: the render kernels are launched on it
         # through the C ABI (a NULL stream would mean "the context's own stream"), torch.distributed's
@@ -968,7 +971,7 @@ def run_b200_arm(args):
                 "note": "instruction-issue bound, not FP32-pipe bound; flops = box_tests*21 + tri_tests*45 counted by the "
                         "instrumented kernel variant on the same frame -- the grids REMOVE algorithmic work (84 box + 4.6 triangle "
                         "tests per ray with the BVH alone, 0.04 + 3.7 with the grids), so TFLOP/s falls while Mrays/s rises; "
-                        "kernel_ms includes the per-frame screen-grid build (5 small launches before the render kernel)"}
+                        "kernel_ms includes the per-frame screen-grid build (4 small launches before the render kernel)"}
     launches_per_step = 6 * world + (1 if world > 1 and main["exchange"] != "reduce_sum" else 0)
     config = {"workload": wl["name"], "width": wl["width"], "height": wl["height"], "spp": spp,
               "triangles": wl["triangles"], "shade": "lambert+shadow", "accel": "bvh+grids",

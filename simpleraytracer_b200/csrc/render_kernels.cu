@@ -648,15 +648,16 @@ __device__ __forceinline__ bool grid_tile_range(GridBuild const& G, float4 box, 
 }
 
 
-// Can any query inside tile (tx, ty) pass the triangle's edge functions?  The functions already carry the
-// margin of ONE query (half_extent); a tile is a square of `tile` units, so its centre gets the remaining
-// half width in the L1 norm of each normal.  Evaluated identically by the count and the fill kernel.
+// Does this build own tile row ty (GridBuild::ty_*)?
 __device__ __forceinline__ bool grid_row_owned(GridBuild const& G, int ty)
 {
     uint32_t const t = static_cast<uint32_t>(ty);
     return t >= G.ty_begin && t < G.ty_end && (G.ty_stride <= 1u || t % G.ty_stride == G.ty_phase);
 }
 
+// Can any query inside tile (tx, ty) pass the triangle's edge functions?  The functions already carry the
+// margin of ONE query (half_extent); a tile is a square of `tile` units, so its centre gets the remaining
+// half width in the L1 norm of each normal.  Evaluated identically by the count and the fill kernel.
 __device__ __forceinline__ bool grid_tile_touches(GridBuild const& G, float4 const (&edge)[3], int tx, int ty)
 {
     float const t = static_cast<float>(G.tile);
@@ -669,23 +670,53 @@ __device__ __forceinline__ bool grid_tile_touches(GridBuild const& G, float4 con
     return ok;
 }
 
-// Tiles of one triangle's box, visited by the calling thread alone (COOP = false) or by the 32 lanes of its
-// warp together (COOP = true: lane t takes tiles t, t + 32, ...).  A thread per triangle serialises the few
-// triangles that cover hundreds of tiles -- up to max_tiles_per_tri dependent atomics in one thread, which was
-// most of the build time of frames with large triangles; the warp walks those boxes 32 tiles at a time.
-constexpr uint32_t kGridCoopTiles = 16;   // boxes with more tiles are walked by the whole warp
+// The tile rows of [ty0, ty1] this build owns (GridBuild::ty_*): `rows` of them, the first one `fy`, `step` apart.
+// The walk below visits ONLY these: at 8 ranks a triangle's box holds an owned row about once in eight, and testing
+// every tile of every box for ownership (a modulo per tile) was most of the count and fill kernels' instructions.
+__device__ __forceinline__ void grid_owned_rows(GridBuild const& G, int ty0, int ty1, int& fy, uint32_t& rows)
+{
+    int lo = max(ty0, static_cast<int>(G.ty_begin));
+    int const hi = min(ty1, static_cast<int>(G.ty_end) - 1);
+    if (G.ty_stride > 1u)
+    {
+        if (G.ty_phase >= G.ty_stride) { fy = 0; rows = 0; return; }
+        uint32_t const m = static_cast<uint32_t>(lo) % G.ty_stride;
+        lo += static_cast<int>((G.ty_phase + G.ty_stride - m) % G.ty_stride);
+    }
+    fy = lo;
+    rows = hi >= lo ? static_cast<uint32_t>(hi - lo) / max(G.ty_stride, 1u) + 1u : 0u;
+}
+
+// Owned tiles of one triangle's box, visited by the calling thread alone (COOP = false: row by row, no division)
+// or by the 32 lanes of its warp together (COOP = true: lane t takes tiles t, t + 32, ...).  A thread per
+// triangle serialises the few triangles that cover hundreds of tiles -- up to max_tiles_per_tri dependent atomics
+// in one thread, which was most of the build time of frames with large triangles; the warp walks those boxes 32
+// tiles at a time.  The threshold is not lower because the warp walks its large boxes ONE AFTER ANOTHER (~100
+// instructions of broadcast and loop each, at one warp's issue rate): with 16, the slowest warp of the benchmark
+// frame (24 boxes of 17..42 tiles) set the duration of the whole launch.
+constexpr uint32_t kGridCoopTiles = 32;   // boxes with more owned tiles are walked by the whole warp
 
 template <bool COOP, class Visit>
-__device__ __forceinline__ void grid_visit_tiles(GridBuild const& G, float4 const (&edge)[3], int tx0, int tx1, int ty0,
-                                                 int ty1, Visit&& visit)
+__device__ __forceinline__ void grid_visit_tiles(GridBuild const& G, float4 const (&edge)[3], int tx0, int tx1, int fy,
+                                                 uint32_t rows, Visit&& visit)
 {
-    uint32_t const w = static_cast<uint32_t>(tx1 - tx0 + 1), n = w * static_cast<uint32_t>(ty1 - ty0 + 1);
-    uint32_t const first = COOP ? (threadIdx.x & 31u) : 0u, step = COOP ? 32u : 1u;
-    for (uint32_t t = first; t < n; t += step)
+    int const step = static_cast<int>(max(G.ty_stride, 1u));
+    if (COOP)
     {
-        uint32_t const r = t / w;
-        int const ty = ty0 + static_cast<int>(r), tx = tx0 + static_cast<int>(t - r * w);
-        if (grid_row_owned(G, ty) && grid_tile_touches(G, edge, tx, ty)) visit(static_cast<uint32_t>(ty) * G.tiles_w + tx);
+        uint32_t const w = static_cast<uint32_t>(tx1 - tx0 + 1), n = w * rows;
+        for (uint32_t t = threadIdx.x & 31u; t < n; t += 32u)
+        {
+            uint32_t const r = t / w;
+            int const ty = fy + static_cast<int>(r) * step, tx = tx0 + static_cast<int>(t - r * w);
+            if (grid_tile_touches(G, edge, tx, ty)) visit(static_cast<uint32_t>(ty) * G.tiles_w + tx);
+        }
+    }
+    else
+    {
+        int ty = fy;
+        for (uint32_t r = 0; r < rows; r++, ty += step)
+            for (int tx = tx0; tx <= tx1; tx++)
+                if (grid_tile_touches(G, edge, tx, ty)) visit(static_cast<uint32_t>(ty) * G.tiles_w + tx);
     }
 }
 
@@ -695,10 +726,13 @@ template <class Visit>
 __device__ __forceinline__ void grid_walk_warp(GridBuild const& G, bool binned, uint32_t slot, float4 box,
                                                float4 const (&edge)[3], int tx0, int tx1, int ty0, int ty1, Visit&& visit)
 {
-    uint32_t const n = binned ? static_cast<uint32_t>((tx1 - tx0 + 1) * (ty1 - ty0 + 1)) : 0u;
+    int fy = 0;
+    uint32_t rows = 0;
+    if (binned) grid_owned_rows(G, ty0, ty1, fy, rows);
+    uint32_t const n = binned ? static_cast<uint32_t>(tx1 - tx0 + 1) * rows : 0u;
     bool const big = n > kGridCoopTiles;
     if (binned && !big)
-        grid_visit_tiles<false>(G, edge, tx0, tx1, ty0, ty1, [&](uint32_t tile) { visit(tile, slot, box); });
+        grid_visit_tiles<false>(G, edge, tx0, tx1, fy, rows, [&](uint32_t tile) { visit(tile, slot, box); });
     uint32_t todo = __ballot_sync(0xffffffffu, big);
     while (todo)
     {
@@ -714,17 +748,22 @@ __device__ __forceinline__ void grid_walk_warp(GridBuild const& G, bool binned, 
             e[k].w = 0.f;
         }
         int const bx0 = __shfl_sync(0xffffffffu, tx0, src), bx1 = __shfl_sync(0xffffffffu, tx1, src);
-        int const by0 = __shfl_sync(0xffffffffu, ty0, src), by1 = __shfl_sync(0xffffffffu, ty1, src);
+        int const bfy = __shfl_sync(0xffffffffu, fy, src);
+        uint32_t const brows = __shfl_sync(0xffffffffu, rows, src);
         uint32_t const bslot = __shfl_sync(0xffffffffu, slot, src);
         float4 const bbox = make_float4(__shfl_sync(0xffffffffu, box.x, src), __shfl_sync(0xffffffffu, box.y, src),
                                         __shfl_sync(0xffffffffu, box.z, src), __shfl_sync(0xffffffffu, box.w, src));
-        grid_visit_tiles<true>(G, e, bx0, bx1, by0, by1, [&](uint32_t tile) { visit(tile, bslot, bbox); });
+        grid_visit_tiles<true>(G, e, bx0, bx1, bfy, brows, [&](uint32_t tile) { visit(tile, bslot, bbox); });
     }
 }
 
 // Phase bodies of the grid build (`vb` = block index; called by all threads of the block).  Negative result kept for
-// the record: all five phases in ONE cooperative launch with counter barriers between them was not faster than five
-// launches (config 3: 95 vs 91 us, config 4: 318 vs 243 us) -- the build is atomic-throughput, not launch-latency, bound.
+// the record: all phases in ONE cooperative launch with counter barriers between them was not faster than one launch
+// per phase (config 3: 95 vs 91 us, config 4: 318 vs 243 us, round-2 figures before the walk below was rewritten).
+// What the build's time was made of, measured per launch (ncu, warm, one rank's share of the 100k-triangle frame at
+// 8 ranks): count 20 us + fill 30 us, both set by ONE warp -- the one whose triangles had 17..42-tile boxes, walked one
+// after the other by the whole warp, with an ownership modulo and a division per tile.  Visiting owned rows only, row
+// by row, brought them to 6.9 + 6.8 us (whole build with the scan changes below: 71 -> 31 us at 8 ranks, 75 -> 56 us on one GPU).
 __device__ __forceinline__ void grid_phase_count(GridBuild const& G, uint32_t vb)
 {
     uint32_t const i = vb * blockDim.x + threadIdx.x;     // n_tris_padded is a multiple of the block size
@@ -753,9 +792,12 @@ __device__ __forceinline__ void grid_phase_count(GridBuild const& G, uint32_t vb
     }
 }
 
-// Exclusive prefix sum of the tile counts in three small launches (the light grid has ~10^6 cells):
-// per-block sums of 4096 cells, one block scanning those sums (+ the verdict), per-block scans.
-constexpr uint32_t kScanBlock = 1024, kScanPerThread = 4, kScanCells = kScanBlock * kScanPerThread;
+// Exclusive prefix sum of the tile counts in two small launches (the light grid has ~10^6 cells): per-block sums of
+// 1024 cells -- the block that finishes last scans those sums and writes the verdict -- then per-block scans.  Small
+// blocks on purpose: the frame's 32 400 tiles spread over 32 SMs instead of 8 (a per-block scan is a chain of
+// dependent global loads, a shared-memory scan and one atomic per class: latency, which more SMs hide).
+constexpr uint32_t kScanBlock = 256, kScanPerThread = 4, kScanCells = kScanBlock * kScanPerThread;
+static_assert(kScanCells == kGridScanCells, "GridBuild::block_sums is sized by kGridScanCells");
 
 __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s_warp, uint32_t& block_total)
 {
@@ -787,7 +829,29 @@ __device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* s
     return s_warp[warp] + inc - v;
 }
 
-__device__ __forceinline__ void grid_phase_block_sums(GridBuild const& G, uint32_t vb)
+__device__ __forceinline__ void grid_phase_scan_sums(GridBuild const& G, uint32_t n_blocks, uint32_t* s_warp)
+{
+    uint32_t const per = (n_blocks + kScanBlock - 1u) / kScanBlock;
+    uint32_t const b = threadIdx.x * per, e = min(n_blocks, b + per);
+    uint32_t sum = 0;
+    for (uint32_t t = b; t < e; t++) sum += __ldcg(G.block_sums + t);
+    uint32_t total;
+    uint32_t run = block_exclusive_scan(sum, s_warp, total);
+    for (uint32_t t = b; t < e; t++)
+    {
+        uint32_t const v = __ldcg(G.block_sums + t);
+        G.block_sums[t] = run;
+        run += v;
+    }
+    if (threadIdx.x == 0)
+    {
+        G.tile_off[G.tiles_w * G.tiles_h] = total;
+        G.flags->total = total;
+        G.flags->ok = (total <= G.cap && G.flags->n_global <= kGridMaxGlobal) ? 1u : 0u;
+    }
+}
+
+__device__ __forceinline__ void grid_phase_block_sums(GridBuild const& G, uint32_t vb, uint32_t n_blocks)
 {
     __shared__ uint32_t s_warp[33];
     uint32_t const tiles = G.tiles_w * G.tiles_h;
@@ -798,30 +862,19 @@ __device__ __forceinline__ void grid_phase_block_sums(GridBuild const& G, uint32
         if (base + k < tiles) sum += G.tile_cnt[base + k];
     uint32_t total;
     block_exclusive_scan(sum, s_warp, total);
-    if (threadIdx.x == 0) G.block_sums[vb] = total;
-}
-
-__device__ __forceinline__ void grid_phase_scan_sums(GridBuild const& G, uint32_t n_blocks)
-{
-    __shared__ uint32_t s_warp[33];
-    uint32_t const per = (n_blocks + kScanBlock - 1u) / kScanBlock;
-    uint32_t const b = threadIdx.x * per, e = min(n_blocks, b + per);
-    uint32_t sum = 0;
-    for (uint32_t t = b; t < e; t++) sum += G.block_sums[t];
-    uint32_t total;
-    uint32_t run = block_exclusive_scan(sum, s_warp, total);
-    for (uint32_t t = b; t < e; t++)
-    {
-        uint32_t const v = G.block_sums[t];
-        G.block_sums[t] = run;
-        run += v;
-    }
+    // The block that finishes last scans the block sums (and writes the verdict): one launch less than a kernel of
+    // its own.  Ticket pattern: publish, fence, count; the last arrival fences again and reads through L2.
+    __shared__ bool s_last;
     if (threadIdx.x == 0)
     {
-        G.tile_off[G.tiles_w * G.tiles_h] = total;
-        G.flags->total = total;
-        G.flags->ok = (total <= G.cap && G.flags->n_global <= kGridMaxGlobal) ? 1u : 0u;
+        G.block_sums[vb] = total;
+        __threadfence();
+        s_last = atomicAdd(&G.flags->ticket, 1u) == n_blocks - 1u;
     }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    grid_phase_scan_sums(G, n_blocks, s_warp);
 }
 
 __device__ __forceinline__ void grid_phase_scan_blocks(GridBuild const& G, uint32_t vb)
@@ -835,16 +888,19 @@ __device__ __forceinline__ void grid_phase_scan_blocks(GridBuild const& G, uint3
     __syncthreads();
     uint32_t const tiles = G.tiles_w * G.tiles_h;
     uint32_t const base = vb * kScanCells + threadIdx.x * kScanPerThread;
-    uint32_t c[kScanPerThread];
+    uint32_t c[kScanPerThread], ns_prev[kScanPerThread];
     uint32_t sum = 0;
 #pragma unroll
     for (uint32_t k = 0; k < kScanPerThread; k++)
     {
         c[k] = base + k < tiles ? G.tile_cnt[base + k] : 0u;
+        // last frame's tile times, fetched with the counts: their latency hides behind the scan's barriers
+        ns_prev[k] = (G.order != nullptr && base + k < tiles) ? G.tile_time[base + k] : 0u;
         sum += c[k];
     }
+    uint32_t const carry = G.block_sums[vb];
     uint32_t total;
-    uint32_t run = G.block_sums[vb] + block_exclusive_scan(sum, s_warp, total);
+    uint32_t run = carry + block_exclusive_scan(sum, s_warp, total);
 #pragma unroll
     for (uint32_t k = 0; k < kScanPerThread; k++)
         if (base + k < tiles)
@@ -862,7 +918,7 @@ __device__ __forceinline__ void grid_phase_scan_blocks(GridBuild const& G, uint3
             // entry = tile | first column << 24 | columns << 28 (0 columns = whole tile)
             if (G.order != nullptr)
             {
-                uint32_t const ns = G.tile_time[base + k];
+                uint32_t const ns = ns_prev[k];
                 G.tile_time[base + k] = 0;
                 if (grid_row_owned(G, static_cast<int>((base + k) / G.tiles_w)))
                 {
@@ -927,8 +983,7 @@ __device__ __forceinline__ void grid_phase_fill(GridBuild const& G, uint32_t vb)
 }
 
 __global__ void __launch_bounds__(256) grid_count_kernel(const __grid_constant__ GridBuild G) { grid_phase_count(G, blockIdx.x); }
-__global__ void __launch_bounds__(kScanBlock) grid_block_sums_kernel(const __grid_constant__ GridBuild G) { grid_phase_block_sums(G, blockIdx.x); }
-__global__ void __launch_bounds__(kScanBlock) grid_scan_sums_kernel(const __grid_constant__ GridBuild G, uint32_t n_blocks) { grid_phase_scan_sums(G, n_blocks); }
+__global__ void __launch_bounds__(kScanBlock) grid_block_sums_kernel(const __grid_constant__ GridBuild G) { grid_phase_block_sums(G, blockIdx.x, gridDim.x); }
 __global__ void __launch_bounds__(kScanBlock) grid_scan_blocks_kernel(const __grid_constant__ GridBuild G) { grid_phase_scan_blocks(G, blockIdx.x); }
 __global__ void __launch_bounds__(256) grid_fill_kernel(const __grid_constant__ GridBuild G) { grid_phase_fill(G, blockIdx.x); }
 
@@ -1720,7 +1775,6 @@ void BuildScreenGrid(GridBuild const& build, cudaStream_t stream)
     uint32_t const blocks = (build.scene.n_tris_padded + 255u) / 256u;
     grid_count_kernel<<<blocks, 256, 0, stream>>>(build);
     grid_block_sums_kernel<<<scan_blocks, kScanBlock, 0, stream>>>(build);
-    grid_scan_sums_kernel<<<1, kScanBlock, 0, stream>>>(build, scan_blocks);
     grid_scan_blocks_kernel<<<scan_blocks, kScanBlock, 0, stream>>>(build);
     grid_fill_kernel<<<blocks, 256, 0, stream>>>(build);
     ML_CUDA_CHECK(cudaGetLastError());
@@ -1897,7 +1951,7 @@ constexpr size_t NaRound(size_t n) { return (n + kNaAlign - 1) / kNaAlign * kNaA
 constexpr size_t kNaFrameBytes = 256;                                        // counters | tickets | GridFlags (as Scene's scratch)
 constexpr size_t kNaGlobalOff = kNaFrameBytes;                               // kGridMaxGlobal u32
 constexpr size_t kNaTilesOff = NaRound(kNaGlobalOff + kGridMaxGlobal * 4);   // tile_cnt | tile_off | cursor | block_sums
-constexpr size_t kNaTileWords = 3 * kNaTiles + 16 + kNaTiles / 4096 + 8;
+constexpr size_t kNaTileWords = 3 * kNaTiles + 16 + kNaTiles / kGridScanCells + 8;
 constexpr size_t kNaItemsOff = NaRound(kNaTilesOff + kNaTileWords * 4);
 constexpr size_t kNaItems = 16 * kNaTris;                                    // list entries; more: flags.ok = 0, BVH walk
 constexpr size_t kNaBoxOff = NaRound(kNaItemsOff + kNaItems * 4);            // bbox | edges: 4 float4 per triangle slot

@@ -257,9 +257,9 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
         cudaFree(m_d_lgrid_tiles); cudaFree(m_d_lgrid_items); cudaFree(m_d_lgrid_bbox); cudaFree(m_d_lgrid_misc);
         m_d_lgrid_tiles = m_d_lgrid_items = m_d_lgrid_bbox = m_d_lgrid_misc = nullptr;
         m_lgrid_tiles = m_lgrid_cap = 0;
-        ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t)));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / kGridScanCells + 8) * sizeof(uint32_t)));
         // tile counts are zero between builds (grid_scan_blocks_kernel re-zeroes them): no per-build memset
-        ML_CUDA_CHECK(cudaMemsetAsync(m_d_lgrid_tiles, 0, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t), stream));
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_lgrid_tiles, 0, (3 * static_cast<size_t>(tiles) + 8 + tiles / kGridScanCells + 8) * sizeof(uint32_t), stream));
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_bbox, 4 * static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_lgrid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));
@@ -378,8 +378,8 @@ void Scene::PrepareGrid(srt_camera const* camera, srt_render_params const* param
         ML_CUDA_CHECK(cudaStreamSynchronize(stream));
         if (m_grid_free) ML_CUDA_CHECK(cudaEventSynchronize(m_grid_free));
         FreeGrid();
-        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t)));
-        ML_CUDA_CHECK(cudaMemsetAsync(m_d_grid_tiles, 0, (3 * static_cast<size_t>(tiles) + 8 + tiles / 4096 + 8) * sizeof(uint32_t), stream));
+        ML_CUDA_CHECK(cudaMalloc(&m_d_grid_tiles, (3 * static_cast<size_t>(tiles) + 8 + tiles / kGridScanCells + 8) * sizeof(uint32_t)));
+        ML_CUDA_CHECK(cudaMemsetAsync(m_d_grid_tiles, 0, (3 * static_cast<size_t>(tiles) + 8 + tiles / kGridScanCells + 8) * sizeof(uint32_t), stream));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_items, static_cast<size_t>(cap) * sizeof(uint32_t)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_bbox, 4 * static_cast<size_t>(m_view.n_tris_padded) * sizeof(F4)));
         ML_CUDA_CHECK(cudaMalloc(&m_d_grid_misc, sizeof(GridFlags) + kGridMaxGlobal * sizeof(uint32_t)));

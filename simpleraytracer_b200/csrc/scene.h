@@ -68,10 +68,12 @@ struct DeviceSceneView
 // irrelevant.  Rebuilt on the device for every render call (three small kernels); a frame the grid
 // cannot serve (flags.ok == 0) and tiles with long lists fall back to the BVH.
 constexpr uint32_t kGridTile = 8;        // pixels; equals the render kernels' 8-row blocks
+constexpr uint32_t kGridScanCells = 1024; // cells per block of the grid build's prefix sum (sizes GridBuild::block_sums)
 constexpr uint32_t kGridMaxList = 192;   // longer tile lists: that tile walks the BVH instead
 constexpr uint32_t kGridMaxGlobal = 32;  // triangles that cannot be projected safely (near or crossing the
                                          // camera plane, or huge on screen): tested by every ray
-struct GridFlags { uint32_t ok; uint32_t n_global; uint32_t total; uint32_t pad; };
+// ticket: blocks of the build's block-sum launch that have finished (the last one scans the sums); zeroed with the rest
+struct GridFlags { uint32_t ok; uint32_t n_global; uint32_t total; uint32_t ticket; };
 struct GridView
 {
     uint32_t const* tile_off;   // [tiles + 1] exclusive prefix of the list lengths
@@ -263,7 +265,7 @@ struct GridBuild
     uint32_t ty_begin, ty_end, ty_stride, ty_phase;
     float lo_bias;          // 1: queries are closed unit squares [x, x+1] (pixels); 0: points
     uint32_t* tile_cnt; uint32_t* tile_off; uint32_t* cursor; uint32_t* items;
-    uint32_t* block_sums;   // [tiles / 4096 + 1] scratch of the prefix sum
+    uint32_t* block_sums;   // [tiles / kGridScanCells + 1] scratch of the prefix sum
     uint32_t* tile_time;    // [tiles] or NULL: ns each tile took in the previous frame (render kernel adds, build clears)
     uint32_t* order;        // [kGridBuckets * order_stride] or NULL (light grid, no-alloc path): see GridView::order
     uint32_t* bucket_cnt;   // [kGridBuckets], zeroed by the caller's per-frame scratch memset
