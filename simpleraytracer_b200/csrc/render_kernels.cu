@@ -89,7 +89,9 @@ __device__ __forceinline__ uint32_t hash_sample(uint32_t pix, uint32_t s, uint32
 __device__ __forceinline__ float u01(uint32_t h) { return static_cast<float>(h >> 8) * (1.0f / 16777216.0f); }
 
 // section 2: primary ray direction through pixel (x,y), sample s.
-__device__ __forceinline__ V3 primary_dir(RenderLaunch const& L, uint32_t x, uint32_t y, uint32_t s)
+// `len_out`: |forward + sx*right + sy*up| of the sample, the factor between a point's depth coefficient along
+// `forward` and its distance t along the unit direction (t = cz * len, exactly, for any invertible camera basis).
+__device__ __forceinline__ V3 primary_dir(RenderLaunch const& L, uint32_t x, uint32_t y, uint32_t s, float* len_out = nullptr)
 {
     float jx = 0.5f, jy = 0.5f;
     if (L.params.jitter)
@@ -108,6 +110,7 @@ __device__ __forceinline__ V3 primary_dir(RenderLaunch const& L, uint32_t x, uin
     r.z = fma_(sy, L.camera.up[2], fma_(sx, L.camera.right[2], L.camera.forward[2]));
     float len = __fsqrt_rn(dot3(r, r));
     float inv = __fdiv_rn(1.0f, len);
+    if (len_out != nullptr) *len_out = len;
     return V3{mul(r.x, inv), mul(r.y, inv), mul(r.z, inv)};
 }
 
@@ -1455,6 +1458,7 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
     __shared__ float4 s_ce1[kCand], s_ce2[kCand], s_ctv[kCand], s_cq[kCand], s_cn[kCand], s_calb[kCand];
     __shared__ float4 s_cbox[kCand], s_cedge[3][kCand];
     __shared__ uint8_t s_pixlist[PIX == 1 ? 8 : 1][kCand];
+    __shared__ float s_key[kCand];      // depth keys of the candidates while they are being ranked
     V3 const o = v3(L.camera.origin);
     uint32_t const W = L.params.width;
     uint32_t const warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1531,27 +1535,47 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
         if (use_grid)   // block-uniform
         {
             n_cand = cnt + fl.n_global;
-            if (threadIdx.x < n_cand)
+            // The candidates are staged NEAREST FIRST (rank sort on the depth key the grid build left in
+            // edges[3*slot].w: nearest vertex depth along `forward` minus the projection slack; global triangles
+            // -inf): a sample stops walking its pixel's list at the first candidate that lies wholly behind the hit
+            // it already has, which skips the hidden layers (the benchmark frame: 1.8 layers per covered pixel).
+            bool const mine = threadIdx.x < n_cand;
+            bool const glob = threadIdx.x >= cnt;
+            uint32_t slot = 0;
+            float4 edge0 = make_float4(0.f, 0.f, 1.f, -pos_inf());
+            if (mine)
             {
-                bool const glob = threadIdx.x >= cnt;
-                uint32_t const slot = glob ? L.grid.global[threadIdx.x - cnt] : L.grid.items[off + threadIdx.x];
+                slot = glob ? L.grid.global[threadIdx.x - cnt] : L.grid.items[off + threadIdx.x];
+                if (!glob) edge0 = __ldg(reinterpret_cast<float4 const*>(L.grid.edges) + 3 * slot);
+                s_key[threadIdx.x] = edge0.w;
+            }
+            __syncthreads();
+            if (mine)
+            {
+                uint32_t at = 0;
+                for (uint32_t k = 0; k < n_cand; k++)
+                {
+                    float const other = s_key[k];      // same address in every lane: broadcast
+                    at += (other < edge0.w || (other == edge0.w && k < threadIdx.x)) ? 1u : 0u;
+                }
                 float4 const v0 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_v0) + slot);
                 float4 const e1 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e1) + slot);
                 float4 const e2 = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_e2) + slot);
                 V3 const tv = V3{sub(o.x, v0.x), sub(o.y, v0.y), sub(o.z, v0.z)};
                 V3 const q = cross3(tv, v3(e1));
-                s_ce1[threadIdx.x] = make_float4(e1.x, e1.y, e1.z, dot3(v3(e2), q));
-                s_ce2[threadIdx.x] = make_float4(e2.x, e2.y, e2.z, v0.w);          // .w = bits(triangle id)
-                s_ctv[threadIdx.x] = make_float4(tv.x, tv.y, tv.z, 0.f);
-                s_cq[threadIdx.x] = make_float4(q.x, q.y, q.z, 0.f);
-                s_cn[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_n) + slot);
-                s_calb[threadIdx.x] = __ldg(reinterpret_cast<float4 const*>(L.scene.albedo) + __float_as_int(v0.w));
-                s_cbox[threadIdx.x] = glob ? make_float4(-pos_inf(), -pos_inf(), pos_inf(), pos_inf())
-                                           : __ldg(reinterpret_cast<float4 const*>(L.grid.bbox) + slot);
+                s_ce1[at] = make_float4(e1.x, e1.y, e1.z, dot3(v3(e2), q));
+                s_ce2[at] = make_float4(e2.x, e2.y, e2.z, v0.w);          // .w = bits(triangle id)
+                s_ctv[at] = make_float4(tv.x, tv.y, tv.z, 0.f);
+                s_cq[at] = make_float4(q.x, q.y, q.z, edge0.w);           // .w = depth key
+                s_cn[at] = __ldg(reinterpret_cast<float4 const*>(L.scene.tri_n) + slot);
+                s_calb[at] = __ldg(reinterpret_cast<float4 const*>(L.scene.albedo) + __float_as_int(v0.w));
+                s_cbox[at] = glob ? make_float4(-pos_inf(), -pos_inf(), pos_inf(), pos_inf())
+                                  : __ldg(reinterpret_cast<float4 const*>(L.grid.bbox) + slot);
+                s_cedge[0][at] = edge0;
 #pragma unroll
-                for (int k = 0; k < 3; k++)
-                    s_cedge[k][threadIdx.x] = glob ? make_float4(0.f, 0.f, 1.f, 0.f)
-                                                   : __ldg(reinterpret_cast<float4 const*>(L.grid.edges) + 3 * slot + k);
+                for (int k = 1; k < 3; k++)
+                    s_cedge[k][at] = glob ? make_float4(0.f, 0.f, 1.f, 0.f)
+                                          : __ldg(reinterpret_cast<float4 const*>(L.grid.edges) + 3 * slot + k);
             }
             __syncthreads();
         }
@@ -1594,7 +1618,8 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                 V3 rgb = V3{0.f, 0.f, 0.f};
                 if (in_frame && s < spp)
                 {
-                    V3 d = primary_dir(L, x, y, s);
+                    float len;
+                    V3 d = primary_dir(L, x, y, s, &len);
                     Hit best = no_hit();
                     bool occ = false;
                     n_primary++;
@@ -1602,13 +1627,19 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
                     sh.need_shadow = false;
                     if (PIX == 1 && use_grid)
                     {
-                        if (STATS) n_tri += n_pix;
+                        // A candidate whose depth key is k lies at t >= k * len along this ray.  Stop when that is
+                        // beyond the hit in hand by more than 1/64 -- a margin some 10^5 ulps wide for the rounding of
+                        // the two t values being compared (the spec's winner is the minimum of the COMPUTED t's).
+                        float const t_scale = mul(len, 0.984375f);
                         for (uint32_t k = 0; k < n_pix; k++)
                         {
                             uint32_t const j = s_pixlist[warp][k];       // same address in every lane: broadcast
+                            float4 const cq = s_cq[j];
+                            if (best.t < mul(cq.w, t_scale)) break;      // nearest first: so are all the others
+                            if (STATS) n_tri++;
                             float4 const e1 = s_ce1[j], e2 = s_ce2[j];
                             float ts, adet;
-                            if (mt_inside_pre(d, e1, e2, s_ctv[j], s_cq[j], ts, adet))
+                            if (mt_inside_pre(d, e1, e2, s_ctv[j], cq, ts, adet))
                                 closest_update(best, ts, adet, __float_as_int(e2.w), j, L.params.t_min);   // slot = list index
                         }
                         if (best.id >= 0) sh = shade_hit(L, o, d, best.t, v3(s_cn[best.slot]), v3(s_calb[best.slot]));
