@@ -242,14 +242,19 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     }
     if (!(tmax_x > 0) || !(tmax_y > 0) || tmax_x > 50 || tmax_y > 50) return;
     double const half_w = tmax_x * 1.001 + 1e-6, half_h = tmax_y * 1.001 + 1e-6;
-    // about 32 cells per triangle, split by the aspect of the projected scene: a cell's list then holds little
-    // more than the triangles that really cover it (measured: the list walk was 20 % of the frame at 8)
-    static double const cells_per_tri = std::getenv("SRT_LIGHT_GRID_CELLS") ? std::atof(std::getenv("SRT_LIGHT_GRID_CELLS")) : 32.0;
-    double const g = std::min(4096.0, std::max(256.0, std::sqrt(cells_per_tri * static_cast<double>(m_view.n_tris))));
-    uint32_t const gw = static_cast<uint32_t>(std::min(4096.0, std::max(64.0, g * std::sqrt(half_w / half_h))));
-    uint32_t const gh = static_cast<uint32_t>(std::min(4096.0, std::max(64.0, g * std::sqrt(half_h / half_w))));
+    // about 128 cells per triangle, split by the aspect of the projected scene: a cell's list then holds little
+    // more than the triangles that really cover it.  Measured on the 100k-triangle frame (one B200, Grays/s |
+    // one-time build ms): 16: 48.8 | 1.2, 32: 53.0 | 1.2, 64: 55.6, 128: 57.4 | 1.3, 256: 58.7 | 2.0, 512: 59.3 | 3.4
+    // -- the walk's cost is the entries it visits that do NOT cover the point.  128 is where frame + build is least.
+    static double const cells_per_tri = std::getenv("SRT_LIGHT_GRID_CELLS") ? std::atof(std::getenv("SRT_LIGHT_GRID_CELLS")) : 128.0;
+    static double const max_side = std::getenv("SRT_LIGHT_GRID_MAX") ? std::atof(std::getenv("SRT_LIGHT_GRID_MAX")) : 4096.0;
+    double const g = std::min(max_side, std::max(256.0, std::sqrt(cells_per_tri * static_cast<double>(m_view.n_tris))));
+    uint32_t const gw = static_cast<uint32_t>(std::min(max_side, std::max(64.0, g * std::sqrt(half_w / half_h))));
+    uint32_t const gh = static_cast<uint32_t>(std::min(max_side, std::max(64.0, g * std::sqrt(half_h / half_w))));
     uint32_t const tiles = gw * gh;
-    uint32_t const cap = std::max<uint32_t>(static_cast<uint32_t>(std::min<uint64_t>(96ull * m_view.n_tris, 1ull << 28)), 1u << 20);
+    // entries: a triangle is listed in every cell its projection touches, so the total grows with the cell count
+    uint64_t const want_cap = std::max<uint64_t>(96ull * m_view.n_tris, 3ull * tiles);
+    uint32_t const cap = std::max<uint32_t>(static_cast<uint32_t>(std::min<uint64_t>(want_cap, 1ull << 28)), 1u << 20);
     if (tiles > m_lgrid_tiles || cap > m_lgrid_cap || m_d_lgrid_bbox == nullptr)
     {
         ML_CUDA_CHECK(cudaStreamSynchronize(stream));

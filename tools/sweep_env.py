@@ -23,7 +23,8 @@ def main():
             d = json.loads(r.stdout.strip().splitlines()[-1])
             rl = d["roofline"]
             print(f"{knob}={v} kernel_ms={rl['kernel_ms']:.3f} Mrays/s={d['value']:.0f} box={rl['box_tests']:.3g} "
-                  f"tri={rl['tri_tests']:.3g} nodes={d['config']['bvh_nodes']} build_ms={d['config']['bvh_build_ms']:.0f}",
+                  f"tri={rl['tri_tests']:.3g} nodes={d['config']['bvh_nodes']} build_ms={d['config']['bvh_build_ms']:.0f} "
+                  f"light_grid_ms={d['config'].get('light_grid_build_ms', 0):.2f} e2e={d['e2e']['value']:.0f}",
                   flush=True)
         except Exception as e:  # noqa: BLE001
             print(f"{knob}={v} FAILED {e}: {r.stderr[-400:]}", flush=True)
