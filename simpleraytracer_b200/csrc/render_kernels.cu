@@ -1258,14 +1258,23 @@ __device__ __forceinline__ bool lgrid_shadow(RenderLaunch const& L, V3 so, V3 sd
     for (uint32_t k = b; k < e; k++)
     {
         uint32_t const slot = __ldg(G.grid.items + k);
-        float4 const e0 = __ldg(edges + 3 * slot);
+        // One round trip for everything the entry may need (edge functions and the triangle itself) instead of up
+        // to four dependent ones: with ~1 entry per cell, most entries visited are the ones that cover the point.
+        float4 const e0 = __ldg(edges + 3 * slot), ea = __ldg(edges + 3 * slot + 1), eb = __ldg(edges + 3 * slot + 2);
+        float4 const v0 = __ldg(tv0 + slot), e1 = __ldg(te1 + slot), e2 = __ldg(te2 + slot);
         if (!(e0.w <= cz)) break;
         if (k >= e_walk) return false;
         // the projected triangle must cover the query point
-        if (!edge_pass(e0, gx, gy)) continue;
-        if (!edge_pass(__ldg(edges + 3 * slot + 1), gx, gy) || !edge_pass(__ldg(edges + 3 * slot + 2), gx, gy)) continue;
-        if (STATS) n_tri++;
-        if (test(slot)) return true;
+        if (edge_pass(e0, gx, gy) & edge_pass(ea, gx, gy) & edge_pass(eb, gx, gy))
+        {
+            if (STATS) n_tri++;
+            float ts, adet;
+            if (mt_inside(so, sd, v0, e1, e2, ts, adet))
+            {
+                float const t = __fdiv_rn(ts, adet);
+                if (t > 0.0f && t < 1.0f) { occluded = true; hint = slot; return true; }
+            }
+        }
     }
     return true;
 }
