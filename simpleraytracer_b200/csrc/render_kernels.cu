@@ -925,7 +925,7 @@ __device__ __forceinline__ void grid_phase_scan_blocks(GridBuild const& G, uint3
                 G.tile_time[base + k] = 0;
                 if (grid_row_owned(G, static_cast<int>((base + k) / G.tiles_w)))
                 {
-                    bool const bvh = c[k] > kGridMaxList;      // list too long to stage: every sample walks the BVH (~1 ms)
+                    bool const bvh = c[k] + G.flags->n_global > kSppMaxCand;   // too long to stage: every sample walks the BVH (~1 ms)
                     uint32_t parts, cls;
                     if (ns != 0u)
                     {
@@ -1339,9 +1339,10 @@ __global__ void __launch_bounds__(kBvhThreads, MINB) render_bvh_kernel(const __g
                     uint32_t const slot = glob ? __ldg(L.grid.global + (k - g_cnt)) : __ldg(L.grid.items + g_off + k);
                     if (!glob)
                     {
+                        // box and edge functions in one round trip (the box alone rejects few entries of a tile's list)
                         float4 const b = __ldg(reinterpret_cast<float4 const*>(L.grid.bbox) + slot);
-                        if (!(b.z >= px0 && b.x <= px0 + 1.0f && b.w >= py0 && b.y <= py0 + 1.0f)) continue;
                         float4 const e0 = __ldg(edges + 3 * slot), e1 = __ldg(edges + 3 * slot + 1), e2 = __ldg(edges + 3 * slot + 2);
+                        if (!(b.z >= px0 && b.x <= px0 + 1.0f && b.w >= py0 && b.y <= py0 + 1.0f)) continue;
                         if (!(e0.x * qx + e0.y * qy + e0.z >= 0.0f) || !(e1.x * qx + e1.y * qy + e1.z >= 0.0f)
                             || !(e2.x * qx + e2.y * qy + e2.z >= 0.0f))
                             continue;
@@ -1463,7 +1464,8 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
     // Moller-Trumbore terms, unit normal and albedo, so that neither the test nor the shading of a sample
     // touches global memory; every warp filters them against its current pixel (lanes test different
     // candidates, ballot-compacted), and every sample of that pixel then tests the few survivors.
-    constexpr uint32_t kCand = PIX == 1 ? kGridMaxList + kGridMaxGlobal : 1;
+    constexpr uint32_t kCand = PIX == 1 ? kSppMaxCand : 1;
+    static_assert(kCand <= 256, "s_pixlist holds candidate indices in one byte; one staging thread per candidate");
     __shared__ float4 s_ce1[kCand], s_ce2[kCand], s_ctv[kCand], s_cq[kCand], s_cn[kCand], s_calb[kCand];
     __shared__ float4 s_cbox[kCand], s_cedge[3][kCand];
     __shared__ uint8_t s_pixlist[PIX == 1 ? 8 : 1][kCand];
@@ -1540,7 +1542,7 @@ __global__ void __launch_bounds__(256, MINB) render_bvh_spp_kernel(const __grid_
         uint32_t const tile = ty * L.grid.tiles_w + bx;
         uint32_t const off = L.grid.tile_off[tile], cnt = L.grid.tile_off[tile + 1] - off;
         trace_tile = tile; trace_cnt = cnt;
-        use_grid = fl.ok != 0 && cnt <= kGridMaxList && bx < L.grid.tiles_w && ty < L.grid.tiles_h;
+        use_grid = fl.ok != 0 && cnt + fl.n_global <= kCand && bx < L.grid.tiles_w && ty < L.grid.tiles_h;
         if (use_grid)   // block-uniform
         {
             n_cand = cnt + fl.n_global;

@@ -69,7 +69,8 @@ struct DeviceSceneView
 // cannot serve (flags.ok == 0) and tiles with long lists fall back to the BVH.
 constexpr uint32_t kGridTile = 8;        // pixels; equals the render kernels' 8-row blocks
 constexpr uint32_t kGridScanCells = 1024; // cells per block of the grid build's prefix sum (sizes GridBuild::block_sums)
-constexpr uint32_t kGridMaxList = 192;   // longer tile lists: that tile walks the BVH instead
+constexpr uint32_t kSppMaxCand = 256;    // sample-parallel kernel: candidates (tile list + global list) it can stage; a tile
+                                         // with more walks the BVH instead (one byte indexes a candidate)
 constexpr uint32_t kGridMaxGlobal = 32;  // triangles that cannot be projected safely (near or crossing the
                                          // camera plane, or huge on screen): tested by every ray
 // ticket: blocks of the build's block-sum launch that have finished (the last one scans the sums); zeroed with the rest
