@@ -288,12 +288,20 @@ class Env:
         torch.cuda.set_stream(self.stream)
         assert self.stream.cuda_stream != 0
         self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)   # > 126 MB L2
+        self._token = torch.zeros(1, dtype=torch.float32, device=self.dev)
 
     def barrier(self):
         self.torch.cuda.synchronize()
         if self.world > 1:
             self.dist.barrier()
         self.torch.cuda.synchronize()
+
+    def device_barrier(self):
+        """Aligns the ranks ON THE DEVICE: a one-element all-reduce enqueued on the launching stream (the host does not
+        wait).  Work enqueued behind it starts on every GPU when the collective completes there, within a microsecond
+        or two of the others, whatever the jitter with which the host threads left the host barrier."""
+        if self.world > 1:
+            self.dist.all_reduce(self._token)
 
     def reduce(self, values, op="max"):
         """MAX / SUM / MIN over the ranks of a list of floats (float64)."""
@@ -483,9 +491,11 @@ def median(xs):
 
 
 def timed_device_steps(env, rig, steps, warmup):
-    """K frames, inputs resident: every step is bracketed by CUDA events on the launching stream, the L2 is
-    flushed (untimed) before it and all ranks start it together (host barrier, untimed).  On rank 0 the
-    bracket ends behind the device-side flag wait, i.e. when the whole frame is in its memory.
+    """K frames, inputs resident: every step is bracketed by CUDA events on the launching stream.  Before it,
+    untimed: a host barrier, the L2 flush, and a device-side barrier on the launching stream, so that the ranks'
+    GPUs start the step together (the hosts leave a host barrier tens of microseconds apart, which at 8 ranks
+    was charged to a 0.59 ms step) with the step's launches already queued behind the flush, as they are at N = 1.
+    On rank 0 the bracket ends behind the device-side flag wait, i.e. when the whole frame is in its memory.
     Returns per-rank lists (step_ms, own_span_ms, grid_build_ms) and the instrumented counts."""
     torch = env.torch
     for _ in range(max(warmup, 3)):
@@ -494,8 +504,9 @@ def timed_device_steps(env, rig, steps, warmup):
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     span, grid = [], []
     for k in range(steps):
-        env.flush.zero_()
         env.barrier()
+        env.flush.zero_()
+        env.device_barrier()
         ev[k][0].record(env.stream)
         rig.step()
         ev[k][1].record(env.stream)
@@ -977,6 +988,7 @@ def run_b200_arm(args):
               "triangles": wl["triangles"], "shade": "lambert+shadow", "accel": "bvh+grids",
               "parallelism": f"interleaved_row_blocks{world}" if world > 1 else "single_gpu",
               "exchange": main["exchange"], "l2_flush_between_steps": True,
+              "step_start": "host barrier, L2 flush, device-side barrier on the launching stream (untimed), then the start event",
               "rays_per_step": main["rays_per_step"], "primary_rays": main["primary_rays"],
               "shadow_rays": main["shadow_rays"], "bvh_nodes": main["bvh_nodes"],
               "bvh_build_ms": main["bvh_build_ms"], "scene_upload_ms": main["scene_upload_ms"],
