@@ -277,9 +277,9 @@ class Env:
         torch.cuda.set_device(self.local_rank)
         self.dev = torch.device("cuda", self.local_rank)
         if self.world > 1:
-            # NCCL's "NCCL version ..." banner goes to stdout at VERSION level: keep stdout to the one JSON line
-            if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-                os.environ["NCCL_DEBUG"] = "WARN"
+            # NCCL prints its "NCCL version ..." banner (VERSION and WARN levels) and its log to stdout: send them to
+            # stderr, stdout carries the one JSON line
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
             dist.init_process_group("nccl", device_id=self.dev)
         # A dedicated torch stream is made current for everything below: the render kernels are launched on it
         # through the C ABI (a NULL stream would mean "the context's own stream"), torch.distributed's
