@@ -277,8 +277,11 @@ class Env:
         torch.cuda.set_device(self.local_rank)
         self.dev = torch.device("cuda", self.local_rank)
         if self.world > 1:
-            # NCCL prints its "NCCL version ..." banner (VERSION and WARN levels) and its log to stdout: send them to
-            # stderr, stdout carries the one JSON line
+            # NCCL prints its "NCCL version ..." banner (VERSION and WARN levels) and its log to stdout, and honours
+            # NCCL_DEBUG_FILE only above the VERSION level: raise VERSION to WARN and send everything to stderr, so
+            # that stdout carries the one JSON line
+            if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+                os.environ["NCCL_DEBUG"] = "WARN"
             os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
             dist.init_process_group("nccl", device_id=self.dev)
         # A dedicated torch stream is made current for everything below: the render kernels are launched on it

@@ -141,7 +141,7 @@ private:
 
 void ParallelMemcpy(void* dst, void const* src, size_t bytes)
 {
-    if (bytes < (size_t(2) << 20))
+    if (bytes < (size_t(1) << 20))     // below ~1 MiB one thread is done before the pool has woken up
     {
         std::memcpy(dst, src, bytes);
         return;

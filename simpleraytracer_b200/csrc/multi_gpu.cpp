@@ -57,8 +57,10 @@ void GatherFrameHost(DeviceState& dev, srt_render_params const& p, void const* d
     char* const dst = reinterpret_cast<char*>(rgb_host) + static_cast<size_t>(p.y0 - p.buf_y0) * row_bytes;
     // Every flag chunk is copied as up to `pieces` transfers, so that with a pageable destination the host copy of
     // piece k runs while piece k + 1 crosses PCIe -- also when the frame is ONE flag chunk (a work-list render
-    // finishes rows in no particular order and signals once).  At most 16 pieces in all.
-    uint32_t const pieces = direct ? 1u : std::max(1u, std::min(4u, 16u / n_chunks));
+    // finishes rows in no particular order and signals once).  At most 8 pieces for a multi-chunk frame: a piece must
+    // stay large enough for the copy pool (16 pieces of a 1080p frame are 1.5 MB each, which one thread copied alone
+    // at ~11 GB/s: 2.2 ms of host copy behind a 0.6 ms render at 8 GPUs).
+    uint32_t const pieces = direct ? 1u : std::max(1u, std::min(4u, 8u / n_chunks));
     struct Piece { size_t r0, r1; };
     Piece piece[16];
     uint32_t n_pieces = 0;
