@@ -126,3 +126,32 @@ def test_oracle_side_generator_equals_the_product_generator():
     v1, a1, c1, l1 = api.gen_cornell_box(512, 512)
     v2, a2, c2, l2 = O.gen_cornell_box(512, 512)
     assert np.array_equal(v1, v2) and np.array_equal(a1, a2) and bytes(c1) == bytes(c2) and bytes(l1) == bytes(l2)
+
+
+@pytest.mark.parametrize("height,stride,requested", [(1080, 8, 4), (1080, 8, 16), (1080, 2, 4), (2160, 4, 1), (2160, 8, 16),
+                                                      (360, 8, 4), (64, 8, 4), (7, 1, 3), (1080, 0, 8), (8, 8, 16)])
+def test_chunk_layout_of_a_sharded_frame(height, stride, requested):
+    """srtChunkLayout (include/srt_render.h; host arithmetic only, no device): the rows of a frame cut into at most
+    `requested` flag chunks of whole (8 * stride)-row groups -- the layout srtRenderDeviceSignal's producers and
+    srtGatherFrameHost's consumer must agree on.  Every chunk but the last holds the same number of 8-row blocks of
+    every rank, the chunks tile the frame, and no chunk is empty."""
+    from simpleraytracer_b200 import api
+    p = api.make_params(1920, height, spp=1, row_block_stride=stride, row_block_phase=0)
+    rows, n = api.chunk_layout(p, requested)
+    group = 8 * max(stride, 1)
+    assert rows % group == 0 and rows > 0
+    assert 1 <= n <= max(requested, 1)
+    assert (n - 1) * rows < height <= n * rows                  # tiles the frame, last chunk not empty
+    per_rank = rows // group                                    # row blocks of each rank in a full chunk
+    for k in range(n):
+        y0, y1 = k * rows, min(height, (k + 1) * rows)
+        blocks = [b for b in range(y0 // 8, (y1 + 7) // 8)]
+        owners = [b % max(stride, 1) for b in blocks]
+        counts = [owners.count(r) for r in range(max(stride, 1))]
+        if k < n - 1:
+            assert counts == [per_rank] * max(stride, 1)
+        else:
+            assert max(counts) <= per_rank and sum(counts) == len(blocks)
+    # asking for more chunks than there are groups gives one chunk per group
+    rows1, n1 = api.chunk_layout(p, 10_000)
+    assert rows1 == group and n1 == (height + group - 1) // group
