@@ -26,6 +26,14 @@
 namespace ML {
 namespace {
 
+// Largest stride / dilation a graph may ask for (TensorFlow accepts any positive value; image networks use 1..4).
+// The bound keeps the int arithmetic of shape inference and padding far from overflow for any frame that fits in memory.
+constexpr int64_t kMaxStrideOrDilation = 64;
+// Largest tensor side and element count a plan may reach: the kernels index elements with 32-bit arithmetic, and an
+// untrusted graph must not be able to wrap the plan's int shape arithmetic (a resize by 2^31 - 1, say).
+constexpr int64_t kMaxTensorSide = int64_t(1) << 20;
+constexpr uint64_t kMaxTensorElements = uint64_t(1) << 31;
+
 // dtype from attr "dtype" or "T"; H,W,C = last three dims of _output_shapes[0]
 // with -1 -> 0 (reference model.cpp:23-48).  Divergence: a node without
 // _output_shapes falls back to a Placeholder's "shape" attr, else all-unknown,
@@ -317,14 +325,17 @@ Model::Value Model::Evaluate(pb::Graph const& graph, int idx, std::vector<Value>
         if (pb::Attr const* s = node.Find("strides"))
             if (s->list_i.size() == 4)
             {
-                if (s->list_i[0] != 1 || s->list_i[3] != 1 || s->list_i[1] != s->list_i[2] || s->list_i[1] < 1)
+                // bounded above as well: shape inference does int arithmetic on (H + stride - 1) and (K - 1) * dilation
+                if (s->list_i[0] != 1 || s->list_i[3] != 1 || s->list_i[1] != s->list_i[2] || s->list_i[1] < 1
+                    || s->list_i[1] > kMaxStrideOrDilation)
                     Unimplemented(node, "strides");
                 op.stride = static_cast<int>(s->list_i[1]);
             }
         if (pb::Attr const* dl = node.Find("dilations"))
             if (dl->list_i.size() == 4)
             {
-                if (dl->list_i[0] != 1 || dl->list_i[3] != 1 || dl->list_i[1] != dl->list_i[2] || dl->list_i[1] < 1)
+                if (dl->list_i[0] != 1 || dl->list_i[3] != 1 || dl->list_i[1] != dl->list_i[2] || dl->list_i[1] < 1
+                    || dl->list_i[1] > kMaxStrideOrDilation)
                     Unimplemented(node, "dilations");
                 op.dilation = static_cast<int>(dl->list_i[1]);
             }
@@ -423,7 +434,7 @@ Model::Value Model::Evaluate(pb::Graph const& graph, int idx, std::vector<Value>
             || ks->list_i[1] != ks->list_i[2] || ks->list_i[1] < 1 || ks->list_i[1] > 16)
             Unimplemented(node, "ksize (square windows over H and W only)");
         if (st == nullptr || st->list_i.size() != 4 || st->list_i[0] != 1 || st->list_i[3] != 1
-            || st->list_i[1] != st->list_i[2] || st->list_i[1] < 1)
+            || st->list_i[1] != st->list_i[2] || st->list_i[1] < 1 || st->list_i[1] > kMaxStrideOrDilation)
             Unimplemented(node, "strides");
         if (pad == nullptr || !pad->has_s || (pad->s != "SAME" && pad->s != "VALID")) Unimplemented(node, "padding");
         Op op;
@@ -453,6 +464,8 @@ Model::Value Model::Evaluate(pb::Graph const& graph, int idx, std::vector<Value>
         {
             if (size.constant->ints.size() != 2 || size.constant->ints[0] < 1 || size.constant->ints[1] < 1)
                 Unimplemented(node, "size must hold two positive integers");
+            if (size.constant->ints[0] > kMaxTensorSide || size.constant->ints[1] > kMaxTensorSide)
+                Unimplemented(node, "size beyond " + std::to_string(kMaxTensorSide) + " rows or columns");
             op.size_h = static_cast<int>(size.constant->ints[0]);
             op.size_w = static_cast<int>(size.constant->ints[1]);
         }
@@ -503,9 +516,14 @@ Model::Value Model::Evaluate(pb::Graph const& graph, int idx, std::vector<Value>
                 if (!sh.shape_hw || !k.is_const || (k.constant->ints.size() != 2 && k.constant->ints.size() != 1)
                     || k.constant->ints[0] < 1 || k.constant->ints.back() < 1)
                     Unimplemented(node, "shape arithmetic other than Shape(x)[1:3] * positive constants");
+                int64_t const mh = static_cast<int64_t>(sh.shape_mul_h) * k.constant->ints[0];
+                int64_t const mw = static_cast<int64_t>(sh.shape_mul_w) * k.constant->ints.back();
+                if (k.constant->ints[0] > kMaxTensorSide || k.constant->ints.back() > kMaxTensorSide || mh > kMaxTensorSide
+                    || mw > kMaxTensorSide)
+                    Unimplemented(node, "shape factor beyond " + std::to_string(kMaxTensorSide));
                 result = sh;
-                result.shape_mul_h = sh.shape_mul_h * static_cast<int>(k.constant->ints[0]);
-                result.shape_mul_w = sh.shape_mul_w * static_cast<int>(k.constant->ints.back());
+                result.shape_mul_h = static_cast<int>(mh);
+                result.shape_mul_w = static_cast<int>(mw);
             }
             else if (a.shape_ref >= 0 || b.shape_ref >= 0) Unimplemented(node, "shape arithmetic");
             else if (a.is_const && b.is_const) Unimplemented(node, "constant folding");
@@ -797,6 +815,14 @@ void Model::InferShapes(size_t H, size_t W, size_t C)
                                      + std::to_string(in.C));
         in.C = static_cast<int>(C);
     }
+    auto too_large = [](int64_t h, int64_t w, int64_t c) {
+        return h < 0 || w < 0 || h > kMaxTensorSide || w > kMaxTensorSide
+               || static_cast<uint64_t>(h) * static_cast<uint64_t>(w) * static_cast<uint64_t>(std::max<int64_t>(c, 1)) >= kMaxTensorElements;
+    };
+    if (H > static_cast<size_t>(kMaxTensorSide) || W > static_cast<size_t>(kMaxTensorSide)
+        || too_large(static_cast<int64_t>(H), static_cast<int64_t>(W), in.C))
+        throw std::runtime_error("input of " + std::to_string(W) + " x " + std::to_string(H) + " x " + std::to_string(in.C)
+                                 + " exceeds the largest supported tensor (2^31 elements, 2^20 rows or columns)");
     in.H = static_cast<int>(H);
     in.W = static_cast<int>(W);
 
@@ -875,12 +901,19 @@ void Model::InferShapes(size_t H, size_t W, size_t C)
                 if (o.C == 0) o.C = a.C;
                 if (op.size_ref >= 0)
                 {
-                    o.H = m_tensors[op.size_ref].H * op.mul_h;
-                    o.W = m_tensors[op.size_ref].W * op.mul_w;
+                    int64_t const h = static_cast<int64_t>(m_tensors[op.size_ref].H) * op.mul_h;
+                    int64_t const w = static_cast<int64_t>(m_tensors[op.size_ref].W) * op.mul_w;
+                    if (too_large(h, w, o.C))
+                        throw std::runtime_error("'" + op.name + "' output of " + std::to_string(w) + " x " + std::to_string(h)
+                                                 + " exceeds the largest supported tensor");
+                    o.H = static_cast<int>(h);
+                    o.W = static_cast<int>(w);
                 }
                 else if (a.H != 0 && a.W != 0) { o.H = op.size_h; o.W = op.size_w; }
                 break;
             case OpKind::DepthToSpace:
+                if (too_large(static_cast<int64_t>(a.H) * op.block, static_cast<int64_t>(a.W) * op.block, o.C))
+                    throw std::runtime_error("'" + op.name + "' output exceeds the largest supported tensor");
                 o.H = a.H * op.block; o.W = a.W * op.block;
                 break;
             case OpKind::Pad:
@@ -893,6 +926,8 @@ void Model::InferShapes(size_t H, size_t W, size_t C)
                         if (op.pad_t > lim_h || op.pad_b > lim_h || op.pad_l > lim_w || op.pad_r > lim_w)
                             throw std::runtime_error("'" + op.name + "' mirrors more rows or columns than the input has");
                     }
+                    if (too_large(static_cast<int64_t>(a.H) + op.pad_t + op.pad_b, static_cast<int64_t>(a.W) + op.pad_l + op.pad_r, o.C))
+                        throw std::runtime_error("'" + op.name + "' output exceeds the largest supported tensor");
                     o.H = a.H + op.pad_t + op.pad_b; o.W = a.W + op.pad_l + op.pad_r;
                 }
                 break;
@@ -906,6 +941,9 @@ void Model::InferShapes(size_t H, size_t W, size_t C)
                 break;
             }
         }
+        if (too_large(o.H, o.W, o.C))
+            throw std::runtime_error("'" + op.name + "' output of " + std::to_string(o.W) + " x " + std::to_string(o.H) + " x "
+                                     + std::to_string(o.C) + " exceeds the largest supported tensor (2^31 elements)");
     }
     AssignPrecision();
 }

@@ -1,5 +1,7 @@
 """CPU: the GraphDef writer and the C++ wire-format reader, cross-checked
 against the protobuf runtime (an independent encoder/decoder)."""
+from pathlib import Path
+
 import numpy as np
 import pytest
 
@@ -8,6 +10,7 @@ from simpleraytracer_b200 import api
 from simpleraytracer_b200 import graphdef_writer as gw
 
 P = tf_protos.build()
+ROOT = Path(__file__).resolve().parent.parent
 
 
 def test_writer_bytes_parse_with_protobuf_runtime():
@@ -232,3 +235,85 @@ def test_add_is_folded_into_the_conv_only_when_the_order_allows(tmp_path):
     ops = build(par)
     assert [o.split()[0] for o in ops] == ["Conv", "Conv"]
     assert "residual" not in ops[0] and "name=b " in ops[1] and "residual=t" in ops[1]
+
+
+def _one_op_graph(tmp_path, build, shape=(1, 64, 48, 3)):
+    g = gw.GraphBuilder()
+    x = g.placeholder("input", shape=shape)
+    build(g, x)
+    path = tmp_path / "one.pb"
+    path.write_bytes(g.finish())
+    return api.inspect_model(path)
+
+
+def test_untrusted_sizes_cannot_wrap_the_plan(tmp_path):
+    """A graph is untrusted input (the reference hands it to TensorFlow, model.cpp:87).  Sizes that would wrap the plan's
+    shape arithmetic or exceed what the kernels can index (2^31 elements, 2^20 rows or columns per tensor) are refused
+    when the graph is read, with a message; ordinary values next to them still pass.  Host only: no device involved."""
+    ok, text = _one_op_graph(tmp_path, lambda g, x: g.resize(x, size=(128, 96), bilinear=True, name="out"))
+    assert ok and "output dtype=0 w=96 h=128 c=3" in text
+    for size in ((2**31 - 1, 2**31 - 1), (65536, 65536), (2**20, 4096)):
+        ok, text = _one_op_graph(tmp_path, lambda g, x: g.resize(x, size=size, bilinear=True, name="out"))
+        assert not ok and ("beyond" in text or "exceeds the largest supported tensor" in text), text
+    ok, text = _one_op_graph(tmp_path, lambda g, x: g.resize(x, factor=4, name="out"))
+    assert ok and "output dtype=0 w=192 h=256 c=3" in text
+    for factor in (65536, 2**24, 2**31 - 1):
+        ok, text = _one_op_graph(tmp_path, lambda g, x: g.resize(x, factor=factor, name="out"))
+        assert not ok and ("beyond" in text or "exceeds the largest supported tensor" in text), text
+    w = np.zeros((3, 3, 3, 4), np.float32)
+    for kw in (dict(stride=2**31 - 1), dict(dilation=2**31 - 1), dict(stride=65), dict(dilation=65)):
+        ok, text = _one_op_graph(tmp_path, lambda g, x: g.conv2d(x, w, name="out", **kw))
+        assert not ok and "Unimplemented" in text and ("strides" in text or "dilations" in text), text
+    ok, text = _one_op_graph(tmp_path, lambda g, x: g.conv2d(x, w, stride=64, name="out"))
+    assert ok and "output dtype=0 w=1 h=1 c=4" in text
+    ok, text = _one_op_graph(tmp_path, lambda g, x: g.pool(x, "max", 2, 2**31 - 1, name="out"))
+    assert not ok and "strides" in text
+    for pad in (2**31 - 1, 2**20, -1):
+        ok, text = _one_op_graph(tmp_path, lambda g, x: g.pad(x, pad, pad, pad, pad, name="out"))
+        assert not ok and "padding amount" in text
+    # a frame the kernels cannot index is refused at the input already
+    ok, text = _one_op_graph(tmp_path, lambda g, x: g.unary("Relu", x, name="out"), shape=(1, 2**16, 2**16, 3))
+    assert not ok and "exceeds the largest supported tensor" in text
+
+
+def test_reader_survives_damaged_files(tmp_path):
+    """Truncated, bit-flipped, spliced and cut copies of a valid U-Net graph: the reader either builds a plan or returns
+    a message -- it never crashes, hangs or reports success without a plan.  Runs in a child process so that a crash is a
+    test failure rather than the end of the test run.  Host only."""
+    import subprocess
+    import sys
+    import textwrap
+    base = tmp_path / "u.pb"
+    gw.make_unet(base, channels=3, width=8, levels=2, seed=1, up="bilinear", down="max", batch_norm=True, act="Relu")
+    ok, text = api.inspect_model(base)
+    assert ok, text
+    script = textwrap.dedent(f"""
+        import sys
+        import numpy as np
+        sys.path.insert(0, {str(ROOT)!r})
+        from simpleraytracer_b200 import api
+        data = open({str(base)!r}, "rb").read()
+        rng = np.random.default_rng(7)
+        n_ok = n_err = 0
+        for it in range(600):
+            b = bytearray(data)
+            mode = it % 4
+            if mode == 0:
+                b = b[:rng.integers(0, len(b))]
+            elif mode == 1:
+                for _ in range(rng.integers(1, 4)):
+                    b[rng.integers(0, len(b))] = rng.integers(0, 256)
+            elif mode == 2:
+                i = rng.integers(0, len(b)); b[i:i] = bytes(rng.integers(0, 256, rng.integers(1, 9)).tolist())
+            else:
+                i = rng.integers(0, len(b)); del b[i:min(len(b), i + rng.integers(1, 64))]
+            open({str(tmp_path / "f.pb")!r}, "wb").write(bytes(b))
+            ok, text = api.inspect_model({str(tmp_path / "f.pb")!r})
+            assert text, "neither a plan nor a message"
+            n_ok += ok; n_err += not ok
+        print("ok", n_ok, "err", n_err)
+    """)
+    r = subprocess.run([sys.executable, "-c", script], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.returncode, r.stdout[-500:], r.stderr[-1500:])
+    n_ok, n_err = int(r.stdout.split()[1]), int(r.stdout.split()[3])
+    assert n_ok + n_err == 600 and n_err > 100          # most damage is detected; some flips only touch weights
