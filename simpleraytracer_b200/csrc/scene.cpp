@@ -330,11 +330,11 @@ void Scene::PrepareLightGrid(srt_light const* light, srt_render_params const* pa
     static int const debug = std::getenv("SRT_GRID_DEBUG") ? std::atoi(std::getenv("SRT_GRID_DEBUG")) : 0;
     if (debug)
     {
-        GridFlags fl{};
+        GridFlags verdict{};
         ML_CUDA_CHECK(cudaStreamSynchronize(stream));
-        ML_CUDA_CHECK(cudaMemcpy(&fl, b.flags, sizeof(fl), cudaMemcpyDeviceToHost));
-        std::fprintf(stderr, "[srt grid] light %ux%u cells, entries %u (cap %u), global %u, ok %u\n", gw, gh, fl.total, cap,
-                     fl.n_global, fl.ok);
+        ML_CUDA_CHECK(cudaMemcpy(&verdict, b.flags, sizeof(verdict), cudaMemcpyDeviceToHost));
+        std::fprintf(stderr, "[srt grid] light %ux%u cells, entries %u (cap %u), global %u, ok %u\n", gw, gh, verdict.total,
+                     cap, verdict.n_global, verdict.ok);
     }
 }
 
