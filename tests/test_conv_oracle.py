@@ -69,6 +69,21 @@ def test_conv_oracle_matches_golden_network():
     assert np.array_equal(y, g["y"])
 
 
+def test_oracle_matches_golden_unet():
+    """The committed encoder / decoder fixture (tests/golden/make_golden.py::unet): conv + folded batch norm, max pool,
+    bilinear resize, concat, 1x1 head.  Pins the writer (same bytes) and the oracle's program runner (same output)."""
+    import sys
+    sys.path.insert(0, str(GOLD))
+    from make_golden import UNET
+    from simpleraytracer_b200 import graphdef_writer as gw
+    g = np.load(GOLD / "unet_24x32.npz")
+    data, prog = gw.make_unet(None, **UNET)
+    assert np.array_equal(np.frombuffer(data, np.uint8), g["graphdef"])
+    y = O.run_program(g["x"], prog)
+    assert y.shape == (24, 32, 3) and np.array_equal(y, g["y"])
+    assert float(np.abs(y - g["x"]).max()) > 1e-3            # the net does something
+
+
 def test_conv_oracle_threads_do_not_change_results():
     rng = np.random.default_rng(0)
     x = rng.standard_normal((33, 20, 6)).astype(np.float32)

@@ -166,3 +166,20 @@ def test_unet_through_the_unmodified_reference_test_app(tmp_path):
     assert "Output: 256 x 256 x 3" in r.stderr
     y = np.frombuffer((tmp_path / "out.bin").read_bytes(), np.float32).reshape(256, 256, 3)
     close(y, O.run_program(x, prog), "test_app unet")
+
+
+def test_golden_unet(ctx, tmp_path):
+    """The committed encoder / decoder fixture (tests/golden/unet_24x32.npz: graph bytes, input, oracle output; the CPU
+    suite pins the oracle and the writer against it) through the C ABI on the fp32 path."""
+    g = np.load(ROOT / "tests" / "golden" / "unet_24x32.npz")
+    path = tmp_path / "unet.pb"
+    path.write_bytes(g["graphdef"].tobytes())
+    model, i, o = prepared_model(ctx, path, 32, 24)
+    assert (o.width, o.height, o.channels) == (32, 24, 3)
+    model.set_precision(api.MLX_PRECISION_FP32)
+    inp, out = ctx.create_image(32, 24, 3), ctx.create_image(32, 24, 3)
+    inp.write(g["x"])
+    model.infer(inp, out)
+    close(out.read(), g["y"], "golden unet")
+    for obj in (inp, out, model):
+        obj.release()
